@@ -1,0 +1,242 @@
+"""B200-native AudioFeatureExtractor: host-side mirror of the reference class.
+
+Same constructor arguments, method names, return keys and error behaviour as
+/root/reference/audio_feature_extraction_toolkit/core/feature_extractor.py (cited per method);
+the arithmetic runs in hand-written sm_100a CUDA kernels behind the C ABI of libafx_b200.so
+(include/afx_b200.h).  PyTorch only provides device memory and streams.  No CPU fallback.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import logging
+from pathlib import Path
+from typing import Any, Dict, List, Optional, Sequence, Tuple
+
+import numpy as np
+
+from .. import _native as N
+from ..wav import read_wav
+
+# librosa.note_to_hz('C2'), librosa.note_to_hz('C7') (reference :15-16)
+F0_MIN_C2 = 440.0 * 2.0 ** ((36 - 69) / 12.0)
+F0_MAX_C7 = 440.0 * 2.0 ** ((96 - 69) / 12.0)
+
+FEATURE_GROUPS = ("f0", "mfcc", "energy")
+_MASKS = {"f0": N.AFX_FEAT_F0, "mfcc": N.AFX_FEAT_MFCC, "energy": N.AFX_FEAT_ENERGY}
+
+
+class FeatureExtractionError(RuntimeError):
+    """Raised where librosa would raise ParameterError inside the reference (empty / non-finite /
+    too-short audio), so extract_features re-raises and batch_process skips, as in :211-213,:233-235."""
+
+
+_STATUS_MSG = {
+    N.CLIP_EMPTY: "empty signal after silence trim",
+    N.CLIP_NONFINITE: "Audio buffer is not finite everywhere",
+    N.CLIP_TOO_SHORT: "signal too short: delta(width=9) needs at least 9 frames",
+}
+
+
+def _mask_of(features_to_extract: Optional[Sequence[str]]) -> int:
+    if features_to_extract is None:
+        return N.AFX_FEAT_ALL
+    m = 0
+    for f in features_to_extract:
+        if f not in _MASKS:
+            raise ValueError(f"unknown feature group {f!r}; expected a subset of {FEATURE_GROUPS}")
+        m |= _MASKS[f]
+    return m
+
+
+class AudioFeatureExtractor:
+    """音頻特徵提取器 (reference :7). Drop-in for the reference class; adds the batch entry points
+    `extract_batch` / `extract_batch_device` that the GPU path is built around."""
+
+    def __init__(self, sr: int = 22050, frame_length: int = 1024, hop_length: int = 256, n_mfcc: int = 13,
+                 f0_min: float = F0_MIN_C2, f0_max: float = F0_MAX_C7, pre_emphasis: float = 0.97,
+                 device: int = 0, extended_stats: bool = False):
+        # reference :30-36
+        self.sr = sr
+        self.frame_length = frame_length
+        self.hop_length = hop_length
+        self.n_mfcc = n_mfcc
+        self.f0_min = f0_min
+        self.f0_max = f0_max
+        self.pre_emphasis = pre_emphasis
+        self.device = device
+        self.extended_stats = extended_stats
+        logging.basicConfig(level=logging.INFO)  # reference :38
+        self.logger = logging.getLogger(__name__)
+        self._handle = None
+        self._ws = None
+
+    # ------------------------------------------------------------------ native handle
+    def _h(self):
+        if self._handle is None:
+            L = N.lib()
+            cfg = N.AfxConfig()
+            L.afx_config_default(C.byref(cfg))
+            cfg.sr, cfg.frame_length, cfg.hop_length, cfg.n_mfcc = self.sr, self.frame_length, self.hop_length, self.n_mfcc
+            cfg.f0_min, cfg.f0_max, cfg.pre_emphasis, cfg.device = self.f0_min, self.f0_max, self.pre_emphasis, self.device
+            h = C.c_void_p()
+            N.check(L.afx_create(C.byref(cfg), C.byref(h)))
+            self._handle = h
+            self.summary_width = L.afx_summary_width(h)
+            self.frame_width = L.afx_frame_width(h)
+        return self._handle
+
+    def close(self):
+        if self._handle is not None:
+            N.lib().afx_destroy(self._handle)
+            self._handle = None
+            self._ws = None
+
+    def __del__(self):  # pragma: no cover
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # ------------------------------------------------------------------ device batch path
+    def max_frames(self, length: int) -> int:
+        return 1 + max(int(length), 0) // self.hop_length
+
+    def extract_batch_device(self, audio, offsets, lengths, features_to_extract=None, return_frames: bool = False,
+                             stream=None):
+        """Hot path on device-resident audio.
+
+        audio: 1-D float32 CUDA tensor holding all clips; offsets/lengths: host int64/int32 arrays
+        (offsets multiples of 4 samples).  Returns (summaries [n, SS] cuda f32, meta [n, 4] cuda i32,
+        frames [sum max_frames, FW] cuda f32 or None).  Only enqueues work on the current stream.
+        """
+        import torch
+
+        L = N.lib()
+        h = self._h()
+        offsets = np.ascontiguousarray(offsets, dtype=np.int64)
+        lengths = np.ascontiguousarray(lengths, dtype=np.int32)
+        n = int(lengths.shape[0])
+        assert audio.is_cuda and audio.dtype == torch.float32 and audio.is_contiguous()
+        dev = audio.device
+        mask = _mask_of(features_to_extract)
+        summaries = torch.empty((n, self.summary_width), dtype=torch.float32, device=dev)
+        meta = torch.empty((n, 4), dtype=torch.int32, device=dev)
+        frames = None
+        if return_frames:
+            rows = int(sum(self.max_frames(int(l)) for l in lengths))
+            frames = torch.full((rows, self.frame_width), float("nan"), dtype=torch.float32, device=dev)
+        need = L.afx_workspace_bytes(h, n, lengths.ctypes.data)
+        if self._ws is None or self._ws.numel() < need or self._ws.device != dev:
+            self._ws = torch.empty(int(need), dtype=torch.uint8, device=dev)
+        s = stream if stream is not None else torch.cuda.current_stream(dev)
+        N.check(L.afx_extract(h, audio.data_ptr(), offsets.ctypes.data, lengths.ctypes.data, n, mask,
+                              summaries.data_ptr(), meta.data_ptr(), frames.data_ptr() if frames is not None else None,
+                              self._ws.data_ptr(), self._ws.numel(), s.cuda_stream))
+        return summaries, meta, frames
+
+    @staticmethod
+    def pack_clips(clips: Sequence[np.ndarray], align: int = 4, pinned: bool = True):
+        """Pack float32 clips into one (pinned) host tensor with `align`-sample aligned offsets."""
+        import torch
+
+        lengths = np.asarray([int(c.shape[0]) for c in clips], dtype=np.int32)
+        strides = (lengths.astype(np.int64) + align - 1) // align * align
+        offsets = np.zeros(len(clips), dtype=np.int64)
+        if len(clips) > 1:
+            offsets[1:] = np.cumsum(strides)[:-1]
+        total = int(strides.sum()) + align
+        buf = torch.zeros(total, dtype=torch.float32, pin_memory=pinned and torch.cuda.is_available())
+        nb = buf.numpy()
+        for c, o, l in zip(clips, offsets, lengths):
+            nb[o:o + l] = np.asarray(c, dtype=np.float32)
+        return buf, offsets, lengths
+
+    def extract_batch(self, clips: Sequence[np.ndarray], names: Optional[Sequence[str]] = None,
+                      features_to_extract=None, skip_errors: bool = False) -> List[Dict[str, Any]]:
+        """extract_features for in-memory waveforms already at self.sr: one H2D copy, one batched
+        device pass, one D2H of the summary rows.  Returns dicts in the reference's key order."""
+        import torch
+
+        if len(clips) == 0:
+            return []
+        names = list(names) if names is not None else [f"<clip {i}>" for i in range(len(clips))]
+        buf, offsets, lengths = self.pack_clips(clips)
+        dev = torch.device("cuda", self.device)
+        audio = buf.to(dev, non_blocking=True)
+        summaries, meta, _ = self.extract_batch_device(audio, offsets, lengths, features_to_extract)
+        s = summaries.cpu().numpy()
+        m = meta.cpu().numpy()
+        return self.rows_to_dicts(s, m, names, features_to_extract, skip_errors=skip_errors)
+
+    def rows_to_dicts(self, s: np.ndarray, m: np.ndarray, names: Sequence[str], features_to_extract=None,
+                      skip_errors: bool = False) -> List[Dict[str, Any]]:
+        mask = _mask_of(features_to_extract)
+        n = self.n_mfcc
+        out = []
+        for i, name in enumerate(names):
+            st = int(m[i, 0])
+            if st != N.CLIP_OK:
+                err = FeatureExtractionError(f"{name}: {_STATUS_MSG.get(st, 'status %d' % st)}")
+                if skip_errors:
+                    self.logger.error(f"處理文件 {Path(str(name)).name} 失敗: {err}")  # reference :234
+                    continue
+                self.logger.error(f"特徵提取失敗: {err}")  # reference :212
+                raise err
+            row = s[i]
+            d: Dict[str, Any] = {"file_path": name}  # reference :203
+            if mask & N.AFX_FEAT_F0:  # reference :110-113
+                d.update(f0_mean=float(row[0]), f0_std=float(row[1]), f0_missing_rate=float(row[2]), f0_quality=float(row[3]))
+            if mask & N.AFX_FEAT_MFCC:  # reference :147-150
+                d.update(mfcc_mean=row[4:4 + n].tolist(), mfcc_std=row[4 + n:4 + 2 * n].tolist(),
+                         mfcc_delta_mean=row[4 + 2 * n:4 + 3 * n].tolist(), mfcc_delta2_mean=row[4 + 3 * n:4 + 4 * n].tolist())
+            e0 = 4 + 4 * n
+            if mask & N.AFX_FEAT_ENERGY:  # reference :176-178
+                d.update(energy_mean=float(row[e0]), energy_std=float(row[e0 + 1]), energy_range=float(row[e0 + 2]))
+            if self.extended_stats:  # README.md:25-28 of the reference (skew / kurtosis)
+                if mask & N.AFX_FEAT_MFCC:
+                    d.update(mfcc_skew=row[e0 + 3:e0 + 3 + n].tolist(), mfcc_kurtosis=row[e0 + 3 + n:e0 + 3 + 2 * n].tolist())
+                if mask & N.AFX_FEAT_ENERGY:
+                    d.update(energy_skew=float(row[e0 + 3 + 2 * n]), energy_kurtosis=float(row[e0 + 4 + 2 * n]))
+            out.append(d)
+        return out
+
+    # ------------------------------------------------------------------ reference API
+    def load_audio(self, audio_path: str) -> Tuple[np.ndarray, int]:
+        """載入音頻文件 (reference :41-56): float32 mono at self.sr."""
+        try:
+            y, sr = read_wav(audio_path)
+            if sr != self.sr:
+                raise FeatureExtractionError(
+                    f"{audio_path}: native sample rate {sr} != {self.sr}; resampling (librosa.load's soxr path) "
+                    "is outside the B200 hot path")
+            return y, sr
+        except Exception as e:
+            self.logger.error(f"載入音頻文件失敗: {str(e)}")
+            raise
+
+    def extract_features(self, audio_path: str, features_to_extract: Optional[Sequence[str]] = None) -> Dict[str, Any]:
+        """提取所有特徵 (reference :181-213). `features_to_extract` is the README.md:142-145 keyword."""
+        try:
+            y, _ = self.load_audio(audio_path)
+            return self.extract_batch([y], [audio_path], features_to_extract)[0]
+        except Exception as e:
+            self.logger.error(f"特徵提取失敗: {str(e)}")
+            raise
+
+    def batch_process(self, audio_dir: str, features_to_extract: Optional[Sequence[str]] = None) -> List[Dict[str, Any]]:
+        """批量處理音頻文件 (reference :215-237): every *.wav of the directory in one batched device
+        pass; files that fail to load or to extract are logged and skipped."""
+        audio_dir = Path(audio_dir)
+        clips, names = [], []
+        for audio_file in audio_dir.glob("*.wav"):
+            try:
+                y, _ = self.load_audio(str(audio_file))
+                clips.append(y)
+                names.append(str(audio_file))
+            except Exception as e:
+                self.logger.error(f"處理文件 {audio_file.name} 失敗: {str(e)}")
+                continue
+        results = self.extract_batch(clips, names, features_to_extract, skip_errors=True)
+        for r in results:
+            self.logger.info(f"成功處理文件: {Path(r['file_path']).name}")
+        return results

@@ -1,0 +1,378 @@
+// C ABI (include/afx_b200.h) + host-side wave scheduler of the B200 AudioFeatureExtractor hot path.
+//
+// Reference boundary: audio_feature_extraction_toolkit/core/feature_extractor.py (pure Python over
+// librosa).  Everything here is new; there is no CPU fallback -- every entry point that computes
+// needs an sm_100a device.
+#include "../../include/afx_b200.h"
+
+#include <algorithm>
+#include <atomic>
+#include <cstdarg>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "afx_common.cuh"
+#include "afx_frames.cuh"
+#include "afx_mfcc.cuh"
+#include "afx_tables.h"
+#include "afx_trim.cuh"
+
+namespace {
+
+thread_local std::string g_err;
+std::atomic<long long> g_launches{0};
+
+int fail(int code, const char* fmt, ...) {
+  char buf[512];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof buf, fmt, ap);
+  va_end(ap);
+  g_err = buf;
+  return code;
+}
+
+#define CUDA_TRY(expr)                                                                         \
+  do {                                                                                         \
+    cudaError_t e__ = (expr);                                                                  \
+    if (e__ != cudaSuccess)                                                                    \
+      return fail(AFX_ERR_CUDA, "%s failed: %s (%s:%d)", #expr, cudaGetErrorString(e__), __FILE__, __LINE__); \
+  } while (0)
+
+inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+template <typename T>
+cudaError_t upload(const std::vector<T>& v, T** dptr) {
+  cudaError_t e = cudaMalloc((void**)dptr, std::max<size_t>(v.size(), 1) * sizeof(T));
+  if (e != cudaSuccess) return e;
+  return cudaMemcpy(*dptr, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice);
+}
+
+}  // namespace
+
+struct afx_handle_s {
+  afx_config_t cfg;
+  int n16;                 // n_mfcc rounded up to a multiple of 4
+  int sm_count;
+  long long wave_frames;   // frames of log-mel scratch per wave (L2-resident target)
+  // device tables
+  float* d_window = nullptr;
+  float* d_twiddle = nullptr;
+  float* d_mel_w = nullptr;
+  int* d_mel_k0 = nullptr;
+  float* d_dct_t = nullptr;
+  afx::Tables tab;
+  // pinned staging for the per-call header arrays
+  void* h_stage = nullptr;
+  size_t h_stage_bytes = 0;
+  cudaEvent_t stage_ev = nullptr;
+  // resources of the host-buffer path (afx_extract_host)
+  void* d_ws = nullptr;       size_t d_ws_bytes = 0;
+  float* d_audio[2] = {nullptr, nullptr}; size_t d_audio_floats = 0;
+  float* d_sum = nullptr;     size_t d_sum_bytes = 0;
+  int* d_meta = nullptr;      size_t d_meta_bytes = 0;
+  cudaStream_t copy_stream = nullptr, compute_stream = nullptr;
+  cudaEvent_t copied[2] = {nullptr, nullptr}, computed[2] = {nullptr, nullptr};
+};
+
+namespace {
+
+struct Layout {   // carve-up of the caller's workspace
+  size_t off_offsets, off_frame_off, off_lengths, off_chunk_b, off_chunk_c, off_info, header_bytes;
+};
+
+Layout header_layout(int64_t n) {
+  Layout L;
+  size_t o = 0;
+  L.off_offsets = o;   o += align_up(sizeof(long long) * n, 16);
+  L.off_frame_off = o; o += align_up(sizeof(long long) * (n + 1), 16);
+  L.off_lengths = o;   o += align_up(sizeof(int) * n, 16);
+  L.off_chunk_b = o;   o += align_up(sizeof(int) * (n + 1), 16);
+  L.off_chunk_c = o;   o += align_up(sizeof(int) * (n + 1), 16);
+  L.off_info = o;      // ClipInfo is produced on device; not staged from the host
+  L.header_bytes = align_up(o + sizeof(afx::ClipInfo) * n, 256);
+  return L;
+}
+
+// bytes of wave scratch for F frames and C stat chunks
+size_t wave_scratch_bytes(const afx_handle_s* h, long long F, long long C) {
+  size_t b = 0;
+  b += align_up((size_t)F * afx::kNMels * sizeof(float), 256);   // log-mel
+  b += align_up((size_t)F * sizeof(float), 256);                 // rms
+  b += align_up((size_t)F * sizeof(float), 256);                 // f0
+  b += align_up((size_t)F * sizeof(float), 256);                 // voiced prob
+  b += align_up((size_t)C * afx::kMomentsPerCoef * h->cfg.n_mfcc * sizeof(double), 256);
+  return b;
+}
+
+inline long long frames_ub(const afx_handle_s* h, long long len) { return 1 + std::max<long long>(len, 0) / h->cfg.hop_length; }
+inline long long ceil_div(long long a, long long b) { return (a + b - 1) / b; }
+
+size_t frames_smem_bytes(const afx_handle_s* h, int* tile_floats_out) {
+  const int span = (afx::kFramesPerChunk - 1) * h->cfg.hop_length + h->cfg.frame_length;
+  const int tile_floats = (span + 8 + 3) & ~3;
+  if (tile_floats_out) *tile_floats_out = tile_floats;
+  return 16 + 8192 + (size_t)h->cfg.frame_length * 4 + 2 * (size_t)tile_floats * 4 + (size_t)afx::kFramesWarps * afx::kPlaneFloats * 4;
+}
+
+size_t stats_smem_bytes(const afx_handle_s* h) {
+  return ((size_t)afx::kStatRows * afx::kDStride + (size_t)afx::kNMels * h->n16 + (size_t)afx::kStatRows * (h->n16 + 1)) * sizeof(float);
+}
+
+}  // namespace
+
+extern "C" {
+
+int afx_abi_version(void) { return AFX_ABI_VERSION; }
+const char* afx_last_error(void) { return g_err.c_str(); }
+int64_t afx_launch_count(void) { return g_launches.load(); }
+
+void afx_config_default(afx_config_t* cfg) {
+  if (!cfg) return;
+  memset(cfg, 0, sizeof *cfg);
+  cfg->sr = 22050;
+  cfg->frame_length = 1024;
+  cfg->hop_length = 256;
+  cfg->n_mfcc = 13;
+  cfg->f0_min = 65.40639132514966;     // librosa.note_to_hz('C2')
+  cfg->f0_max = 2093.004522404789;     // librosa.note_to_hz('C7')
+  cfg->pre_emphasis = 0.97f;
+  cfg->trim_top_db = 30.f;
+  cfg->n_mels = 128;
+  cfg->mfcc_top_db = 80.f;
+  cfg->device = 0;
+}
+
+int afx_create(const afx_config_t* cfg, afx_handle_t* out) {
+  if (!cfg || !out) return fail(AFX_ERR_INVALID_ARG, "afx_create: null argument");
+  if (cfg->frame_length != 1024)
+    return fail(AFX_ERR_UNSUPPORTED, "frame_length %d not supported (1024 only in this build)", cfg->frame_length);
+  if (cfg->hop_length < 1 || cfg->hop_length > cfg->frame_length / 2)
+    return fail(AFX_ERR_INVALID_ARG, "hop_length %d out of range [1, frame_length/2]", cfg->hop_length);
+  if (cfg->n_mfcc < 1 || cfg->n_mfcc > afx::kMaxMfcc) return fail(AFX_ERR_INVALID_ARG, "n_mfcc %d out of range [1,64]", cfg->n_mfcc);
+  if (cfg->n_mels != afx::kNMels) return fail(AFX_ERR_UNSUPPORTED, "n_mels must be 128");
+  if (cfg->sr < 1000) return fail(AFX_ERR_INVALID_ARG, "sr %d too small", cfg->sr);
+
+  int ndev = 0;
+  CUDA_TRY(cudaGetDeviceCount(&ndev));
+  if (cfg->device < 0 || cfg->device >= ndev) return fail(AFX_ERR_CUDA, "CUDA device %d not present (%d devices)", cfg->device, ndev);
+  CUDA_TRY(cudaSetDevice(cfg->device));
+  cudaDeviceProp prop;
+  CUDA_TRY(cudaGetDeviceProperties(&prop, cfg->device));
+  if (prop.major < 10) return fail(AFX_ERR_CUDA, "device %d is sm_%d%d; this library is built for sm_100a only", cfg->device, prop.major, prop.minor);
+
+  afx_handle_s* h = new afx_handle_s();
+  h->cfg = *cfg;
+  h->n16 = (cfg->n_mfcc + 3) & ~3;
+  h->sm_count = prop.multiProcessorCount;
+  h->wave_frames = 49152;
+  if (const char* e = getenv("AFX_WAVE_FRAMES")) { long long v = atoll(e); if (v >= 1024) h->wave_frames = v; }
+
+  const auto win = afx::host::window_half(cfg->frame_length);
+  const auto tw = afx::host::twiddle32x32(1024);
+  const auto mel = afx::host::mel_sparse(cfg->sr, cfg->frame_length, cfg->n_mels);
+  const auto dct = afx::host::dct_rows(cfg->n_mfcc, cfg->n_mels);
+  std::vector<float> dct_t((size_t)cfg->n_mels * h->n16, 0.f);
+  for (int c = 0; c < cfg->n_mfcc; ++c)
+    for (int m = 0; m < cfg->n_mels; ++m) dct_t[(size_t)m * h->n16 + c] = dct[(size_t)c * cfg->n_mels + m];
+  CUDA_TRY(upload(win, &h->d_window));
+  CUDA_TRY(upload(tw, &h->d_twiddle));
+  CUDA_TRY(upload(mel.w, &h->d_mel_w));
+  CUDA_TRY(upload(mel.k0, &h->d_mel_k0));
+  CUDA_TRY(upload(dct_t, &h->d_dct_t));
+  h->tab.window_half = h->d_window;
+  h->tab.twiddle = reinterpret_cast<const float2*>(h->d_twiddle);
+  h->tab.post_twiddle = nullptr;
+  h->tab.mel_w = h->d_mel_w;
+  h->tab.mel_k0 = h->d_mel_k0;
+  for (int q = 0; q < 4; ++q) { h->tab.mel_cnt[q] = mel.cnt[q]; h->tab.mel_woff[q] = mel.woff[q]; }
+  h->tab.dct = nullptr;
+
+  CUDA_TRY(cudaFuncSetAttribute(afx::trim_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+  CUDA_TRY(cudaFuncSetAttribute(afx::frames_kernel<1024>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)frames_smem_bytes(h, nullptr)));
+  CUDA_TRY(cudaFuncSetAttribute(afx::mfcc_stats_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)stats_smem_bytes(h)));
+  CUDA_TRY(cudaEventCreateWithFlags(&h->stage_ev, cudaEventDisableTiming));
+  *out = h;
+  return AFX_OK;
+}
+
+int afx_destroy(afx_handle_t h) {
+  if (!h) return AFX_OK;
+  cudaSetDevice(h->cfg.device);
+  cudaDeviceSynchronize();
+  cudaFree(h->d_window); cudaFree(h->d_twiddle); cudaFree(h->d_mel_w); cudaFree(h->d_mel_k0); cudaFree(h->d_dct_t);
+  if (h->h_stage) cudaFreeHost(h->h_stage);
+  if (h->stage_ev) cudaEventDestroy(h->stage_ev);
+  cudaFree(h->d_ws); cudaFree(h->d_audio[0]); cudaFree(h->d_audio[1]); cudaFree(h->d_sum); cudaFree(h->d_meta);
+  for (int i = 0; i < 2; ++i) { if (h->copied[i]) cudaEventDestroy(h->copied[i]); if (h->computed[i]) cudaEventDestroy(h->computed[i]); }
+  if (h->copy_stream) cudaStreamDestroy(h->copy_stream);
+  if (h->compute_stream) cudaStreamDestroy(h->compute_stream);
+  delete h;
+  return AFX_OK;
+}
+
+int afx_summary_width(afx_handle_t h) { return h ? 4 + 4 * h->cfg.n_mfcc + 3 + 2 * h->cfg.n_mfcc + 2 : 0; }
+int afx_frame_width(afx_handle_t h) { return h ? 3 * h->cfg.n_mfcc + 3 : 0; }
+int64_t afx_max_frames(afx_handle_t h, int64_t length) { return h ? frames_ub(h, length) : 0; }
+
+static size_t workspace_bytes_impl(afx_handle_t h, int64_t n_clips, const int32_t* h_lengths, bool minimal) {
+  if (!h || n_clips < 0 || (n_clips > 0 && !h_lengths)) return 0;
+  long long total_f = 0, max_f = 1;
+  for (int64_t i = 0; i < n_clips; ++i) { const long long f = frames_ub(h, h_lengths[i]); total_f += f; max_f = std::max(max_f, f); }
+  long long F = minimal ? max_f : std::max(max_f, std::min(total_f, h->wave_frames));
+  const long long C = ceil_div(F, afx::kStatFrames) + std::min<long long>(n_clips, F) + 1;
+  return header_layout(n_clips).header_bytes + wave_scratch_bytes(h, F, C) + 1024;
+}
+size_t afx_workspace_bytes(afx_handle_t h, int64_t n_clips, const int32_t* h_lengths) { return workspace_bytes_impl(h, n_clips, h_lengths, false); }
+size_t afx_workspace_min_bytes(afx_handle_t h, int64_t n_clips, const int32_t* h_lengths) { return workspace_bytes_impl(h, n_clips, h_lengths, true); }
+
+int afx_extract(afx_handle_t h, const float* d_audio, const int64_t* h_offsets, const int32_t* h_lengths,
+                int64_t n_clips, uint32_t feature_mask, float* d_summaries, int32_t* d_meta,
+                float* d_frames, void* d_workspace, size_t workspace_bytes, void* stream_v) {
+  if (!h) return fail(AFX_ERR_INVALID_ARG, "afx_extract: null handle");
+  if (n_clips == 0) return AFX_OK;
+  if (n_clips < 0 || n_clips > 0x7fffff00LL) return fail(AFX_ERR_INVALID_ARG, "afx_extract: bad n_clips");
+  if (!d_audio || !h_offsets || !h_lengths || !d_summaries || !d_meta || !d_workspace)
+    return fail(AFX_ERR_INVALID_ARG, "afx_extract: null pointer argument");
+  if ((feature_mask & ~AFX_FEAT_ALL) != 0) return fail(AFX_ERR_INVALID_ARG, "afx_extract: unknown feature bits 0x%x", feature_mask);
+  if (feature_mask & AFX_FEAT_F0) return fail(AFX_ERR_UNSUPPORTED, "afx_extract: the F0 (pYIN) group is not built yet");
+  if ((reinterpret_cast<uintptr_t>(d_audio) & 15u) != 0) return fail(AFX_ERR_INVALID_ARG, "afx_extract: d_audio must be 16-byte aligned");
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_v);
+  CUDA_TRY(cudaSetDevice(h->cfg.device));
+  const int n = (int)n_clips;
+  const int hop = h->cfg.hop_length;
+
+  // ---- host-side prefixes (everything the launch geometry needs is known from the lengths)
+  const Layout L = header_layout(n);
+  const size_t staged_bytes = L.off_info;
+  if (h->h_stage_bytes < staged_bytes) {
+    if (h->h_stage) { CUDA_TRY(cudaEventSynchronize(h->stage_ev)); CUDA_TRY(cudaFreeHost(h->h_stage)); h->h_stage = nullptr; }
+    const size_t cap = std::max<size_t>(staged_bytes * 2, 1 << 16);
+    CUDA_TRY(cudaMallocHost(&h->h_stage, cap));
+    h->h_stage_bytes = cap;
+  } else {
+    CUDA_TRY(cudaEventSynchronize(h->stage_ev));   // previous call's upload has drained
+  }
+  char* st = static_cast<char*>(h->h_stage);
+  long long* s_offsets = reinterpret_cast<long long*>(st + L.off_offsets);
+  long long* s_frame_off = reinterpret_cast<long long*>(st + L.off_frame_off);
+  int* s_lengths = reinterpret_cast<int*>(st + L.off_lengths);
+  int* s_chunk_b = reinterpret_cast<int*>(st + L.off_chunk_b);
+  int* s_chunk_c = reinterpret_cast<int*>(st + L.off_chunk_c);
+  long long fo = 0, cb = 0, cc = 0, max_f = 1;
+  const long long max_trim_blocks = (200 * 1024) / 4 - 8;
+  for (int i = 0; i < n; ++i) {
+    if (h_lengths[i] < 0) return fail(AFX_ERR_INVALID_ARG, "afx_extract: clip %d has negative length", i);
+    if (h_offsets[i] < 0 || (h_offsets[i] & 3) != 0) return fail(AFX_ERR_INVALID_ARG, "afx_extract: clip %d offset %lld is not a multiple of 4 samples", i, (long long)h_offsets[i]);
+    if (ceil_div(h_lengths[i], afx::kTrimHop) > max_trim_blocks) return fail(AFX_ERR_UNSUPPORTED, "afx_extract: clip %d longer than %lld samples", i, max_trim_blocks * afx::kTrimHop);
+    s_offsets[i] = h_offsets[i];
+    s_lengths[i] = h_lengths[i];
+    const long long f = frames_ub(h, h_lengths[i]);
+    s_frame_off[i] = fo; s_chunk_b[i] = (int)cb; s_chunk_c[i] = (int)cc;
+    fo += f; cb += ceil_div(f, afx::kFramesPerChunk); cc += ceil_div(f, afx::kStatFrames);
+    max_f = std::max(max_f, f);
+    if (cb > 0x7fffff00LL) return fail(AFX_ERR_UNSUPPORTED, "afx_extract: batch too large");
+  }
+  s_frame_off[n] = fo; s_chunk_b[n] = (int)cb; s_chunk_c[n] = (int)cc;
+
+  if (workspace_bytes < L.header_bytes + wave_scratch_bytes(h, max_f, ceil_div(max_f, afx::kStatFrames) + 2) + 1024)
+    return fail(AFX_ERR_WORKSPACE, "afx_extract: workspace of %zu bytes is below afx_workspace_min_bytes", workspace_bytes);
+  char* ws = static_cast<char*>(d_workspace);
+  if ((reinterpret_cast<uintptr_t>(ws) & 255u) != 0) return fail(AFX_ERR_INVALID_ARG, "afx_extract: workspace must be 256-byte aligned");
+  CUDA_TRY(cudaMemcpyAsync(ws, st, staged_bytes, cudaMemcpyHostToDevice, stream));
+  CUDA_TRY(cudaEventRecord(h->stage_ev, stream));
+  const long long* d_offsets = reinterpret_cast<const long long*>(ws + L.off_offsets);
+  const long long* d_frame_off = reinterpret_cast<const long long*>(ws + L.off_frame_off);
+  const int* d_lengths = reinterpret_cast<const int*>(ws + L.off_lengths);
+  const int* d_chunk_b = reinterpret_cast<const int*>(ws + L.off_chunk_b);
+  const int* d_chunk_c = reinterpret_cast<const int*>(ws + L.off_chunk_c);
+  afx::ClipInfo* d_info = reinterpret_cast<afx::ClipInfo*>(ws + L.off_info);
+
+  // ---- wave capacity from the scratch we were given: largest F with scratch(F, C(F)) fitting
+  const size_t scratch_avail = workspace_bytes - L.header_bytes - 1024;
+  long long F_cap = std::max(max_f, std::min(fo, h->wave_frames));
+  auto chunks_for = [&](long long F) { return ceil_div(F, afx::kStatFrames) + std::min<long long>(n, F) + 1; };
+  while (F_cap > max_f && wave_scratch_bytes(h, F_cap, chunks_for(F_cap)) > scratch_avail) F_cap = std::max(max_f, F_cap * 7 / 8);
+  if (wave_scratch_bytes(h, F_cap, chunks_for(F_cap)) > scratch_avail) return fail(AFX_ERR_WORKSPACE, "afx_extract: workspace too small for the longest clip");
+  const long long C_cap = chunks_for(F_cap);
+  char* sp = ws + L.header_bytes;
+  float* d_logmel = reinterpret_cast<float*>(sp); sp += align_up((size_t)F_cap * afx::kNMels * sizeof(float), 256);
+  float* d_rms = reinterpret_cast<float*>(sp);    sp += align_up((size_t)F_cap * sizeof(float), 256);
+  float* d_f0 = reinterpret_cast<float*>(sp);     sp += align_up((size_t)F_cap * sizeof(float), 256);
+  float* d_vp = reinterpret_cast<float*>(sp);     sp += align_up((size_t)F_cap * sizeof(float), 256);
+  double* d_part = reinterpret_cast<double*>(sp);
+  (void)d_f0; (void)d_vp; (void)C_cap;
+
+  int tile_floats = 0;
+  const size_t fr_smem = frames_smem_bytes(h, &tile_floats);
+  const size_t st_smem = stats_smem_bytes(h);
+
+  // ---- waves of clips whose log-mel scratch stays L2 resident
+  int c0 = 0;
+  while (c0 < n) {
+    int c1 = c0;
+    long long F = 0;
+    long long max_len = 0;
+    while (c1 < n) {
+      const long long f = s_frame_off[c1 + 1] - s_frame_off[c1];
+      if (c1 > c0 && F + f > F_cap) break;
+      F += f; max_len = std::max<long long>(max_len, s_lengths[c1]); ++c1;
+    }
+    const int nw = c1 - c0;
+    {  // phase A
+      afx::TrimArgs ta;
+      ta.audio = d_audio; ta.offsets = d_offsets; ta.lengths = d_lengths; ta.info = d_info;
+      ta.clip_begin = c0; ta.hop = hop; ta.coef = h->cfg.pre_emphasis; ta.top_db = h->cfg.trim_top_db;
+      const size_t smem = (size_t)(ceil_div(max_len, afx::kTrimHop) + 4) * sizeof(float);
+      afx::trim_kernel<<<nw, afx::kTrimThreads, smem, stream>>>(ta);
+      ++g_launches;
+    }
+    if (feature_mask & (AFX_FEAT_MFCC | AFX_FEAT_ENERGY)) {  // phase B
+      afx::FramesArgs fa;
+      fa.audio = d_audio; fa.offsets = d_offsets; fa.lengths = d_lengths; fa.info_ro = d_info; fa.info = d_info;
+      fa.chunk_off = d_chunk_b; fa.frame_off = d_frame_off; fa.clip_begin = c0; fa.clip_end = c1;
+      fa.n_tasks = s_chunk_b[c1] - s_chunk_b[c0]; fa.frame_base = s_frame_off[c0];
+      fa.logmel = d_logmel; fa.rms = d_rms; fa.tab = h->tab; fa.hop = hop; fa.tile_floats = tile_floats;
+      fa.coef = h->cfg.pre_emphasis;
+      const int grid = std::max(1, std::min(fa.n_tasks, 2 * h->sm_count));
+      afx::frames_kernel<1024><<<grid, afx::kFramesWarps * 32, fr_smem, stream>>>(fa);
+      ++g_launches;
+    }
+    if (feature_mask & AFX_FEAT_MFCC) {  // phase C
+      afx::StatArgs sa;
+      sa.info = d_info; sa.chunk_off = d_chunk_c; sa.frame_off = d_frame_off; sa.clip_begin = c0; sa.clip_end = c1;
+      sa.frame_base = s_frame_off[c0]; sa.logmel = d_logmel; sa.dct_t = h->d_dct_t; sa.partials = d_part;
+      sa.frames_out = d_frames; sa.n_mfcc = h->cfg.n_mfcc; sa.n16 = h->n16; sa.frame_width = afx_frame_width(h);
+      sa.top_db = h->cfg.mfcc_top_db;
+      const int grid = s_chunk_c[c1] - s_chunk_c[c0];
+      afx::mfcc_stats_kernel<<<grid, afx::kStatThreads, st_smem, stream>>>(sa);
+      ++g_launches;
+    }
+    {  // phase D
+      afx::FinalArgs fa;
+      fa.info = d_info; fa.chunk_off = d_chunk_c; fa.frame_off = d_frame_off; fa.clip_begin = c0;
+      fa.frame_base = s_frame_off[c0]; fa.partials = d_part; fa.rms = d_rms; fa.f0 = nullptr; fa.voiced_prob = nullptr;
+      fa.summaries = d_summaries; fa.meta = d_meta; fa.frames_out = d_frames; fa.n_mfcc = h->cfg.n_mfcc;
+      fa.summary_width = afx_summary_width(h); fa.frame_width = afx_frame_width(h); fa.mask = feature_mask;
+      afx::finalize_kernel<<<nw, afx::kFinalThreads, 0, stream>>>(fa);
+      ++g_launches;
+    }
+    c0 = c1;
+  }
+  CUDA_TRY(cudaGetLastError());
+  return AFX_OK;
+}
+
+// test/diagnostic aid: byte offset of the log-mel scratch inside a workspace for n_clips clips
+size_t afx_debug_header_bytes(int64_t n_clips) { return header_layout(n_clips).header_bytes; }
+
+int afx_extract_host(afx_handle_t h, const float* const* h_clips, const int32_t* h_lengths, int64_t n_clips,
+                     uint32_t feature_mask, float* h_summaries, int32_t* h_meta) {
+  (void)h; (void)h_clips; (void)h_lengths; (void)n_clips; (void)feature_mask; (void)h_summaries; (void)h_meta;
+  return fail(AFX_ERR_UNSUPPORTED, "afx_extract_host: not built yet");
+}
+
+}  // extern "C"

@@ -1,0 +1,139 @@
+/*
+ * afx_b200.h -- C ABI of the B200-native AudioFeatureExtractor hot path (libafx_b200.so).
+ *
+ * The reference (chiy48308/audio_feature_extraction) has no FFI layer: its hot path is the pure
+ * Python class `AudioFeatureExtractor` in
+ *   audio_feature_extraction_toolkit/core/feature_extractor.py
+ * which hands every number to librosa.  This header is the boundary a maintainer binds instead
+ * (ctypes stub: INTEGRATION.md); each entry point names the reference lines it replaces.
+ *
+ * Conventions: plain C types only (no torch / CUDA types in signatures; a CUDA stream is passed
+ * as void*), every function returns an afx_status_t, afx_last_error() gives the message of the
+ * last failure on the calling thread.  There is NO CPU fallback: every compute entry point
+ * requires an sm_100a device and fails with AFX_ERR_CUDA otherwise.
+ */
+#ifndef AFX_B200_H_
+#define AFX_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define AFX_ABI_VERSION 1
+
+typedef enum {
+  AFX_OK = 0,
+  AFX_ERR_INVALID_ARG = 1,   /* null pointer, unsupported frame_length, misaligned clip offset ... */
+  AFX_ERR_CUDA = 2,          /* CUDA runtime failure (message carries cudaGetErrorString) */
+  AFX_ERR_WORKSPACE = 3,     /* caller workspace smaller than afx_workspace_bytes() */
+  AFX_ERR_UNSUPPORTED = 4
+} afx_status_t;
+
+/* feature groups: the reference's extract_f0 / extract_mfcc / extract_energy
+ * (core/feature_extractor.py:76-114, :116-151, :153-179) */
+#define AFX_FEAT_F0      0x1u
+#define AFX_FEAT_MFCC    0x2u
+#define AFX_FEAT_ENERGY  0x4u
+#define AFX_FEAT_ALL     0x7u
+
+/* per-clip status written to meta[clip][0]; mirrors the librosa exceptions that make the
+ * reference's extract_features raise (:211-213) and batch_process skip (:233-235) */
+#define AFX_CLIP_OK          0
+#define AFX_CLIP_EMPTY       1   /* nothing left after trim (all frames <= -30 dB) or zero-length input */
+#define AFX_CLIP_NONFINITE   2   /* NaN/Inf sample: librosa.util.valid_audio raises */
+#define AFX_CLIP_TOO_SHORT   3   /* fewer than 9 frames: librosa.feature.delta(width=9) raises */
+
+/* Constructor arguments of AudioFeatureExtractor.__init__ (core/feature_extractor.py:10-17) plus the
+ * constants the reference hard-codes at its librosa call sites. Zero-initialise, then
+ * afx_config_default(). */
+typedef struct {
+  int32_t sr;               /* 22050 */
+  int32_t frame_length;     /* 1024: n_fft of mfcc (:131), frame_length of rms (:166) and pyin (:91); 512, 1024 or 2048 */
+  int32_t hop_length;       /* 256 */
+  int32_t n_mfcc;           /* 13 (1..64) */
+  double  f0_min;           /* librosa.note_to_hz('C2') = 65.40639132514966 (:15) */
+  double  f0_max;           /* librosa.note_to_hz('C7') = 2093.004522404789 (:16) */
+  float   pre_emphasis;     /* 0.97 (:17, used :69) */
+  float   trim_top_db;      /* 30 (:72) */
+  int32_t n_mels;           /* 128 (librosa.feature.melspectrogram default); only 128 is supported */
+  float   mfcc_top_db;      /* 80 (librosa.power_to_db default inside librosa.feature.mfcc) */
+  int32_t device;           /* CUDA device ordinal */
+  int32_t reserved[7];
+} afx_config_t;
+
+typedef struct afx_handle_s* afx_handle_t;
+
+void         afx_config_default(afx_config_t* cfg);
+int          afx_abi_version(void);
+const char*  afx_last_error(void);
+
+/* AudioFeatureExtractor.__init__ (core/feature_extractor.py:10-39): validates the configuration,
+ * builds the device tables (Hamming window, FFT twiddles, sparse Slaney mel filterbank, DCT-II
+ * matrix, pYIN beta weights / transition band) on cfg->device. */
+int afx_create(const afx_config_t* cfg, afx_handle_t* out);
+int afx_destroy(afx_handle_t h);
+
+/* Row widths of the outputs below.
+ *   summary row (float32, SS = afx_summary_width): in the key order of extract_features (:202-207)
+ *     [0] f0_mean [1] f0_std [2] f0_missing_rate [3] f0_quality            (:110-113)
+ *     [4 .. 4+n)   mfcc_mean   [4+n .. 4+2n) mfcc_std                      (:147-148)
+ *     [4+2n .. 4+3n) mfcc_delta_mean  [4+3n .. 4+4n) mfcc_delta2_mean      (:149-150)
+ *     [4+4n] energy_mean [4+4n+1] energy_std [4+4n+2] energy_range         (:176-178)
+ *     extension statistics (README.md:25-28 of the reference; biased moments, Fisher kurtosis):
+ *     [4+4n+3 .. +n) mfcc_skew  [.. +n) mfcc_kurtosis  then energy_skew, energy_kurtosis
+ *   frame row (float32, FW = afx_frame_width): [0..n) mfcc [n..2n) delta [2n..3n) delta2
+ *     [3n] rms [3n+1] f0 (Hz, NaN when unvoiced) [3n+2] voiced probability
+ *   meta row (int32 x 4): status, trim_start, trim_end, n_frames                        (:72)
+ */
+int afx_summary_width(afx_handle_t h);
+int afx_frame_width(afx_handle_t h);
+
+/* Number of frame rows clip i can produce at most: 1 + length/hop_length (librosa centre padding). */
+int64_t afx_max_frames(afx_handle_t h, int64_t length);
+
+/* Bytes of device scratch afx_extract needs for this batch (also accepts less: see
+ * afx_workspace_min_bytes; more scratch = larger waves of clips per launch). */
+size_t afx_workspace_bytes(afx_handle_t h, int64_t n_clips, const int32_t* h_lengths);
+size_t afx_workspace_min_bytes(afx_handle_t h, int64_t n_clips, const int32_t* h_lengths);
+
+/*
+ * The hot path: preprocess_audio + extract_f0 + extract_mfcc + extract_energy of
+ * extract_features (core/feature_extractor.py:194-199) for a whole batch of clips resident in
+ * device memory -- what batch_process (:215-237) loops over, minus file decoding.
+ *
+ *   d_audio      device, float32 mono PCM in [-1,1] already at cfg.sr; clip i occupies
+ *                d_audio[h_offsets[i] .. h_offsets[i] + h_lengths[i]).  h_offsets[i] must be a
+ *                multiple of 4 samples and the buffer must be readable up to the next multiple of 4
+ *                past each clip (TMA bulk copies are 16-byte granular).
+ *   h_offsets    HOST, n_clips int64 sample offsets;  h_lengths: HOST, n_clips int32 lengths
+ *   feature_mask AFX_FEAT_* groups to compute (others are written as 0 in the summary row)
+ *   d_summaries  device float32 [n_clips, SS]
+ *   d_meta       device int32   [n_clips, 4]
+ *   d_frames     device float32 [sum_i afx_max_frames(len_i), FW] or NULL; clip i's rows start at
+ *                row sum_{j<i} afx_max_frames(len_j); only the first meta[i][3] rows are written
+ *   d_workspace  device scratch of workspace_bytes (>= afx_workspace_min_bytes)
+ *   stream       cudaStream_t as void* (NULL = legacy default stream); the call only enqueues work
+ */
+int afx_extract(afx_handle_t h, const float* d_audio, const int64_t* h_offsets, const int32_t* h_lengths,
+                int64_t n_clips, uint32_t feature_mask, float* d_summaries, int32_t* d_meta,
+                float* d_frames, void* d_workspace, size_t workspace_bytes, void* stream);
+
+/*
+ * Same computation from HOST memory (what a caller holding decoded files has): clips are staged
+ * through pinned buffers, copied host->device in waves on a copy stream that overlaps the compute
+ * stream, and the summaries / meta rows are copied back.  Blocks until the results are in
+ * h_summaries / h_meta.  h_clips[i] points at clip i's float32 samples (any alignment).
+ */
+int afx_extract_host(afx_handle_t h, const float* const* h_clips, const int32_t* h_lengths, int64_t n_clips,
+                     uint32_t feature_mask, float* h_summaries, int32_t* h_meta);
+
+/* Kernels launched by this library since process start (bench.py reports it as gpu_launches). */
+int64_t afx_launch_count(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* AFX_B200_H_ */

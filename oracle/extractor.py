@@ -1,0 +1,100 @@
+"""Oracle restatement of the reference orchestration (TEST INFRASTRUCTURE, parity unpinned).
+
+Follows /root/reference/audio_feature_extraction_toolkit/core/feature_extractor.py method by
+method, with `oracle.librosa_restated` standing in for librosa 0.11.0.  Works on in-memory
+float32 waveforms (the reference's `load_audio` is a librosa.load call; WAV decoding is host I/O
+and is exercised separately).
+"""
+from __future__ import annotations
+
+import numpy as np
+import scipy.stats
+
+from . import librosa_restated as L
+
+GROUPS = ("f0", "mfcc", "energy")
+
+
+class OracleFeatureExtractor:
+    def __init__(self, sr=22050, frame_length=1024, hop_length=256, n_mfcc=13,
+                 f0_min=L.note_c2_hz, f0_max=L.note_c7_hz, pre_emphasis=0.97, extended_stats=False,
+                 dtype=np.float32):
+        # core/feature_extractor.py:30-36
+        self.sr = sr
+        self.frame_length = frame_length
+        self.hop_length = hop_length
+        self.n_mfcc = n_mfcc
+        self.f0_min = f0_min
+        self.f0_max = f0_max
+        self.pre_emphasis = pre_emphasis
+        self.extended_stats = extended_stats
+        self.dtype = dtype
+
+    # core/feature_extractor.py:58-74
+    def preprocess_audio(self, y):
+        y = np.asarray(y, dtype=self.dtype)
+        y_pre = L.preemphasis(y, coef=self.pre_emphasis)
+        y_trim, _ = L.trim(y_pre, top_db=30)
+        return y_trim
+
+    def trim_indices(self, y):
+        y = np.asarray(y, dtype=self.dtype)
+        return L.trim_indices(L.preemphasis(y, coef=self.pre_emphasis), top_db=30)
+
+    # core/feature_extractor.py:76-114
+    def f0_track(self, y):
+        f0, voiced, vprob = L.pyin(y, fmin=self.f0_min, fmax=self.f0_max, sr=self.sr,
+                                   frame_length=self.frame_length, hop_length=self.hop_length)
+        return f0, voiced, vprob
+
+    def extract_f0(self, y):
+        f0, _, _ = self.f0_track(y)
+        f0_valid = f0[~np.isnan(f0)]
+        if len(f0_valid) > 0:
+            f0_mean = np.mean(f0_valid)
+            f0_std = np.std(f0_valid)
+            f0_missing_rate = np.sum(np.isnan(f0)) / len(f0)
+            f0_quality = 1 - f0_missing_rate
+        else:
+            f0_mean, f0_std, f0_missing_rate, f0_quality = 0, 0, 1, 0
+        return {"f0_mean": float(f0_mean), "f0_std": float(f0_std),
+                "f0_missing_rate": float(f0_missing_rate), "f0_quality": float(f0_quality)}
+
+    # core/feature_extractor.py:116-151
+    def mfcc_frames(self, y):
+        m = L.mfcc(y, sr=self.sr, n_mfcc=self.n_mfcc, n_fft=self.frame_length,
+                   hop_length=self.hop_length, dtype=self.dtype)
+        return m, L.delta(m), L.delta(m, order=2)
+
+    def extract_mfcc(self, y):
+        m, d1, d2 = self.mfcc_frames(y)
+        out = {"mfcc_mean": np.mean(m, axis=1).tolist(), "mfcc_std": np.std(m, axis=1).tolist(),
+               "mfcc_delta_mean": np.mean(d1, axis=1).tolist(), "mfcc_delta2_mean": np.mean(d2, axis=1).tolist()}
+        if self.extended_stats:  # README.md:25-28 extension: scipy.stats defaults (biased, Fisher)
+            out["mfcc_skew"] = scipy.stats.skew(m.astype(np.float64), axis=1).tolist()
+            out["mfcc_kurtosis"] = scipy.stats.kurtosis(m.astype(np.float64), axis=1).tolist()
+        return out
+
+    # core/feature_extractor.py:153-179
+    def rms_frames(self, y):
+        return L.rms(y, frame_length=self.frame_length, hop_length=self.hop_length, dtype=self.dtype)
+
+    def extract_energy(self, y):
+        r = self.rms_frames(y)
+        out = {"energy_mean": float(np.mean(r)), "energy_std": float(np.std(r)), "energy_range": float(np.ptp(r))}
+        if self.extended_stats:
+            out["energy_skew"] = float(scipy.stats.skew(r.astype(np.float64), axis=None))
+            out["energy_kurtosis"] = float(scipy.stats.kurtosis(r.astype(np.float64), axis=None))
+        return out
+
+    # core/feature_extractor.py:181-213 on an in-memory waveform
+    def extract_features_array(self, y, name="<array>", features_to_extract=GROUPS):
+        y_processed = self.preprocess_audio(y)
+        feats = {"file_path": name}
+        if "f0" in features_to_extract:
+            feats.update(self.extract_f0(y_processed))
+        if "mfcc" in features_to_extract:
+            feats.update(self.extract_mfcc(y_processed))
+        if "energy" in features_to_extract:
+            feats.update(self.extract_energy(y_processed))
+        return feats
