@@ -15,12 +15,15 @@ LIB_PATH = _PKG / "lib" / "libafx_b200.so"
 AFX_FEAT_F0, AFX_FEAT_MFCC, AFX_FEAT_ENERGY, AFX_FEAT_ALL = 0x1, 0x2, 0x4, 0x7
 CLIP_OK, CLIP_EMPTY, CLIP_NONFINITE, CLIP_TOO_SHORT = 0, 1, 2, 3
 ABI_VERSION = 1
+ERR_INVALID_ARG, ERR_CUDA, ERR_WORKSPACE, ERR_UNSUPPORTED = 1, 2, 3, 4
 
 EXPORTS = [
     "afx_config_default", "afx_abi_version", "afx_last_error", "afx_create", "afx_destroy",
     "afx_summary_width", "afx_frame_width", "afx_max_frames", "afx_workspace_bytes",
-    "afx_workspace_min_bytes", "afx_extract", "afx_extract_host", "afx_launch_count",
+    "afx_workspace_min_bytes", "afx_extract", "afx_extract_host", "afx_extract_host_packed",
+    "afx_launch_count",
 ]
+SAMPLE_F32, SAMPLE_S16 = 0, 1
 
 
 class AfxConfig(C.Structure):
@@ -65,6 +68,8 @@ def lib():
     L.afx_workspace_min_bytes.argtypes = [vp, i64, vp]; L.afx_workspace_min_bytes.restype = sz
     L.afx_extract.argtypes = [vp, vp, vp, vp, i64, u32, vp, vp, vp, vp, sz, vp]; L.afx_extract.restype = C.c_int
     L.afx_extract_host.argtypes = [vp, vp, vp, vp, i64, u32, vp, vp, vp]; L.afx_extract_host.restype = C.c_int
+    L.afx_extract_host_packed.argtypes = [vp, vp, C.c_int, i64, vp, vp, i64, u32, vp, vp]
+    L.afx_extract_host_packed.restype = C.c_int
     L.afx_launch_count.argtypes = []; L.afx_launch_count.restype = i64
     L.afx_debug_header_bytes.argtypes = [i64]; L.afx_debug_header_bytes.restype = sz
     if L.afx_abi_version() != ABI_VERSION:

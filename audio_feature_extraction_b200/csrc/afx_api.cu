@@ -12,6 +12,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include "afx_common.cuh"
@@ -69,13 +70,16 @@ struct afx_handle_s {
   void* h_stage = nullptr;
   size_t h_stage_bytes = 0;
   cudaEvent_t stage_ev = nullptr;
-  // resources of the host-buffer path (afx_extract_host)
+  // resources of the host-buffer paths (afx_extract_host / afx_extract_host_packed)
   void* d_ws = nullptr;       size_t d_ws_bytes = 0;
   float* d_audio[2] = {nullptr, nullptr}; size_t d_audio_floats = 0;
+  int16_t* d_pcm[2] = {nullptr, nullptr}; size_t d_pcm_samples = 0;
+  float* h_pin[2] = {nullptr, nullptr};   size_t h_pin_floats = 0;
   float* d_sum = nullptr;     size_t d_sum_bytes = 0;
   int* d_meta = nullptr;      size_t d_meta_bytes = 0;
   cudaStream_t copy_stream = nullptr, compute_stream = nullptr;
   cudaEvent_t copied[2] = {nullptr, nullptr}, computed[2] = {nullptr, nullptr};
+  long long host_wave_samples = 16ll << 20;   // samples per host->device wave (AFX_HOST_WAVE_SAMPLES)
 };
 
 namespace {
@@ -369,10 +373,201 @@ int afx_extract(afx_handle_t h, const float* d_audio, const int64_t* h_offsets, 
 // test/diagnostic aid: byte offset of the log-mel scratch inside a workspace for n_clips clips
 size_t afx_debug_header_bytes(int64_t n_clips) { return header_layout(n_clips).header_bytes; }
 
+}  // extern "C"
+
+namespace {
+
+__global__ void pcm16_to_f32_kernel(const int16_t* __restrict__ in, float* __restrict__ out, long long n8) {
+  // libsndfile / librosa.load scaling of 16-bit PCM: x / 32768 (exact in float32); 8 samples per thread
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n8; i += (long long)gridDim.x * blockDim.x) {
+    const int4 v = __ldg(reinterpret_cast<const int4*>(in) + i);
+    const int w[4] = {v.x, v.y, v.z, v.w};
+    float o[8];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      o[2 * k] = (float)(short)(w[k] & 0xffff) * (1.0f / 32768.0f);
+      o[2 * k + 1] = (float)(short)(w[k] >> 16) * (1.0f / 32768.0f);
+    }
+    float4* dst = reinterpret_cast<float4*>(out) + 2 * i;
+    dst[0] = make_float4(o[0], o[1], o[2], o[3]);
+    dst[1] = make_float4(o[4], o[5], o[6], o[7]);
+  }
+}
+
+int ensure_host_path(afx_handle_s* h, size_t wave_floats, bool need_pcm, bool need_pin, int64_t n_clips) {
+  if (!h->copy_stream) {
+    CUDA_TRY(cudaStreamCreateWithFlags(&h->copy_stream, cudaStreamNonBlocking));
+    CUDA_TRY(cudaStreamCreateWithFlags(&h->compute_stream, cudaStreamNonBlocking));
+    for (int i = 0; i < 2; ++i) {
+      CUDA_TRY(cudaEventCreateWithFlags(&h->copied[i], cudaEventDisableTiming));
+      CUDA_TRY(cudaEventCreateWithFlags(&h->computed[i], cudaEventDisableTiming));
+    }
+  }
+  if (h->d_audio_floats < wave_floats) {
+    for (int i = 0; i < 2; ++i) { if (h->d_audio[i]) CUDA_TRY(cudaFree(h->d_audio[i])); h->d_audio[i] = nullptr; }
+    for (int i = 0; i < 2; ++i) CUDA_TRY(cudaMalloc((void**)&h->d_audio[i], wave_floats * sizeof(float)));
+    h->d_audio_floats = wave_floats;
+  }
+  if (need_pcm && h->d_pcm_samples < wave_floats) {
+    for (int i = 0; i < 2; ++i) { if (h->d_pcm[i]) CUDA_TRY(cudaFree(h->d_pcm[i])); h->d_pcm[i] = nullptr; }
+    for (int i = 0; i < 2; ++i) CUDA_TRY(cudaMalloc((void**)&h->d_pcm[i], wave_floats * sizeof(int16_t)));
+    h->d_pcm_samples = wave_floats;
+  }
+  if (need_pin && h->h_pin_floats < wave_floats) {
+    for (int i = 0; i < 2; ++i) { if (h->h_pin[i]) CUDA_TRY(cudaFreeHost(h->h_pin[i])); h->h_pin[i] = nullptr; }
+    for (int i = 0; i < 2; ++i) CUDA_TRY(cudaMallocHost((void**)&h->h_pin[i], wave_floats * sizeof(float)));
+    h->h_pin_floats = wave_floats;
+  }
+  const size_t sum_bytes = (size_t)n_clips * afx_summary_width(h) * sizeof(float);
+  const size_t meta_bytes = (size_t)n_clips * 4 * sizeof(int);
+  if (h->d_sum_bytes < sum_bytes) { if (h->d_sum) CUDA_TRY(cudaFree(h->d_sum)); h->d_sum = nullptr; CUDA_TRY(cudaMalloc((void**)&h->d_sum, sum_bytes)); h->d_sum_bytes = sum_bytes; }
+  if (h->d_meta_bytes < meta_bytes) { if (h->d_meta) CUDA_TRY(cudaFree(h->d_meta)); h->d_meta = nullptr; CUDA_TRY(cudaMalloc((void**)&h->d_meta, meta_bytes)); h->d_meta_bytes = meta_bytes; }
+  return AFX_OK;
+}
+
+struct HostWave { int64_t c0, c1; long long base, span; };   // clips [c0,c1); samples [base, base+span) of the packed buffer
+
+// Shared driver of the two host entry points.  `fill(slot, wave)` makes wave's samples available for the
+// H2D copy and returns the host source pointer (the caller's packed buffer, or a pinned staging slot).
+template <typename Fill>
+int run_host_waves(afx_handle_s* h, const std::vector<HostWave>& waves, const std::vector<long long>& rel_off,
+                   const int32_t* h_lengths, int64_t n_clips, uint32_t feature_mask, int sample_format,
+                   float* h_summaries, int32_t* h_meta, Fill fill) {
+  const int SS = afx_summary_width(h);
+  const size_t elt = sample_format == AFX_SAMPLE_S16 ? sizeof(int16_t) : sizeof(float);
+  // workspace for the largest wave
+  size_t ws_need = 0;
+  for (const HostWave& w : waves) ws_need = std::max(ws_need, afx_workspace_bytes(h, w.c1 - w.c0, h_lengths + w.c0));
+  if (h->d_ws_bytes < ws_need) { if (h->d_ws) CUDA_TRY(cudaFree(h->d_ws)); h->d_ws = nullptr; CUDA_TRY(cudaMalloc(&h->d_ws, ws_need)); h->d_ws_bytes = ws_need; }
+
+  auto enqueue_copy = [&](size_t wi) -> int {
+    const HostWave& w = waves[wi];
+    const int slot = (int)(wi & 1);
+    CUDA_TRY(cudaStreamWaitEvent(h->copy_stream, h->computed[slot], 0));   // slot's previous wave has been consumed
+    const void* src = fill(slot, w);
+    if (!src) return AFX_ERR_CUDA;
+    void* dst = sample_format == AFX_SAMPLE_S16 ? (void*)h->d_pcm[slot] : (void*)h->d_audio[slot];
+    CUDA_TRY(cudaMemcpyAsync(dst, src, (size_t)w.span * elt, cudaMemcpyHostToDevice, h->copy_stream));
+    CUDA_TRY(cudaEventRecord(h->copied[slot], h->copy_stream));
+    return AFX_OK;
+  };
+
+  if (int rc = enqueue_copy(0)) return rc;
+  for (size_t wi = 0; wi < waves.size(); ++wi) {
+    const HostWave& w = waves[wi];
+    const int slot = (int)(wi & 1);
+    if (wi + 1 < waves.size()) { if (int rc = enqueue_copy(wi + 1)) return rc; }
+    CUDA_TRY(cudaStreamWaitEvent(h->compute_stream, h->copied[slot], 0));
+    if (sample_format == AFX_SAMPLE_S16) {
+      const long long n8 = (w.span + 7) / 8;
+      const int grid = (int)std::min<long long>((n8 + 255) / 256, 8LL * h->sm_count);
+      pcm16_to_f32_kernel<<<grid, 256, 0, h->compute_stream>>>(h->d_pcm[slot], h->d_audio[slot], n8);
+      ++g_launches;
+    }
+    const int rc = afx_extract(h, h->d_audio[slot], reinterpret_cast<const int64_t*>(rel_off.data() + w.c0), h_lengths + w.c0, w.c1 - w.c0,
+                               feature_mask, h->d_sum + (size_t)w.c0 * SS, h->d_meta + (size_t)w.c0 * 4, nullptr,
+                               h->d_ws, h->d_ws_bytes, h->compute_stream);
+    if (rc != AFX_OK) { cudaDeviceSynchronize(); return rc; }
+    CUDA_TRY(cudaEventRecord(h->computed[slot], h->compute_stream));
+  }
+  CUDA_TRY(cudaMemcpyAsync(h_summaries, h->d_sum, (size_t)n_clips * SS * sizeof(float), cudaMemcpyDeviceToHost, h->compute_stream));
+  CUDA_TRY(cudaMemcpyAsync(h_meta, h->d_meta, (size_t)n_clips * 4 * sizeof(int), cudaMemcpyDeviceToHost, h->compute_stream));
+  CUDA_TRY(cudaStreamSynchronize(h->compute_stream));
+  CUDA_TRY(cudaStreamSynchronize(h->copy_stream));
+  return AFX_OK;
+}
+
+// split clips [0,n) with (4-aligned) sample offsets `off` into waves of at most `cap` samples (a longer clip gets its own wave)
+int plan_waves(const int64_t* off, const int32_t* len, int64_t n, long long cap, std::vector<HostWave>& waves,
+               std::vector<long long>& rel_off, long long* max_span) {
+  rel_off.resize(n);
+  *max_span = 0;
+  int64_t c0 = 0;
+  while (c0 < n) {
+    const long long base = off[c0];
+    int64_t c1 = c0;
+    long long end = base;
+    while (c1 < n) {
+      if (c1 > c0 && off[c1] < off[c1 - 1] + len[c1 - 1]) return fail(AFX_ERR_INVALID_ARG, "host path: clip offsets must be ascending and non-overlapping (clip %lld)", (long long)c1);
+      const long long e = (off[c1] + len[c1] + 7) & ~7LL;   // 8-sample granularity (s16 conversion, TMA tail reads)
+      if (c1 > c0 && e - base > cap) break;
+      end = e; rel_off[c1] = off[c1] - base; ++c1;
+    }
+    waves.push_back(HostWave{c0, c1, base, end - base});
+    *max_span = std::max(*max_span, end - base);
+    c0 = c1;
+  }
+  return AFX_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int afx_extract_host_packed(afx_handle_t h, const void* h_audio, int sample_format, int64_t h_audio_samples,
+                            const int64_t* h_offsets, const int32_t* h_lengths, int64_t n_clips,
+                            uint32_t feature_mask, float* h_summaries, int32_t* h_meta) {
+  if (!h) return fail(AFX_ERR_INVALID_ARG, "afx_extract_host_packed: null handle");
+  if (n_clips == 0) return AFX_OK;
+  if (n_clips < 0 || !h_audio || !h_offsets || !h_lengths || !h_summaries || !h_meta)
+    return fail(AFX_ERR_INVALID_ARG, "afx_extract_host_packed: bad argument");
+  if (sample_format != AFX_SAMPLE_F32 && sample_format != AFX_SAMPLE_S16)
+    return fail(AFX_ERR_INVALID_ARG, "afx_extract_host_packed: unknown sample format %d", sample_format);
+  CUDA_TRY(cudaSetDevice(h->cfg.device));
+  for (int64_t i = 0; i < n_clips; ++i) {
+    if (h_lengths[i] < 0 || h_offsets[i] < 0 || (h_offsets[i] & 7) != 0)
+      return fail(AFX_ERR_INVALID_ARG, "afx_extract_host_packed: clip %lld offset must be a non-negative multiple of 8 samples", (long long)i);
+    if (h_offsets[i] + h_lengths[i] > h_audio_samples)
+      return fail(AFX_ERR_INVALID_ARG, "afx_extract_host_packed: clip %lld runs past the %lld-sample buffer", (long long)i, (long long)h_audio_samples);
+  }
+  std::vector<HostWave> waves;
+  std::vector<long long> rel_off;
+  long long max_span = 0;
+  if (int rc = plan_waves(h_offsets, h_lengths, n_clips, h->host_wave_samples, waves, rel_off, &max_span)) return rc;
+  if (int rc = ensure_host_path(h, (size_t)max_span + 8, sample_format == AFX_SAMPLE_S16, false, n_clips)) return rc;
+  const size_t elt = sample_format == AFX_SAMPLE_S16 ? sizeof(int16_t) : sizeof(float);
+  const char* base = static_cast<const char*>(h_audio);
+  // the last wave's 8-sample rounding may run past the caller's buffer: clamp the copy there
+  for (HostWave& w : waves) w.span = std::min<long long>(w.span, std::max<long long>(h_audio_samples - w.base, 0));
+  return run_host_waves(h, waves, rel_off, h_lengths, n_clips, feature_mask, sample_format, h_summaries, h_meta,
+                        [&](int, const HostWave& w) -> const void* { return base + (size_t)w.base * elt; });
+}
+
 int afx_extract_host(afx_handle_t h, const float* const* h_clips, const int32_t* h_lengths, int64_t n_clips,
                      uint32_t feature_mask, float* h_summaries, int32_t* h_meta) {
-  (void)h; (void)h_clips; (void)h_lengths; (void)n_clips; (void)feature_mask; (void)h_summaries; (void)h_meta;
-  return fail(AFX_ERR_UNSUPPORTED, "afx_extract_host: not built yet");
+  if (!h) return fail(AFX_ERR_INVALID_ARG, "afx_extract_host: null handle");
+  if (n_clips == 0) return AFX_OK;
+  if (n_clips < 0 || !h_clips || !h_lengths || !h_summaries || !h_meta) return fail(AFX_ERR_INVALID_ARG, "afx_extract_host: bad argument");
+  CUDA_TRY(cudaSetDevice(h->cfg.device));
+  std::vector<long long> off(n_clips);
+  long long o = 0;
+  for (int64_t i = 0; i < n_clips; ++i) {
+    if (h_lengths[i] < 0 || (h_lengths[i] > 0 && !h_clips[i])) return fail(AFX_ERR_INVALID_ARG, "afx_extract_host: clip %lld is null or has negative length", (long long)i);
+    off[i] = o; o += ((long long)h_lengths[i] + 7) & ~7LL;
+  }
+  std::vector<HostWave> waves;
+  std::vector<long long> rel_off;
+  long long max_span = 0;
+  if (int rc = plan_waves(reinterpret_cast<const int64_t*>(off.data()), h_lengths, n_clips, h->host_wave_samples, waves, rel_off, &max_span)) return rc;
+  if (int rc = ensure_host_path(h, (size_t)max_span + 8, false, true, n_clips)) return rc;
+  // pack each wave into a pinned slot with a few host threads (the gather is a plain memcpy per clip)
+  auto fill = [&](int slot, const HostWave& w) -> const void* {
+    if (cudaEventSynchronize(h->copied[slot]) != cudaSuccess) return nullptr;   // slot's previous H2D has drained
+    float* dst = h->h_pin[slot];
+    const int nthreads = (int)std::min<int64_t>(std::max(1u, std::min(8u, std::thread::hardware_concurrency())), w.c1 - w.c0);
+    auto work = [&](int t) {
+      for (int64_t c = w.c0 + t; c < w.c1; c += nthreads) {
+        float* d = dst + rel_off[c];
+        const long long len = h_lengths[c], padded = (len + 7) & ~7LL;
+        if (len > 0) memcpy(d, h_clips[c], (size_t)len * sizeof(float));
+        for (long long k = len; k < padded; ++k) d[k] = 0.f;
+      }
+    };
+    if (nthreads <= 1) work(0);
+    else { std::vector<std::thread> th; for (int t = 0; t < nthreads; ++t) th.emplace_back(work, t); for (auto& x : th) x.join(); }
+    return dst;
+  };
+  return run_host_waves(h, waves, rel_off, h_lengths, n_clips, feature_mask, AFX_SAMPLE_F32, h_summaries, h_meta, fill);
 }
 
 }  // extern "C"

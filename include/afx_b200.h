@@ -130,6 +130,24 @@ int afx_extract(afx_handle_t h, const float* d_audio, const int64_t* h_offsets, 
 int afx_extract_host(afx_handle_t h, const float* const* h_clips, const int32_t* h_lengths, int64_t n_clips,
                      uint32_t feature_mask, float* h_summaries, int32_t* h_meta);
 
+/* sample formats of afx_extract_host_packed */
+#define AFX_SAMPLE_F32 0   /* float32 in [-1, 1] */
+#define AFX_SAMPLE_S16 1   /* 16-bit PCM as stored in a WAV data chunk; converted on the device as
+                              x / 32768, the libsndfile scaling librosa.load applies (:52) */
+
+/*
+ * Host path without the gather: the caller already holds the clips in ONE host buffer (ideally
+ * pinned -- cudaHostRegister / torch pin_memory -- so the H2D copies run at PCIe speed and truly
+ * overlap the kernels).  Clip i occupies h_audio[h_offsets[i] .. + h_lengths[i]) in units of
+ * samples; offsets must be ascending, non-overlapping multiples of 8 samples.  h_audio_samples is
+ * the buffer's size in samples.  Copies waves of clips on a copy stream, double buffered against
+ * the compute stream; blocks until h_summaries [n_clips, SS] / h_meta [n_clips, 4] are filled.
+ * This is the call batch_process (core/feature_extractor.py:215-237) makes once per directory.
+ */
+int afx_extract_host_packed(afx_handle_t h, const void* h_audio, int sample_format, int64_t h_audio_samples,
+                            const int64_t* h_offsets, const int32_t* h_lengths, int64_t n_clips,
+                            uint32_t feature_mask, float* h_summaries, int32_t* h_meta);
+
 /* Kernels launched by this library since process start (bench.py reports it as gpu_launches). */
 int64_t afx_launch_count(void);
 
