@@ -21,8 +21,10 @@ EXPORTS = [
     "afx_config_default", "afx_abi_version", "afx_last_error", "afx_create", "afx_destroy",
     "afx_summary_width", "afx_frame_width", "afx_max_frames", "afx_workspace_bytes",
     "afx_workspace_min_bytes", "afx_extract", "afx_extract_host", "afx_extract_host_packed",
-    "afx_launch_count",
+    "afx_launch_count", "afx_profile_enable", "afx_profile_read",
 ]
+PHASES = ("trim", "frames", "mfcc", "finalize", "pcm", "yin", "viterbi", "reserved")
+N_PHASES = 8
 SAMPLE_F32, SAMPLE_S16 = 0, 1
 
 
@@ -67,10 +69,12 @@ def lib():
     L.afx_workspace_bytes.argtypes = [vp, i64, vp]; L.afx_workspace_bytes.restype = sz
     L.afx_workspace_min_bytes.argtypes = [vp, i64, vp]; L.afx_workspace_min_bytes.restype = sz
     L.afx_extract.argtypes = [vp, vp, vp, vp, i64, u32, vp, vp, vp, vp, sz, vp]; L.afx_extract.restype = C.c_int
-    L.afx_extract_host.argtypes = [vp, vp, vp, vp, i64, u32, vp, vp, vp]; L.afx_extract_host.restype = C.c_int
+    L.afx_extract_host.argtypes = [vp, vp, vp, i64, u32, vp, vp]; L.afx_extract_host.restype = C.c_int
     L.afx_extract_host_packed.argtypes = [vp, vp, C.c_int, i64, vp, vp, i64, u32, vp, vp]
     L.afx_extract_host_packed.restype = C.c_int
     L.afx_launch_count.argtypes = []; L.afx_launch_count.restype = i64
+    L.afx_profile_enable.argtypes = [vp, C.c_int]; L.afx_profile_enable.restype = C.c_int
+    L.afx_profile_read.argtypes = [vp, vp, vp, C.c_int]; L.afx_profile_read.restype = C.c_int
     L.afx_debug_header_bytes.argtypes = [i64]; L.afx_debug_header_bytes.restype = sz
     if L.afx_abi_version() != ABI_VERSION:
         raise ImportError(f"libafx_b200.so ABI {L.afx_abi_version()} != binding {ABI_VERSION}; rebuild")

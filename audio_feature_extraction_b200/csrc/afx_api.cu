@@ -80,9 +80,34 @@ struct afx_handle_s {
   cudaStream_t copy_stream = nullptr, compute_stream = nullptr;
   cudaEvent_t copied[2] = {nullptr, nullptr}, computed[2] = {nullptr, nullptr};
   long long host_wave_samples = 16ll << 20;   // samples per host->device wave (AFX_HOST_WAVE_SAMPLES)
+  // per-phase device-time accounting (afx_profile_enable / afx_profile_read)
+  bool profiling = false;
+  struct Span { cudaEvent_t a, b; int phase; };
+  std::vector<Span> spans;            // recorded, not yet folded into prof_ms
+  std::vector<cudaEvent_t> ev_pool;   // recycled events
+  double prof_ms[AFX_N_PHASES] = {0};
+  long long prof_launches[AFX_N_PHASES] = {0};
 };
 
 namespace {
+
+cudaEvent_t prof_event(afx_handle_s* h) {
+  cudaEvent_t e = nullptr;
+  if (!h->ev_pool.empty()) { e = h->ev_pool.back(); h->ev_pool.pop_back(); }
+  else cudaEventCreate(&e);
+  return e;
+}
+// RAII: brackets the launches of one phase with two events on `stream` when profiling is on
+struct PhaseTimer {
+  afx_handle_s* h; cudaStream_t s; int phase; cudaEvent_t a = nullptr;
+  PhaseTimer(afx_handle_s* h_, cudaStream_t s_, int phase_) : h(h_), s(s_), phase(phase_) {
+    ++h->prof_launches[phase];
+    if (h->profiling) { a = prof_event(h); cudaEventRecord(a, s); }
+  }
+  ~PhaseTimer() {
+    if (a) { cudaEvent_t b = prof_event(h); cudaEventRecord(b, s); h->spans.push_back({a, b, phase}); }
+  }
+};
 
 struct Layout {   // carve-up of the caller's workspace
   size_t off_offsets, off_frame_off, off_lengths, off_chunk_b, off_chunk_c, off_info, header_bytes;
@@ -211,6 +236,11 @@ int afx_destroy(afx_handle_t h) {
   if (h->h_stage) cudaFreeHost(h->h_stage);
   if (h->stage_ev) cudaEventDestroy(h->stage_ev);
   cudaFree(h->d_ws); cudaFree(h->d_audio[0]); cudaFree(h->d_audio[1]); cudaFree(h->d_sum); cudaFree(h->d_meta);
+  for (auto& sp : h->spans) { cudaEventDestroy(sp.a); cudaEventDestroy(sp.b); }
+  for (auto e : h->ev_pool) cudaEventDestroy(e);
+  cudaFree(h->d_pcm[0]); cudaFree(h->d_pcm[1]);
+  if (h->h_pin[0]) cudaFreeHost(h->h_pin[0]);
+  if (h->h_pin[1]) cudaFreeHost(h->h_pin[1]);
   for (int i = 0; i < 2; ++i) { if (h->copied[i]) cudaEventDestroy(h->copied[i]); if (h->computed[i]) cudaEventDestroy(h->computed[i]); }
   if (h->copy_stream) cudaStreamDestroy(h->copy_stream);
   if (h->compute_stream) cudaStreamDestroy(h->compute_stream);
@@ -331,6 +361,7 @@ int afx_extract(afx_handle_t h, const float* d_audio, const int64_t* h_offsets, 
       ta.audio = d_audio; ta.offsets = d_offsets; ta.lengths = d_lengths; ta.info = d_info;
       ta.clip_begin = c0; ta.hop = hop; ta.coef = h->cfg.pre_emphasis; ta.top_db = h->cfg.trim_top_db;
       const size_t smem = (size_t)(ceil_div(max_len, afx::kTrimHop) + 4) * sizeof(float);
+      PhaseTimer pt(h, stream, AFX_PHASE_TRIM);
       afx::trim_kernel<<<nw, afx::kTrimThreads, smem, stream>>>(ta);
       ++g_launches;
     }
@@ -342,6 +373,7 @@ int afx_extract(afx_handle_t h, const float* d_audio, const int64_t* h_offsets, 
       fa.logmel = d_logmel; fa.rms = d_rms; fa.tab = h->tab; fa.hop = hop; fa.tile_floats = tile_floats;
       fa.coef = h->cfg.pre_emphasis;
       const int grid = std::max(1, std::min(fa.n_tasks, 2 * h->sm_count));
+      PhaseTimer pt(h, stream, AFX_PHASE_FRAMES);
       afx::frames_kernel<1024><<<grid, afx::kFramesWarps * 32, fr_smem, stream>>>(fa);
       ++g_launches;
     }
@@ -352,6 +384,7 @@ int afx_extract(afx_handle_t h, const float* d_audio, const int64_t* h_offsets, 
       sa.frames_out = d_frames; sa.n_mfcc = h->cfg.n_mfcc; sa.n16 = h->n16; sa.frame_width = afx_frame_width(h);
       sa.top_db = h->cfg.mfcc_top_db;
       const int grid = s_chunk_c[c1] - s_chunk_c[c0];
+      PhaseTimer pt(h, stream, AFX_PHASE_MFCC);
       afx::mfcc_stats_kernel<<<grid, afx::kStatThreads, st_smem, stream>>>(sa);
       ++g_launches;
     }
@@ -361,12 +394,38 @@ int afx_extract(afx_handle_t h, const float* d_audio, const int64_t* h_offsets, 
       fa.frame_base = s_frame_off[c0]; fa.partials = d_part; fa.rms = d_rms; fa.f0 = nullptr; fa.voiced_prob = nullptr;
       fa.summaries = d_summaries; fa.meta = d_meta; fa.frames_out = d_frames; fa.n_mfcc = h->cfg.n_mfcc;
       fa.summary_width = afx_summary_width(h); fa.frame_width = afx_frame_width(h); fa.mask = feature_mask;
+      PhaseTimer pt(h, stream, AFX_PHASE_FINALIZE);
       afx::finalize_kernel<<<nw, afx::kFinalThreads, 0, stream>>>(fa);
       ++g_launches;
     }
     c0 = c1;
   }
   CUDA_TRY(cudaGetLastError());
+  return AFX_OK;
+}
+
+int afx_profile_enable(afx_handle_t h, int on) {
+  if (!h) return fail(AFX_ERR_INVALID_ARG, "afx_profile_enable: null handle");
+  h->profiling = on != 0;
+  return AFX_OK;
+}
+
+int afx_profile_read(afx_handle_t h, double* ms, int64_t* launches, int reset) {
+  if (!h) return fail(AFX_ERR_INVALID_ARG, "afx_profile_read: null handle");
+  CUDA_TRY(cudaSetDevice(h->cfg.device));
+  for (auto& sp : h->spans) {
+    CUDA_TRY(cudaEventSynchronize(sp.b));
+    float t = 0.f;
+    CUDA_TRY(cudaEventElapsedTime(&t, sp.a, sp.b));
+    h->prof_ms[sp.phase] += t;
+    h->ev_pool.push_back(sp.a); h->ev_pool.push_back(sp.b);
+  }
+  h->spans.clear();
+  for (int p = 0; p < AFX_N_PHASES; ++p) {
+    if (ms) ms[p] = h->prof_ms[p];
+    if (launches) launches[p] = h->prof_launches[p];
+    if (reset) { h->prof_ms[p] = 0; h->prof_launches[p] = 0; }
+  }
   return AFX_OK;
 }
 
@@ -461,6 +520,7 @@ int run_host_waves(afx_handle_s* h, const std::vector<HostWave>& waves, const st
     if (sample_format == AFX_SAMPLE_S16) {
       const long long n8 = (w.span + 7) / 8;
       const int grid = (int)std::min<long long>((n8 + 255) / 256, 8LL * h->sm_count);
+      PhaseTimer pt(h, h->compute_stream, AFX_PHASE_PCM);
       pcm16_to_f32_kernel<<<grid, 256, 0, h->compute_stream>>>(h->d_pcm[slot], h->d_audio[slot], n8);
       ++g_launches;
     }

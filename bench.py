@@ -1,0 +1,394 @@
+#!/usr/bin/env python
+"""Benchmark of the AudioFeatureExtractor hot path (BASELINE.json metric: audio-hours/sec, 22.05 kHz
+MFCC+delta+delta2+energy, and its fraction of the HBM roofline).
+
+    python bench.py --gpus N --steps K --warmup W            # native arm (CUDA kernels via the C ABI)
+    python bench.py --impl reference --gpus N --steps K ...  # restated-librosa CPU path on the host cores
+
+Workload (config "c2" = BASELINE.json configs[1]): 10 000 synthetic 10 s clips at 22.05 kHz per GPU
+(8.82 GB of float32, generated on the device; larger than L2, so no flush is needed between steps),
+frame 1024 / hop 256 / n_mfcc 13, feature groups mfcc + energy.  One step = one pass of
+afx_extract over the whole resident batch.  Multi-GPU: one process per GPU (torchrun), clips sharded by
+rank (weak scaling), one NCCL gather of the summary rows to rank 0 inside every step.
+
+One JSON line is printed by rank 0; see DESIGN.md "Measurement" for the definition of every key.
+"""
+from __future__ import annotations
+
+import argparse
+import ctypes as C
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+from pathlib import Path
+
+import numpy as np
+
+ROOT = Path(__file__).resolve().parent
+if str(ROOT) not in sys.path:
+    sys.path.insert(0, str(ROOT))
+
+METRIC = "audio_hours_per_sec"
+UNIT = "audio-hours/s"
+GROUPS = ("mfcc", "energy")
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", choices=("native", "reference"), default="native")
+    ap.add_argument("--config", default="c2", help="synth.CONFIGS key (c2 = the headline workload)")
+    ap.add_argument("--clips", type=int, default=10000, help="clips per GPU")
+    ap.add_argument("--features", default="mfcc,energy")
+    ap.add_argument("--e2e-clips", type=int, default=0, help="clips of the host-buffer (e2e) leg; 0 = clips/4")
+    ap.add_argument("--cpu-clips", type=int, default=0, help="clips of the CPU baseline sample; 0 = auto")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    return ap.parse_args()
+
+
+# ----------------------------------------------------------------------------- clocks sampler
+class ClockSampler:
+    """nvidia-smi clocks + throttle reasons sampled every 200 ms while the timed region runs."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.index = index
+        self.proc = None
+        self.lines = []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "200"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._pump, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+
+    def _pump(self):
+        for ln in self.proc.stdout:
+            self.lines.append(ln.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, smax, reasons, power = [], [], set(), []
+        names = ("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap")
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 7:
+                continue
+            try:
+                sm.append(float(f[0])); smax.append(float(f[1])); power.append(float(f[2]))
+            except ValueError:
+                continue
+            for nm, v in zip(names, f[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(smax) if smax else None,
+                "power_w_max": max(power) if power else None, "samples": len(sm), "reasons": sorted(reasons)}
+
+
+# ----------------------------------------------------------------------------- CPU (oracle) leg
+def _cpu_worker_init():
+    for k in ("OMP_NUM_THREADS", "MKL_NUM_THREADS", "OPENBLAS_NUM_THREADS"):
+        os.environ[k] = "1"
+    import oracle  # noqa: F401  (bench.py's cpu_baseline / --impl reference legs may execute oracle/)
+
+
+def _cpu_worker(task):
+    shm_name, n_total, stride, length, kw, groups, idxs = task
+    from multiprocessing import shared_memory
+    from oracle import OracleFeatureExtractor
+    shm = shared_memory.SharedMemory(name=shm_name)
+    try:
+        a = np.ndarray((n_total, stride), dtype=np.float32, buffer=shm.buf)
+        ora = OracleFeatureExtractor(**kw)
+        out = []
+        for i in idxs:
+            try:
+                f = ora.extract_features_array(a[i, :length], features_to_extract=groups)
+                out.append(float(f.get("energy_mean", f.get("f0_mean", 0.0))))
+            except Exception:
+                out.append(float("nan"))
+        del a
+        return out
+    finally:
+        shm.close()
+
+
+class CpuPath:
+    """The restated-librosa oracle over a pool of host processes: one clip per task, all host cores
+    (the reference's own scale-out idiom is multiprocessing.Pool over files,
+    04_feature_extraction_experiment/feature_extraction_for_student.py:168-171)."""
+
+    def __init__(self, clips2d: np.ndarray, length: int, ex_kw: dict, groups):
+        import multiprocessing as mp
+        from multiprocessing import shared_memory
+        self.cores = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
+        self.n, self.stride = clips2d.shape
+        self.length, self.kw, self.groups = length, ex_kw, tuple(groups)
+        self.shm = shared_memory.SharedMemory(create=True, size=clips2d.nbytes)
+        np.ndarray(clips2d.shape, dtype=np.float32, buffer=self.shm.buf)[:] = clips2d
+        for k in ("OMP_NUM_THREADS", "MKL_NUM_THREADS", "OPENBLAS_NUM_THREADS", "NUMBA_NUM_THREADS"):
+            os.environ[k] = "1"   # inherited by the spawned workers (this process's libraries are already loaded)
+        self.pool = mp.get_context("spawn").Pool(self.cores, initializer=_cpu_worker_init)
+        self.run(list(range(min(self.n, self.cores))))   # spin the workers up (imports, numba-free path)
+
+    def run(self, idxs):
+        """process clips `idxs`; returns wall seconds"""
+        chunks = [idxs[k::self.cores] for k in range(self.cores)]
+        tasks = [(self.shm.name, self.n, self.stride, self.length, self.kw, self.groups, c) for c in chunks if c]
+        t0 = time.perf_counter()
+        self.pool.map(_cpu_worker, tasks, chunksize=1)
+        return time.perf_counter() - t0
+
+    def close(self):
+        self.pool.close(); self.pool.join()
+        self.shm.close(); self.shm.unlink()
+
+
+def _ex_kwargs(cfg):
+    return dict(sr=cfg["sr"], frame_length=cfg["frame_length"], hop_length=cfg["hop_length"], n_mfcc=cfg["n_mfcc"])
+
+
+def _workload_name(args, cfg, n_clips):
+    return (f"{args.config}: {n_clips} synthetic {cfg['seconds']:g} s clips/GPU @ {cfg['sr']} Hz, frame {cfg['frame_length']} "
+            f"hop {cfg['hop_length']} n_mfcc {cfg['n_mfcc']}, features {'+'.join(args.features.split(','))}")
+
+
+def _hours(n_clips, cfg):
+    return n_clips * cfg["seconds"] / 3600.0
+
+
+# ----------------------------------------------------------------------------- reference arm
+def run_reference(args):
+    """The reference's own CPU implementation of the path is librosa (absent here and on the GPU box), so
+    this arm times its restatement (oracle/, kind "port") on all host cores, on a bounded sample of the
+    same workload per step."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    import torch
+    from audio_feature_extraction_b200.synth import CONFIGS, make_batch_torch
+    cfg = CONFIGS[args.config]
+    groups = tuple(args.features.split(","))
+    cores = len(os.sched_getaffinity(0))
+    per_clip_s = 0.03 * cfg["seconds"] / 10.0 if "f0" not in groups else 8.0 * cfg["seconds"] / 10.0
+    n = args.cpu_clips or int(max(cores, min(1024, round(4.0 * cores / per_clip_s))))   # ~4 s wall per step
+    dev = "cuda" if torch.cuda.is_available() else "cpu"   # input synthesis only; nothing of ours runs on the timed path
+    n_unique = min(n, 256)
+    audio, offsets, lengths = make_batch_torch(n_unique, sr=cfg["sr"], seconds=cfg["seconds"], f_lo=cfg["f_lo"], f_hi=cfg["f_hi"],
+                                               kind=cfg["kind"], seed=1234, device=dev)
+    length = int(lengths[0]); stride = int(offsets[1] - offsets[0]) if n_unique > 1 else audio.numel()
+    clips2d = audio.cpu().numpy().reshape(n_unique, stride)
+    cpu = CpuPath(clips2d, length, _ex_kwargs(cfg), groups)
+    idxs = [i % n_unique for i in range(n)]
+    for _ in range(args.warmup):
+        cpu.run(idxs)
+    t = [cpu.run(idxs) for _ in range(args.steps)]
+    cpu.close()
+    sec = float(np.sum(t))
+    value = _hours(n, cfg) * args.steps / sec
+    sample = f"{n} clips x {cfg['seconds']:g} s per step ({n_unique} unique), multiprocessing.Pool({cpu.cores}), 1 BLAS thread each"
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": 1e3 * sec / args.steps, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": _workload_name(args, cfg, args.clips), "sample": sample},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cpu.cores, "kind": "port", "sample": sample},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+        "note": "librosa (the reference's arithmetic) is not installable offline: this is the numpy/scipy restatement in oracle/",
+    }
+    print(json.dumps(line), flush=True)
+    return 0
+
+
+# ----------------------------------------------------------------------------- native arm
+def _peak_hbm():
+    p = ROOT / "MEASURED_PEAKS.json"
+    try:
+        return float(json.loads(p.read_text())["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def _ncu_traffic(kernel: str):
+    """dram bytes per launch of `kernel` from the committed ncu --set full summary, if one exists."""
+    p = ROOT / "profiles" / "ncu_traffic.json"
+    try:
+        return json.loads(p.read_text())[kernel]["dram_bytes_per_launch"]
+    except Exception:
+        return None
+
+
+def run_native(args):
+    import torch
+    import torch.distributed as dist
+    from audio_feature_extraction_b200 import AudioFeatureExtractor, _native as N
+    from audio_feature_extraction_b200.synth import CONFIGS, make_batch_torch
+
+    rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py (native arm) needs a CUDA device: there is no CPU fallback")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    L = N.lib()
+    cfg = CONFIGS[args.config]
+    groups = tuple(args.features.split(","))
+    n = args.clips
+    audio, offsets, lengths = make_batch_torch(n, sr=cfg["sr"], seconds=cfg["seconds"], f_lo=cfg["f_lo"], f_hi=cfg["f_hi"],
+                                               kind=cfg["kind"], seed=1000 + rank, device=dev, align=8)
+    offsets, lengths = offsets.numpy(), lengths.numpy()
+    ex = AudioFeatureExtractor(device=local, **_ex_kwargs(cfg))
+    h = ex._h()
+    SS = ex.summary_width
+    gathered = [torch.empty((n, SS), dtype=torch.float32, device=dev) for _ in range(world)] if (world > 1 and rank == 0) else None
+
+    def step():
+        summ, meta, _ = ex.extract_batch_device(audio, offsets, lengths, groups)
+        if world > 1:   # the path's only inter-GPU step: per-file summary rows -> rank 0 (NCCL over NVLink)
+            dist.gather(summ, gathered, dst=0)
+        return summ, meta
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(args.warmup):
+        step()
+    barrier()
+    L.afx_profile_read(h, None, None, 1)
+    L.afx_profile_enable(h, 1)
+    launches0 = L.afx_launch_count()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    e0.record()
+    for _ in range(args.steps):
+        summ, meta = step()
+    e1.record()
+    barrier()
+    ms_total = e0.elapsed_time(e1)
+    clocks = sampler.stop() if rank == 0 else None
+    launches = L.afx_launch_count() - launches0
+    L.afx_profile_enable(h, 0)
+    ph_ms = (C.c_double * N.N_PHASES)(); ph_n = (C.c_int64 * N.N_PHASES)()
+    N.check(L.afx_profile_read(h, ph_ms, ph_n, 1))
+    t = torch.tensor([ms_total], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_total = float(t.item())
+    ok = int((meta[:, 0] == 0).sum().item())
+    ms_per_step = ms_total / args.steps
+    value = world * _hours(n, cfg) / (ms_per_step * 1e-3)
+
+    # ---- roofline of the dominant kernel (algorithmic bytes: every sample read once + the output rows)
+    phases = {N.PHASES[p]: {"ms_per_step": ph_ms[p] / args.steps, "launches_per_step": ph_n[p] / args.steps}
+              for p in range(N.N_PHASES) if ph_n[p]}
+    dom = max(phases, key=lambda k: phases[k]["ms_per_step"])
+    bytes_per_step = float(4 * int(lengths.astype(np.int64).sum()) + n * (4 * SS + 16))
+    peak, peak_src = _peak_hbm()
+    dom_ms = phases[dom]["ms_per_step"]
+    achieved = bytes_per_step / (dom_ms * 1e-3) / 1e9
+    kernel_name = {"frames": "frames_kernel", "trim": "trim_kernel", "mfcc": "mfcc_stats_kernel", "finalize": "finalize_kernel",
+                   "yin": "yin_kernel", "viterbi": "viterbi_kernel", "pcm": "pcm16_to_f32_kernel"}.get(dom, dom)
+    roofline = {"bound": "hbm", "kernel": kernel_name, "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                "traffic": _ncu_traffic(kernel_name), "peak_source": peak_src,
+                "algorithmic_bytes_per_launch": bytes_per_step / max(phases[dom]["launches_per_step"], 1),
+                "avg_launch_ms": dom_ms / max(phases[dom]["launches_per_step"], 1),
+                "whole_path_frac": bytes_per_step / (ms_per_step * 1e-3) / 1e9 / peak, "phases": phases}
+
+    # ---- e2e: the same metric through the C-ABI host entry (pinned host buffer -> H2D waves -> kernels -> D2H rows)
+    e2e = None
+    if not args.no_e2e:
+        ne = args.e2e_clips or max(1, n // 4)
+        ne = min(ne, n)
+        stride = int(offsets[1] - offsets[0]) if n > 1 else int(audio.numel())
+        span = ne * stride
+        host = torch.empty(span, dtype=torch.float32, pin_memory=True)
+        host.copy_(audio[:span]); torch.cuda.synchronize()
+        hs = np.zeros((ne, SS), np.float32); hm = np.zeros((ne, 4), np.int32)
+        mask = sum({"f0": 1, "mfcc": 2, "energy": 4}[g] for g in groups)
+        off8 = np.ascontiguousarray(offsets[:ne]); len8 = np.ascontiguousarray(lengths[:ne])
+        assert (off8 % 8 == 0).all()
+
+        def e2e_step():
+            N.check(L.afx_extract_host_packed(h, host.data_ptr(), N.SAMPLE_F32, span, off8.ctypes.data, len8.ctypes.data,
+                                              ne, mask, hs.ctypes.data, hm.ctypes.data))
+        for _ in range(max(1, min(args.warmup, 2))):
+            e2e_step()
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            e2e_step()
+        dt = time.perf_counter() - t0
+        t = torch.tensor([dt], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dt = float(t.item())
+        assert np.array_equal(hm[:, 0], meta[:ne, 0].cpu().numpy())
+        e2e = {"value": world * _hours(ne, cfg) * args.steps / dt, "unit": UNIT,
+               "h2d_bytes_per_step": int(4 * span), "d2h_bytes_per_step": int(ne * (4 * SS + 16)),
+               "clips_per_gpu": ne, "api": "afx_extract_host_packed (pinned float32 host buffer)"}
+        del host
+
+    # ---- CPU baseline beside it (rank 0, N = 1 only): the oracle on a bounded sample of the same clips
+    cpu_baseline = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        cores = len(os.sched_getaffinity(0))
+        per_clip_s = 0.03 * cfg["seconds"] / 10.0 if "f0" not in groups else 8.0 * cfg["seconds"] / 10.0
+        nc = args.cpu_clips or int(max(cores, min(2048, n, round(20.0 / per_clip_s))))   # ~20 s of CPU work
+        stride = int(offsets[1] - offsets[0]) if n > 1 else int(audio.numel())
+        clips2d = audio[:nc * stride].cpu().numpy().reshape(nc, stride)
+        cpu = CpuPath(clips2d, int(lengths[0]), _ex_kwargs(cfg), groups)
+        sec = cpu.run(list(range(nc)))
+        cpu.close()
+        cpu_baseline = {"value": _hours(nc, cfg) / sec, "unit": UNIT, "cores": cpu.cores, "kind": "port",
+                        "sample": f"first {nc} clips of the GPU batch, multiprocessing.Pool({cpu.cores}) over clips, 1 BLAS thread each, {sec:.2f} s wall"}
+
+    if rank == 0:
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic",
+            "config": {"workload": _workload_name(args, cfg, n), "clips_ok": ok, "l2": "inputs (8.8 GB/GPU) larger than L2, no flush",
+                       "sharding": f"clips by rank x{world}, NCCL gather of summary rows to rank 0 each step" if world > 1 else "single GPU"},
+            "roofline": roofline, "cpu_baseline": cpu_baseline, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks,
+        }
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    return 0
+
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        return run_reference(args)
+    return run_native(args)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

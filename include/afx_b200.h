@@ -148,6 +148,21 @@ int afx_extract_host_packed(afx_handle_t h, const void* h_audio, int sample_form
                             const int64_t* h_offsets, const int32_t* h_lengths, int64_t n_clips,
                             uint32_t feature_mask, float* h_summaries, int32_t* h_meta);
 
+/* Per-phase device-time accounting, for bench.py's roofline line: when enabled, every kernel launch
+ * of afx_extract is bracketed by two CUDA events on the launching stream.  afx_profile_read
+ * synchronises on the recorded events and returns, per phase, the accumulated milliseconds and the
+ * number of launches since the last reset. */
+#define AFX_PHASE_TRIM     0   /* pre-emphasis + trim decision            (trim_kernel) */
+#define AFX_PHASE_FRAMES   1   /* frames -> FFT -> mel -> dB, RMS          (frames_kernel) */
+#define AFX_PHASE_MFCC     2   /* clamp, DCT, delta, delta2, moments       (mfcc_stats_kernel) */
+#define AFX_PHASE_FINALIZE 3   /* per-clip statistics -> summary rows      (finalize_kernel) */
+#define AFX_PHASE_PCM      4   /* PCM16 -> float32                         (pcm16_to_f32_kernel) */
+#define AFX_PHASE_YIN      5   /* YIN difference / CMND / pYIN observations */
+#define AFX_PHASE_VITERBI  6   /* pYIN HMM decode */
+#define AFX_N_PHASES       8
+int afx_profile_enable(afx_handle_t h, int on);
+int afx_profile_read(afx_handle_t h, double* ms /*[AFX_N_PHASES]*/, int64_t* launches /*[AFX_N_PHASES]*/, int reset);
+
 /* Kernels launched by this library since process start (bench.py reports it as gpu_launches). */
 int64_t afx_launch_count(void);
 

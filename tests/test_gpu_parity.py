@@ -1,0 +1,205 @@
+"""GPU parity: the CUDA path (through the C ABI of libafx_b200.so) against the CPU oracle on the same
+seeded clips, at BASELINE.json's tolerances:
+  frame counts / trim indices bit-exact; MFCC <= 1e-3 abs (after the dB step); energy <= 1e-5 rel.
+Needs a B200: run with `-m gpu`."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+MFCC_ATOL = 1e-3      # BASELINE.json north_star: "MFCC: within 1e-3 absolute after the dB step"
+ENERGY_RTOL = 1e-5    # "energy: within 1e-5 relative"
+GROUPS = ("mfcc", "energy")
+
+
+@pytest.fixture(scope="module")
+def torch_cuda(built_lib):
+    import torch
+    if not torch.cuda.is_available():
+        pytest.fail("-m gpu tests need a CUDA device (there is no CPU fallback)")
+    return torch
+
+
+def _framewise(ex, clips, groups=GROUPS):
+    import torch
+    buf, offsets, lengths = ex.pack_clips(clips)
+    audio = buf.cuda()
+    summ, meta, frames = ex.extract_batch_device(audio, offsets, lengths, groups, return_frames=True)
+    torch.cuda.synchronize()
+    rows = np.concatenate([[0], np.cumsum([ex.max_frames(int(l)) for l in lengths])])
+    return summ.cpu().numpy(), meta.cpu().numpy(), frames.cpu().numpy(), rows
+
+
+def _check_clip(ex, ora, y, summ, meta, frames, row0, n):
+    s, e = ora.trim_indices(y)
+    yt = ora.preprocess_audio(y)
+    m, d1, d2 = ora.mfcc_frames(yt)
+    r = ora.rms_frames(yt)[0]
+    T = m.shape[1]
+    # frame counts and indexing: bit-exact
+    assert meta.tolist() == [0, s, e, T]
+    fr = frames[row0:row0 + T]
+    assert np.max(np.abs(fr[:, 0:n].T - m)) <= MFCC_ATOL
+    assert np.max(np.abs(fr[:, n:2 * n].T - d1)) <= MFCC_ATOL
+    assert np.max(np.abs(fr[:, 2 * n:3 * n].T - d2)) <= MFCC_ATOL
+    np.testing.assert_allclose(fr[:, 3 * n], r, rtol=ENERGY_RTOL, atol=1e-12)
+    # summary row in the reference's key order (include/afx_b200.h)
+    assert np.max(np.abs(summ[4:4 + n] - m.mean(axis=1))) <= MFCC_ATOL
+    assert np.max(np.abs(summ[4 + n:4 + 2 * n] - m.std(axis=1))) <= MFCC_ATOL
+    assert np.max(np.abs(summ[4 + 2 * n:4 + 3 * n] - d1.mean(axis=1))) <= MFCC_ATOL
+    assert np.max(np.abs(summ[4 + 3 * n:4 + 4 * n] - d2.mean(axis=1))) <= MFCC_ATOL
+    e0 = 4 + 4 * n
+    np.testing.assert_allclose(summ[e0:e0 + 3], [r.mean(), r.std(), np.ptp(r)], rtol=ENERGY_RTOL)
+
+
+def test_c2_config_framewise_and_summary_parity(torch_cuda):
+    from audio_feature_extraction_b200 import AudioFeatureExtractor
+    from audio_feature_extraction_b200.synth import make_clip
+    from oracle import OracleFeatureExtractor
+
+    secs = [10.0, 5.0, 3.3, 1.0, 0.5, 7.77, 10.0, 2.0]
+    clips = [make_clip(s, seconds=sec) for s, sec in enumerate(secs)]
+    ex = AudioFeatureExtractor()
+    ora = OracleFeatureExtractor()
+    summ, meta, frames, rows = _framewise(ex, clips)
+    for i, y in enumerate(clips):
+        _check_clip(ex, ora, y, summ[i], meta[i], frames, rows[i], ex.n_mfcc)
+
+
+def test_extended_statistics_match_scipy(torch_cuda):
+    from audio_feature_extraction_b200 import AudioFeatureExtractor
+    from audio_feature_extraction_b200.synth import make_clip
+    from oracle import OracleFeatureExtractor
+
+    clips = [make_clip(40 + s, seconds=4.0) for s in range(3)]
+    ex = AudioFeatureExtractor(extended_stats=True)
+    ora = OracleFeatureExtractor(extended_stats=True)
+    got = ex.extract_batch(clips, features_to_extract=GROUPS)
+    for y, g in zip(clips, got):
+        ref = ora.extract_features_array(y, features_to_extract=GROUPS)
+        np.testing.assert_allclose(g["mfcc_skew"], ref["mfcc_skew"], atol=2e-3)
+        np.testing.assert_allclose(g["mfcc_kurtosis"], ref["mfcc_kurtosis"], atol=5e-3)
+        assert g["energy_skew"] == pytest.approx(ref["energy_skew"], abs=1e-4)
+        assert g["energy_kurtosis"] == pytest.approx(ref["energy_kurtosis"], abs=1e-4)
+
+
+def test_edge_cases_status_codes(torch_cuda):
+    """empty / non-finite / all-silent-after-trim / too-short clips: the librosa exceptions the reference
+    re-raises (core/feature_extractor.py:211-213) become per-clip status codes; neighbours are unaffected."""
+    from audio_feature_extraction_b200 import AudioFeatureExtractor, FeatureExtractionError, _native as N
+    from audio_feature_extraction_b200.synth import make_clip
+    from oracle import OracleFeatureExtractor
+
+    good = make_clip(7, seconds=2.0)
+    nan = good.copy(); nan[12345] = np.nan
+    inf = good.copy(); inf[-1] = np.inf
+    short = make_clip(8, seconds=2.0)[6000:6000 + 1500]       # T = 1 + 1500 // 256 = 6 < 9
+    empty = np.zeros(0, dtype=np.float32)
+    one = np.array([0.25], dtype=np.float32)
+    loud_then_zero = np.concatenate([good, np.zeros(50000, dtype=np.float32)])
+    clips = [good, nan, empty, short, inf, one, loud_then_zero, good]
+    ex = AudioFeatureExtractor()
+    ora = OracleFeatureExtractor()
+    summ, meta, frames, rows = _framewise(ex, clips)
+    assert meta[:, 0].tolist() == [0, N.CLIP_NONFINITE, N.CLIP_EMPTY, N.CLIP_TOO_SHORT, N.CLIP_NONFINITE,
+                                   N.CLIP_TOO_SHORT, 0, 0]
+    assert (summ[[1, 2, 3, 4, 5]] == 0).all()
+    for i in (0, 6, 7):
+        _check_clip(ex, ora, clips[i], summ[i], meta[i], frames, rows[i], ex.n_mfcc)
+    with pytest.raises(FeatureExtractionError):
+        ex.extract_batch(clips, features_to_extract=GROUPS)
+    kept = ex.extract_batch(clips, names=[f"c{i}.wav" for i in range(len(clips))], features_to_extract=GROUPS, skip_errors=True)
+    assert [k["file_path"] for k in kept] == ["c0.wav", "c6.wav", "c7.wav"]
+
+
+def test_ragged_batch_small_workspace_waves(torch_cuda):
+    """Many ragged clips with a workspace at the documented minimum: the wave scheduler must split the
+    batch and still produce the same rows as one big wave."""
+    import torch
+    from audio_feature_extraction_b200 import AudioFeatureExtractor, _native as N
+    from audio_feature_extraction_b200.synth import make_clip
+
+    rng = np.random.default_rng(0)
+    clips = [make_clip(100 + i, seconds=float(rng.uniform(0.3, 3.0))) for i in range(40)]
+    ex = AudioFeatureExtractor()
+    buf, offsets, lengths = ex.pack_clips(clips)
+    audio = buf.cuda()
+    s_ref, m_ref, _ = ex.extract_batch_device(audio, offsets, lengths, GROUPS)
+    L, h = N.lib(), ex._h()
+    need = L.afx_workspace_min_bytes(h, len(clips), lengths.ctypes.data)
+    ws = torch.empty(int(need), dtype=torch.uint8, device="cuda")
+    s2 = torch.empty_like(s_ref); m2 = torch.empty_like(m_ref)
+    N.check(L.afx_extract(h, audio.data_ptr(), offsets.ctypes.data, lengths.ctypes.data, len(clips), 0x6,
+                          s2.data_ptr(), m2.data_ptr(), None, ws.data_ptr(), ws.numel(), None))
+    torch.cuda.synchronize()
+    assert torch.equal(m_ref, m2)
+    assert torch.equal(s_ref, s2)          # same kernels, same order of operations -> bit-identical
+    rc = L.afx_extract(h, audio.data_ptr(), offsets.ctypes.data, lengths.ctypes.data, len(clips), 0x6,
+                       s2.data_ptr(), m2.data_ptr(), None, ws.data_ptr(), 4096, None)
+    assert rc == N.ERR_WORKSPACE
+
+
+def test_host_entry_points_match_device_entry(torch_cuda):
+    import torch
+    from audio_feature_extraction_b200 import AudioFeatureExtractor, _native as N
+    from audio_feature_extraction_b200.synth import make_clip
+
+    clips = [make_clip(200 + i, seconds=1.0 + 0.37 * i) for i in range(9)]
+    ex = AudioFeatureExtractor()
+    buf, offsets, lengths = ex.pack_clips(clips, align=8)
+    s_ref, m_ref, _ = ex.extract_batch_device(buf.cuda(), offsets, lengths, GROUPS)
+    s_ref, m_ref = s_ref.cpu().numpy(), m_ref.cpu().numpy()
+    L, h = N.lib(), ex._h()
+    n, SS = len(clips), ex.summary_width
+    # (1) array of clip pointers
+    ptrs = (C.c_void_p * n)(*[c.ctypes.data for c in clips])
+    s1 = np.zeros((n, SS), np.float32); m1 = np.zeros((n, 4), np.int32)
+    N.check(L.afx_extract_host(h, ptrs, lengths.ctypes.data, n, 0x6, s1.ctypes.data, m1.ctypes.data))
+    np.testing.assert_array_equal(m1, m_ref); np.testing.assert_array_equal(s1, s_ref)
+    # (2) one packed float32 buffer
+    s2 = np.zeros((n, SS), np.float32); m2 = np.zeros((n, 4), np.int32)
+    N.check(L.afx_extract_host_packed(h, buf.data_ptr(), N.SAMPLE_F32, buf.numel(), offsets.ctypes.data, lengths.ctypes.data,
+                                      n, 0x6, s2.ctypes.data, m2.ctypes.data))
+    np.testing.assert_array_equal(m2, m_ref); np.testing.assert_array_equal(s2, s_ref)
+    # (3) packed PCM16 == float32 path fed x / 32768
+    pcm = np.clip(np.round(buf.numpy() * 32768.0), -32768, 32767).astype(np.int16)
+    f_from_pcm = torch.from_numpy(pcm.astype(np.float32) / np.float32(32768.0))
+    s_q, m_q, _ = ex.extract_batch_device(f_from_pcm.cuda(), offsets, lengths, GROUPS)
+    s3 = np.zeros((n, SS), np.float32); m3 = np.zeros((n, 4), np.int32)
+    N.check(L.afx_extract_host_packed(h, pcm.ctypes.data, N.SAMPLE_S16, pcm.size, offsets.ctypes.data, lengths.ctypes.data,
+                                      n, 0x6, s3.ctypes.data, m3.ctypes.data))
+    np.testing.assert_array_equal(m3, m_q.cpu().numpy()); np.testing.assert_array_equal(s3, s_q.cpu().numpy())
+
+
+def test_reference_api_files_and_evaluator(torch_cuda, tmp_path):
+    """extract_features(path, features_to_extract=[...]) / batch_process(dir) on WAV files, and the
+    reference's FeatureEvaluator contract (evaluation/evaluator.py:16-147) on the returned dicts."""
+    import json
+    from audio_feature_extraction_toolkit import AudioFeatureExtractor, FeatureEvaluator
+    from audio_feature_extraction_b200.synth import make_clip
+    from audio_feature_extraction_b200.wav import write_wav
+    from oracle import OracleFeatureExtractor
+
+    clips = {f"clip{i}.wav": make_clip(300 + i, seconds=1.5 + i) for i in range(3)}
+    for name, y in clips.items():
+        write_wav(str(tmp_path / name), y, 22050, subtype="FLOAT")
+    (tmp_path / "notes.txt").write_text("ignored")
+    write_wav(str(tmp_path / "silent.wav"), np.zeros(100, np.float32), 22050, subtype="FLOAT")   # too short -> skipped
+    ex = AudioFeatureExtractor(sr=22050, frame_length=1024, hop_length=256, n_mfcc=13, pre_emphasis=0.97)
+    ora = OracleFeatureExtractor()
+    one = ex.extract_features(str(tmp_path / "clip1.wav"), features_to_extract=["mfcc", "energy"])
+    ref = ora.extract_features_array(clips["clip1.wav"], features_to_extract=("mfcc", "energy"))
+    assert list(one) == ["file_path", "mfcc_mean", "mfcc_std", "mfcc_delta_mean", "mfcc_delta2_mean",
+                         "energy_mean", "energy_std", "energy_range"]
+    np.testing.assert_allclose(one["mfcc_mean"], ref["mfcc_mean"], atol=MFCC_ATOL)
+    assert one["energy_mean"] == pytest.approx(ref["energy_mean"], rel=ENERGY_RTOL)
+    res = ex.batch_process(str(tmp_path), features_to_extract=["mfcc", "energy"])
+    assert sorted(r["file_path"] for r in res) == sorted(str(tmp_path / n) for n in clips)
+    json.dumps(res)
+    ev = FeatureEvaluator()
+    rep = ev.generate_evaluation_report(res, str(tmp_path / "report"))
+    assert (tmp_path / "report" / "evaluation_detailed.json").exists()
+    assert (tmp_path / "report" / "evaluation_summary.csv").exists()
+    assert rep["quality_metrics"]["total_files"] == 3
