@@ -16,8 +16,7 @@
 #include <vector>
 
 #include "afx_common.cuh"
-#include "afx_frames.cuh"
-#include "afx_mfcc.cuh"
+#include "afx_clip.cuh"
 #include "afx_tables.h"
 #include "afx_trim.cuh"
 
@@ -58,7 +57,7 @@ struct afx_handle_s {
   afx_config_t cfg;
   int n16;                 // n_mfcc rounded up to a multiple of 4
   int sm_count;
-  long long wave_frames;   // frames of log-mel scratch per wave (L2-resident target)
+  void (*clip_fn)(afx::ClipArgs) = nullptr;   // clip_kernel<frame_length, hop_length>
   // device tables
   float* d_window = nullptr;
   float* d_twiddle = nullptr;
@@ -110,7 +109,7 @@ struct PhaseTimer {
 };
 
 struct Layout {   // carve-up of the caller's workspace
-  size_t off_offsets, off_frame_off, off_lengths, off_chunk_b, off_chunk_c, off_info, header_bytes;
+  size_t off_offsets, off_frame_off, off_lengths, off_info, off_counter, header_bytes;
 };
 
 Layout header_layout(int64_t n) {
@@ -119,36 +118,42 @@ Layout header_layout(int64_t n) {
   L.off_offsets = o;   o += align_up(sizeof(long long) * n, 16);
   L.off_frame_off = o; o += align_up(sizeof(long long) * (n + 1), 16);
   L.off_lengths = o;   o += align_up(sizeof(int) * n, 16);
-  L.off_chunk_b = o;   o += align_up(sizeof(int) * (n + 1), 16);
-  L.off_chunk_c = o;   o += align_up(sizeof(int) * (n + 1), 16);
-  L.off_info = o;      // ClipInfo is produced on device; not staged from the host
-  L.header_bytes = align_up(o + sizeof(afx::ClipInfo) * n, 256);
+  L.off_info = o;      o += align_up(sizeof(afx::ClipInfo) * n, 16);   // produced on device; not staged from the host
+  L.off_counter = o;   o += 256;
+  L.header_bytes = align_up(o, 256);
   return L;
-}
-
-// bytes of wave scratch for F frames and C stat chunks
-size_t wave_scratch_bytes(const afx_handle_s* h, long long F, long long C) {
-  size_t b = 0;
-  b += align_up((size_t)F * afx::kNMels * sizeof(float), 256);   // log-mel
-  b += align_up((size_t)F * sizeof(float), 256);                 // rms
-  b += align_up((size_t)F * sizeof(float), 256);                 // f0
-  b += align_up((size_t)F * sizeof(float), 256);                 // voiced prob
-  b += align_up((size_t)C * afx::kMomentsPerCoef * h->cfg.n_mfcc * sizeof(double), 256);
-  return b;
 }
 
 inline long long frames_ub(const afx_handle_s* h, long long len) { return 1 + std::max<long long>(len, 0) / h->cfg.hop_length; }
 inline long long ceil_div(long long a, long long b) { return (a + b - 1) / b; }
 
-size_t frames_smem_bytes(const afx_handle_s* h, int* tile_floats_out) {
-  const int span = (afx::kFramesPerChunk - 1) * h->cfg.hop_length + h->cfg.frame_length;
-  const int tile_floats = (span + 8 + 3) & ~3;
-  if (tile_floats_out) *tile_floats_out = tile_floats;
-  return 16 + 8192 + (size_t)h->cfg.frame_length * 4 + 2 * (size_t)tile_floats * 4 + (size_t)afx::kFramesWarps * afx::kPlaneFloats * 4;
+// per-CTA scratch slab of the fused kernel for clips of at most max_len samples: log-mel rows, RMS, row maxima, block sums
+inline int slab_rows(const afx_handle_s* h, long long max_len) { return (int)((frames_ub(h, max_len) + 3) & ~3LL); }
+size_t slab_bytes_for(const afx_handle_s* h, long long max_len) {
+  const size_t rows = (size_t)slab_rows(h, max_len);
+  return align_up((rows * (afx::kNMels + 3) + 8) * sizeof(float), 256);   // + hop-block sums (one per frame row)
+}
+inline int grid_for(const afx_handle_s* h, long long n_clips) { return (int)std::max<long long>(1, std::min<long long>(n_clips, h->sm_count)); }
+
+// the speculative single pass needs every trimmed frame centre (start = k*512) on the absolute hop grid
+inline bool single_pass(const afx_handle_s* h) { return afx::kTrimHop % h->cfg.hop_length == 0 && h->cfg.hop_length >= 16; }
+
+// the fused kernel is instantiated per (frame_length, hop_length): hop = frame_length / 2, / 4, / 8
+typedef void (*clip_fn_t)(afx::ClipArgs);
+clip_fn_t clip_kernel_for(int n_fft, int hop) {
+  if (n_fft == 1024) {
+    if (hop == 512) return afx::clip_kernel<1024, 512>;
+    if (hop == 256) return afx::clip_kernel<1024, 256>;
+    if (hop == 128) return afx::clip_kernel<1024, 128>;
+  }
+  return nullptr;
 }
 
-size_t stats_smem_bytes(const afx_handle_s* h) {
-  return ((size_t)afx::kStatRows * afx::kDStride + (size_t)afx::kNMels * h->n16 + (size_t)afx::kStatRows * (h->n16 + 1)) * sizeof(float);
+size_t clip_smem_bytes(const afx_handle_s* h, int* tile_floats_out) {
+  const int tile_floats = h->cfg.hop_length + h->cfg.frame_length + 8;   // per-warp raw tile
+  if (tile_floats_out) *tile_floats_out = tile_floats;
+  return 128 + 8192 + (size_t)h->cfg.frame_length * 4 + (size_t)(afx::kMoments * afx::kMaxMfcc + 64) * 8 +
+         (size_t)afx::kNMels * h->n16 * 4 + (size_t)afx::kClipWarps * (tile_floats + afx::kPlaneFloats) * 4;
 }
 
 }  // namespace
@@ -181,6 +186,9 @@ int afx_create(const afx_config_t* cfg, afx_handle_t* out) {
     return fail(AFX_ERR_UNSUPPORTED, "frame_length %d not supported (1024 only in this build)", cfg->frame_length);
   if (cfg->hop_length < 1 || cfg->hop_length > cfg->frame_length / 2)
     return fail(AFX_ERR_INVALID_ARG, "hop_length %d out of range [1, frame_length/2]", cfg->hop_length);
+  if (!clip_kernel_for(cfg->frame_length, cfg->hop_length))
+    return fail(AFX_ERR_UNSUPPORTED, "frame_length %d / hop_length %d: this build has kernels for hop = frame_length/2, /4, /8",
+                cfg->frame_length, cfg->hop_length);
   if (cfg->n_mfcc < 1 || cfg->n_mfcc > afx::kMaxMfcc) return fail(AFX_ERR_INVALID_ARG, "n_mfcc %d out of range [1,64]", cfg->n_mfcc);
   if (cfg->n_mels != afx::kNMels) return fail(AFX_ERR_UNSUPPORTED, "n_mels must be 128");
   if (cfg->sr < 1000) return fail(AFX_ERR_INVALID_ARG, "sr %d too small", cfg->sr);
@@ -197,8 +205,6 @@ int afx_create(const afx_config_t* cfg, afx_handle_t* out) {
   h->cfg = *cfg;
   h->n16 = (cfg->n_mfcc + 3) & ~3;
   h->sm_count = prop.multiProcessorCount;
-  h->wave_frames = 49152;
-  if (const char* e = getenv("AFX_WAVE_FRAMES")) { long long v = atoll(e); if (v >= 1024) h->wave_frames = v; }
 
   const auto win = afx::host::window_half(cfg->frame_length);
   const auto tw = afx::host::twiddle32x32(1024);
@@ -221,8 +227,8 @@ int afx_create(const afx_config_t* cfg, afx_handle_t* out) {
   h->tab.dct = nullptr;
 
   CUDA_TRY(cudaFuncSetAttribute(afx::trim_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-  CUDA_TRY(cudaFuncSetAttribute(afx::frames_kernel<1024>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)frames_smem_bytes(h, nullptr)));
-  CUDA_TRY(cudaFuncSetAttribute(afx::mfcc_stats_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)stats_smem_bytes(h)));
+  h->clip_fn = clip_kernel_for(cfg->frame_length, cfg->hop_length);
+  CUDA_TRY(cudaFuncSetAttribute(h->clip_fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)clip_smem_bytes(h, nullptr)));
   CUDA_TRY(cudaEventCreateWithFlags(&h->stage_ev, cudaEventDisableTiming));
   *out = h;
   return AFX_OK;
@@ -252,16 +258,15 @@ int afx_summary_width(afx_handle_t h) { return h ? 4 + 4 * h->cfg.n_mfcc + 3 + 2
 int afx_frame_width(afx_handle_t h) { return h ? 3 * h->cfg.n_mfcc + 3 : 0; }
 int64_t afx_max_frames(afx_handle_t h, int64_t length) { return h ? frames_ub(h, length) : 0; }
 
-static size_t workspace_bytes_impl(afx_handle_t h, int64_t n_clips, const int32_t* h_lengths, bool minimal) {
+static size_t workspace_bytes_impl(afx_handle_t h, int64_t n_clips, const int32_t* h_lengths) {
   if (!h || n_clips < 0 || (n_clips > 0 && !h_lengths)) return 0;
-  long long total_f = 0, max_f = 1;
-  for (int64_t i = 0; i < n_clips; ++i) { const long long f = frames_ub(h, h_lengths[i]); total_f += f; max_f = std::max(max_f, f); }
-  long long F = minimal ? max_f : std::max(max_f, std::min(total_f, h->wave_frames));
-  const long long C = ceil_div(F, afx::kStatFrames) + std::min<long long>(n_clips, F) + 1;
-  return header_layout(n_clips).header_bytes + wave_scratch_bytes(h, F, C) + 1024;
+  long long max_len = 0;
+  for (int64_t i = 0; i < n_clips; ++i) max_len = std::max<long long>(max_len, h_lengths[i]);
+  return header_layout(n_clips).header_bytes + (size_t)grid_for(h, n_clips) * slab_bytes_for(h, max_len) + 1024;
 }
-size_t afx_workspace_bytes(afx_handle_t h, int64_t n_clips, const int32_t* h_lengths) { return workspace_bytes_impl(h, n_clips, h_lengths, false); }
-size_t afx_workspace_min_bytes(afx_handle_t h, int64_t n_clips, const int32_t* h_lengths) { return workspace_bytes_impl(h, n_clips, h_lengths, true); }
+// one private slab per resident CTA (at most one per SM); there is no smaller configuration, so both agree
+size_t afx_workspace_bytes(afx_handle_t h, int64_t n_clips, const int32_t* h_lengths) { return workspace_bytes_impl(h, n_clips, h_lengths); }
+size_t afx_workspace_min_bytes(afx_handle_t h, int64_t n_clips, const int32_t* h_lengths) { return workspace_bytes_impl(h, n_clips, h_lengths); }
 
 int afx_extract(afx_handle_t h, const float* d_audio, const int64_t* h_offsets, const int32_t* h_lengths,
                 int64_t n_clips, uint32_t feature_mask, float* d_summaries, int32_t* d_meta,
@@ -279,7 +284,7 @@ int afx_extract(afx_handle_t h, const float* d_audio, const int64_t* h_offsets, 
   const int n = (int)n_clips;
   const int hop = h->cfg.hop_length;
 
-  // ---- host-side prefixes (everything the launch geometry needs is known from the lengths)
+  // ---- host-side header: offsets, lengths, output-row prefix (pinned staging, one async copy)
   const Layout L = header_layout(n);
   const size_t staged_bytes = L.off_info;
   if (h->h_stage_bytes < staged_bytes) {
@@ -294,111 +299,60 @@ int afx_extract(afx_handle_t h, const float* d_audio, const int64_t* h_offsets, 
   long long* s_offsets = reinterpret_cast<long long*>(st + L.off_offsets);
   long long* s_frame_off = reinterpret_cast<long long*>(st + L.off_frame_off);
   int* s_lengths = reinterpret_cast<int*>(st + L.off_lengths);
-  int* s_chunk_b = reinterpret_cast<int*>(st + L.off_chunk_b);
-  int* s_chunk_c = reinterpret_cast<int*>(st + L.off_chunk_c);
-  long long fo = 0, cb = 0, cc = 0, max_f = 1;
-  const long long max_trim_blocks = (200 * 1024) / 4 - 8;
+  long long fo = 0, max_len = 0;
   for (int i = 0; i < n; ++i) {
     if (h_lengths[i] < 0) return fail(AFX_ERR_INVALID_ARG, "afx_extract: clip %d has negative length", i);
     if (h_offsets[i] < 0 || (h_offsets[i] & 3) != 0) return fail(AFX_ERR_INVALID_ARG, "afx_extract: clip %d offset %lld is not a multiple of 4 samples", i, (long long)h_offsets[i]);
-    if (ceil_div(h_lengths[i], afx::kTrimHop) > max_trim_blocks) return fail(AFX_ERR_UNSUPPORTED, "afx_extract: clip %d longer than %lld samples", i, max_trim_blocks * afx::kTrimHop);
     s_offsets[i] = h_offsets[i];
     s_lengths[i] = h_lengths[i];
-    const long long f = frames_ub(h, h_lengths[i]);
-    s_frame_off[i] = fo; s_chunk_b[i] = (int)cb; s_chunk_c[i] = (int)cc;
-    fo += f; cb += ceil_div(f, afx::kFramesPerChunk); cc += ceil_div(f, afx::kStatFrames);
-    max_f = std::max(max_f, f);
-    if (cb > 0x7fffff00LL) return fail(AFX_ERR_UNSUPPORTED, "afx_extract: batch too large");
+    s_frame_off[i] = fo;
+    fo += frames_ub(h, h_lengths[i]);
+    max_len = std::max<long long>(max_len, h_lengths[i]);
   }
-  s_frame_off[n] = fo; s_chunk_b[n] = (int)cb; s_chunk_c[n] = (int)cc;
+  s_frame_off[n] = fo;
+  const bool one_pass = single_pass(h);
+  const long long max_trim_blocks = (200 * 1024) / 4 - 8;
+  if (!one_pass && ceil_div(max_len, afx::kTrimHop) > max_trim_blocks)
+    return fail(AFX_ERR_UNSUPPORTED, "afx_extract: clips longer than %lld samples need hop_length dividing 512", max_trim_blocks * afx::kTrimHop);
 
-  if (workspace_bytes < L.header_bytes + wave_scratch_bytes(h, max_f, ceil_div(max_f, afx::kStatFrames) + 2) + 1024)
-    return fail(AFX_ERR_WORKSPACE, "afx_extract: workspace of %zu bytes is below afx_workspace_min_bytes", workspace_bytes);
+  const int grid = grid_for(h, n);
+  const size_t slab_bytes = slab_bytes_for(h, max_len);
+  if (workspace_bytes < L.header_bytes + (size_t)grid * slab_bytes)
+    return fail(AFX_ERR_WORKSPACE, "afx_extract: workspace of %zu bytes is below afx_workspace_bytes", workspace_bytes);
   char* ws = static_cast<char*>(d_workspace);
   if ((reinterpret_cast<uintptr_t>(ws) & 255u) != 0) return fail(AFX_ERR_INVALID_ARG, "afx_extract: workspace must be 256-byte aligned");
   CUDA_TRY(cudaMemcpyAsync(ws, st, staged_bytes, cudaMemcpyHostToDevice, stream));
   CUDA_TRY(cudaEventRecord(h->stage_ev, stream));
+  CUDA_TRY(cudaMemsetAsync(ws + L.off_counter, 0, 256, stream));
   const long long* d_offsets = reinterpret_cast<const long long*>(ws + L.off_offsets);
   const long long* d_frame_off = reinterpret_cast<const long long*>(ws + L.off_frame_off);
   const int* d_lengths = reinterpret_cast<const int*>(ws + L.off_lengths);
-  const int* d_chunk_b = reinterpret_cast<const int*>(ws + L.off_chunk_b);
-  const int* d_chunk_c = reinterpret_cast<const int*>(ws + L.off_chunk_c);
   afx::ClipInfo* d_info = reinterpret_cast<afx::ClipInfo*>(ws + L.off_info);
 
-  // ---- wave capacity from the scratch we were given: largest F with scratch(F, C(F)) fitting
-  const size_t scratch_avail = workspace_bytes - L.header_bytes - 1024;
-  long long F_cap = std::max(max_f, std::min(fo, h->wave_frames));
-  auto chunks_for = [&](long long F) { return ceil_div(F, afx::kStatFrames) + std::min<long long>(n, F) + 1; };
-  while (F_cap > max_f && wave_scratch_bytes(h, F_cap, chunks_for(F_cap)) > scratch_avail) F_cap = std::max(max_f, F_cap * 7 / 8);
-  if (wave_scratch_bytes(h, F_cap, chunks_for(F_cap)) > scratch_avail) return fail(AFX_ERR_WORKSPACE, "afx_extract: workspace too small for the longest clip");
-  const long long C_cap = chunks_for(F_cap);
-  char* sp = ws + L.header_bytes;
-  float* d_logmel = reinterpret_cast<float*>(sp); sp += align_up((size_t)F_cap * afx::kNMels * sizeof(float), 256);
-  float* d_rms = reinterpret_cast<float*>(sp);    sp += align_up((size_t)F_cap * sizeof(float), 256);
-  float* d_f0 = reinterpret_cast<float*>(sp);     sp += align_up((size_t)F_cap * sizeof(float), 256);
-  float* d_vp = reinterpret_cast<float*>(sp);     sp += align_up((size_t)F_cap * sizeof(float), 256);
-  double* d_part = reinterpret_cast<double*>(sp);
-  (void)d_f0; (void)d_vp; (void)C_cap;
-
-  int tile_floats = 0;
-  const size_t fr_smem = frames_smem_bytes(h, &tile_floats);
-  const size_t st_smem = stats_smem_bytes(h);
-
-  // ---- waves of clips whose log-mel scratch stays L2 resident
-  int c0 = 0;
-  while (c0 < n) {
-    int c1 = c0;
-    long long F = 0;
-    long long max_len = 0;
-    while (c1 < n) {
-      const long long f = s_frame_off[c1 + 1] - s_frame_off[c1];
-      if (c1 > c0 && F + f > F_cap) break;
-      F += f; max_len = std::max<long long>(max_len, s_lengths[c1]); ++c1;
-    }
-    const int nw = c1 - c0;
-    {  // phase A
-      afx::TrimArgs ta;
-      ta.audio = d_audio; ta.offsets = d_offsets; ta.lengths = d_lengths; ta.info = d_info;
-      ta.clip_begin = c0; ta.hop = hop; ta.coef = h->cfg.pre_emphasis; ta.top_db = h->cfg.trim_top_db;
-      const size_t smem = (size_t)(ceil_div(max_len, afx::kTrimHop) + 4) * sizeof(float);
-      PhaseTimer pt(h, stream, AFX_PHASE_TRIM);
-      afx::trim_kernel<<<nw, afx::kTrimThreads, smem, stream>>>(ta);
-      ++g_launches;
-    }
-    if (feature_mask & (AFX_FEAT_MFCC | AFX_FEAT_ENERGY)) {  // phase B
-      afx::FramesArgs fa;
-      fa.audio = d_audio; fa.offsets = d_offsets; fa.lengths = d_lengths; fa.info_ro = d_info; fa.info = d_info;
-      fa.chunk_off = d_chunk_b; fa.frame_off = d_frame_off; fa.clip_begin = c0; fa.clip_end = c1;
-      fa.n_tasks = s_chunk_b[c1] - s_chunk_b[c0]; fa.frame_base = s_frame_off[c0];
-      fa.logmel = d_logmel; fa.rms = d_rms; fa.tab = h->tab; fa.hop = hop; fa.tile_floats = tile_floats;
-      fa.coef = h->cfg.pre_emphasis;
-      const int grid = std::max(1, std::min(fa.n_tasks, 2 * h->sm_count));
-      PhaseTimer pt(h, stream, AFX_PHASE_FRAMES);
-      afx::frames_kernel<1024><<<grid, afx::kFramesWarps * 32, fr_smem, stream>>>(fa);
-      ++g_launches;
-    }
-    if (feature_mask & AFX_FEAT_MFCC) {  // phase C
-      afx::StatArgs sa;
-      sa.info = d_info; sa.chunk_off = d_chunk_c; sa.frame_off = d_frame_off; sa.clip_begin = c0; sa.clip_end = c1;
-      sa.frame_base = s_frame_off[c0]; sa.logmel = d_logmel; sa.dct_t = h->d_dct_t; sa.partials = d_part;
-      sa.frames_out = d_frames; sa.n_mfcc = h->cfg.n_mfcc; sa.n16 = h->n16; sa.frame_width = afx_frame_width(h);
-      sa.top_db = h->cfg.mfcc_top_db;
-      const int grid = s_chunk_c[c1] - s_chunk_c[c0];
-      PhaseTimer pt(h, stream, AFX_PHASE_MFCC);
-      afx::mfcc_stats_kernel<<<grid, afx::kStatThreads, st_smem, stream>>>(sa);
-      ++g_launches;
-    }
-    {  // phase D
-      afx::FinalArgs fa;
-      fa.info = d_info; fa.chunk_off = d_chunk_c; fa.frame_off = d_frame_off; fa.clip_begin = c0;
-      fa.frame_base = s_frame_off[c0]; fa.partials = d_part; fa.rms = d_rms; fa.f0 = nullptr; fa.voiced_prob = nullptr;
-      fa.summaries = d_summaries; fa.meta = d_meta; fa.frames_out = d_frames; fa.n_mfcc = h->cfg.n_mfcc;
-      fa.summary_width = afx_summary_width(h); fa.frame_width = afx_frame_width(h); fa.mask = feature_mask;
-      PhaseTimer pt(h, stream, AFX_PHASE_FINALIZE);
-      afx::finalize_kernel<<<nw, afx::kFinalThreads, 0, stream>>>(fa);
-      ++g_launches;
-    }
-    c0 = c1;
+  if (!one_pass) {  // hop does not divide 512: the trim decision needs its own pass over the batch first
+    afx::TrimArgs ta;
+    ta.audio = d_audio; ta.offsets = d_offsets; ta.lengths = d_lengths; ta.info = d_info;
+    ta.clip_begin = 0; ta.hop = hop; ta.coef = h->cfg.pre_emphasis; ta.top_db = h->cfg.trim_top_db;
+    const size_t smem = (size_t)(ceil_div(max_len, afx::kTrimHop) + 4) * sizeof(float);
+    PhaseTimer pt(h, stream, AFX_PHASE_TRIM);
+    afx::trim_kernel<<<n, afx::kTrimThreads, smem, stream>>>(ta);
+    ++g_launches;
+  }
+  {
+    afx::ClipArgs ca;
+    int tile_floats = 0;
+    const size_t smem = clip_smem_bytes(h, &tile_floats);
+    ca.audio = d_audio; ca.offsets = d_offsets; ca.lengths = d_lengths; ca.frame_off = d_frame_off; ca.info = d_info;
+    ca.counter = reinterpret_cast<int*>(ws + L.off_counter); ca.n_clips = n;
+    ca.slabs = ws + L.header_bytes; ca.slab_bytes = slab_bytes; ca.a_max = slab_rows(h, max_len);
+    ca.tab = h->tab; ca.dct_t = h->d_dct_t; ca.hop = hop; ca.tile_floats = tile_floats;
+    ca.coef = h->cfg.pre_emphasis; ca.trim_top_db = h->cfg.trim_top_db; ca.mfcc_top_db = h->cfg.mfcc_top_db;
+    ca.n_mfcc = h->cfg.n_mfcc; ca.n16 = h->n16; ca.summary_width = afx_summary_width(h); ca.frame_width = afx_frame_width(h);
+    ca.mask = feature_mask; ca.summaries = d_summaries; ca.meta = d_meta; ca.frames_out = d_frames;
+    ca.pretrimmed = one_pass ? 0 : 1;
+    PhaseTimer pt(h, stream, AFX_PHASE_FRAMES);
+    h->clip_fn<<<grid, afx::kClipThreads, smem, stream>>>(ca);
+    ++g_launches;
   }
   CUDA_TRY(cudaGetLastError());
   return AFX_OK;

@@ -1,0 +1,598 @@
+// The fused single-pass hot path: ONE persistent kernel takes every clip from raw samples to its
+// summary row.  Replaces, for a whole batch, preprocess_audio + extract_mfcc + extract_energy of
+// audio_feature_extraction_toolkit/core/feature_extractor.py:58-74,116-151,153-179 (reference).
+//
+// One CTA (16 warps) owns one clip at a time (clips are handed out by an atomic counter):
+//
+//  S  streaming pass -- the clip is read from HBM exactly once, 32 frames per step, by 1-D TMA bulk
+//     copies (cp.async.bulk + mbarrier) that overlap the FFTs of the previous step.  Per step:
+//     pre-emphasis into shared memory; the sums of squares of the 512-sample blocks the step owns
+//     (all librosa.effects.trim needs); two frames per warp as one complex 1024-point FFT in
+//     registers -> power -> sparse Slaney mel -> 10 log10; log-mel rows, per-frame RMS and per-frame
+//     row maxima go to the CTA's private scratch slab (441 KB per 10 s clip; reused clip after clip,
+//     so it lives in L2, never in HBM).
+//     The frame grid of the trimmed signal starts at trim_start, a multiple of 512; when hop divides
+//     512 every trimmed frame centre is also a multiple of hop of the UNtrimmed signal, so the pass
+//     runs speculatively on the absolute grid before the trim decision exists.
+//  T  trim decision from the block sums (first / last 2048/512 RMS frame above max - top_db).
+//  F  fix-up: only the first and last n_fft/(2 hop) (+1) trimmed frames see different zero padding
+//     than their absolute-grid twins; they are recomputed (a few KB re-read, L2 hits).
+//  C  power_to_db clamp at (clip max - 80 dB) -> DCT-II -> delta / delta-delta (SavGol 9) -> moments.
+//  Z  statistics -> summary row, meta row.
+//
+// If hop does not divide 512 the host runs trim_kernel first and this kernel takes the trim as given
+// (`pretrimmed`), skipping T and F.
+#pragma once
+#include "afx_common.cuh"
+#include "fft_gen.cuh"
+#include "afx_trim.cuh"
+
+namespace afx {
+
+constexpr int kClipWarps = 16;
+constexpr int kClipThreads = kClipWarps * 32;
+constexpr int kChunkFrames = 2 * kClipWarps;     // frames per streaming step
+constexpr int kTilePad = 4;                      // floats in front of the first frame sample inside the tile
+constexpr int kPlaneFloats = 32 * 33;
+constexpr int kStatThreads = kClipThreads;
+constexpr int kStatRows = kStatFrames + 2 * kStatHalo;   // 64 frames incl. halo
+constexpr int kDStride = kNMels + 1;                      // padded log-mel row in shared memory
+constexpr int kMoments = 6;                               // sum x, x^2, x^3, x^4, sum delta, sum delta2
+
+struct ClipArgs {
+  const float* audio;
+  const long long* offsets;     // device [n_clips] sample offsets
+  const int* lengths;           // device [n_clips]
+  const long long* frame_off;   // device [n_clips + 1] prefix of 1 + len/hop (rows of frames_out)
+  ClipInfo* info;               // [n_clips]: input when pretrimmed, always written back
+  int* counter;                 // work counter (zeroed before launch)
+  int n_clips;
+  char* slabs;                  // per-CTA scratch
+  size_t slab_bytes;
+  int a_max;                    // frame rows per slab (multiple of 4)
+  Tables tab;
+  const float* dct_t;           // [128][n16]
+  int hop;
+  int tile_floats;
+  float coef, trim_top_db, mfcc_top_db;
+  int n_mfcc, n16, summary_width, frame_width;
+  unsigned mask;                // AFX_FEAT_*
+  float* summaries;             // [n_clips][SS]
+  int* meta;                    // [n_clips][4]
+  float* frames_out;            // nullable
+  int pretrimmed;
+};
+
+struct Slab {
+  float* logmel;   // [a_max][128]
+  float* rms;      // [a_max]
+  float* rowmax;   // [a_max]
+  float* blk;      // [rows + 2] sums of squares of the hop-sized blocks [u*hop, (u+1)*hop) of the pre-emphasised clip
+};
+
+__device__ __forceinline__ Slab carve_slab(const ClipArgs& a, int cta) {
+  Slab s;
+  char* p = a.slabs + (size_t)cta * a.slab_bytes;
+  s.logmel = reinterpret_cast<float*>(p);
+  s.rms = s.logmel + (size_t)a.a_max * kNMels;
+  s.rowmax = s.rms + a.a_max;
+  s.blk = s.rowmax + a.a_max;
+  return s;
+}
+
+// shared-memory carve-up of the streaming phase (phase C aliases everything after the tables)
+struct Smem {
+  uint64_t* mbar;  // [16] one TMA barrier per warp
+  float2* tw;      // [1024]
+  float* win;      // [NFFT]
+  float* raw;      // [16][HOP + NFFT + 8] per-warp raw-sample tiles
+  float* planes;   // [16][32*33]
+};
+
+// where a streaming step reads: frames f (relative to `origin`) cover origin + f*hop - n_fft/2 + [0, n_fft),
+// samples outside [lo, hi) count as zero (librosa centre padding of the trimmed signal)
+struct Region { int origin, lo, hi; };
+
+// raw sample range a frame pair starting at frame fA needs; tile position p holds absolute sample gA - 4 + p,
+// gA = origin + fA*hop - n_fft/2.  Returns the bytes to copy (0: nothing of the pair lies inside [lo, hi)).
+__device__ __forceinline__ unsigned pair_copy_range(const Region& rg, int gA, int span, int L0, int& g_lo, int& s_lo) {
+  const int lo = max(rg.lo, gA), hi = min(rg.hi, gA + span);
+  if (hi <= lo) return 0u;
+  g_lo = max(0, lo - 1) & ~3;
+  const int g_hi4 = (min(hi, L0) + 3) & ~3;
+  s_lo = g_lo - gA + 4;                                             // multiple of 4, >= 0
+  return (unsigned)(g_hi4 - g_lo) * 4u;
+}
+
+// per-warp state of the streaming pass
+struct WarpCtx {
+  float* raw;        // [HOP + NFFT + 8] this warp's raw-sample tile (TMA destination)
+  float* plane;      // [32*33] transpose scratch / power spectrum
+  uint64_t* mbar;    // this warp's TMA barrier
+  unsigned parity;
+};
+
+// ---- one warp: two real frames fA, fA + 1 -> log-mel rows row, row + 1 of the slab, RMS, row maxima, and (own_sums)
+// the sums of squares of the two hop-sized blocks [fA*hop, fA*hop + 2 hop) of the pre-emphasised signal.
+// n_fft = 1024: the two frames ride the real and imaginary lanes of one complex 1024-point FFT held in registers
+// (32 complex values per lane): 32-point FFT, twiddle, transpose through shared memory, 32-point FFT.
+// Pre-emphasis is applied while the samples are loaded (frame B's values are frame A's shifted by HOP/32 rows).
+// next_bytes/next_src/next_dst: the warp's next tile, issued as soon as this one sits in registers.
+template <int HOP>
+__device__ __forceinline__ void warp_frames_1024(const ClipArgs& a, const Smem& sm, const Slab& sl, WarpCtx& wc, const Region& rg,
+                                                 int gA, int L0, bool vB, int row, bool own_sums, int usum_idx,
+                                                 unsigned next_bytes, const float* next_src, float* next_dst, int& bad) {
+  constexpr int NFFT = 1024;
+  constexpr int SH = HOP / 32;            // rows by which frame B trails frame A
+  constexpr int NG = NFFT / HOP + 1;      // hop-sized groups the pair spans
+  const int lane = threadIdx.x & 31;
+  float r[32], im[32];
+  float eg[NG];
+#pragma unroll
+  for (int g = 0; g < NG; ++g) eg[g] = 0.f;
+  const float* rp = wc.raw + 4 + lane;
+  const bool fast = (gA >= 1) && (gA >= rg.lo) && (gA + HOP + NFFT <= rg.hi);   // warp-uniform
+  if (fast) {
+#pragma unroll
+    for (int n1 = 0; n1 < 32 + SH; ++n1) {
+      const float y = preemph_sample(rp[32 * n1], rp[32 * n1 - 1], a.coef);
+      eg[n1 / SH] = fmaf(y, y, eg[n1 / SH]);
+      if (n1 < 32) r[bitrev32(n1)] = sm.win[32 * n1 + lane] * y;
+      if (n1 >= SH) im[bitrev32(n1 - SH)] = sm.win[32 * (n1 - SH) + lane] * y;
+    }
+  } else {
+#pragma unroll
+    for (int n1 = 0; n1 < 32 + SH; ++n1) {
+      const int g = gA + 32 * n1 + lane;
+      float y = 0.f;
+      if (g >= rg.lo && g < rg.hi) {
+        const float xv = rp[32 * n1];
+        if (g == 0) {
+          const float x1 = (L0 > 1) ? rp[32 * n1 + 1] : 0.f;
+          y = xv + (2.f * xv - x1);          // zi = 2*y[0]-y[1] handed to lfilter as state
+        } else {
+          y = preemph_sample(xv, rp[32 * n1 - 1], a.coef);
+        }
+      }
+      eg[n1 / SH] = fmaf(y, y, eg[n1 / SH]);
+      if (n1 < 32) r[bitrev32(n1)] = sm.win[32 * n1 + lane] * y;
+      if (n1 >= SH) im[bitrev32(n1 - SH)] = sm.win[32 * (n1 - SH) + lane] * y;
+    }
+  }
+  // the tile now lives in registers: let the TMA fetch this warp's next pair while the FFT runs
+  __syncwarp();
+  if (lane == 0 && next_bytes) {
+    fence_proxy_async();
+    mbar_expect_tx(wc.mbar, next_bytes);
+    tma_load_1d(next_dst, next_src, next_bytes, wc.mbar);
+  }
+  float* plane = wc.plane;
+  fft32_dit(r, im);
+#pragma unroll
+  for (int k1 = 1; k1 < 32; ++k1) {   // twiddle by W_1024^(k1 * lane)
+    const float2 w = sm.tw[k1 * 32 + lane];
+    const float tr = r[k1] * w.x - im[k1] * w.y;
+    const float ti = fmaf(r[k1], w.y, im[k1] * w.x);
+    r[k1] = tr; im[k1] = ti;
+  }
+  // transpose (lane n2, reg k1) -> (lane k1, reg n2) through the warp's plane, re then im
+#pragma unroll
+  for (int k1 = 0; k1 < 32; ++k1) plane[k1 * 33 + lane] = r[k1];
+  __syncwarp();
+#pragma unroll
+  for (int n2 = 0; n2 < 32; ++n2) r[bitrev32(n2)] = plane[lane * 33 + n2];
+  __syncwarp();
+#pragma unroll
+  for (int k1 = 0; k1 < 32; ++k1) plane[k1 * 33 + lane] = im[k1];
+  __syncwarp();
+#pragma unroll
+  for (int n2 = 0; n2 < 32; ++n2) im[bitrev32(n2)] = plane[lane * 33 + n2];
+  __syncwarp();
+  fft32_dit(r, im);   // now (r[k2], im[k2]) = Z[lane + 32 k2]
+  // split the two real spectra, power -> P2[k] = (|A_k|^2, |B_k|^2), k = 0..512
+  float2* P2 = reinterpret_cast<float2*>(plane);
+  const int src = (32 - lane) & 31;
+#pragma unroll
+  for (int k2 = 0; k2 <= 16; ++k2) {
+    const int pk = (k2 < 16) ? 31 - k2 : 15;
+    float pr = __shfl_sync(0xffffffffu, r[pk], src);
+    float pi = __shfl_sync(0xffffffffu, im[pk], src);
+    if (lane == 0) { pr = r[(32 - k2) & 31]; pi = im[(32 - k2) & 31]; }
+    const float sr = r[k2] + pr, di = im[k2] - pi;
+    const float si = im[k2] + pi, dr = r[k2] - pr;
+    const float pa = fmaf(sr, sr, di * di);
+    const float pb = fmaf(si, si, dr * dr);
+    if (k2 < 16 || lane == 0) P2[lane + 32 * k2] = make_float2(pa, pb);
+  }
+  __syncwarp();
+  // sparse mel (4 bands per lane), 10 log10, rows to the slab, per-row maxima
+  float mxa = -3.0e38f, mxb = -3.0e38f;
+  float* outA = sl.logmel + (size_t)row * kNMels;
+#pragma unroll
+  for (int q = 0; q < 4; ++q) {
+    const int band = 32 * q + lane;
+    const int k0 = __ldg(a.tab.mel_k0 + band);
+    const float* wq = a.tab.mel_w + a.tab.mel_woff[q] + lane;
+    const int cnt = a.tab.mel_cnt[q];
+    float ma = 0.f, mb = 0.f;
+#pragma unroll 4
+    for (int i = 0; i < cnt; ++i) {
+      const float w = __ldg(wq + 32 * i);
+      const float2 p = P2[k0 + i];
+      ma = fmaf(w, p.x, ma);
+      mb = fmaf(w, p.y, mb);
+    }
+    const float da = 3.0102999566398120f * __log2f(fmaxf(ma, 1e-10f));
+    const float db = 3.0102999566398120f * __log2f(fmaxf(mb, 1e-10f));
+    __stcg(outA + band, da);
+    mxa = fmaxf(mxa, da);
+    if (vB) { __stcg(outA + kNMels + band, db); mxb = fmaxf(mxb, db); }
+  }
+  mxa = warp_max(mxa); mxb = warp_max(mxb);
+#pragma unroll
+  for (int g = 0; g < NG; ++g) eg[g] = warp_sum(eg[g]);
+  float eA = 0.f, eB = 0.f;
+#pragma unroll
+  for (int g = 0; g < NG - 1; ++g) { eA += eg[g]; eB += eg[g + 1]; }
+  if (!isfinite(eA + eB)) bad = 1;   // a NaN / Inf sample poisons the sums of squares (librosa.util.valid_audio)
+  if (lane == 0) {
+    __stcg(sl.rms + row, sqrtf(eA * (1.0f / NFFT)));
+    __stcg(sl.rowmax + row, mxa);
+    if (vB) { __stcg(sl.rms + row + 1, sqrtf(eB * (1.0f / NFFT))); __stcg(sl.rowmax + row + 1, mxb); }
+    if (own_sums) {   // blocks [fA*hop, +hop) and [+hop, +2hop) are groups NFFT/(2 HOP) and the next one
+      __stcg(sl.blk + usum_idx, eg[NFFT / (2 * HOP)]);
+      __stcg(sl.blk + usum_idx + 1, eg[NFFT / (2 * HOP) + 1]);
+    }
+  }
+  __syncwarp();   // plane reusable
+}
+
+// ---- streaming pass over frames [f_begin, f_end) of `rg`; slab row = row_shift + f.  Warp w takes the frame pairs
+// f_begin + 2w, + 2*16, ...; no CTA-wide barrier inside.  own_sums: rg.origin == 0 and the hop-block sums are wanted.
+template <int NFFT, int HOP>
+__device__ __forceinline__ void stream_frames(const ClipArgs& a, const Smem& sm, const Slab& sl, WarpCtx& wc,
+                                              const float* __restrict__ clip_audio, int L0, Region rg, int f_begin, int f_end,
+                                              int row_shift, bool own_sums, int& bad) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  constexpr int SPAN = HOP + NFFT;
+  int fA = f_begin + 2 * warp;
+  if (fA >= f_end) return;
+  int gA = rg.origin + fA * HOP - NFFT / 2;
+  unsigned cur_bytes;
+  {
+    int g_lo = 0, s_lo = 0;
+    cur_bytes = pair_copy_range(rg, gA, SPAN, L0, g_lo, s_lo);
+    if (lane == 0 && cur_bytes) {
+      fence_proxy_async();
+      mbar_expect_tx(wc.mbar, cur_bytes);
+      tma_load_1d(wc.raw + s_lo, clip_audio + g_lo, cur_bytes, wc.mbar);
+    }
+  }
+  while (fA < f_end) {
+    const int fN = fA + kChunkFrames;
+    const int gN = gA + kChunkFrames * HOP;
+    unsigned next_bytes = 0;
+    int g_lo = 0, s_lo = 0;
+    if (fN < f_end) next_bytes = pair_copy_range(rg, gN, SPAN, L0, g_lo, s_lo);
+    if (cur_bytes) { mbar_wait(wc.mbar, wc.parity); wc.parity ^= 1u; }
+    warp_frames_1024<HOP>(a, sm, sl, wc, rg, gA, L0, fA + 1 < f_end, row_shift + fA, own_sums, fA,
+                          next_bytes, clip_audio + g_lo, wc.raw + s_lo, bad);
+    fA = fN; gA = gN; cur_bytes = next_bytes;
+  }
+}
+
+// ---- block-wide helpers (all kClipThreads threads call them; red = shared scratch of >= 64 doubles)
+__device__ __forceinline__ float block_max(float v, float* red) {
+  v = warp_max(v);
+  __syncthreads();
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = v;
+  __syncthreads();
+  float t = red[0];
+#pragma unroll
+  for (int w = 1; w < kClipWarps; ++w) t = fmaxf(t, red[w]);
+  return t;
+}
+__device__ __forceinline__ float block_min(float v, float* red) {
+  v = warp_min(v);
+  __syncthreads();
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = v;
+  __syncthreads();
+  float t = red[0];
+#pragma unroll
+  for (int w = 1; w < kClipWarps; ++w) t = fminf(t, red[w]);
+  return t;
+}
+__device__ __forceinline__ double block_sum(double v, double* red) {
+  v = warp_sum(v);
+  __syncthreads();
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = v;
+  __syncthreads();
+  double t = 0;
+#pragma unroll
+  for (int w = 0; w < kClipWarps; ++w) t += red[w];
+  return t;
+}
+
+// ---- T: librosa.effects.trim(top_db) from the block sums (core/feature_extractor.py:72)
+//   r_i = sqrt(mean(y_pre[512 i - 1024 .. 512 i + 1024)^2)), zero padded, i = 0 .. L0/512
+//   keep frames with 10 log10(max(1e-10, r_i^2)) - 10 log10(max(1e-10, max_i r_i^2)) > -top_db
+//   start = 512 * first, end = min(L0, 512 * (last + 1))
+__device__ __forceinline__ float trim_block(const float* usum, int b, int nb, int R, int nu) {
+  // sum of squares of 512-sample block b from the hop-sized unit sums (fixed order); zero outside the clip
+  if (b < 0 || b >= nb) return 0.f;
+  float s = 0.f;
+  for (int i = 0; i < R; ++i) { const int u = b * R + i; if (u < nu) s += __ldcg(usum + u); }
+  return s;
+}
+__device__ __forceinline__ ClipInfo trim_decide(const float* usum, int nu, int L0, int hop, float top_db, int bad, float* red_f, int* red_i) {
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int n_rms = 1 + L0 / kTrimHop;
+  const int nb = (L0 + kTrimHop - 1) / kTrimHop;
+  const int R = kTrimHop / hop;
+  float mx = 0.f;
+  for (int i = tid; i < n_rms; i += kClipThreads) {
+    // frame i covers blocks i-2 .. i+1
+    const float s = (trim_block(usum, i - 2, nb, R, nu) + trim_block(usum, i - 1, nb, R, nu)) +
+                    (trim_block(usum, i, nb, R, nu) + trim_block(usum, i + 1, nb, R, nu));
+    mx = fmaxf(mx, sqrtf(s * (1.0f / kTrimFrame)));
+  }
+  mx = block_max(mx, red_f);
+  const float ref_db = 10.0f * log10f(fmaxf(1e-10f, mx * mx));
+  int first = 0x7fffffff, last = -1;
+  for (int i = tid; i < n_rms; i += kClipThreads) {
+    const float s = (trim_block(usum, i - 2, nb, R, nu) + trim_block(usum, i - 1, nb, R, nu)) +
+                    (trim_block(usum, i, nb, R, nu) + trim_block(usum, i + 1, nb, R, nu));
+    const float r = sqrtf(s * (1.0f / kTrimFrame));
+    float db = 10.0f * log10f(fmaxf(1e-10f, r * r));
+    db -= ref_db;
+    if (db > -top_db) { first = min(first, i); last = max(last, i); }
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    first = min(first, __shfl_xor_sync(0xffffffffu, first, o));
+    last = max(last, __shfl_xor_sync(0xffffffffu, last, o));
+  }
+  __syncthreads();
+  if (lane == 0) { red_i[warp] = first; red_i[kClipWarps + warp] = last; }
+  __syncthreads();
+#pragma unroll
+  for (int w = 0; w < kClipWarps; ++w) { first = min(first, red_i[w]); last = max(last, red_i[kClipWarps + w]); }
+  ClipInfo ci;
+  ci.start = 0; ci.end = 0; ci.len = 0; ci.n_frames = 0; ci.max_key = 0u; ci.pad0 = ci.pad1 = 0; ci.status = 0;
+  if (L0 <= 0) ci.status = 1;                 // AFX_CLIP_EMPTY
+  else if (bad) ci.status = 2;                // AFX_CLIP_NONFINITE
+  else if (last < 0) ci.status = 1;           // every frame silent -> empty signal
+  else {
+    ci.start = first * kTrimHop;
+    ci.end = min(L0, (last + 1) * kTrimHop);
+    ci.len = ci.end - ci.start;
+    const int T = 1 + ci.len / hop;
+    if (ci.len <= 0) ci.status = 1;
+    else if (T < kDeltaWidth) ci.status = 3;  // AFX_CLIP_TOO_SHORT
+    else ci.n_frames = T;
+  }
+  return ci;
+}
+
+// ---- C: clamp -> DCT-II -> delta / delta2 -> moment sums for trimmed frames [0, T) (slab rows a0 + t).
+// sD [64][129], sM [64][n16+1] alias the streaming buffers; sDct [128][n16] is resident; acc [6][64] doubles.
+__device__ __forceinline__ void mfcc_phase(const ClipArgs& a, const Slab& sl, int a0, int T, float floor_db, long long out_row0,
+                                           float* sD, const float* sDct, float* sM, double* acc) {
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int mstride = a.n16 + 1;
+  for (int i = tid; i < kMoments * kMaxMfcc; i += kClipThreads) acc[i] = 0.0;
+  for (int f_lo = 0; f_lo < T; f_lo += kStatFrames) {
+    const int f_hi = min(f_lo + kStatFrames, T);             // exclusive
+    const int e_lo = min(max(f_lo, kStatHalo), T - 1 - kStatHalo) - kStatHalo;
+    const int e_hi = min(max(f_hi - 1, kStatHalo), T - 1 - kStatHalo) + kStatHalo;   // inclusive
+    const int ne = e_hi - e_lo + 1;                           // <= 64
+    __syncthreads();   // previous sub-chunk's readers are done with sD / sM
+    for (int e = warp; e < ne; e += kClipWarps) {
+      const float* src = sl.logmel + (size_t)(a0 + e_lo + e) * kNMels;
+#pragma unroll
+      for (int q = 0; q < 4; ++q) sD[e * kDStride + q * 32 + lane] = fmaxf(__ldcg(src + q * 32 + lane), floor_db);
+    }
+    __syncthreads();
+    {  // DCT: thread (frame e = tid & 63, coefficient group g = tid >> 6) computes 4 coefficients at a time
+      const int e = tid & 63;
+      for (int c0 = (tid >> 6) * 4; c0 < a.n16; c0 += 4 * (kClipThreads / 64)) {
+        float acc0 = 0.f, acc1 = 0.f, acc2 = 0.f, acc3 = 0.f;
+        if (e < ne) {
+          const float* drow = sD + e * kDStride;
+#pragma unroll 8
+          for (int m = 0; m < kNMels; ++m) {
+            const float d = drow[m];
+            const float4 w = *reinterpret_cast<const float4*>(sDct + m * a.n16 + c0);
+            acc0 = fmaf(d, w.x, acc0);
+            acc1 = fmaf(d, w.y, acc1);
+            acc2 = fmaf(d, w.z, acc2);
+            acc3 = fmaf(d, w.w, acc3);
+          }
+        }
+        float* mrow = sM + e * mstride + c0;
+        mrow[0] = acc0; mrow[1] = acc1; mrow[2] = acc2; mrow[3] = acc3;
+      }
+    }
+    __syncthreads();
+    // deltas + moments: warp w handles coefficients w, w+16, ...; lanes stride over the sub-chunk's frames
+    for (int c = warp; c < a.n_mfcc; c += kClipWarps) {
+      double s1 = 0, s2 = 0, s3 = 0, s4 = 0, sd1 = 0, sd2 = 0;
+      for (int f = f_lo + lane; f < f_hi; f += 32) {
+        const int te = min(max(f, kStatHalo), T - 1 - kStatHalo) - e_lo;   // centre row of the 9-tap window
+        const float* col = sM + c;
+        // savgol(9, polyorder=deriv=1): sum k x[t+k] / 60 ; (9, 2, 2): sum c_k x[t+k] / 462  (double, cast to f32)
+        const double xm4 = col[(te - 4) * mstride], xm3 = col[(te - 3) * mstride], xm2 = col[(te - 2) * mstride],
+                     xm1 = col[(te - 1) * mstride], x0 = col[te * mstride], xp1 = col[(te + 1) * mstride],
+                     xp2 = col[(te + 2) * mstride], xp3 = col[(te + 3) * mstride], xp4 = col[(te + 4) * mstride];
+        const double d1 = (4.0 * (xp4 - xm4) + 3.0 * (xp3 - xm3) + 2.0 * (xp2 - xm2) + (xp1 - xm1)) / 60.0;
+        const double d2 = (28.0 * (xp4 + xm4) + 7.0 * (xp3 + xm3) - 8.0 * (xp2 + xm2) - 17.0 * (xp1 + xm1) - 20.0 * x0) / 462.0;
+        const float d1f = (float)d1, d2f = (float)d2;
+        const float xf = col[(f - e_lo) * mstride];
+        const double x = xf;
+        s1 += x; s2 += x * x; s3 += x * x * x; s4 += (x * x) * (x * x);
+        sd1 += (double)d1f; sd2 += (double)d2f;
+        if (a.frames_out) {
+          float* fr = a.frames_out + (size_t)(out_row0 + f) * a.frame_width;
+          fr[c] = xf; fr[a.n_mfcc + c] = d1f; fr[2 * a.n_mfcc + c] = d2f;
+        }
+      }
+      s1 = warp_sum(s1); s2 = warp_sum(s2); s3 = warp_sum(s3); s4 = warp_sum(s4);
+      sd1 = warp_sum(sd1); sd2 = warp_sum(sd2);
+      if (lane == 0) {   // coefficient c belongs to this warp alone: no race on acc[.][c]
+        acc[0 * kMaxMfcc + c] += s1; acc[1 * kMaxMfcc + c] += s2; acc[2 * kMaxMfcc + c] += s3;
+        acc[3 * kMaxMfcc + c] += s4; acc[4 * kMaxMfcc + c] += sd1; acc[5 * kMaxMfcc + c] += sd2;
+      }
+    }
+  }
+  __syncthreads();
+}
+
+// ---- the kernel
+template <int NFFT, int HOP>
+__global__ void __launch_bounds__(kClipThreads, 1) clip_kernel(ClipArgs a) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  // layout: [16 mbarriers 128B][twiddle 8KB][window NFFT*4][acc 6*64 doubles][red 64 doubles][sDct 128*n16 floats]
+  //         [raw tiles 16 x (HOP+NFFT+8) floats][planes 16 x 4224B]   (phase C's sD / sM alias the raw tiles)
+  constexpr int RAWW = HOP + NFFT + 8;
+  Smem sm;
+  sm.mbar = reinterpret_cast<uint64_t*>(smem_raw);
+  sm.tw = reinterpret_cast<float2*>(smem_raw + 128);
+  sm.win = reinterpret_cast<float*>(smem_raw + 128 + 8192);
+  double* acc = reinterpret_cast<double*>(sm.win + NFFT);
+  double* red = acc + kMoments * kMaxMfcc;
+  float* sDct = reinterpret_cast<float*>(red + 64);
+  sm.raw = sDct + kNMels * a.n16;
+  sm.planes = sm.raw + kClipWarps * RAWW;
+  float* sD = sm.raw;
+  float* sM = sD + kStatRows * kDStride;
+  __shared__ int s_clip, s_bad;
+
+  const int tid = threadIdx.x, warp = tid >> 5;
+  for (int i = tid; i < 1024; i += kClipThreads) sm.tw[i] = a.tab.twiddle[i];
+  for (int i = tid; i < NFFT; i += kClipThreads) sm.win[i] = a.tab.window_half[i];
+  for (int i = tid; i < kNMels * a.n16; i += kClipThreads) sDct[i] = a.dct_t[i];
+  if (tid < kClipWarps) mbar_init(sm.mbar + tid, 1);
+  if (tid == 0) fence_mbar_init();
+  __syncthreads();
+
+  const Slab sl = carve_slab(a, blockIdx.x);
+  WarpCtx wc;
+  wc.raw = sm.raw + warp * RAWW;
+  wc.plane = sm.planes + warp * kPlaneFloats;
+  wc.mbar = sm.mbar + warp;
+  wc.parity = 0;
+  const int hop = HOP;
+  const int n = a.n_mfcc;
+
+  for (;;) {
+    __syncthreads();   // everyone is done with the previous clip (s_clip, aliased buffers)
+    if (tid == 0) { s_clip = atomicAdd(a.counter, 1); s_bad = 0; }
+    __syncthreads();
+    const int clip = s_clip;
+    if (clip >= a.n_clips) break;
+    const int L0 = a.lengths[clip];
+    const float* clip_audio = a.audio + a.offsets[clip];
+    const long long out_row0 = a.frame_off[clip];
+    const bool want_frames = (a.mask & 0x6u) != 0;   // MFCC or ENERGY
+
+    ClipInfo ci;
+    ci.start = 0; ci.end = 0; ci.len = 0; ci.n_frames = 0; ci.max_key = 0u; ci.pad0 = ci.pad1 = 0; ci.status = 1;
+    int a0 = 0;          // slab row of trimmed frame 0
+    int head_end = 0;
+    int bad = 0;
+    // pass 0: S (speculative, absolute frame grid) or the whole pretrimmed clip; pass 1 / 2: head / tail fix-ups (F)
+    for (int pass = 0; pass < 3; ++pass) {
+      Region rg{0, 0, L0};
+      int fb = 0, fe = 0, shift = 0;
+      bool own = false;
+      if (pass == 0) {
+        if (a.pretrimmed) {
+          ci = a.info[clip];
+          rg = Region{ci.start, ci.start, ci.end};
+          fe = (ci.status == 0 && want_frames) ? ci.n_frames : 0;
+        } else {
+          fe = L0 > 0 ? 1 + L0 / hop : 0;
+          own = true;
+        }
+      } else {
+        if (a.pretrimmed || ci.status != 0 || !want_frames) break;
+        rg = Region{ci.start, ci.start, ci.end};
+        shift = a0;
+        if (pass == 1) {           // frames t with t*hop < n_fft/2 reach in front of the trimmed signal
+          if (ci.start > 0) { head_end = min(ci.n_frames, (NFFT / 2 + hop - 1) / hop); fe = head_end; }
+        } else if (ci.end < L0) {  // frames t with t*hop + n_fft/2 > len reach behind it
+          const int t_tail = (ci.len >= NFFT / 2) ? (ci.len - NFFT / 2) / hop + 1 : 0;
+          fb = max(t_tail, head_end); fe = ci.n_frames;
+        }
+      }
+      stream_frames<NFFT, HOP>(a, sm, sl, wc, clip_audio, L0, rg, fb, fe, shift, own, bad);
+      if (pass == 0 && !a.pretrimmed) {
+        if (bad) s_bad = 1;
+        __syncthreads();
+        // ---- T
+        const int nu = 2 * ((fe + 1) / 2);   // hop-block sums written by the pass
+        ci = trim_decide(sl.blk, nu, L0, hop, a.trim_top_db, s_bad, reinterpret_cast<float*>(red), reinterpret_cast<int*>(red + 32));
+        a0 = ci.start / hop;
+      }
+    }
+    __syncthreads();
+    if (tid == 0) {
+      a.info[clip] = ci;
+      int* m = a.meta + (size_t)clip * 4;
+      m[0] = ci.status; m[1] = ci.start; m[2] = ci.end; m[3] = ci.n_frames;
+    }
+    float* out = a.summaries + (size_t)clip * a.summary_width;
+    for (int i = tid; i < a.summary_width; i += kClipThreads) out[i] = 0.f;
+    const int T = ci.n_frames;
+    if (T <= 0) continue;   // status != OK: summary row stays zero (uniform branch)
+    const double invT = 1.0 / (double)T;
+
+    if (a.mask & 0x2u) {
+      // ---- C: power_to_db(top_db): clamp at the clip-global maximum - top_db
+      float mx = -3.0e38f;
+      for (int t = tid; t < T; t += kClipThreads) mx = fmaxf(mx, __ldcg(sl.rowmax + a0 + t));
+      mx = block_max(mx, reinterpret_cast<float*>(red));
+      mfcc_phase(a, sl, a0, T, mx - a.mfcc_top_db, out_row0, sD, sDct, sM, acc);
+      if (tid < n) {
+        const double s1 = acc[tid], s2 = acc[kMaxMfcc + tid], s3 = acc[2 * kMaxMfcc + tid], s4 = acc[3 * kMaxMfcc + tid];
+        const double mean = s1 * invT;
+        const double ex2 = s2 * invT, ex3 = s3 * invT, ex4 = s4 * invT;
+        const double m2 = fmax(ex2 - mean * mean, 0.0);
+        const double m3 = ex3 - 3.0 * mean * ex2 + 2.0 * mean * mean * mean;
+        const double m4 = ex4 - 4.0 * mean * ex3 + 6.0 * mean * mean * ex2 - 3.0 * mean * mean * mean * mean;
+        out[4 + tid] = (float)mean;
+        out[4 + n + tid] = (float)sqrt(m2);
+        out[4 + 2 * n + tid] = (float)(acc[4 * kMaxMfcc + tid] * invT);
+        out[4 + 3 * n + tid] = (float)(acc[5 * kMaxMfcc + tid] * invT);
+        out[4 + 4 * n + 3 + tid] = (m2 > 0.0) ? (float)(m3 / (m2 * sqrt(m2))) : 0.f;
+        out[4 + 4 * n + 3 + n + tid] = (m2 > 0.0) ? (float)(m4 / (m2 * m2) - 3.0) : 0.f;
+      }
+    }
+    if (a.mask & 0x4u) {   // RMS energy statistics (core/feature_extractor.py:171-173)
+      double s1 = 0, s2 = 0, s3 = 0, s4 = 0;
+      float mn = 3.0e38f, mx = -3.0e38f;
+      for (int t = tid; t < T; t += kClipThreads) {
+        const float rf = __ldcg(sl.rms + a0 + t);
+        const double r = rf;
+        s1 += r; s2 += r * r; s3 += r * r * r; s4 += (r * r) * (r * r);
+        mn = fminf(mn, rf); mx = fmaxf(mx, rf);
+        if (a.frames_out) a.frames_out[(size_t)(out_row0 + t) * a.frame_width + 3 * n] = rf;
+      }
+      s1 = block_sum(s1, red); s2 = block_sum(s2, red); s3 = block_sum(s3, red); s4 = block_sum(s4, red);
+      mn = block_min(mn, reinterpret_cast<float*>(red)); mx = block_max(mx, reinterpret_cast<float*>(red));
+      if (tid == 0) {
+        const double mean = s1 * invT;
+        const double ex2 = s2 * invT, ex3 = s3 * invT, ex4 = s4 * invT;
+        const double m2 = fmax(ex2 - mean * mean, 0.0);
+        const double m3 = ex3 - 3.0 * mean * ex2 + 2.0 * mean * mean * mean;
+        const double m4 = ex4 - 4.0 * mean * ex3 + 6.0 * mean * mean * ex2 - 3.0 * mean * mean * mean * mean;
+        float* e = out + 4 + 4 * n;
+        e[0] = (float)mean; e[1] = (float)sqrt(m2); e[2] = mx - mn;
+        e[3 + 2 * n] = (m2 > 0.0) ? (float)(m3 / (m2 * sqrt(m2))) : 0.f;
+        e[3 + 2 * n + 1] = (m2 > 0.0) ? (float)(m4 / (m2 * m2) - 3.0) : 0.f;
+      }
+    }
+  }
+}
+
+}  // namespace afx

@@ -114,9 +114,9 @@ def test_edge_cases_status_codes(torch_cuda):
     assert [k["file_path"] for k in kept] == ["c0.wav", "c6.wav", "c7.wav"]
 
 
-def test_ragged_batch_small_workspace_waves(torch_cuda):
-    """Many ragged clips with a workspace at the documented minimum: the wave scheduler must split the
-    batch and still produce the same rows as one big wave."""
+def test_ragged_batch_caller_workspace(torch_cuda):
+    """Many ragged clips (dynamic clip -> CTA assignment) with a caller-allocated workspace of exactly
+    afx_workspace_min_bytes: same rows bit for bit, and a short workspace is refused."""
     import torch
     from audio_feature_extraction_b200 import AudioFeatureExtractor, _native as N
     from audio_feature_extraction_b200.synth import make_clip
