@@ -55,7 +55,8 @@ cudaError_t upload(const std::vector<T>& v, T** dptr) {
 
 struct afx_handle_s {
   afx_config_t cfg;
-  int n16;                 // n_mfcc rounded up to a multiple of 4
+  int n16;                 // n_mfcc rounded up to a multiple of 16 (the in-pass DCT works on groups of 16)
+  int mel_floats = 0;      // floats in the padded sparse mel weight table
   int sm_count;
   void (*clip_fn)(afx::ClipArgs) = nullptr;   // clip_kernel<frame_length, hop_length>
   // device tables
@@ -131,7 +132,7 @@ inline long long ceil_div(long long a, long long b) { return (a + b - 1) / b; }
 inline int slab_rows(const afx_handle_s* h, long long max_len) { return (int)((frames_ub(h, max_len) + 3) & ~3LL); }
 size_t slab_bytes_for(const afx_handle_s* h, long long max_len) {
   const size_t rows = (size_t)slab_rows(h, max_len);
-  return align_up((rows * (afx::kNMels + 3) + 8) * sizeof(float), 256);   // + hop-block sums (one per frame row)
+  return align_up((rows * ((size_t)h->n16 + 4) + 8) * sizeof(float), 256);   // MFCC rows, rms, row max / min, hop-block sums
 }
 inline int grid_for(const afx_handle_s* h, long long n_clips) { return (int)std::max<long long>(1, std::min<long long>(n_clips, h->sm_count)); }
 
@@ -153,7 +154,8 @@ size_t clip_smem_bytes(const afx_handle_s* h, int* tile_floats_out) {
   const int tile_floats = h->cfg.hop_length + h->cfg.frame_length + 8;   // per-warp raw tile
   if (tile_floats_out) *tile_floats_out = tile_floats;
   return 128 + 8192 + (size_t)h->cfg.frame_length * 4 + (size_t)(afx::kMoments * afx::kMaxMfcc + 64) * 8 +
-         (size_t)afx::kNMels * h->n16 * 4 + (size_t)afx::kClipWarps * (tile_floats + afx::kPlaneFloats) * 4;
+         (size_t)afx::kNMels * (h->n16 + 4) * 4 + (size_t)h->mel_floats * 4 +
+         (size_t)afx::kClipWarps * (tile_floats + afx::kPlaneFloats) * 4;
 }
 
 }  // namespace
@@ -203,7 +205,7 @@ int afx_create(const afx_config_t* cfg, afx_handle_t* out) {
 
   afx_handle_s* h = new afx_handle_s();
   h->cfg = *cfg;
-  h->n16 = (cfg->n_mfcc + 3) & ~3;
+  h->n16 = (cfg->n_mfcc + 15) & ~15;
   h->sm_count = prop.multiProcessorCount;
 
   const auto win = afx::host::window_half(cfg->frame_length);
@@ -215,6 +217,7 @@ int afx_create(const afx_config_t* cfg, afx_handle_t* out) {
     for (int m = 0; m < cfg->n_mels; ++m) dct_t[(size_t)m * h->n16 + c] = dct[(size_t)c * cfg->n_mels + m];
   CUDA_TRY(upload(win, &h->d_window));
   CUDA_TRY(upload(tw, &h->d_twiddle));
+  h->mel_floats = (int)mel.w.size();
   CUDA_TRY(upload(mel.w, &h->d_mel_w));
   CUDA_TRY(upload(mel.k0, &h->d_mel_k0));
   CUDA_TRY(upload(dct_t, &h->d_dct_t));
@@ -345,7 +348,7 @@ int afx_extract(afx_handle_t h, const float* d_audio, const int64_t* h_offsets, 
     ca.audio = d_audio; ca.offsets = d_offsets; ca.lengths = d_lengths; ca.frame_off = d_frame_off; ca.info = d_info;
     ca.counter = reinterpret_cast<int*>(ws + L.off_counter); ca.n_clips = n;
     ca.slabs = ws + L.header_bytes; ca.slab_bytes = slab_bytes; ca.a_max = slab_rows(h, max_len);
-    ca.tab = h->tab; ca.dct_t = h->d_dct_t; ca.hop = hop; ca.tile_floats = tile_floats;
+    ca.tab = h->tab; ca.dct_t = h->d_dct_t; ca.hop = hop; ca.mel_floats = h->mel_floats;
     ca.coef = h->cfg.pre_emphasis; ca.trim_top_db = h->cfg.trim_top_db; ca.mfcc_top_db = h->cfg.mfcc_top_db;
     ca.n_mfcc = h->cfg.n_mfcc; ca.n16 = h->n16; ca.summary_width = afx_summary_width(h); ca.frame_width = afx_frame_width(h);
     ca.mask = feature_mask; ca.summaries = d_summaries; ca.meta = d_meta; ca.frames_out = d_frames;

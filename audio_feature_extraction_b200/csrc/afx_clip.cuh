@@ -35,8 +35,7 @@ constexpr int kChunkFrames = 2 * kClipWarps;     // frames per streaming step
 constexpr int kTilePad = 4;                      // floats in front of the first frame sample inside the tile
 constexpr int kPlaneFloats = 32 * 33;
 constexpr int kStatThreads = kClipThreads;
-constexpr int kStatRows = kStatFrames + 2 * kStatHalo;   // 64 frames incl. halo
-constexpr int kDStride = kNMels + 1;                      // padded log-mel row in shared memory
+constexpr int kStatRows = kStatFrames + 2 * kStatHalo;   // frames per sub-chunk incl. halo
 constexpr int kMoments = 6;                               // sum x, x^2, x^3, x^4, sum delta, sum delta2
 
 struct ClipArgs {
@@ -53,7 +52,7 @@ struct ClipArgs {
   Tables tab;
   const float* dct_t;           // [128][n16]
   int hop;
-  int tile_floats;
+  int mel_floats;               // floats in Tables::mel_w (multiple of 4)
   float coef, trim_top_db, mfcc_top_db;
   int n_mfcc, n16, summary_width, frame_width;
   unsigned mask;                // AFX_FEAT_*
@@ -64,19 +63,21 @@ struct ClipArgs {
 };
 
 struct Slab {
-  float* logmel;   // [a_max][128]
+  float* mfcc;     // [a_max][n16] DCT rows (speculative: no top_db clamp; rewritten by the redo pass where it bites)
   float* rms;      // [a_max]
-  float* rowmax;   // [a_max]
+  float* rowmax;   // [a_max] per-frame max of the unclamped log-mel row
+  float* rowmin;   // [a_max] per-frame min
   float* blk;      // [rows + 2] sums of squares of the hop-sized blocks [u*hop, (u+1)*hop) of the pre-emphasised clip
 };
 
 __device__ __forceinline__ Slab carve_slab(const ClipArgs& a, int cta) {
   Slab s;
   char* p = a.slabs + (size_t)cta * a.slab_bytes;
-  s.logmel = reinterpret_cast<float*>(p);
-  s.rms = s.logmel + (size_t)a.a_max * kNMels;
+  s.mfcc = reinterpret_cast<float*>(p);
+  s.rms = s.mfcc + (size_t)a.a_max * a.n16;
   s.rowmax = s.rms + a.a_max;
-  s.blk = s.rowmax + a.a_max;
+  s.rowmin = s.rowmax + a.a_max;
+  s.blk = s.rowmin + a.a_max;
   return s;
 }
 
@@ -85,6 +86,8 @@ struct Smem {
   uint64_t* mbar;  // [16] one TMA barrier per warp
   float2* tw;      // [1024]
   float* win;      // [NFFT]
+  const float* dct;   // [128][n16 + 4] DCT-II rows, transposed, padded stride (conflict-free float4 reads)
+  const float* melw;  // copy of Tables::mel_w
   float* raw;      // [16][HOP + NFFT + 8] per-warp raw-sample tiles
   float* planes;   // [16][32*33]
 };
@@ -110,6 +113,8 @@ struct WarpCtx {
   float* plane;      // [32*33] transpose scratch / power spectrum
   uint64_t* mbar;    // this warp's TMA barrier
   unsigned parity;
+  uint64_t pol_in;   // L2 policy of the audio stream (evict_first)
+  uint64_t pol_slab; // L2 policy of the scratch slab (evict_last)
 };
 
 // ---- one warp: two real frames fA, fA + 1 -> log-mel rows row, row + 1 of the slab, RMS, row maxima, and (own_sums)
@@ -120,7 +125,7 @@ struct WarpCtx {
 // next_bytes/next_src/next_dst: the warp's next tile, issued as soon as this one sits in registers.
 template <int HOP>
 __device__ __forceinline__ void warp_frames_1024(const ClipArgs& a, const Smem& sm, const Slab& sl, WarpCtx& wc, const Region& rg,
-                                                 int gA, int L0, bool vB, int row, bool own_sums, int usum_idx,
+                                                 int gA, int L0, bool vB, int row, bool own_sums, int usum_idx, float floor_db,
                                                  unsigned next_bytes, const float* next_src, float* next_dst, int& bad) {
   constexpr int NFFT = 1024;
   constexpr int SH = HOP / 32;            // rows by which frame B trails frame A
@@ -164,7 +169,7 @@ __device__ __forceinline__ void warp_frames_1024(const ClipArgs& a, const Smem& 
   if (lane == 0 && next_bytes) {
     fence_proxy_async();
     mbar_expect_tx(wc.mbar, next_bytes);
-    tma_load_1d(next_dst, next_src, next_bytes, wc.mbar);
+    tma_load_1d_hint(next_dst, next_src, next_bytes, wc.mbar, wc.pol_in);
   }
   float* plane = wc.plane;
   fft32_dit(r, im);
@@ -205,30 +210,64 @@ __device__ __forceinline__ void warp_frames_1024(const ClipArgs& a, const Smem& 
     if (k2 < 16 || lane == 0) P2[lane + 32 * k2] = make_float2(pa, pb);
   }
   __syncwarp();
-  // sparse mel (4 bands per lane), 10 log10, rows to the slab, per-row maxima
-  float mxa = -3.0e38f, mxb = -3.0e38f;
-  float* outA = sl.logmel + (size_t)row * kNMels;
+  // sparse mel (4 bands per lane), 10 log10, per-row extrema of the unclamped values, clamp at floor_db
+  float mxa = -3.0e38f, mxb = -3.0e38f, mna = 3.0e38f, mnb = 3.0e38f;
+  float da[4], db[4];
 #pragma unroll
   for (int q = 0; q < 4; ++q) {
     const int band = 32 * q + lane;
     const int k0 = __ldg(a.tab.mel_k0 + band);
-    const float* wq = a.tab.mel_w + a.tab.mel_woff[q] + lane;
+    const float* wq = sm.melw + a.tab.mel_woff[q] + lane;
     const int cnt = a.tab.mel_cnt[q];
     float ma = 0.f, mb = 0.f;
 #pragma unroll 4
     for (int i = 0; i < cnt; ++i) {
-      const float w = __ldg(wq + 32 * i);
+      const float w = wq[32 * i];
       const float2 p = P2[k0 + i];
       ma = fmaf(w, p.x, ma);
       mb = fmaf(w, p.y, mb);
     }
-    const float da = 3.0102999566398120f * __log2f(fmaxf(ma, 1e-10f));
-    const float db = 3.0102999566398120f * __log2f(fmaxf(mb, 1e-10f));
-    __stcg(outA + band, da);
-    mxa = fmaxf(mxa, da);
-    if (vB) { __stcg(outA + kNMels + band, db); mxb = fmaxf(mxb, db); }
+    const float va = 3.0102999566398120f * __log2f(fmaxf(ma, 1e-10f));
+    const float vb = 3.0102999566398120f * __log2f(fmaxf(mb, 1e-10f));
+    mxa = fmaxf(mxa, va); mna = fminf(mna, va);
+    mxb = fmaxf(mxb, vb); mnb = fminf(mnb, vb);
+    da[q] = fmaxf(va, floor_db); db[q] = fmaxf(vb, floor_db);
+  }
+  __syncwarp();   // P2 consumed: the plane is free for the DCT reduction
+  // DCT-II (ortho), 16 coefficients at a time: lane-partial sums over its 4 bands, then a transposed reduction
+  // through the plane (lane j sums row j = (frame j/16, coefficient j%16) over the 32 lanes' partials)
+  {
+    const int stride = a.n16 + 4;
+    for (int kg = 0; kg < a.n16; kg += 16) {
+      float pa[16], pb[16];
+#pragma unroll
+      for (int k = 0; k < 16; ++k) { pa[k] = 0.f; pb[k] = 0.f; }
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const float* crow = sm.dct + (32 * q + lane) * stride + kg;
+#pragma unroll
+        for (int k4 = 0; k4 < 4; ++k4) {
+          const float4 c = *reinterpret_cast<const float4*>(crow + 4 * k4);
+          pa[4 * k4 + 0] = fmaf(da[q], c.x, pa[4 * k4 + 0]); pb[4 * k4 + 0] = fmaf(db[q], c.x, pb[4 * k4 + 0]);
+          pa[4 * k4 + 1] = fmaf(da[q], c.y, pa[4 * k4 + 1]); pb[4 * k4 + 1] = fmaf(db[q], c.y, pb[4 * k4 + 1]);
+          pa[4 * k4 + 2] = fmaf(da[q], c.z, pa[4 * k4 + 2]); pb[4 * k4 + 2] = fmaf(db[q], c.z, pb[4 * k4 + 2]);
+          pa[4 * k4 + 3] = fmaf(da[q], c.w, pa[4 * k4 + 3]); pb[4 * k4 + 3] = fmaf(db[q], c.w, pb[4 * k4 + 3]);
+        }
+      }
+#pragma unroll
+      for (int k = 0; k < 16; ++k) { plane[k * 33 + lane] = pa[k]; plane[(16 + k) * 33 + lane] = pb[k]; }
+      __syncwarp();
+      float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+      const float* prow = plane + lane * 33;
+#pragma unroll
+      for (int i = 0; i < 32; i += 4) { s0 += prow[i]; s1 += prow[i + 1]; s2 += prow[i + 2]; s3 += prow[i + 3]; }
+      const float cval = (s0 + s1) + (s2 + s3);
+      if (lane < 16 || vB) st_slab(sl.mfcc + (size_t)(row + (lane >> 4)) * a.n16 + kg + (lane & 15), cval, wc.pol_slab);
+      __syncwarp();
+    }
   }
   mxa = warp_max(mxa); mxb = warp_max(mxb);
+  mna = warp_min(mna); mnb = warp_min(mnb);
 #pragma unroll
   for (int g = 0; g < NG; ++g) eg[g] = warp_sum(eg[g]);
   float eA = 0.f, eB = 0.f;
@@ -237,8 +276,8 @@ __device__ __forceinline__ void warp_frames_1024(const ClipArgs& a, const Smem& 
   if (!isfinite(eA + eB)) bad = 1;   // a NaN / Inf sample poisons the sums of squares (librosa.util.valid_audio)
   if (lane == 0) {
     __stcg(sl.rms + row, sqrtf(eA * (1.0f / NFFT)));
-    __stcg(sl.rowmax + row, mxa);
-    if (vB) { __stcg(sl.rms + row + 1, sqrtf(eB * (1.0f / NFFT))); __stcg(sl.rowmax + row + 1, mxb); }
+    __stcg(sl.rowmax + row, mxa); __stcg(sl.rowmin + row, mna);
+    if (vB) { __stcg(sl.rms + row + 1, sqrtf(eB * (1.0f / NFFT))); __stcg(sl.rowmax + row + 1, mxb); __stcg(sl.rowmin + row + 1, mnb); }
     if (own_sums) {   // blocks [fA*hop, +hop) and [+hop, +2hop) are groups NFFT/(2 HOP) and the next one
       __stcg(sl.blk + usum_idx, eg[NFFT / (2 * HOP)]);
       __stcg(sl.blk + usum_idx + 1, eg[NFFT / (2 * HOP) + 1]);
@@ -249,13 +288,22 @@ __device__ __forceinline__ void warp_frames_1024(const ClipArgs& a, const Smem& 
 
 // ---- streaming pass over frames [f_begin, f_end) of `rg`; slab row = row_shift + f.  Warp w takes the frame pairs
 // f_begin + 2w, + 2*16, ...; no CTA-wide barrier inside.  own_sums: rg.origin == 0 and the hop-block sums are wanted.
+// floor_db: power_to_db clamp applied before the DCT (-3e38 = none, the speculative pass).  redo: only pairs whose
+// unclamped row minimum lies below floor_db are (re)computed -- the pass that makes the speculation exact.
 template <int NFFT, int HOP>
 __device__ __forceinline__ void stream_frames(const ClipArgs& a, const Smem& sm, const Slab& sl, WarpCtx& wc,
                                               const float* __restrict__ clip_audio, int L0, Region rg, int f_begin, int f_end,
-                                              int row_shift, bool own_sums, int& bad) {
+                                              int row_shift, bool own_sums, float floor_db, bool redo, int& bad) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   constexpr int SPAN = HOP + NFFT;
+  auto need = [&](int f) -> bool {   // warp-uniform
+    if (!redo) return true;
+    float m = __ldcg(sl.rowmin + row_shift + f);
+    if (f + 1 < f_end) m = fminf(m, __ldcg(sl.rowmin + row_shift + f + 1));
+    return m < floor_db;
+  };
   int fA = f_begin + 2 * warp;
+  while (fA < f_end && !need(fA)) fA += kChunkFrames;
   if (fA >= f_end) return;
   int gA = rg.origin + fA * HOP - NFFT / 2;
   unsigned cur_bytes;
@@ -265,17 +313,18 @@ __device__ __forceinline__ void stream_frames(const ClipArgs& a, const Smem& sm,
     if (lane == 0 && cur_bytes) {
       fence_proxy_async();
       mbar_expect_tx(wc.mbar, cur_bytes);
-      tma_load_1d(wc.raw + s_lo, clip_audio + g_lo, cur_bytes, wc.mbar);
+      tma_load_1d_hint(wc.raw + s_lo, clip_audio + g_lo, cur_bytes, wc.mbar, wc.pol_in);
     }
   }
   while (fA < f_end) {
-    const int fN = fA + kChunkFrames;
-    const int gN = gA + kChunkFrames * HOP;
+    int fN = fA + kChunkFrames;
+    while (fN < f_end && !need(fN)) fN += kChunkFrames;
+    const int gN = rg.origin + fN * HOP - NFFT / 2;
     unsigned next_bytes = 0;
     int g_lo = 0, s_lo = 0;
     if (fN < f_end) next_bytes = pair_copy_range(rg, gN, SPAN, L0, g_lo, s_lo);
     if (cur_bytes) { mbar_wait(wc.mbar, wc.parity); wc.parity ^= 1u; }
-    warp_frames_1024<HOP>(a, sm, sl, wc, rg, gA, L0, fA + 1 < f_end, row_shift + fA, own_sums, fA,
+    warp_frames_1024<HOP>(a, sm, sl, wc, rg, gA, L0, fA + 1 < f_end, row_shift + fA, own_sums, fA, floor_db,
                           next_bytes, clip_audio + g_lo, wc.raw + s_lo, bad);
     fA = fN; gA = gN; cur_bytes = next_bytes;
   }
@@ -374,10 +423,10 @@ __device__ __forceinline__ ClipInfo trim_decide(const float* usum, int nu, int L
   return ci;
 }
 
-// ---- C: clamp -> DCT-II -> delta / delta2 -> moment sums for trimmed frames [0, T) (slab rows a0 + t).
-// sD [64][129], sM [64][n16+1] alias the streaming buffers; sDct [128][n16] is resident; acc [6][64] doubles.
-__device__ __forceinline__ void mfcc_phase(const ClipArgs& a, const Slab& sl, int a0, int T, float floor_db, long long out_row0,
-                                           float* sD, const float* sDct, float* sM, double* acc) {
+// ---- C: delta / delta2 (SavGol 9) -> moment sums for trimmed frames [0, T) from the slab's MFCC rows a0 + t.
+// sM [256][n16+1] aliases the streaming buffers; acc [6][64] doubles.
+__device__ __forceinline__ void mfcc_phase(const ClipArgs& a, const Slab& sl, int a0, int T, long long out_row0,
+                                           float* sM, double* acc, uint64_t pol_slab) {
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int mstride = a.n16 + 1;
   for (int i = tid; i < kMoments * kMaxMfcc; i += kClipThreads) acc[i] = 0.0;
@@ -385,32 +434,13 @@ __device__ __forceinline__ void mfcc_phase(const ClipArgs& a, const Slab& sl, in
     const int f_hi = min(f_lo + kStatFrames, T);             // exclusive
     const int e_lo = min(max(f_lo, kStatHalo), T - 1 - kStatHalo) - kStatHalo;
     const int e_hi = min(max(f_hi - 1, kStatHalo), T - 1 - kStatHalo) + kStatHalo;   // inclusive
-    const int ne = e_hi - e_lo + 1;                           // <= 64
-    __syncthreads();   // previous sub-chunk's readers are done with sD / sM
-    for (int e = warp; e < ne; e += kClipWarps) {
-      const float* src = sl.logmel + (size_t)(a0 + e_lo + e) * kNMels;
-#pragma unroll
-      for (int q = 0; q < 4; ++q) sD[e * kDStride + q * 32 + lane] = fmaxf(__ldcg(src + q * 32 + lane), floor_db);
-    }
-    __syncthreads();
-    {  // DCT: thread (frame e = tid & 63, coefficient group g = tid >> 6) computes 4 coefficients at a time
-      const int e = tid & 63;
-      for (int c0 = (tid >> 6) * 4; c0 < a.n16; c0 += 4 * (kClipThreads / 64)) {
-        float acc0 = 0.f, acc1 = 0.f, acc2 = 0.f, acc3 = 0.f;
-        if (e < ne) {
-          const float* drow = sD + e * kDStride;
-#pragma unroll 8
-          for (int m = 0; m < kNMels; ++m) {
-            const float d = drow[m];
-            const float4 w = *reinterpret_cast<const float4*>(sDct + m * a.n16 + c0);
-            acc0 = fmaf(d, w.x, acc0);
-            acc1 = fmaf(d, w.y, acc1);
-            acc2 = fmaf(d, w.z, acc2);
-            acc3 = fmaf(d, w.w, acc3);
-          }
-        }
-        float* mrow = sM + e * mstride + c0;
-        mrow[0] = acc0; mrow[1] = acc1; mrow[2] = acc2; mrow[3] = acc3;
+    const int ne = e_hi - e_lo + 1;                           // <= kStatRows
+    __syncthreads();   // previous sub-chunk's readers are done with sM
+    {
+      const float* src = sl.mfcc + (size_t)(a0 + e_lo) * a.n16;
+      for (int i = tid; i < ne * a.n16; i += kClipThreads) {
+        const int e = i / a.n16, c = i - e * a.n16;
+        sM[e * mstride + c] = ld_slab(src + i, pol_slab);
       }
     }
     __syncthreads();
@@ -451,8 +481,9 @@ __device__ __forceinline__ void mfcc_phase(const ClipArgs& a, const Slab& sl, in
 template <int NFFT, int HOP>
 __global__ void __launch_bounds__(kClipThreads, 1) clip_kernel(ClipArgs a) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
-  // layout: [16 mbarriers 128B][twiddle 8KB][window NFFT*4][acc 6*64 doubles][red 64 doubles][sDct 128*n16 floats]
-  //         [raw tiles 16 x (HOP+NFFT+8) floats][planes 16 x 4224B]   (phase C's sD / sM alias the raw tiles)
+  // layout: [16 mbarriers 128B][twiddle 8KB][window NFFT*4][acc 6*64 doubles][red 64 doubles]
+  //         [sDct 128*(n16+4) floats][mel weights][raw tiles 16 x (HOP+NFFT+8) floats][planes 16 x 4224B]
+  //         (phase C's sM aliases the raw tiles)
   constexpr int RAWW = HOP + NFFT + 8;
   Smem sm;
   sm.mbar = reinterpret_cast<uint64_t*>(smem_raw);
@@ -461,16 +492,19 @@ __global__ void __launch_bounds__(kClipThreads, 1) clip_kernel(ClipArgs a) {
   double* acc = reinterpret_cast<double*>(sm.win + NFFT);
   double* red = acc + kMoments * kMaxMfcc;
   float* sDct = reinterpret_cast<float*>(red + 64);
-  sm.raw = sDct + kNMels * a.n16;
+  const int dstride = a.n16 + 4;
+  float* sMel = sDct + kNMels * dstride;
+  sm.dct = sDct; sm.melw = sMel;
+  sm.raw = sMel + a.mel_floats;
   sm.planes = sm.raw + kClipWarps * RAWW;
-  float* sD = sm.raw;
-  float* sM = sD + kStatRows * kDStride;
+  float* sM = sm.raw;
   __shared__ int s_clip, s_bad;
 
   const int tid = threadIdx.x, warp = tid >> 5;
   for (int i = tid; i < 1024; i += kClipThreads) sm.tw[i] = a.tab.twiddle[i];
   for (int i = tid; i < NFFT; i += kClipThreads) sm.win[i] = a.tab.window_half[i];
-  for (int i = tid; i < kNMels * a.n16; i += kClipThreads) sDct[i] = a.dct_t[i];
+  for (int i = tid; i < kNMels * a.n16; i += kClipThreads) sDct[(i / a.n16) * dstride + (i % a.n16)] = a.dct_t[i];
+  for (int i = tid; i < a.mel_floats; i += kClipThreads) sMel[i] = a.tab.mel_w[i];
   if (tid < kClipWarps) mbar_init(sm.mbar + tid, 1);
   if (tid == 0) fence_mbar_init();
   __syncthreads();
@@ -481,6 +515,8 @@ __global__ void __launch_bounds__(kClipThreads, 1) clip_kernel(ClipArgs a) {
   wc.plane = sm.planes + warp * kPlaneFloats;
   wc.mbar = sm.mbar + warp;
   wc.parity = 0;
+  wc.pol_in = l2_policy_evict_first();
+  wc.pol_slab = l2_policy_evict_last();
   const int hop = HOP;
   const int n = a.n_mfcc;
 
@@ -500,8 +536,10 @@ __global__ void __launch_bounds__(kClipThreads, 1) clip_kernel(ClipArgs a) {
     int a0 = 0;          // slab row of trimmed frame 0
     int head_end = 0;
     int bad = 0;
-    // pass 0: S (speculative, absolute frame grid) or the whole pretrimmed clip; pass 1 / 2: head / tail fix-ups (F)
-    for (int pass = 0; pass < 3; ++pass) {
+    // pass 0: S (speculative, absolute frame grid) or the whole pretrimmed clip; pass 1 / 2: head / tail fix-ups (F);
+    // pass 3: R, redo with the top_db clamp the frames whose log-mel minimum lies below (clip max - top_db)
+    float floor_db = -3.0e38f;
+    for (int pass = 0; pass < 4; ++pass) {
       Region rg{0, 0, L0};
       int fb = 0, fe = 0, shift = 0;
       bool own = false;
@@ -515,17 +553,31 @@ __global__ void __launch_bounds__(kClipThreads, 1) clip_kernel(ClipArgs a) {
           own = true;
         }
       } else {
-        if (a.pretrimmed || ci.status != 0 || !want_frames) break;
+        if (ci.status != 0 || !want_frames) break;
         rg = Region{ci.start, ci.start, ci.end};
-        shift = a0;
+        shift = a0;                // 0 when pretrimmed
         if (pass == 1) {           // frames t with t*hop < n_fft/2 reach in front of the trimmed signal
-          if (ci.start > 0) { head_end = min(ci.n_frames, (NFFT / 2 + hop - 1) / hop); fe = head_end; }
-        } else if (ci.end < L0) {  // frames t with t*hop + n_fft/2 > len reach behind it
-          const int t_tail = (ci.len >= NFFT / 2) ? (ci.len - NFFT / 2) / hop + 1 : 0;
-          fb = max(t_tail, head_end); fe = ci.n_frames;
+          if (!a.pretrimmed && ci.start > 0) { head_end = min(ci.n_frames, (NFFT / 2 + hop - 1) / hop); fe = head_end; }
+        } else if (pass == 2) {
+          if (!a.pretrimmed && ci.end < L0) {       // frames t with t*hop + n_fft/2 > len reach behind it
+            const int t_tail = (ci.len >= NFFT / 2) ? (ci.len - NFFT / 2) / hop + 1 : 0;
+            fb = max(t_tail, head_end); fe = ci.n_frames;
+          }
+        } else {
+          if (!(a.mask & 0x2u)) break;
+          __syncthreads();         // every row's extrema are in the slab
+          float mx = -3.0e38f, mn = 3.0e38f;
+          for (int t = tid; t < ci.n_frames; t += kClipThreads) {
+            mx = fmaxf(mx, __ldcg(sl.rowmax + a0 + t)); mn = fminf(mn, __ldcg(sl.rowmin + a0 + t));
+          }
+          mx = block_max(mx, reinterpret_cast<float*>(red));
+          mn = block_min(mn, reinterpret_cast<float*>(red));
+          floor_db = mx - a.mfcc_top_db;   // power_to_db(top_db): clamp at the clip-global maximum - top_db
+          if (mn >= floor_db) break;       // nothing is clamped: the speculative DCT rows are exact
+          fe = ci.n_frames;
         }
       }
-      stream_frames<NFFT, HOP>(a, sm, sl, wc, clip_audio, L0, rg, fb, fe, shift, own, bad);
+      stream_frames<NFFT, HOP>(a, sm, sl, wc, clip_audio, L0, rg, fb, fe, shift, own, floor_db, pass == 3, bad);
       if (pass == 0 && !a.pretrimmed) {
         if (bad) s_bad = 1;
         __syncthreads();
@@ -548,11 +600,8 @@ __global__ void __launch_bounds__(kClipThreads, 1) clip_kernel(ClipArgs a) {
     const double invT = 1.0 / (double)T;
 
     if (a.mask & 0x2u) {
-      // ---- C: power_to_db(top_db): clamp at the clip-global maximum - top_db
-      float mx = -3.0e38f;
-      for (int t = tid; t < T; t += kClipThreads) mx = fmaxf(mx, __ldcg(sl.rowmax + a0 + t));
-      mx = block_max(mx, reinterpret_cast<float*>(red));
-      mfcc_phase(a, sl, a0, T, mx - a.mfcc_top_db, out_row0, sD, sDct, sM, acc);
+      // ---- C
+      mfcc_phase(a, sl, a0, T, out_row0, sM, acc, wc.pol_slab);
       if (tid < n) {
         const double s1 = acc[tid], s2 = acc[kMaxMfcc + tid], s3 = acc[2 * kMaxMfcc + tid], s4 = acc[3 * kMaxMfcc + tid];
         const double mean = s1 * invT;

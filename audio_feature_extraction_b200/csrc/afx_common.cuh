@@ -13,7 +13,7 @@ constexpr int kMaxMfcc = 64;
 
 constexpr int kFramesPerChunk = 16;    // frames one CTA iteration of the frames kernel covers (8 warps x 2)
 constexpr int kFramesWarps = 8;
-constexpr int kStatFrames = 56;        // frames per CTA of the mfcc/delta/statistics kernel (+8 halo = 64)
+constexpr int kStatFrames = 248;       // frames per sub-chunk of the delta/statistics phase (+8 halo = 256)
 constexpr int kStatHalo = 4;
 
 // per-clip record produced by the trim kernel and consumed by everything after it
@@ -97,6 +97,31 @@ __device__ __forceinline__ void fence_proxy_async() {
 __device__ __forceinline__ void tma_load_1d(void* smem_dst, const void* gsrc, unsigned bytes, uint64_t* bar) {
   asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
                ::"r"(smem_u32(smem_dst)), "l"(gsrc), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+
+// ---- L2 eviction-priority hints: the input stream is read once (evict_first), the per-CTA scratch slab is
+// rewritten clip after clip and must stay resident (evict_last)
+__device__ __forceinline__ uint64_t l2_policy_evict_first() {
+  uint64_t p;
+  asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(p));
+  return p;
+}
+__device__ __forceinline__ uint64_t l2_policy_evict_last() {
+  uint64_t p;
+  asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(p));
+  return p;
+}
+__device__ __forceinline__ void tma_load_1d_hint(void* smem_dst, const void* gsrc, unsigned bytes, uint64_t* bar, uint64_t policy) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;"
+               ::"r"(smem_u32(smem_dst)), "l"(gsrc), "r"(bytes), "r"(smem_u32(bar)), "l"(policy) : "memory");
+}
+__device__ __forceinline__ void st_slab(float* p, float v, uint64_t policy) {
+  asm volatile("st.global.L2::cache_hint.f32 [%0], %1, %2;" ::"l"(p), "f"(v), "l"(policy) : "memory");
+}
+__device__ __forceinline__ float ld_slab(const float* p, uint64_t policy) {
+  float v;
+  asm volatile("ld.global.L2::cache_hint.f32 %0, [%1], %2;" : "=f"(v) : "l"(p), "l"(policy) : "memory");
+  return v;
 }
 
 }  // namespace afx

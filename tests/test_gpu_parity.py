@@ -68,6 +68,29 @@ def test_c2_config_framewise_and_summary_parity(torch_cuda):
         _check_clip(ex, ora, y, summ[i], meta[i], frames, rows[i], ex.n_mfcc)
 
 
+def test_top_db_clamp_redo_pass(torch_cuda):
+    """Clips whose log-mel range exceeds 80 dB inside the trimmed region: power_to_db(top_db=80) clamps, so the
+    speculative (unclamped) DCT rows must be redone with the clip-global floor (core/feature_extractor.py:127-134)."""
+    from audio_feature_extraction_b200 import AudioFeatureExtractor
+    from audio_feature_extraction_b200.synth import make_clip
+    from oracle import OracleFeatureExtractor
+
+    rng = np.random.default_rng(5)
+    a, b = make_clip(60, seconds=1.5), make_clip(61, seconds=2.0)
+    hush = (1e-6 * rng.standard_normal(15000)).astype(np.float32)          # ~ -120 dBFS gap, kept by the trim
+    digital_silence = np.zeros(9000, dtype=np.float32)                     # exact zeros -> amin floor, clamped
+    tone = (0.5 * np.sin(2 * np.pi * 440.0 * np.arange(44100) / 22050.0)).astype(np.float32)   # pure tone: empty bins
+    clips = [np.concatenate([a, hush, b]), np.concatenate([b, digital_silence, a]), tone, make_clip(62, seconds=1.0)]
+    ex = AudioFeatureExtractor()
+    ora = OracleFeatureExtractor()
+    for y in clips[:3]:   # the oracle really clamps on these
+        _, D = __import__("oracle").mfcc(ora.preprocess_audio(y), sr=22050, n_mfcc=13, n_fft=1024, hop_length=256, return_logmel=True)
+        assert D.min() == pytest.approx(D.max() - 80.0, abs=1e-4)
+    summ, meta, frames, rows = _framewise(ex, clips)
+    for i, y in enumerate(clips):
+        _check_clip(ex, ora, y, summ[i], meta[i], frames, rows[i], ex.n_mfcc)
+
+
 def test_extended_statistics_match_scipy(torch_cuda):
     from audio_feature_extraction_b200 import AudioFeatureExtractor
     from audio_feature_extraction_b200.synth import make_clip
