@@ -56,6 +56,8 @@ cudaError_t upload(const std::vector<T>& v, T** dptr) {
 struct afx_handle_s {
   afx_config_t cfg;
   int n16;                 // n_mfcc rounded up to a multiple of 16 (the in-pass DCT works on groups of 16)
+  int clip_warps = 16;     // warps per CTA of the fused kernel
+  int ctas_per_sm = 1;
   int mel_floats = 0;      // floats in the padded sparse mel weight table
   int sm_count;
   void (*clip_fn)(afx::ClipArgs) = nullptr;   // clip_kernel<frame_length, hop_length>
@@ -134,7 +136,7 @@ size_t slab_bytes_for(const afx_handle_s* h, long long max_len) {
   const size_t rows = (size_t)slab_rows(h, max_len);
   return align_up((rows * ((size_t)h->n16 + 4) + 8) * sizeof(float), 256);   // MFCC rows, rms, row max / min, hop-block sums
 }
-inline int grid_for(const afx_handle_s* h, long long n_clips) { return (int)std::max<long long>(1, std::min<long long>(n_clips, h->sm_count)); }
+inline int grid_for(const afx_handle_s* h, long long n_clips) { return (int)std::max<long long>(1, std::min<long long>(n_clips, (long long)h->sm_count * h->ctas_per_sm)); }
 
 // the speculative single pass needs every trimmed frame centre (start = k*512) on the absolute hop grid
 inline bool single_pass(const afx_handle_s* h) { return afx::kTrimHop % h->cfg.hop_length == 0 && h->cfg.hop_length >= 16; }
@@ -155,7 +157,7 @@ size_t clip_smem_bytes(const afx_handle_s* h, int* tile_floats_out) {
   if (tile_floats_out) *tile_floats_out = tile_floats;
   return 128 + 8192 + (size_t)h->cfg.frame_length * 4 + (size_t)(afx::kMoments * afx::kMaxMfcc + 64) * 8 +
          (size_t)afx::kNMels * (h->n16 + 4) * 4 + (size_t)h->mel_floats * 4 +
-         (size_t)afx::kClipWarps * (tile_floats + afx::kPlaneFloats) * 4;
+         (size_t)h->clip_warps * (tile_floats + afx::kPlaneFloats) * 4;
 }
 
 }  // namespace
@@ -231,6 +233,11 @@ int afx_create(const afx_config_t* cfg, afx_handle_t* out) {
 
   CUDA_TRY(cudaFuncSetAttribute(afx::trim_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
   h->clip_fn = clip_kernel_for(cfg->frame_length, cfg->hop_length);
+  // two 8-warp CTAs per SM (one clip each: the serial trim / fix-up / statistics phases of one hide behind the
+  // streaming phase of the other) when their shared memory fits twice; else one 16-warp CTA
+  h->clip_warps = 8; h->ctas_per_sm = 2;
+  if (2 * (clip_smem_bytes(h, nullptr) + 1024) > (size_t)prop.sharedMemPerMultiprocessor) { h->clip_warps = 16; h->ctas_per_sm = 1; }
+  if (const char* e = getenv("AFX_CLIP_WARPS")) { if (atoi(e) == 16) { h->clip_warps = 16; h->ctas_per_sm = 1; } }
   CUDA_TRY(cudaFuncSetAttribute(h->clip_fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)clip_smem_bytes(h, nullptr)));
   CUDA_TRY(cudaEventCreateWithFlags(&h->stage_ev, cudaEventDisableTiming));
   *out = h;
@@ -354,7 +361,7 @@ int afx_extract(afx_handle_t h, const float* d_audio, const int64_t* h_offsets, 
     ca.mask = feature_mask; ca.summaries = d_summaries; ca.meta = d_meta; ca.frames_out = d_frames;
     ca.pretrimmed = one_pass ? 0 : 1;
     PhaseTimer pt(h, stream, AFX_PHASE_FRAMES);
-    h->clip_fn<<<grid, afx::kClipThreads, smem, stream>>>(ca);
+    h->clip_fn<<<grid, h->clip_warps * 32, smem, stream>>>(ca);
     ++g_launches;
   }
   CUDA_TRY(cudaGetLastError());

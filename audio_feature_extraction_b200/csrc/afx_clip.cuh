@@ -29,12 +29,10 @@
 
 namespace afx {
 
-constexpr int kClipWarps = 16;
-constexpr int kClipThreads = kClipWarps * 32;
-constexpr int kChunkFrames = 2 * kClipWarps;     // frames per streaming step
+constexpr int kMaxClipWarps = 16;                // CTA = 8 warps (two CTAs per SM) or 16 warps (one per SM), chosen by the host
+constexpr int kMaxClipThreads = kMaxClipWarps * 32;
 constexpr int kTilePad = 4;                      // floats in front of the first frame sample inside the tile
 constexpr int kPlaneFloats = 32 * 33;
-constexpr int kStatThreads = kClipThreads;
 constexpr int kStatRows = kStatFrames + 2 * kStatHalo;   // frames per sub-chunk incl. halo
 constexpr int kMoments = 6;                               // sum x, x^2, x^3, x^4, sum delta, sum delta2
 
@@ -303,7 +301,7 @@ __device__ __forceinline__ void stream_frames(const ClipArgs& a, const Smem& sm,
     return m < floor_db;
   };
   int fA = f_begin + 2 * warp;
-  while (fA < f_end && !need(fA)) fA += kChunkFrames;
+  while (fA < f_end && !need(fA)) fA += (int)(blockDim.x >> 4);
   if (fA >= f_end) return;
   int gA = rg.origin + fA * HOP - NFFT / 2;
   unsigned cur_bytes;
@@ -317,8 +315,8 @@ __device__ __forceinline__ void stream_frames(const ClipArgs& a, const Smem& sm,
     }
   }
   while (fA < f_end) {
-    int fN = fA + kChunkFrames;
-    while (fN < f_end && !need(fN)) fN += kChunkFrames;
+    int fN = fA + (int)(blockDim.x >> 4);
+    while (fN < f_end && !need(fN)) fN += (int)(blockDim.x >> 4);
     const int gN = rg.origin + fN * HOP - NFFT / 2;
     unsigned next_bytes = 0;
     int g_lo = 0, s_lo = 0;
@@ -330,7 +328,7 @@ __device__ __forceinline__ void stream_frames(const ClipArgs& a, const Smem& sm,
   }
 }
 
-// ---- block-wide helpers (all kClipThreads threads call them; red = shared scratch of >= 64 doubles)
+// ---- block-wide helpers (all (int)blockDim.x threads call them; red = shared scratch of >= 64 doubles)
 __device__ __forceinline__ float block_max(float v, float* red) {
   v = warp_max(v);
   __syncthreads();
@@ -338,7 +336,7 @@ __device__ __forceinline__ float block_max(float v, float* red) {
   __syncthreads();
   float t = red[0];
 #pragma unroll
-  for (int w = 1; w < kClipWarps; ++w) t = fmaxf(t, red[w]);
+  for (int w = 1; w < (int)(blockDim.x >> 5); ++w) t = fmaxf(t, red[w]);
   return t;
 }
 __device__ __forceinline__ float block_min(float v, float* red) {
@@ -348,7 +346,7 @@ __device__ __forceinline__ float block_min(float v, float* red) {
   __syncthreads();
   float t = red[0];
 #pragma unroll
-  for (int w = 1; w < kClipWarps; ++w) t = fminf(t, red[w]);
+  for (int w = 1; w < (int)(blockDim.x >> 5); ++w) t = fminf(t, red[w]);
   return t;
 }
 __device__ __forceinline__ double block_sum(double v, double* red) {
@@ -358,7 +356,7 @@ __device__ __forceinline__ double block_sum(double v, double* red) {
   __syncthreads();
   double t = 0;
 #pragma unroll
-  for (int w = 0; w < kClipWarps; ++w) t += red[w];
+  for (int w = 0; w < (int)(blockDim.x >> 5); ++w) t += red[w];
   return t;
 }
 
@@ -379,7 +377,7 @@ __device__ __forceinline__ ClipInfo trim_decide(const float* usum, int nu, int L
   const int nb = (L0 + kTrimHop - 1) / kTrimHop;
   const int R = kTrimHop / hop;
   float mx = 0.f;
-  for (int i = tid; i < n_rms; i += kClipThreads) {
+  for (int i = tid; i < n_rms; i += (int)blockDim.x) {
     // frame i covers blocks i-2 .. i+1
     const float s = (trim_block(usum, i - 2, nb, R, nu) + trim_block(usum, i - 1, nb, R, nu)) +
                     (trim_block(usum, i, nb, R, nu) + trim_block(usum, i + 1, nb, R, nu));
@@ -388,7 +386,7 @@ __device__ __forceinline__ ClipInfo trim_decide(const float* usum, int nu, int L
   mx = block_max(mx, red_f);
   const float ref_db = 10.0f * log10f(fmaxf(1e-10f, mx * mx));
   int first = 0x7fffffff, last = -1;
-  for (int i = tid; i < n_rms; i += kClipThreads) {
+  for (int i = tid; i < n_rms; i += (int)blockDim.x) {
     const float s = (trim_block(usum, i - 2, nb, R, nu) + trim_block(usum, i - 1, nb, R, nu)) +
                     (trim_block(usum, i, nb, R, nu) + trim_block(usum, i + 1, nb, R, nu));
     const float r = sqrtf(s * (1.0f / kTrimFrame));
@@ -402,10 +400,10 @@ __device__ __forceinline__ ClipInfo trim_decide(const float* usum, int nu, int L
     last = max(last, __shfl_xor_sync(0xffffffffu, last, o));
   }
   __syncthreads();
-  if (lane == 0) { red_i[warp] = first; red_i[kClipWarps + warp] = last; }
+  if (lane == 0) { red_i[warp] = first; red_i[kMaxClipWarps + warp] = last; }
   __syncthreads();
 #pragma unroll
-  for (int w = 0; w < kClipWarps; ++w) { first = min(first, red_i[w]); last = max(last, red_i[kClipWarps + w]); }
+  for (int w = 0; w < (int)(blockDim.x >> 5); ++w) { first = min(first, red_i[w]); last = max(last, red_i[kMaxClipWarps + w]); }
   ClipInfo ci;
   ci.start = 0; ci.end = 0; ci.len = 0; ci.n_frames = 0; ci.max_key = 0u; ci.pad0 = ci.pad1 = 0; ci.status = 0;
   if (L0 <= 0) ci.status = 1;                 // AFX_CLIP_EMPTY
@@ -429,7 +427,7 @@ __device__ __forceinline__ void mfcc_phase(const ClipArgs& a, const Slab& sl, in
                                            float* sM, double* acc, uint64_t pol_slab) {
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int mstride = a.n16 + 1;
-  for (int i = tid; i < kMoments * kMaxMfcc; i += kClipThreads) acc[i] = 0.0;
+  for (int i = tid; i < kMoments * kMaxMfcc; i += (int)blockDim.x) acc[i] = 0.0;
   for (int f_lo = 0; f_lo < T; f_lo += kStatFrames) {
     const int f_hi = min(f_lo + kStatFrames, T);             // exclusive
     const int e_lo = min(max(f_lo, kStatHalo), T - 1 - kStatHalo) - kStatHalo;
@@ -438,14 +436,14 @@ __device__ __forceinline__ void mfcc_phase(const ClipArgs& a, const Slab& sl, in
     __syncthreads();   // previous sub-chunk's readers are done with sM
     {
       const float* src = sl.mfcc + (size_t)(a0 + e_lo) * a.n16;
-      for (int i = tid; i < ne * a.n16; i += kClipThreads) {
+      for (int i = tid; i < ne * a.n16; i += (int)blockDim.x) {
         const int e = i / a.n16, c = i - e * a.n16;
         sM[e * mstride + c] = ld_slab(src + i, pol_slab);
       }
     }
     __syncthreads();
     // deltas + moments: warp w handles coefficients w, w+16, ...; lanes stride over the sub-chunk's frames
-    for (int c = warp; c < a.n_mfcc; c += kClipWarps) {
+    for (int c = warp; c < a.n_mfcc; c += (int)(blockDim.x >> 5)) {
       double s1 = 0, s2 = 0, s3 = 0, s4 = 0, sd1 = 0, sd2 = 0;
       for (int f = f_lo + lane; f < f_hi; f += 32) {
         const int te = min(max(f, kStatHalo), T - 1 - kStatHalo) - e_lo;   // centre row of the 9-tap window
@@ -479,7 +477,7 @@ __device__ __forceinline__ void mfcc_phase(const ClipArgs& a, const Slab& sl, in
 
 // ---- the kernel
 template <int NFFT, int HOP>
-__global__ void __launch_bounds__(kClipThreads, 1) clip_kernel(ClipArgs a) {
+__global__ void __launch_bounds__(kMaxClipThreads, 1) clip_kernel(ClipArgs a) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   // layout: [16 mbarriers 128B][twiddle 8KB][window NFFT*4][acc 6*64 doubles][red 64 doubles]
   //         [sDct 128*(n16+4) floats][mel weights][raw tiles 16 x (HOP+NFFT+8) floats][planes 16 x 4224B]
@@ -496,16 +494,16 @@ __global__ void __launch_bounds__(kClipThreads, 1) clip_kernel(ClipArgs a) {
   float* sMel = sDct + kNMels * dstride;
   sm.dct = sDct; sm.melw = sMel;
   sm.raw = sMel + a.mel_floats;
-  sm.planes = sm.raw + kClipWarps * RAWW;
+  sm.planes = sm.raw + (blockDim.x >> 5) * RAWW;
   float* sM = sm.raw;
   __shared__ int s_clip, s_bad;
 
   const int tid = threadIdx.x, warp = tid >> 5;
-  for (int i = tid; i < 1024; i += kClipThreads) sm.tw[i] = a.tab.twiddle[i];
-  for (int i = tid; i < NFFT; i += kClipThreads) sm.win[i] = a.tab.window_half[i];
-  for (int i = tid; i < kNMels * a.n16; i += kClipThreads) sDct[(i / a.n16) * dstride + (i % a.n16)] = a.dct_t[i];
-  for (int i = tid; i < a.mel_floats; i += kClipThreads) sMel[i] = a.tab.mel_w[i];
-  if (tid < kClipWarps) mbar_init(sm.mbar + tid, 1);
+  for (int i = tid; i < 1024; i += (int)blockDim.x) sm.tw[i] = a.tab.twiddle[i];
+  for (int i = tid; i < NFFT; i += (int)blockDim.x) sm.win[i] = a.tab.window_half[i];
+  for (int i = tid; i < kNMels * a.n16; i += (int)blockDim.x) sDct[(i / a.n16) * dstride + (i % a.n16)] = a.dct_t[i];
+  for (int i = tid; i < a.mel_floats; i += (int)blockDim.x) sMel[i] = a.tab.mel_w[i];
+  if (tid < kMaxClipWarps) mbar_init(sm.mbar + tid, 1);
   if (tid == 0) fence_mbar_init();
   __syncthreads();
 
@@ -567,7 +565,7 @@ __global__ void __launch_bounds__(kClipThreads, 1) clip_kernel(ClipArgs a) {
           if (!(a.mask & 0x2u)) break;
           __syncthreads();         // every row's extrema are in the slab
           float mx = -3.0e38f, mn = 3.0e38f;
-          for (int t = tid; t < ci.n_frames; t += kClipThreads) {
+          for (int t = tid; t < ci.n_frames; t += (int)blockDim.x) {
             mx = fmaxf(mx, __ldcg(sl.rowmax + a0 + t)); mn = fminf(mn, __ldcg(sl.rowmin + a0 + t));
           }
           mx = block_max(mx, reinterpret_cast<float*>(red));
@@ -594,7 +592,7 @@ __global__ void __launch_bounds__(kClipThreads, 1) clip_kernel(ClipArgs a) {
       m[0] = ci.status; m[1] = ci.start; m[2] = ci.end; m[3] = ci.n_frames;
     }
     float* out = a.summaries + (size_t)clip * a.summary_width;
-    for (int i = tid; i < a.summary_width; i += kClipThreads) out[i] = 0.f;
+    for (int i = tid; i < a.summary_width; i += (int)blockDim.x) out[i] = 0.f;
     const int T = ci.n_frames;
     if (T <= 0) continue;   // status != OK: summary row stays zero (uniform branch)
     const double invT = 1.0 / (double)T;
@@ -620,7 +618,7 @@ __global__ void __launch_bounds__(kClipThreads, 1) clip_kernel(ClipArgs a) {
     if (a.mask & 0x4u) {   // RMS energy statistics (core/feature_extractor.py:171-173)
       double s1 = 0, s2 = 0, s3 = 0, s4 = 0;
       float mn = 3.0e38f, mx = -3.0e38f;
-      for (int t = tid; t < T; t += kClipThreads) {
+      for (int t = tid; t < T; t += (int)blockDim.x) {
         const float rf = __ldcg(sl.rms + a0 + t);
         const double r = rf;
         s1 += r; s2 += r * r; s3 += r * r * r; s4 += (r * r) * (r * r);
