@@ -64,6 +64,7 @@ struct afx_handle_s {
   // device tables
   float* d_window = nullptr;
   float* d_twiddle = nullptr;
+  float* d_ptw = nullptr;
   float* d_mel_w = nullptr;
   int* d_mel_k0 = nullptr;
   float* d_dct_t = nullptr;
@@ -148,14 +149,24 @@ clip_fn_t clip_kernel_for(int n_fft, int hop) {
     if (hop == 512) return afx::clip_kernel<1024, 512>;
     if (hop == 256) return afx::clip_kernel<1024, 256>;
     if (hop == 128) return afx::clip_kernel<1024, 128>;
+  } else if (n_fft == 512) {
+    if (hop == 256) return afx::clip_kernel<512, 256>;
+    if (hop == 128) return afx::clip_kernel<512, 128>;
+    if (hop == 64) return afx::clip_kernel<512, 64>;
+  } else if (n_fft == 2048) {
+    if (hop == 1024) return afx::clip_kernel<2048, 1024>;
+    if (hop == 512) return afx::clip_kernel<2048, 512>;
+    if (hop == 256) return afx::clip_kernel<2048, 256>;
   }
   return nullptr;
 }
 
 size_t clip_smem_bytes(const afx_handle_s* h, int* tile_floats_out) {
-  const int tile_floats = h->cfg.hop_length + h->cfg.frame_length + 8;   // per-warp raw tile
+  const int n_fft = h->cfg.frame_length;
+  const int fpw = n_fft == 2048 ? 1 : (n_fft == 1024 ? 2 : 4);           // afx::Geo<>::FPW
+  const int tile_floats = (fpw - 1) * h->cfg.hop_length + n_fft + 8;     // per-warp raw tile, afx::Geo<>::RAWW
   if (tile_floats_out) *tile_floats_out = tile_floats;
-  return 128 + 8192 + (size_t)h->cfg.frame_length * 4 + (size_t)(afx::kMoments * afx::kMaxMfcc + 64) * 8 +
+  return 128 + 8192 + (n_fft == 2048 ? 4112 : 0) + (size_t)n_fft * 4 + (size_t)(afx::kMoments * afx::kMaxMfcc + 64) * 8 +
          (size_t)afx::kNMels * (h->n16 + 4) * 4 + (size_t)h->mel_floats * 4 +
          (size_t)h->clip_warps * (tile_floats + afx::kPlaneFloats) * 4;
 }
@@ -186,8 +197,8 @@ void afx_config_default(afx_config_t* cfg) {
 
 int afx_create(const afx_config_t* cfg, afx_handle_t* out) {
   if (!cfg || !out) return fail(AFX_ERR_INVALID_ARG, "afx_create: null argument");
-  if (cfg->frame_length != 1024)
-    return fail(AFX_ERR_UNSUPPORTED, "frame_length %d not supported (1024 only in this build)", cfg->frame_length);
+  if (cfg->frame_length != 512 && cfg->frame_length != 1024 && cfg->frame_length != 2048)
+    return fail(AFX_ERR_UNSUPPORTED, "frame_length %d not supported (512, 1024 or 2048)", cfg->frame_length);
   if (cfg->hop_length < 1 || cfg->hop_length > cfg->frame_length / 2)
     return fail(AFX_ERR_INVALID_ARG, "hop_length %d out of range [1, frame_length/2]", cfg->hop_length);
   if (!clip_kernel_for(cfg->frame_length, cfg->hop_length))
@@ -211,7 +222,8 @@ int afx_create(const afx_config_t* cfg, afx_handle_t* out) {
   h->sm_count = prop.multiProcessorCount;
 
   const auto win = afx::host::window_half(cfg->frame_length);
-  const auto tw = afx::host::twiddle32x32(1024);
+  const auto tw = afx::host::twiddle32x32(cfg->frame_length == 512 ? 512 : 1024);
+  const auto ptw = afx::host::post_twiddle(2048, 513);
   const auto mel = afx::host::mel_sparse(cfg->sr, cfg->frame_length, cfg->n_mels);
   const auto dct = afx::host::dct_rows(cfg->n_mfcc, cfg->n_mels);
   std::vector<float> dct_t((size_t)cfg->n_mels * h->n16, 0.f);
@@ -219,13 +231,14 @@ int afx_create(const afx_config_t* cfg, afx_handle_t* out) {
     for (int m = 0; m < cfg->n_mels; ++m) dct_t[(size_t)m * h->n16 + c] = dct[(size_t)c * cfg->n_mels + m];
   CUDA_TRY(upload(win, &h->d_window));
   CUDA_TRY(upload(tw, &h->d_twiddle));
+  CUDA_TRY(upload(ptw, &h->d_ptw));
   h->mel_floats = (int)mel.w.size();
   CUDA_TRY(upload(mel.w, &h->d_mel_w));
   CUDA_TRY(upload(mel.k0, &h->d_mel_k0));
   CUDA_TRY(upload(dct_t, &h->d_dct_t));
   h->tab.window_half = h->d_window;
   h->tab.twiddle = reinterpret_cast<const float2*>(h->d_twiddle);
-  h->tab.post_twiddle = nullptr;
+  h->tab.post_twiddle = reinterpret_cast<const float2*>(h->d_ptw);
   h->tab.mel_w = h->d_mel_w;
   h->tab.mel_k0 = h->d_mel_k0;
   for (int q = 0; q < 4; ++q) { h->tab.mel_cnt[q] = mel.cnt[q]; h->tab.mel_woff[q] = mel.woff[q]; }
@@ -235,9 +248,18 @@ int afx_create(const afx_config_t* cfg, afx_handle_t* out) {
   h->clip_fn = clip_kernel_for(cfg->frame_length, cfg->hop_length);
   // two 8-warp CTAs per SM (one clip each: the serial trim / fix-up / statistics phases of one hide behind the
   // streaming phase of the other) when their shared memory fits twice; else one 16-warp CTA
-  h->clip_warps = 8; h->ctas_per_sm = 2;
-  if (2 * (clip_smem_bytes(h, nullptr) + 1024) > (size_t)prop.sharedMemPerMultiprocessor) { h->clip_warps = 16; h->ctas_per_sm = 1; }
-  if (const char* e = getenv("AFX_CLIP_WARPS")) { if (atoi(e) == 16) { h->clip_warps = 16; h->ctas_per_sm = 1; } }
+  {
+    const int cand[4][2] = {{8, 2}, {16, 1}, {12, 1}, {8, 1}};
+    bool found = false;
+    const char* e = getenv("AFX_CLIP_WARPS");
+    for (int c = 0; c < 4 && !found; ++c) {
+      h->clip_warps = cand[c][0]; h->ctas_per_sm = cand[c][1];
+      if (e && atoi(e) != h->clip_warps) continue;
+      const size_t need = clip_smem_bytes(h, nullptr) + 1024;   // + the per-CTA reserve
+      found = need * h->ctas_per_sm <= (size_t)prop.sharedMemPerMultiprocessor && need - 1024 <= (size_t)prop.sharedMemPerBlockOptin;
+    }
+    if (!found) { delete h; return fail(AFX_ERR_UNSUPPORTED, "no CTA shape of the fused kernel fits this device's shared memory"); }
+  }
   CUDA_TRY(cudaFuncSetAttribute(h->clip_fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)clip_smem_bytes(h, nullptr)));
   CUDA_TRY(cudaEventCreateWithFlags(&h->stage_ev, cudaEventDisableTiming));
   *out = h;
@@ -248,7 +270,7 @@ int afx_destroy(afx_handle_t h) {
   if (!h) return AFX_OK;
   cudaSetDevice(h->cfg.device);
   cudaDeviceSynchronize();
-  cudaFree(h->d_window); cudaFree(h->d_twiddle); cudaFree(h->d_mel_w); cudaFree(h->d_mel_k0); cudaFree(h->d_dct_t);
+  cudaFree(h->d_window); cudaFree(h->d_twiddle); cudaFree(h->d_ptw); cudaFree(h->d_mel_w); cudaFree(h->d_mel_k0); cudaFree(h->d_dct_t);
   if (h->h_stage) cudaFreeHost(h->h_stage);
   if (h->stage_ev) cudaEventDestroy(h->stage_ev);
   cudaFree(h->d_ws); cudaFree(h->d_audio[0]); cudaFree(h->d_audio[1]); cudaFree(h->d_sum); cudaFree(h->d_meta);

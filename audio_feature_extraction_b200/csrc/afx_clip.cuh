@@ -24,78 +24,18 @@
 // (`pretrimmed`), skipping T and F.
 #pragma once
 #include "afx_common.cuh"
-#include "fft_gen.cuh"
 #include "afx_trim.cuh"
+#include "afx_warp.cuh"
 
 namespace afx {
 
 constexpr int kMaxClipWarps = 16;                // CTA = 8 warps (two CTAs per SM) or 16 warps (one per SM), chosen by the host
 constexpr int kMaxClipThreads = kMaxClipWarps * 32;
-constexpr int kTilePad = 4;                      // floats in front of the first frame sample inside the tile
-constexpr int kPlaneFloats = 32 * 33;
 constexpr int kStatRows = kStatFrames + 2 * kStatHalo;   // frames per sub-chunk incl. halo
 constexpr int kMoments = 6;                               // sum x, x^2, x^3, x^4, sum delta, sum delta2
 
-struct ClipArgs {
-  const float* audio;
-  const long long* offsets;     // device [n_clips] sample offsets
-  const int* lengths;           // device [n_clips]
-  const long long* frame_off;   // device [n_clips + 1] prefix of 1 + len/hop (rows of frames_out)
-  ClipInfo* info;               // [n_clips]: input when pretrimmed, always written back
-  int* counter;                 // work counter (zeroed before launch)
-  int n_clips;
-  char* slabs;                  // per-CTA scratch
-  size_t slab_bytes;
-  int a_max;                    // frame rows per slab (multiple of 4)
-  Tables tab;
-  const float* dct_t;           // [128][n16]
-  int hop;
-  int mel_floats;               // floats in Tables::mel_w (multiple of 4)
-  float coef, trim_top_db, mfcc_top_db;
-  int n_mfcc, n16, summary_width, frame_width;
-  unsigned mask;                // AFX_FEAT_*
-  float* summaries;             // [n_clips][SS]
-  int* meta;                    // [n_clips][4]
-  float* frames_out;            // nullable
-  int pretrimmed;
-};
-
-struct Slab {
-  float* mfcc;     // [a_max][n16] DCT rows (speculative: no top_db clamp; rewritten by the redo pass where it bites)
-  float* rms;      // [a_max]
-  float* rowmax;   // [a_max] per-frame max of the unclamped log-mel row
-  float* rowmin;   // [a_max] per-frame min
-  float* blk;      // [rows + 2] sums of squares of the hop-sized blocks [u*hop, (u+1)*hop) of the pre-emphasised clip
-};
-
-__device__ __forceinline__ Slab carve_slab(const ClipArgs& a, int cta) {
-  Slab s;
-  char* p = a.slabs + (size_t)cta * a.slab_bytes;
-  s.mfcc = reinterpret_cast<float*>(p);
-  s.rms = s.mfcc + (size_t)a.a_max * a.n16;
-  s.rowmax = s.rms + a.a_max;
-  s.rowmin = s.rowmax + a.a_max;
-  s.blk = s.rowmin + a.a_max;
-  return s;
-}
-
-// shared-memory carve-up of the streaming phase (phase C aliases everything after the tables)
-struct Smem {
-  uint64_t* mbar;  // [16] one TMA barrier per warp
-  float2* tw;      // [1024]
-  float* win;      // [NFFT]
-  const float* dct;   // [128][n16 + 4] DCT-II rows, transposed, padded stride (conflict-free float4 reads)
-  const float* melw;  // copy of Tables::mel_w
-  float* raw;      // [16][HOP + NFFT + 8] per-warp raw-sample tiles
-  float* planes;   // [16][32*33]
-};
-
-// where a streaming step reads: frames f (relative to `origin`) cover origin + f*hop - n_fft/2 + [0, n_fft),
-// samples outside [lo, hi) count as zero (librosa centre padding of the trimmed signal)
-struct Region { int origin, lo, hi; };
-
-// raw sample range a frame pair starting at frame fA needs; tile position p holds absolute sample gA - 4 + p,
-// gA = origin + fA*hop - n_fft/2.  Returns the bytes to copy (0: nothing of the pair lies inside [lo, hi)).
+// raw sample range a warp step starting at absolute sample gA needs; tile position p holds sample gA - 4 + p.
+// Returns the bytes to copy (0: nothing of the step lies inside [lo, hi)).
 __device__ __forceinline__ unsigned pair_copy_range(const Region& rg, int gA, int span, int L0, int& g_lo, int& s_lo) {
   const int lo = max(rg.lo, gA), hi = min(rg.hi, gA + span);
   if (hi <= lo) return 0u;
@@ -103,185 +43,6 @@ __device__ __forceinline__ unsigned pair_copy_range(const Region& rg, int gA, in
   const int g_hi4 = (min(hi, L0) + 3) & ~3;
   s_lo = g_lo - gA + 4;                                             // multiple of 4, >= 0
   return (unsigned)(g_hi4 - g_lo) * 4u;
-}
-
-// per-warp state of the streaming pass
-struct WarpCtx {
-  float* raw;        // [HOP + NFFT + 8] this warp's raw-sample tile (TMA destination)
-  float* plane;      // [32*33] transpose scratch / power spectrum
-  uint64_t* mbar;    // this warp's TMA barrier
-  unsigned parity;
-  uint64_t pol_in;   // L2 policy of the audio stream (evict_first)
-  uint64_t pol_slab; // L2 policy of the scratch slab (evict_last)
-};
-
-// ---- one warp: two real frames fA, fA + 1 -> log-mel rows row, row + 1 of the slab, RMS, row maxima, and (own_sums)
-// the sums of squares of the two hop-sized blocks [fA*hop, fA*hop + 2 hop) of the pre-emphasised signal.
-// n_fft = 1024: the two frames ride the real and imaginary lanes of one complex 1024-point FFT held in registers
-// (32 complex values per lane): 32-point FFT, twiddle, transpose through shared memory, 32-point FFT.
-// Pre-emphasis is applied while the samples are loaded (frame B's values are frame A's shifted by HOP/32 rows).
-// next_bytes/next_src/next_dst: the warp's next tile, issued as soon as this one sits in registers.
-template <int HOP>
-__device__ __forceinline__ void warp_frames_1024(const ClipArgs& a, const Smem& sm, const Slab& sl, WarpCtx& wc, const Region& rg,
-                                                 int gA, int L0, bool vB, int row, bool own_sums, int usum_idx, float floor_db,
-                                                 unsigned next_bytes, const float* next_src, float* next_dst, int& bad) {
-  constexpr int NFFT = 1024;
-  constexpr int SH = HOP / 32;            // rows by which frame B trails frame A
-  constexpr int NG = NFFT / HOP + 1;      // hop-sized groups the pair spans
-  const int lane = threadIdx.x & 31;
-  float r[32], im[32];
-  float eg[NG];
-#pragma unroll
-  for (int g = 0; g < NG; ++g) eg[g] = 0.f;
-  const float* rp = wc.raw + 4 + lane;
-  const bool fast = (gA >= 1) && (gA >= rg.lo) && (gA + HOP + NFFT <= rg.hi);   // warp-uniform
-  if (fast) {
-#pragma unroll
-    for (int n1 = 0; n1 < 32 + SH; ++n1) {
-      const float y = preemph_sample(rp[32 * n1], rp[32 * n1 - 1], a.coef);
-      eg[n1 / SH] = fmaf(y, y, eg[n1 / SH]);
-      if (n1 < 32) r[bitrev32(n1)] = sm.win[32 * n1 + lane] * y;
-      if (n1 >= SH) im[bitrev32(n1 - SH)] = sm.win[32 * (n1 - SH) + lane] * y;
-    }
-  } else {
-#pragma unroll
-    for (int n1 = 0; n1 < 32 + SH; ++n1) {
-      const int g = gA + 32 * n1 + lane;
-      float y = 0.f;
-      if (g >= rg.lo && g < rg.hi) {
-        const float xv = rp[32 * n1];
-        if (g == 0) {
-          const float x1 = (L0 > 1) ? rp[32 * n1 + 1] : 0.f;
-          y = xv + (2.f * xv - x1);          // zi = 2*y[0]-y[1] handed to lfilter as state
-        } else {
-          y = preemph_sample(xv, rp[32 * n1 - 1], a.coef);
-        }
-      }
-      eg[n1 / SH] = fmaf(y, y, eg[n1 / SH]);
-      if (n1 < 32) r[bitrev32(n1)] = sm.win[32 * n1 + lane] * y;
-      if (n1 >= SH) im[bitrev32(n1 - SH)] = sm.win[32 * (n1 - SH) + lane] * y;
-    }
-  }
-  // the tile now lives in registers: let the TMA fetch this warp's next pair while the FFT runs
-  __syncwarp();
-  if (lane == 0 && next_bytes) {
-    fence_proxy_async();
-    mbar_expect_tx(wc.mbar, next_bytes);
-    tma_load_1d_hint(next_dst, next_src, next_bytes, wc.mbar, wc.pol_in);
-  }
-  float* plane = wc.plane;
-  fft32_dit(r, im);
-#pragma unroll
-  for (int k1 = 1; k1 < 32; ++k1) {   // twiddle by W_1024^(k1 * lane)
-    const float2 w = sm.tw[k1 * 32 + lane];
-    const float tr = r[k1] * w.x - im[k1] * w.y;
-    const float ti = fmaf(r[k1], w.y, im[k1] * w.x);
-    r[k1] = tr; im[k1] = ti;
-  }
-  // transpose (lane n2, reg k1) -> (lane k1, reg n2) through the warp's plane, re then im
-#pragma unroll
-  for (int k1 = 0; k1 < 32; ++k1) plane[k1 * 33 + lane] = r[k1];
-  __syncwarp();
-#pragma unroll
-  for (int n2 = 0; n2 < 32; ++n2) r[bitrev32(n2)] = plane[lane * 33 + n2];
-  __syncwarp();
-#pragma unroll
-  for (int k1 = 0; k1 < 32; ++k1) plane[k1 * 33 + lane] = im[k1];
-  __syncwarp();
-#pragma unroll
-  for (int n2 = 0; n2 < 32; ++n2) im[bitrev32(n2)] = plane[lane * 33 + n2];
-  __syncwarp();
-  fft32_dit(r, im);   // now (r[k2], im[k2]) = Z[lane + 32 k2]
-  // split the two real spectra, power -> P2[k] = (|A_k|^2, |B_k|^2), k = 0..512
-  float2* P2 = reinterpret_cast<float2*>(plane);
-  const int src = (32 - lane) & 31;
-#pragma unroll
-  for (int k2 = 0; k2 <= 16; ++k2) {
-    const int pk = (k2 < 16) ? 31 - k2 : 15;
-    float pr = __shfl_sync(0xffffffffu, r[pk], src);
-    float pi = __shfl_sync(0xffffffffu, im[pk], src);
-    if (lane == 0) { pr = r[(32 - k2) & 31]; pi = im[(32 - k2) & 31]; }
-    const float sr = r[k2] + pr, di = im[k2] - pi;
-    const float si = im[k2] + pi, dr = r[k2] - pr;
-    const float pa = fmaf(sr, sr, di * di);
-    const float pb = fmaf(si, si, dr * dr);
-    if (k2 < 16 || lane == 0) P2[lane + 32 * k2] = make_float2(pa, pb);
-  }
-  __syncwarp();
-  // sparse mel (4 bands per lane), 10 log10, per-row extrema of the unclamped values, clamp at floor_db
-  float mxa = -3.0e38f, mxb = -3.0e38f, mna = 3.0e38f, mnb = 3.0e38f;
-  float da[4], db[4];
-#pragma unroll
-  for (int q = 0; q < 4; ++q) {
-    const int band = 32 * q + lane;
-    const int k0 = __ldg(a.tab.mel_k0 + band);
-    const float* wq = sm.melw + a.tab.mel_woff[q] + lane;
-    const int cnt = a.tab.mel_cnt[q];
-    float ma = 0.f, mb = 0.f;
-#pragma unroll 4
-    for (int i = 0; i < cnt; ++i) {
-      const float w = wq[32 * i];
-      const float2 p = P2[k0 + i];
-      ma = fmaf(w, p.x, ma);
-      mb = fmaf(w, p.y, mb);
-    }
-    const float va = 3.0102999566398120f * __log2f(fmaxf(ma, 1e-10f));
-    const float vb = 3.0102999566398120f * __log2f(fmaxf(mb, 1e-10f));
-    mxa = fmaxf(mxa, va); mna = fminf(mna, va);
-    mxb = fmaxf(mxb, vb); mnb = fminf(mnb, vb);
-    da[q] = fmaxf(va, floor_db); db[q] = fmaxf(vb, floor_db);
-  }
-  __syncwarp();   // P2 consumed: the plane is free for the DCT reduction
-  // DCT-II (ortho), 16 coefficients at a time: lane-partial sums over its 4 bands, then a transposed reduction
-  // through the plane (lane j sums row j = (frame j/16, coefficient j%16) over the 32 lanes' partials)
-  {
-    const int stride = a.n16 + 4;
-    for (int kg = 0; kg < a.n16; kg += 16) {
-      float pa[16], pb[16];
-#pragma unroll
-      for (int k = 0; k < 16; ++k) { pa[k] = 0.f; pb[k] = 0.f; }
-#pragma unroll
-      for (int q = 0; q < 4; ++q) {
-        const float* crow = sm.dct + (32 * q + lane) * stride + kg;
-#pragma unroll
-        for (int k4 = 0; k4 < 4; ++k4) {
-          const float4 c = *reinterpret_cast<const float4*>(crow + 4 * k4);
-          pa[4 * k4 + 0] = fmaf(da[q], c.x, pa[4 * k4 + 0]); pb[4 * k4 + 0] = fmaf(db[q], c.x, pb[4 * k4 + 0]);
-          pa[4 * k4 + 1] = fmaf(da[q], c.y, pa[4 * k4 + 1]); pb[4 * k4 + 1] = fmaf(db[q], c.y, pb[4 * k4 + 1]);
-          pa[4 * k4 + 2] = fmaf(da[q], c.z, pa[4 * k4 + 2]); pb[4 * k4 + 2] = fmaf(db[q], c.z, pb[4 * k4 + 2]);
-          pa[4 * k4 + 3] = fmaf(da[q], c.w, pa[4 * k4 + 3]); pb[4 * k4 + 3] = fmaf(db[q], c.w, pb[4 * k4 + 3]);
-        }
-      }
-#pragma unroll
-      for (int k = 0; k < 16; ++k) { plane[k * 33 + lane] = pa[k]; plane[(16 + k) * 33 + lane] = pb[k]; }
-      __syncwarp();
-      float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
-      const float* prow = plane + lane * 33;
-#pragma unroll
-      for (int i = 0; i < 32; i += 4) { s0 += prow[i]; s1 += prow[i + 1]; s2 += prow[i + 2]; s3 += prow[i + 3]; }
-      const float cval = (s0 + s1) + (s2 + s3);
-      if (lane < 16 || vB) st_slab(sl.mfcc + (size_t)(row + (lane >> 4)) * a.n16 + kg + (lane & 15), cval, wc.pol_slab);
-      __syncwarp();
-    }
-  }
-  mxa = warp_max(mxa); mxb = warp_max(mxb);
-  mna = warp_min(mna); mnb = warp_min(mnb);
-#pragma unroll
-  for (int g = 0; g < NG; ++g) eg[g] = warp_sum(eg[g]);
-  float eA = 0.f, eB = 0.f;
-#pragma unroll
-  for (int g = 0; g < NG - 1; ++g) { eA += eg[g]; eB += eg[g + 1]; }
-  if (!isfinite(eA + eB)) bad = 1;   // a NaN / Inf sample poisons the sums of squares (librosa.util.valid_audio)
-  if (lane == 0) {
-    __stcg(sl.rms + row, sqrtf(eA * (1.0f / NFFT)));
-    __stcg(sl.rowmax + row, mxa); __stcg(sl.rowmin + row, mna);
-    if (vB) { __stcg(sl.rms + row + 1, sqrtf(eB * (1.0f / NFFT))); __stcg(sl.rowmax + row + 1, mxb); __stcg(sl.rowmin + row + 1, mnb); }
-    if (own_sums) {   // blocks [fA*hop, +hop) and [+hop, +2hop) are groups NFFT/(2 HOP) and the next one
-      __stcg(sl.blk + usum_idx, eg[NFFT / (2 * HOP)]);
-      __stcg(sl.blk + usum_idx + 1, eg[NFFT / (2 * HOP) + 1]);
-    }
-  }
-  __syncwarp();   // plane reusable
 }
 
 // ---- streaming pass over frames [f_begin, f_end) of `rg`; slab row = row_shift + f.  Warp w takes the frame pairs
@@ -292,22 +53,23 @@ template <int NFFT, int HOP>
 __device__ __forceinline__ void stream_frames(const ClipArgs& a, const Smem& sm, const Slab& sl, WarpCtx& wc,
                                               const float* __restrict__ clip_audio, int L0, Region rg, int f_begin, int f_end,
                                               int row_shift, bool own_sums, float floor_db, bool redo, int& bad) {
+  using G = Geo<NFFT, HOP>;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  constexpr int SPAN = HOP + NFFT;
+  const int stride = G::FPW * (int)(blockDim.x >> 5);   // frames per CTA step
   auto need = [&](int f) -> bool {   // warp-uniform
     if (!redo) return true;
-    float m = __ldcg(sl.rowmin + row_shift + f);
-    if (f + 1 < f_end) m = fminf(m, __ldcg(sl.rowmin + row_shift + f + 1));
+    float m = 3.0e38f;
+    for (int j = 0; j < G::FPW; ++j) if (f + j < f_end) m = fminf(m, __ldcg(sl.rowmin + row_shift + f + j));
     return m < floor_db;
   };
-  int fA = f_begin + 2 * warp;
-  while (fA < f_end && !need(fA)) fA += (int)(blockDim.x >> 4);
+  int fA = f_begin + G::FPW * warp;
+  while (fA < f_end && !need(fA)) fA += stride;
   if (fA >= f_end) return;
   int gA = rg.origin + fA * HOP - NFFT / 2;
   unsigned cur_bytes;
   {
     int g_lo = 0, s_lo = 0;
-    cur_bytes = pair_copy_range(rg, gA, SPAN, L0, g_lo, s_lo);
+    cur_bytes = pair_copy_range(rg, gA, G::SPAN, L0, g_lo, s_lo);
     if (lane == 0 && cur_bytes) {
       fence_proxy_async();
       mbar_expect_tx(wc.mbar, cur_bytes);
@@ -315,15 +77,15 @@ __device__ __forceinline__ void stream_frames(const ClipArgs& a, const Smem& sm,
     }
   }
   while (fA < f_end) {
-    int fN = fA + (int)(blockDim.x >> 4);
-    while (fN < f_end && !need(fN)) fN += (int)(blockDim.x >> 4);
+    int fN = fA + stride;
+    while (fN < f_end && !need(fN)) fN += stride;
     const int gN = rg.origin + fN * HOP - NFFT / 2;
     unsigned next_bytes = 0;
     int g_lo = 0, s_lo = 0;
-    if (fN < f_end) next_bytes = pair_copy_range(rg, gN, SPAN, L0, g_lo, s_lo);
+    if (fN < f_end) next_bytes = pair_copy_range(rg, gN, G::SPAN, L0, g_lo, s_lo);
     if (cur_bytes) { mbar_wait(wc.mbar, wc.parity); wc.parity ^= 1u; }
-    warp_frames_1024<HOP>(a, sm, sl, wc, rg, gA, L0, fA + 1 < f_end, row_shift + fA, own_sums, fA, floor_db,
-                          next_bytes, clip_audio + g_lo, wc.raw + s_lo, bad);
+    WarpStep<NFFT, HOP>::run(a, sm, sl, wc, rg, gA, L0, min(G::FPW, f_end - fA), row_shift + fA, own_sums, fA, floor_db,
+                             next_bytes, clip_audio + g_lo, wc.raw + s_lo, bad);
     fA = fN; gA = gN; cur_bytes = next_bytes;
   }
 }
@@ -482,11 +244,13 @@ __global__ void __launch_bounds__(kMaxClipThreads, 1) clip_kernel(ClipArgs a) {
   // layout: [16 mbarriers 128B][twiddle 8KB][window NFFT*4][acc 6*64 doubles][red 64 doubles]
   //         [sDct 128*(n16+4) floats][mel weights][raw tiles 16 x (HOP+NFFT+8) floats][planes 16 x 4224B]
   //         (phase C's sM aliases the raw tiles)
-  constexpr int RAWW = HOP + NFFT + 8;
+  constexpr int RAWW = Geo<NFFT, HOP>::RAWW;
   Smem sm;
   sm.mbar = reinterpret_cast<uint64_t*>(smem_raw);
   sm.tw = reinterpret_cast<float2*>(smem_raw + 128);
-  sm.win = reinterpret_cast<float*>(smem_raw + 128 + 8192);
+  constexpr int PTW_BYTES = NFFT == 2048 ? 4112 : 0;   // W_2048^k, k = 0..512 (+ pad)
+  sm.ptw = reinterpret_cast<float2*>(smem_raw + 128 + 8192);
+  sm.win = reinterpret_cast<float*>(smem_raw + 128 + 8192 + PTW_BYTES);
   double* acc = reinterpret_cast<double*>(sm.win + NFFT);
   double* red = acc + kMoments * kMaxMfcc;
   float* sDct = reinterpret_cast<float*>(red + 64);
@@ -501,6 +265,7 @@ __global__ void __launch_bounds__(kMaxClipThreads, 1) clip_kernel(ClipArgs a) {
   const int tid = threadIdx.x, warp = tid >> 5;
   for (int i = tid; i < 1024; i += (int)blockDim.x) sm.tw[i] = a.tab.twiddle[i];
   for (int i = tid; i < NFFT; i += (int)blockDim.x) sm.win[i] = a.tab.window_half[i];
+  if (NFFT == 2048) for (int i = tid; i <= 512; i += (int)blockDim.x) sm.ptw[i] = a.tab.post_twiddle[i];
   for (int i = tid; i < kNMels * a.n16; i += (int)blockDim.x) sDct[(i / a.n16) * dstride + (i % a.n16)] = a.dct_t[i];
   for (int i = tid; i < a.mel_floats; i += (int)blockDim.x) sMel[i] = a.tab.mel_w[i];
   if (tid < kMaxClipWarps) mbar_init(sm.mbar + tid, 1);
@@ -580,7 +345,7 @@ __global__ void __launch_bounds__(kMaxClipThreads, 1) clip_kernel(ClipArgs a) {
         if (bad) s_bad = 1;
         __syncthreads();
         // ---- T
-        const int nu = 2 * ((fe + 1) / 2);   // hop-block sums written by the pass
+        const int nu = Geo<NFFT, HOP>::FPW * ((fe + Geo<NFFT, HOP>::FPW - 1) / Geo<NFFT, HOP>::FPW);   // hop-block sums written by the pass
         ci = trim_decide(sl.blk, nu, L0, hop, a.trim_top_db, s_bad, reinterpret_cast<float*>(red), reinterpret_cast<int*>(red + 32));
         a0 = ci.start / hop;
       }

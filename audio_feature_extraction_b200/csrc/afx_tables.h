@@ -39,6 +39,17 @@ inline std::vector<float> twiddle32x32(int n) {
   return t;
 }
 
+// W_n^k = exp(-2 pi i k / n) stored (cos, -sin), k in [0, count)
+inline std::vector<float> post_twiddle(int n, int count) {
+  std::vector<float> t(2 * (size_t)count);
+  for (int k = 0; k < count; ++k) {
+    const double ang = 2.0 * M_PI * (double)k / n;
+    t[2 * k] = (float)std::cos(ang);
+    t[2 * k + 1] = (float)(-std::sin(ang));
+  }
+  return t;
+}
+
 struct MelSparse {
   std::vector<float> dense;   // [128][nbins] float32 weights exactly as librosa.filters.mel builds them
   std::vector<float> w;       // padded [quarter][i][lane]

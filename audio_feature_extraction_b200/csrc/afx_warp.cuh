@@ -1,0 +1,442 @@
+// Warp-level building blocks of the fused kernel: one warp turns the raw samples of 1, 2 or 4 consecutive
+// frames (its private TMA tile) into MFCC rows, RMS and log-mel extrema without any CTA-wide barrier.
+//
+//   n_fft = 1024: two frames per step as the real / imaginary lanes of one complex 1024-point FFT
+//   n_fft =  512: four frames per step as two complex 512-point FFTs (16 + 16 complex values per lane)
+//   n_fft = 2048: one frame per step, even / odd samples packed into one complex 1024-point FFT + a split pass
+//
+// Replaces the framing / STFT / mel / dB / DCT chain of librosa.feature.mfcc and librosa.feature.rms reached from
+// audio_feature_extraction_toolkit/core/feature_extractor.py:127-134,164-168 (reference).
+#pragma once
+#include "afx_args.cuh"
+#include "afx_common.cuh"
+#include "fft_gen.cuh"
+
+namespace afx {
+
+constexpr int kPlaneFloats = 32 * 33;
+
+// where a streaming step reads: frames f (relative to `origin`) cover origin + f*hop - n_fft/2 + [0, n_fft),
+// samples outside [lo, hi) count as zero (librosa centre padding of the trimmed signal)
+struct Region { int origin, lo, hi; };
+
+// shared-memory tables + per-warp buffers
+struct Smem {
+  uint64_t* mbar;     // [16] one TMA barrier per warp
+  float2* tw;         // [32][32] W_1024^(row*col) (n_fft 1024, 2048) or [16][32] W_512^(row*col) (n_fft 512)
+  float2* ptw;        // n_fft 2048: W_2048^k, k = 0..512
+  float* win;         // [NFFT] 0.5 * periodic Hamming
+  const float* dct;   // [128][n16 + 4] DCT-II rows, transposed, padded stride (conflict-free float4 reads)
+  const float* melw;  // copy of Tables::mel_w
+  float* raw;         // [warps][RAWW] per-warp raw-sample tiles
+  float* planes;      // [warps][32*33]
+};
+
+struct WarpCtx {
+  float* raw;        // this warp's raw-sample tile (TMA destination); position p holds sample gA - 4 + p
+  float* plane;      // [32*33] transpose scratch / power spectrum / DCT reduction
+  uint64_t* mbar;    // this warp's TMA barrier
+  unsigned parity;
+  uint64_t pol_in;   // L2 policy of the audio stream (evict_first)
+  uint64_t pol_slab; // L2 policy of the scratch slab (evict_last)
+};
+
+// per-(n_fft, hop) geometry of a warp step
+template <int NFFT, int HOP>
+struct Geo {
+  static constexpr int FPW = NFFT == 2048 ? 1 : (NFFT == 1024 ? 2 : 4);   // frames per warp step
+  static constexpr int SPAN = (FPW - 1) * HOP + NFFT;                     // samples a step spans
+  static constexpr int RAWW = SPAN + 8;                                   // floats of the warp's tile
+  static constexpr int NG = SPAN / HOP;                                   // hop-sized groups in the span
+  static constexpr int G0 = NFFT / (2 * HOP);                             // group holding [fA*hop, (fA+1)*hop)
+};
+
+__device__ __forceinline__ float preemph_op(float x, float xm1, float coef) {
+  // scipy.signal.lfilter with b=[1,-c], a=[1] in float32: fl(x + fl(-c * xm1)), no contraction
+  return __fadd_rn(x, __fmul_rn(-coef, xm1));
+}
+
+// pre-emphasised sample at tile offset t (absolute sample gA + t); rp0 = raw + 4.
+// FAST: the whole step lies inside [max(lo,1), hi), no checks.
+template <bool FAST>
+__device__ __forceinline__ float load_y(const float* rp0, int t, int gA, const Region& rg, int L0, float coef) {
+  if (FAST) return preemph_op(rp0[t], rp0[t - 1], coef);
+  const int g = gA + t;
+  float y = 0.f;
+  if (g >= rg.lo && g < rg.hi) {
+    const float xv = rp0[t];
+    if (g == 0) {
+      const float x1 = (L0 > 1) ? rp0[t + 1] : 0.f;
+      y = xv + (2.f * xv - x1);          // zi = 2*y[0]-y[1] handed to lfilter as state (librosa.effects.preemphasis)
+    } else {
+      y = preemph_op(xv, rp0[t - 1], coef);
+    }
+  }
+  return y;
+}
+
+// issue this warp's next tile as soon as the current one sits in registers
+__device__ __forceinline__ void prefetch_next(WarpCtx& wc, unsigned bytes, const float* src, float* dst, int lane) {
+  __syncwarp();
+  if (lane == 0 && bytes) {
+    fence_proxy_async();
+    mbar_expect_tx(wc.mbar, bytes);
+    tma_load_1d_hint(dst, src, bytes, wc.mbar, wc.pol_in);
+  }
+}
+
+// transpose (lane a, reg b) -> (lane b, reg a) of a 32 x 32 register tile through the warp's plane,
+// writing the result in bit-reversed register order (the input order of the next 32-point DIT)
+__device__ __forceinline__ void transpose32_bitrev(float (&v)[32], float* plane, int lane) {
+#pragma unroll
+  for (int k = 0; k < 32; ++k) plane[k * 33 + lane] = v[k];
+  __syncwarp();
+#pragma unroll
+  for (int n = 0; n < 32; ++n) v[bitrev32(n)] = plane[lane * 33 + n];
+  __syncwarp();
+}
+
+// complex 1024-point FFT of z[32*n1 + lane] held as (r, im)[bitrev32(n1)]; result Z[lane + 32*k2] in (r, im)[k2]
+__device__ __forceinline__ void fft1024_core(float (&r)[32], float (&im)[32], const Smem& sm, float* plane, int lane) {
+  fft32_dit(r, im);
+#pragma unroll
+  for (int k1 = 1; k1 < 32; ++k1) {   // twiddle by W_1024^(k1 * lane)
+    const float2 w = sm.tw[k1 * 32 + lane];
+    const float tr = r[k1] * w.x - im[k1] * w.y;
+    const float ti = fmaf(r[k1], w.y, im[k1] * w.x);
+    r[k1] = tr; im[k1] = ti;
+  }
+  transpose32_bitrev(r, plane, lane);
+  transpose32_bitrev(im, plane, lane);
+  fft32_dit(r, im);
+}
+
+// two complex 512-point FFTs: signal s in registers [16 s, 16 s + 16) as z_s[32*n1 + lane] at bitrev16(n1);
+// result: lane 16 s + k1 holds Z_s[k1 + 16*k2] in (r, im)[k2]
+__device__ __forceinline__ void fft512x2_core(float (&r)[32], float (&im)[32], const Smem& sm, float* plane, int lane) {
+  fft16x2_dit(r, im);
+#pragma unroll
+  for (int j = 0; j < 32; ++j) {      // twiddle by W_512^(k1 * lane), k1 = j & 15
+    if ((j & 15) == 0) continue;
+    const float2 w = sm.tw[(j & 15) * 32 + lane];
+    const float tr = r[j] * w.x - im[j] * w.y;
+    const float ti = fmaf(r[j], w.y, im[j] * w.x);
+    r[j] = tr; im[j] = ti;
+  }
+  transpose32_bitrev(r, plane, lane);
+  transpose32_bitrev(im, plane, lane);
+  fft32_dit(r, im);
+}
+
+// ---- DCT-II (ortho) of two clamped log-mel rows held as 4 bands per lane, 16 coefficients at a time: lane-partial
+// sums over its 4 bands, then a transposed reduction through the plane (lane j sums row j = (frame j/16,
+// coefficient j%16) over the 32 lanes' partials); rows `row` (A) and `row + 1` (B, if vB) of the slab
+__device__ __forceinline__ void dct_pair(const ClipArgs& a, const Smem& sm, const Slab& sl, const WarpCtx& wc,
+                                         const float (&da)[4], const float (&db)[4], int row, bool vB, int lane) {
+  float* plane = wc.plane;
+  const int stride = a.n16 + 4;
+  for (int kg = 0; kg < a.n16; kg += 16) {
+    float pa[16], pb[16];
+#pragma unroll
+    for (int k = 0; k < 16; ++k) { pa[k] = 0.f; pb[k] = 0.f; }
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const float* crow = sm.dct + (32 * q + lane) * stride + kg;
+#pragma unroll
+      for (int k4 = 0; k4 < 4; ++k4) {
+        const float4 c = *reinterpret_cast<const float4*>(crow + 4 * k4);
+        pa[4 * k4 + 0] = fmaf(da[q], c.x, pa[4 * k4 + 0]); pb[4 * k4 + 0] = fmaf(db[q], c.x, pb[4 * k4 + 0]);
+        pa[4 * k4 + 1] = fmaf(da[q], c.y, pa[4 * k4 + 1]); pb[4 * k4 + 1] = fmaf(db[q], c.y, pb[4 * k4 + 1]);
+        pa[4 * k4 + 2] = fmaf(da[q], c.z, pa[4 * k4 + 2]); pb[4 * k4 + 2] = fmaf(db[q], c.z, pb[4 * k4 + 2]);
+        pa[4 * k4 + 3] = fmaf(da[q], c.w, pa[4 * k4 + 3]); pb[4 * k4 + 3] = fmaf(db[q], c.w, pb[4 * k4 + 3]);
+      }
+    }
+#pragma unroll
+    for (int k = 0; k < 16; ++k) { plane[k * 33 + lane] = pa[k]; plane[(16 + k) * 33 + lane] = pb[k]; }
+    __syncwarp();
+    float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+    const float* prow = plane + lane * 33;
+#pragma unroll
+    for (int i = 0; i < 32; i += 4) { s0 += prow[i]; s1 += prow[i + 1]; s2 += prow[i + 2]; s3 += prow[i + 3]; }
+    const float cval = (s0 + s1) + (s2 + s3);
+    if (lane < 16 || vB) st_slab(sl.mfcc + (size_t)(row + (lane >> 4)) * a.n16 + kg + (lane & 15), cval, wc.pol_slab);
+    __syncwarp();
+  }
+}
+
+__device__ __forceinline__ float to_db(float m) { return 3.0102999566398120f * __log2f(fmaxf(m, 1e-10f)); }   // 10 log10(max(1e-10, m))
+
+// ---- tail shared by the three front-ends: per-frame extrema of the unclamped log-mel rows, RMS, hop-block sums,
+// clamp at floor_db, DCT.  d[f][q] = unclamped log-mel of band 32 q + lane, eg = lane-partial hop-group energies.
+template <int NFFT, int HOP>
+__device__ __forceinline__ void finish_step(const ClipArgs& a, const Smem& sm, const Slab& sl, const WarpCtx& wc,
+                                            float (&d)[Geo<NFFT, HOP>::FPW][4], float (&eg)[Geo<NFFT, HOP>::NG], int nv, int row,
+                                            bool own_sums, int usum_idx, float floor_db, int lane, int& bad) {
+  using G = Geo<NFFT, HOP>;
+  constexpr int GPF = NFFT / HOP;   // hop groups per frame
+#pragma unroll
+  for (int g = 0; g < G::NG; ++g) eg[g] = warp_sum(eg[g]);
+  float esum = 0.f;
+#pragma unroll
+  for (int g = 0; g < G::NG; ++g) esum += eg[g];
+  if (!isfinite(esum)) bad = 1;   // a NaN / Inf sample poisons the sums of squares (librosa.util.valid_audio)
+#pragma unroll
+  for (int f = 0; f < G::FPW; ++f) {
+    float mx = fmaxf(fmaxf(d[f][0], d[f][1]), fmaxf(d[f][2], d[f][3]));
+    float mn = fminf(fminf(d[f][0], d[f][1]), fminf(d[f][2], d[f][3]));
+    mx = warp_max(mx); mn = warp_min(mn);
+    float e = 0.f;
+#pragma unroll
+    for (int g = 0; g < GPF; ++g) e += eg[f + g];
+    if (lane == 0 && f < nv) {
+      __stcg(sl.rms + row + f, sqrtf(e * (1.0f / NFFT)));
+      __stcg(sl.rowmax + row + f, mx);
+      __stcg(sl.rowmin + row + f, mn);
+    }
+#pragma unroll
+    for (int q = 0; q < 4; ++q) d[f][q] = fmaxf(d[f][q], floor_db);
+  }
+  if (own_sums && lane == 0) {   // blocks [(fA + f) hop, + hop) are groups G0 + f
+#pragma unroll
+    for (int f = 0; f < G::FPW; ++f) __stcg(sl.blk + usum_idx + f, eg[G::G0 + f]);
+  }
+  if (G::FPW == 1) {
+    dct_pair(a, sm, sl, wc, d[0], d[0], row, false, lane);
+  } else {
+#pragma unroll
+    for (int f = 0; f < G::FPW; f += 2)
+      if (f < nv) dct_pair(a, sm, sl, wc, d[f], d[f + 1 < G::FPW ? f + 1 : f], row + f, f + 1 < nv, lane);
+  }
+}
+
+// =====================================================================================================
+// n_fft = 1024: frames fA, fA + 1 as the real / imaginary lanes of one complex 1024-point FFT
+template <int NFFT, int HOP> struct WarpStep;
+
+template <int HOP>
+struct WarpStep<1024, HOP> {
+  using G = Geo<1024, HOP>;
+  template <bool FAST>
+  static __device__ __forceinline__ void load(float (&r)[32], float (&im)[32], float (&eg)[G::NG], const float* rp0, int gA,
+                                              const Region& rg, int L0, float coef, const Smem& sm, int lane) {
+    constexpr int SH = HOP / 32;            // rows by which frame B trails frame A
+#pragma unroll
+    for (int n1 = 0; n1 < 32 + SH; ++n1) {
+      const float y = load_y<FAST>(rp0, 32 * n1 + lane, gA, rg, L0, coef);
+      eg[n1 / SH] = fmaf(y, y, eg[n1 / SH]);
+      if (n1 < 32) r[bitrev32(n1)] = sm.win[32 * n1 + lane] * y;
+      if (n1 >= SH) im[bitrev32(n1 - SH)] = sm.win[32 * (n1 - SH) + lane] * y;
+    }
+  }
+  static __device__ __forceinline__ void run(const ClipArgs& a, const Smem& sm, const Slab& sl, WarpCtx& wc, const Region& rg,
+                                             int gA, int L0, int nv, int row, bool own_sums, int usum_idx, float floor_db,
+                                             unsigned next_bytes, const float* next_src, float* next_dst, int& bad) {
+    const int lane = threadIdx.x & 31;
+    float r[32], im[32];
+    float eg[G::NG];
+#pragma unroll
+    for (int g = 0; g < G::NG; ++g) eg[g] = 0.f;
+    const bool fast = (gA >= 1) && (gA >= rg.lo) && (gA + G::SPAN <= rg.hi);   // warp-uniform
+    if (fast) load<true>(r, im, eg, wc.raw + 4, gA, rg, L0, a.coef, sm, lane);
+    else load<false>(r, im, eg, wc.raw + 4, gA, rg, L0, a.coef, sm, lane);
+    prefetch_next(wc, next_bytes, next_src, next_dst, lane);
+    float* plane = wc.plane;
+    fft1024_core(r, im, sm, plane, lane);   // (r[k2], im[k2]) = Z[lane + 32 k2]
+    // split the two real spectra, power -> P2[k] = (|A_k|^2, |B_k|^2), k = 0..512
+    float2* P2 = reinterpret_cast<float2*>(plane);
+    const int src = (32 - lane) & 31;
+#pragma unroll
+    for (int k2 = 0; k2 <= 16; ++k2) {
+      const int pk = (k2 < 16) ? 31 - k2 : 15;
+      float pr = __shfl_sync(0xffffffffu, r[pk], src);
+      float pi = __shfl_sync(0xffffffffu, im[pk], src);
+      if (lane == 0) { pr = r[(32 - k2) & 31]; pi = im[(32 - k2) & 31]; }
+      const float sr = r[k2] + pr, di = im[k2] - pi;
+      const float si = im[k2] + pi, dr = r[k2] - pr;
+      const float pa = fmaf(sr, sr, di * di);
+      const float pb = fmaf(si, si, dr * dr);
+      if (k2 < 16 || lane == 0) P2[lane + 32 * k2] = make_float2(pa, pb);
+    }
+    __syncwarp();
+    // sparse mel (4 bands per lane), 10 log10
+    float d[2][4];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const int k0 = __ldg(a.tab.mel_k0 + 32 * q + lane);
+      const float* wq = sm.melw + a.tab.mel_woff[q] + lane;
+      const int cnt = a.tab.mel_cnt[q];
+      float ma = 0.f, mb = 0.f;
+#pragma unroll 4
+      for (int i = 0; i < cnt; ++i) {
+        const float w = wq[32 * i];
+        const float2 p = P2[k0 + i];
+        ma = fmaf(w, p.x, ma);
+        mb = fmaf(w, p.y, mb);
+      }
+      d[0][q] = to_db(ma); d[1][q] = to_db(mb);
+    }
+    __syncwarp();   // P2 consumed: the plane is free for the DCT reduction
+    finish_step<1024, HOP>(a, sm, sl, wc, d, eg, nv, row, own_sums, usum_idx, floor_db, lane, bad);
+  }
+};
+
+// =====================================================================================================
+// n_fft = 512: frames fA .. fA + 3 as two complex 512-point FFTs (signal s: re = frame 2s, im = frame 2s + 1)
+template <int HOP>
+struct WarpStep<512, HOP> {
+  using G = Geo<512, HOP>;
+  static constexpr int PSTRIDE = 260;   // float2 elements between the two signals' power spectra (257 used)
+  template <bool FAST>
+  static __device__ __forceinline__ void load(float (&r)[32], float (&im)[32], float (&eg)[G::NG], const float* rp0, int gA,
+                                              const Region& rg, int L0, float coef, const Smem& sm, int lane) {
+    constexpr int SH = HOP / 32;            // rows between consecutive frames
+    constexpr int NR = G::SPAN / 32;        // rows of 32 samples in the step
+#pragma unroll
+    for (int row = 0; row < NR; ++row) {
+      const float y = load_y<FAST>(rp0, 32 * row + lane, gA, rg, L0, coef);
+      eg[row / SH] = fmaf(y, y, eg[row / SH]);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int n1 = row - j * SH;
+        if (n1 >= 0 && n1 < 16) {
+          const float v = sm.win[32 * n1 + lane] * y;
+          if (j & 1) im[16 * (j >> 1) + bitrev16(n1)] = v; else r[16 * (j >> 1) + bitrev16(n1)] = v;
+        }
+      }
+    }
+  }
+  static __device__ __forceinline__ void run(const ClipArgs& a, const Smem& sm, const Slab& sl, WarpCtx& wc, const Region& rg,
+                                             int gA, int L0, int nv, int row, bool own_sums, int usum_idx, float floor_db,
+                                             unsigned next_bytes, const float* next_src, float* next_dst, int& bad) {
+    const int lane = threadIdx.x & 31;
+    float r[32], im[32];
+    float eg[G::NG];
+#pragma unroll
+    for (int g = 0; g < G::NG; ++g) eg[g] = 0.f;
+    const bool fast = (gA >= 1) && (gA >= rg.lo) && (gA + G::SPAN <= rg.hi);   // warp-uniform
+    if (fast) load<true>(r, im, eg, wc.raw + 4, gA, rg, L0, a.coef, sm, lane);
+    else load<false>(r, im, eg, wc.raw + 4, gA, rg, L0, a.coef, sm, lane);
+    prefetch_next(wc, next_bytes, next_src, next_dst, lane);
+    float* plane = wc.plane;
+    fft512x2_core(r, im, sm, plane, lane);   // lane 16 s + k1: (r[k2], im[k2]) = Z_s[k1 + 16 k2]
+    // split each signal's two real spectra, power -> P2[s][k] = (|X_{2s}[k]|^2, |X_{2s+1}[k]|^2), k = 0..256
+    float2* P2 = reinterpret_cast<float2*>(plane);
+    const int k1 = lane & 15;
+    const int src = (lane & 16) | ((16 - k1) & 15);
+    float2* Ps = P2 + (lane >> 4) * PSTRIDE + k1;
+#pragma unroll
+    for (int k2 = 0; k2 <= 16; ++k2) {
+      const int pk = (k2 < 16) ? 31 - k2 : 15;
+      float pr = __shfl_sync(0xffffffffu, r[pk], src);
+      float pi = __shfl_sync(0xffffffffu, im[pk], src);
+      if (k1 == 0) { pr = r[(32 - k2) & 31]; pi = im[(32 - k2) & 31]; }
+      const float sr = r[k2] + pr, di = im[k2] - pi;
+      const float si = im[k2] + pi, dr = r[k2] - pr;
+      const float pa = fmaf(sr, sr, di * di);
+      const float pb = fmaf(si, si, dr * dr);
+      if (k2 < 16 || k1 == 0) Ps[16 * k2] = make_float2(pa, pb);
+    }
+    __syncwarp();
+    float d[4][4];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const int k0 = __ldg(a.tab.mel_k0 + 32 * q + lane);
+      const float* wq = sm.melw + a.tab.mel_woff[q] + lane;
+      const int cnt = a.tab.mel_cnt[q];
+      float m0 = 0.f, m1 = 0.f, m2 = 0.f, m3 = 0.f;
+#pragma unroll 4
+      for (int i = 0; i < cnt; ++i) {
+        const float w = wq[32 * i];
+        const float2 p = P2[k0 + i];
+        const float2 p2 = P2[PSTRIDE + k0 + i];
+        m0 = fmaf(w, p.x, m0); m1 = fmaf(w, p.y, m1);
+        m2 = fmaf(w, p2.x, m2); m3 = fmaf(w, p2.y, m3);
+      }
+      d[0][q] = to_db(m0); d[1][q] = to_db(m1); d[2][q] = to_db(m2); d[3][q] = to_db(m3);
+    }
+    __syncwarp();
+    finish_step<512, HOP>(a, sm, sl, wc, d, eg, nv, row, own_sums, usum_idx, floor_db, lane, bad);
+  }
+};
+
+// =====================================================================================================
+// n_fft = 2048: one frame per step; z[m] = y[2m] + i y[2m+1] through the complex 1024-point FFT, then
+// X[k] = E[k] + W_2048^k O[k], X[1024-k] = conj(E[k] - W_2048^k O[k]) with E / O the even / odd sample spectra
+template <int HOP>
+struct WarpStep<2048, HOP> {
+  using G = Geo<2048, HOP>;
+  template <bool FAST>
+  static __device__ __forceinline__ void load(float (&r)[32], float (&im)[32], float (&eg)[G::NG], const float* rp0, int gA,
+                                              const Region& rg, int L0, float coef, const Smem& sm, int lane) {
+    const float2* win2 = reinterpret_cast<const float2*>(sm.win);
+#pragma unroll
+    for (int n1 = 0; n1 < 32; ++n1) {
+      const int t = 64 * n1 + 2 * lane;
+      float y0, y1;
+      if (FAST) {
+        const float2 x01 = *reinterpret_cast<const float2*>(rp0 + t);
+        y0 = preemph_op(x01.x, rp0[t - 1], coef);
+        y1 = preemph_op(x01.y, x01.x, coef);
+      } else {
+        y0 = load_y<false>(rp0, t, gA, rg, L0, coef);
+        y1 = load_y<false>(rp0, t + 1, gA, rg, L0, coef);
+      }
+      const float2 w = win2[32 * n1 + lane];
+      eg[(64 * n1) / HOP] = fmaf(y0, y0, fmaf(y1, y1, eg[(64 * n1) / HOP]));
+      r[bitrev32(n1)] = w.x * y0;
+      im[bitrev32(n1)] = w.y * y1;
+    }
+  }
+  static __device__ __forceinline__ void run(const ClipArgs& a, const Smem& sm, const Slab& sl, WarpCtx& wc, const Region& rg,
+                                             int gA, int L0, int nv, int row, bool own_sums, int usum_idx, float floor_db,
+                                             unsigned next_bytes, const float* next_src, float* next_dst, int& bad) {
+    const int lane = threadIdx.x & 31;
+    float r[32], im[32];
+    float eg[G::NG];
+#pragma unroll
+    for (int g = 0; g < G::NG; ++g) eg[g] = 0.f;
+    const bool fast = (gA >= 1) && (gA >= rg.lo) && (gA + G::SPAN <= rg.hi);   // warp-uniform
+    if (fast) load<true>(r, im, eg, wc.raw + 4, gA, rg, L0, a.coef, sm, lane);
+    else load<false>(r, im, eg, wc.raw + 4, gA, rg, L0, a.coef, sm, lane);
+    prefetch_next(wc, next_bytes, next_src, next_dst, lane);
+    float* plane = wc.plane;
+    fft1024_core(r, im, sm, plane, lane);   // (r[k2], im[k2]) = Z[lane + 32 k2]
+    float* P = plane;                        // [1025] power spectrum
+    const int src = (32 - lane) & 31;
+#pragma unroll
+    for (int k2 = 0; k2 <= 16; ++k2) {
+      const int pk = (k2 < 16) ? 31 - k2 : 15;
+      float pr = __shfl_sync(0xffffffffu, r[pk], src);
+      float pi = __shfl_sync(0xffffffffu, im[pk], src);
+      if (lane == 0) { pr = r[(32 - k2) & 31]; pi = im[(32 - k2) & 31]; }
+      const int k = lane + 32 * k2;
+      const float er = r[k2] + pr, ei = im[k2] - pi;        // E = Z_k + conj(Z_{1024-k})   (the 1/2 sits in the window)
+      const float orr = im[k2] + pi, oi = pr - r[k2];       // O = -i (Z_k - conj(Z_{1024-k}))
+      const float2 w = sm.ptw[k2 < 16 ? k : 512];           // W_2048^k = (cos, -sin)
+      const float tr = orr * w.x - oi * w.y;
+      const float ti = fmaf(orr, w.y, oi * w.x);
+      const float ar = er + tr, ai = ei + ti, br = er - tr, bi = ei - ti;
+      if (k2 < 16 || lane == 0) { P[k] = fmaf(ar, ar, ai * ai); P[1024 - k] = fmaf(br, br, bi * bi); }
+    }
+    __syncwarp();
+    float d[1][4];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const int k0 = __ldg(a.tab.mel_k0 + 32 * q + lane);
+      const float* wq = sm.melw + a.tab.mel_woff[q] + lane;
+      const int cnt = a.tab.mel_cnt[q];
+      float m0 = 0.f, m1 = 0.f;
+      int i = 0;
+      for (; i + 1 < cnt; i += 2) {
+        m0 = fmaf(wq[32 * i], P[k0 + i], m0);
+        m1 = fmaf(wq[32 * i + 32], P[k0 + i + 1], m1);
+      }
+      if (i < cnt) m0 = fmaf(wq[32 * i], P[k0 + i], m0);
+      d[0][q] = to_db(m0 + m1);
+    }
+    __syncwarp();
+    finish_step<2048, HOP>(a, sm, sl, wc, d, eg, nv, row, own_sums, usum_idx, floor_db, lane, bad);
+  }
+};
+
+}  // namespace afx

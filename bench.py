@@ -311,8 +311,8 @@ def run_native(args):
     peak, peak_src = _peak_hbm()
     dom_ms = phases[dom]["ms_per_step"]
     achieved = bytes_per_step / (dom_ms * 1e-3) / 1e9
-    kernel_name = {"frames": "frames_kernel", "trim": "trim_kernel", "mfcc": "mfcc_stats_kernel", "finalize": "finalize_kernel",
-                   "yin": "yin_kernel", "viterbi": "viterbi_kernel", "pcm": "pcm16_to_f32_kernel"}.get(dom, dom)
+    kernel_name = {"frames": "clip_kernel", "trim": "trim_kernel", "yin": "yin_kernel", "viterbi": "viterbi_kernel",
+                   "pcm": "pcm16_to_f32_kernel"}.get(dom, dom)
     roofline = {"bound": "hbm", "kernel": kernel_name, "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                 "traffic": _ncu_traffic(kernel_name), "peak_source": peak_src,
                 "algorithmic_bytes_per_launch": bytes_per_step / max(phases[dom]["launches_per_step"], 1),

@@ -94,8 +94,8 @@ int afx_frame_width(afx_handle_t h);
 /* Number of frame rows clip i can produce at most: 1 + length/hop_length (librosa centre padding). */
 int64_t afx_max_frames(afx_handle_t h, int64_t length);
 
-/* Bytes of device scratch afx_extract needs for this batch (also accepts less: see
- * afx_workspace_min_bytes; more scratch = larger waves of clips per launch). */
+/* Bytes of device scratch afx_extract needs for this batch: a small header plus one private slab per
+ * resident CTA of the fused kernel (sized by the longest clip).  afx_workspace_min_bytes returns the same. */
 size_t afx_workspace_bytes(afx_handle_t h, int64_t n_clips, const int32_t* h_lengths);
 size_t afx_workspace_min_bytes(afx_handle_t h, int64_t n_clips, const int32_t* h_lengths);
 
@@ -114,7 +114,7 @@ size_t afx_workspace_min_bytes(afx_handle_t h, int64_t n_clips, const int32_t* h
  *   d_meta       device int32   [n_clips, 4]
  *   d_frames     device float32 [sum_i afx_max_frames(len_i), FW] or NULL; clip i's rows start at
  *                row sum_{j<i} afx_max_frames(len_j); only the first meta[i][3] rows are written
- *   d_workspace  device scratch of workspace_bytes (>= afx_workspace_min_bytes)
+ *   d_workspace  device scratch of workspace_bytes (>= afx_workspace_bytes), 256-byte aligned
  *   stream       cudaStream_t as void* (NULL = legacy default stream); the call only enqueues work
  */
 int afx_extract(afx_handle_t h, const float* d_audio, const int64_t* h_offsets, const int32_t* h_lengths,
@@ -152,10 +152,11 @@ int afx_extract_host_packed(afx_handle_t h, const void* h_audio, int sample_form
  * of afx_extract is bracketed by two CUDA events on the launching stream.  afx_profile_read
  * synchronises on the recorded events and returns, per phase, the accumulated milliseconds and the
  * number of launches since the last reset. */
-#define AFX_PHASE_TRIM     0   /* pre-emphasis + trim decision            (trim_kernel) */
-#define AFX_PHASE_FRAMES   1   /* frames -> FFT -> mel -> dB, RMS          (frames_kernel) */
-#define AFX_PHASE_MFCC     2   /* clamp, DCT, delta, delta2, moments       (mfcc_stats_kernel) */
-#define AFX_PHASE_FINALIZE 3   /* per-clip statistics -> summary rows      (finalize_kernel) */
+#define AFX_PHASE_TRIM     0   /* separate trim pass, only when hop_length does not divide 512 (trim_kernel) */
+#define AFX_PHASE_FRAMES   1   /* the fused single-pass kernel: pre-emphasis, trim, frames -> FFT -> mel -> dB -> DCT,
+                                  RMS, delta / delta2, statistics -> summary rows       (clip_kernel) */
+#define AFX_PHASE_MFCC     2   /* unused since the fusion (kept for ABI stability) */
+#define AFX_PHASE_FINALIZE 3   /* unused since the fusion */
 #define AFX_PHASE_PCM      4   /* PCM16 -> float32                         (pcm16_to_f32_kernel) */
 #define AFX_PHASE_YIN      5   /* YIN difference / CMND / pYIN observations */
 #define AFX_PHASE_VITERBI  6   /* pYIN HMM decode */

@@ -68,6 +68,33 @@ def test_c2_config_framewise_and_summary_parity(torch_cuda):
         _check_clip(ex, ora, y, summ[i], meta[i], frames, rows[i], ex.n_mfcc)
 
 
+@pytest.mark.parametrize("cfg", [
+    dict(sr=16000, frame_length=512, hop_length=128, n_mfcc=40),     # BASELINE.json configs[2] (C3)
+    dict(sr=44100, frame_length=2048, hop_length=512, n_mfcc=13),    # configs[3] (C4)
+    dict(sr=22050, frame_length=1024, hop_length=512, n_mfcc=20),
+    dict(sr=22050, frame_length=1024, hop_length=128, n_mfcc=13),
+    dict(sr=16000, frame_length=512, hop_length=256, n_mfcc=13),
+    dict(sr=16000, frame_length=512, hop_length=64, n_mfcc=13),
+    dict(sr=44100, frame_length=2048, hop_length=256, n_mfcc=13),
+    dict(sr=44100, frame_length=2048, hop_length=1024, n_mfcc=13),   # hop does not divide 512: separate trim pass
+], ids=lambda c: f"{c['sr']}-{c['frame_length']}-{c['hop_length']}-{c['n_mfcc']}")
+def test_other_configs_framewise_and_summary_parity(torch_cuda, cfg):
+    from audio_feature_extraction_b200 import AudioFeatureExtractor
+    from audio_feature_extraction_b200.synth import make_clip
+    from oracle import OracleFeatureExtractor
+
+    kind = "music" if cfg["sr"] == 44100 else "speech"
+    f_lo, f_hi = (80.0, 400.0) if cfg["sr"] == 16000 else (110.0, 880.0)
+    secs = [4.0, 2.5, 0.9, 3.3, 1.7]
+    clips = [make_clip(500 + s, sr=cfg["sr"], seconds=sec, f_lo=f_lo, f_hi=f_hi, kind=kind) for s, sec in enumerate(secs)]
+    clips.append(np.concatenate([clips[1], np.zeros(30000, np.float32)]))     # trailing digital silence -> tail fix-up + clamp
+    ex = AudioFeatureExtractor(**cfg)
+    ora = OracleFeatureExtractor(**cfg)
+    summ, meta, frames, rows = _framewise(ex, clips)
+    for i, y in enumerate(clips):
+        _check_clip(ex, ora, y, summ[i], meta[i], frames, rows[i], ex.n_mfcc)
+
+
 def test_top_db_clamp_redo_pass(torch_cuda):
     """Clips whose log-mel range exceeds 80 dB inside the trimmed region: power_to_db(top_db=80) clamps, so the
     speculative (unclamped) DCT rows must be redone with the clip-global floor (core/feature_extractor.py:127-134)."""
