@@ -17,6 +17,8 @@
 
 #include "afx_common.cuh"
 #include "afx_clip.cuh"
+#include "afx_pyin.cuh"
+#include "afx_pyin_tables.h"
 #include "afx_tables.h"
 #include "afx_trim.cuh"
 
@@ -56,6 +58,15 @@ cudaError_t upload(const std::vector<T>& v, T** dptr) {
 struct afx_handle_s {
   afx_config_t cfg;
   int n16;                 // n_mfcc rounded up to a multiple of 16 (the in-pass DCT works on groups of 16)
+  // pYIN (F0 group)
+  bool f0_ok = false;      // pYIN constants valid for this (sr, frame_length, hop_length, f0_min, f0_max)
+  afx::host::PyinConsts pc;
+  double* d_pyin = nullptr;            // all double tables, one allocation
+  afx::PyinTables ptab;
+  const double *d_lt_same = nullptr, *d_edge_corr = nullptr, *d_freqs = nullptr;
+  int yin_c = 0, yin_cap = 0, yin_rec_bytes = 0, yin_lag_pad = 0, yin_tile = 0, yin_frames_per_chunk = 0;
+  size_t yin_smem = 0, vit_smem = 0;
+  void* d_f0_ws = nullptr; size_t d_f0_ws_bytes = 0;   // handle-owned scratch of the F0 path (observation rows, back-pointers)
   int clip_warps = 16;     // warps per CTA of the fused kernel
   int ctas_per_sm = 1;
   int mel_floats = 0;      // floats in the padded sparse mel weight table
@@ -113,7 +124,7 @@ struct PhaseTimer {
 };
 
 struct Layout {   // carve-up of the caller's workspace
-  size_t off_offsets, off_frame_off, off_lengths, off_info, off_counter, header_bytes;
+  size_t off_offsets, off_frame_off, off_lengths, off_yin_chunk, off_info, off_counter, header_bytes;
 };
 
 Layout header_layout(int64_t n) {
@@ -122,6 +133,7 @@ Layout header_layout(int64_t n) {
   L.off_offsets = o;   o += align_up(sizeof(long long) * n, 16);
   L.off_frame_off = o; o += align_up(sizeof(long long) * (n + 1), 16);
   L.off_lengths = o;   o += align_up(sizeof(int) * n, 16);
+  L.off_yin_chunk = o; o += align_up(sizeof(int) * (n + 1), 16);   // prefix of pYIN frame chunks per clip
   L.off_info = o;      o += align_up(sizeof(afx::ClipInfo) * n, 16);   // produced on device; not staged from the host
   L.off_counter = o;   o += 256;
   L.header_bytes = align_up(o, 256);
@@ -261,6 +273,39 @@ int afx_create(const afx_config_t* cfg, afx_handle_t* out) {
     if (!found) { delete h; return fail(AFX_ERR_UNSUPPORTED, "no CTA shape of the fused kernel fits this device's shared memory"); }
   }
   CUDA_TRY(cudaFuncSetAttribute(h->clip_fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)clip_smem_bytes(h, nullptr)));
+  {  // pYIN constants and tables (F0 group); an unsupported f0 range only disables that group
+    afx::host::PyinConsts& pc = h->pc;
+    h->f0_ok = afx::host::pyin_consts(cfg->sr, cfg->frame_length, cfg->hop_length, cfg->f0_min, cfg->f0_max, pc) &&
+               pc.n_lags <= 32 * afx::kYinMaxGroups * 2 - 4 && pc.max_period <= 32 * 22;
+    if (h->f0_ok) {
+      std::vector<double> all;
+      auto push = [&](const std::vector<double>& v) { const size_t o = all.size(); all.insert(all.end(), v.begin(), v.end()); while (all.size() & 1) all.push_back(0.0); return o; };
+      const size_t o_th = push(pc.thresholds), o_b = push(pc.beta), o_bc = push(pc.beta_cum), o_bf = push(pc.boltz_fact),
+                   o_be = push(pc.boltz_exp), o_lt = push(pc.ltrans_same), o_ec = push(pc.edge_corr), o_fr = push(pc.freqs);
+      CUDA_TRY(upload(all, &h->d_pyin));
+      h->ptab.thresholds = h->d_pyin + o_th; h->ptab.beta = h->d_pyin + o_b; h->ptab.beta_cum = h->d_pyin + o_bc;
+      h->ptab.boltz_fact = h->d_pyin + o_bf; h->ptab.boltz_exp = h->d_pyin + o_be;
+      h->d_lt_same = h->d_pyin + o_lt; h->d_edge_corr = h->d_pyin + o_ec; h->d_freqs = h->d_pyin + o_fr;
+      const int need_c = (pc.max_period + 31) / 32;
+      h->yin_c = need_c <= 8 ? 8 : need_c <= 11 ? 11 : need_c <= 16 ? 16 : 22;
+      h->yin_cap = ((pc.n_lags / 2 + 2) + 3) & ~3;
+      h->yin_rec_bytes = (int)align_up(24 + 10 * (size_t)h->yin_cap, 16);
+      h->yin_lag_pad = (pc.max_period + 1 + 127) & ~127;
+      h->yin_tile = afx::kYinBlocks * cfg->hop_length + h->yin_lag_pad + 8;
+      h->yin_frames_per_chunk = afx::kYinBlocks - (cfg->frame_length / (2 * cfg->hop_length) - 1);
+      const size_t ph1 = (size_t)h->yin_tile * 4 + (size_t)afx::kYinBlocks * h->yin_lag_pad * 4 + ((size_t)h->yin_tile + 2) * 8;
+      const size_t ph2 = (size_t)afx::kYinWarps * 2 * h->yin_cap * 8;
+      h->yin_smem = align_up(std::max(ph1, ph2), 16);
+      h->vit_smem = align_up(((size_t)7 * pc.n_bins + 2 * pc.half_width + 2) * 8 + (size_t)2 * pc.n_bins * 2, 16);
+      if (h->yin_smem > (size_t)prop.sharedMemPerBlockOptin || h->vit_smem > (size_t)prop.sharedMemPerBlockOptin) h->f0_ok = false;
+    }
+    if (h->f0_ok) {
+      const void* yk = h->yin_c == 8 ? (const void*)afx::yin_obs_kernel<8> : h->yin_c == 11 ? (const void*)afx::yin_obs_kernel<11>
+                     : h->yin_c == 16 ? (const void*)afx::yin_obs_kernel<16> : (const void*)afx::yin_obs_kernel<22>;
+      CUDA_TRY(cudaFuncSetAttribute(yk, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->yin_smem));
+      CUDA_TRY(cudaFuncSetAttribute(afx::viterbi_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->vit_smem));
+    }
+  }
   CUDA_TRY(cudaEventCreateWithFlags(&h->stage_ev, cudaEventDisableTiming));
   *out = h;
   return AFX_OK;
@@ -270,7 +315,7 @@ int afx_destroy(afx_handle_t h) {
   if (!h) return AFX_OK;
   cudaSetDevice(h->cfg.device);
   cudaDeviceSynchronize();
-  cudaFree(h->d_window); cudaFree(h->d_twiddle); cudaFree(h->d_ptw); cudaFree(h->d_mel_w); cudaFree(h->d_mel_k0); cudaFree(h->d_dct_t);
+  cudaFree(h->d_window); cudaFree(h->d_twiddle); cudaFree(h->d_ptw); cudaFree(h->d_pyin); cudaFree(h->d_f0_ws); cudaFree(h->d_mel_w); cudaFree(h->d_mel_k0); cudaFree(h->d_dct_t);
   if (h->h_stage) cudaFreeHost(h->h_stage);
   if (h->stage_ev) cudaEventDestroy(h->stage_ev);
   cudaFree(h->d_ws); cudaFree(h->d_audio[0]); cudaFree(h->d_audio[1]); cudaFree(h->d_sum); cudaFree(h->d_meta);
@@ -309,7 +354,8 @@ int afx_extract(afx_handle_t h, const float* d_audio, const int64_t* h_offsets, 
   if (!d_audio || !h_offsets || !h_lengths || !d_summaries || !d_meta || !d_workspace)
     return fail(AFX_ERR_INVALID_ARG, "afx_extract: null pointer argument");
   if ((feature_mask & ~AFX_FEAT_ALL) != 0) return fail(AFX_ERR_INVALID_ARG, "afx_extract: unknown feature bits 0x%x", feature_mask);
-  if (feature_mask & AFX_FEAT_F0) return fail(AFX_ERR_UNSUPPORTED, "afx_extract: the F0 (pYIN) group is not built yet");
+  if ((feature_mask & AFX_FEAT_F0) && !h->f0_ok)
+    return fail(AFX_ERR_UNSUPPORTED, "afx_extract: the F0 (pYIN) group does not support this f0_min / f0_max / frame geometry");
   if ((reinterpret_cast<uintptr_t>(d_audio) & 15u) != 0) return fail(AFX_ERR_INVALID_ARG, "afx_extract: d_audio must be 16-byte aligned");
   cudaStream_t stream = static_cast<cudaStream_t>(stream_v);
   CUDA_TRY(cudaSetDevice(h->cfg.device));
@@ -331,17 +377,23 @@ int afx_extract(afx_handle_t h, const float* d_audio, const int64_t* h_offsets, 
   long long* s_offsets = reinterpret_cast<long long*>(st + L.off_offsets);
   long long* s_frame_off = reinterpret_cast<long long*>(st + L.off_frame_off);
   int* s_lengths = reinterpret_cast<int*>(st + L.off_lengths);
-  long long fo = 0, max_len = 0;
+  int* s_ychunk = reinterpret_cast<int*>(st + L.off_yin_chunk);
+  const int yF = std::max(1, h->yin_frames_per_chunk);
+  long long fo = 0, max_len = 0, yc = 0;
   for (int i = 0; i < n; ++i) {
     if (h_lengths[i] < 0) return fail(AFX_ERR_INVALID_ARG, "afx_extract: clip %d has negative length", i);
     if (h_offsets[i] < 0 || (h_offsets[i] & 3) != 0) return fail(AFX_ERR_INVALID_ARG, "afx_extract: clip %d offset %lld is not a multiple of 4 samples", i, (long long)h_offsets[i]);
     s_offsets[i] = h_offsets[i];
     s_lengths[i] = h_lengths[i];
     s_frame_off[i] = fo;
+    s_ychunk[i] = (int)yc;
+    yc += ceil_div(frames_ub(h, h_lengths[i]), yF);
+    if (yc > 0x7fffff00LL) return fail(AFX_ERR_UNSUPPORTED, "afx_extract: batch too large");
     fo += frames_ub(h, h_lengths[i]);
     max_len = std::max<long long>(max_len, h_lengths[i]);
   }
   s_frame_off[n] = fo;
+  s_ychunk[n] = (int)yc;
   const bool one_pass = single_pass(h);
   const long long max_trim_blocks = (200 * 1024) / 4 - 8;
   if (!one_pass && ceil_div(max_len, afx::kTrimHop) > max_trim_blocks)
@@ -385,6 +437,70 @@ int afx_extract(afx_handle_t h, const float* d_audio, const int64_t* h_offsets, 
     PhaseTimer pt(h, stream, AFX_PHASE_FRAMES);
     h->clip_fn<<<grid, h->clip_warps * 32, smem, stream>>>(ca);
     ++g_launches;
+  }
+  if (feature_mask & AFX_FEAT_F0) {
+    // ---- pYIN: waves of clips sized by the handle-owned scratch (observation rows + back-pointers + states)
+    const afx::host::PyinConsts& pc = h->pc;
+    const size_t per_frame = (size_t)h->yin_rec_bytes + (size_t)4 * pc.n_bins + 2;
+    size_t budget = (size_t)4096 << 20;
+    if (const char* e = getenv("AFX_F0_SCRATCH_MB")) { const long long v = atoll(e); if (v >= 16) budget = (size_t)v << 20; }
+    long long max_f = 1;
+    for (int i = 0; i < n; ++i) max_f = std::max(max_f, s_frame_off[i + 1] - s_frame_off[i]);
+    long long cap_frames = std::max<long long>(max_f, std::min<long long>(fo, (long long)(budget / per_frame)));
+    const size_t need = (size_t)cap_frames * per_frame + 4096;
+    if (h->d_f0_ws_bytes < need) {
+      CUDA_TRY(cudaStreamSynchronize(stream));
+      if (h->d_f0_ws) CUDA_TRY(cudaFree(h->d_f0_ws));
+      h->d_f0_ws = nullptr; h->d_f0_ws_bytes = 0;
+      CUDA_TRY(cudaMalloc(&h->d_f0_ws, need));
+      h->d_f0_ws_bytes = need;
+    }
+    unsigned char* f0ws = static_cast<unsigned char*>(h->d_f0_ws);
+    unsigned char* d_obs = f0ws;
+    unsigned short* d_ptr = reinterpret_cast<unsigned short*>(f0ws + align_up((size_t)cap_frames * h->yin_rec_bytes, 256));
+    short* d_states = reinterpret_cast<short*>(reinterpret_cast<unsigned char*>(d_ptr) + align_up((size_t)cap_frames * 4 * pc.n_bins, 256));
+    const int* d_ychunk = reinterpret_cast<const int*>(ws + L.off_yin_chunk);
+    int c0 = 0;
+    while (c0 < n) {
+      int c1 = c0; long long F = 0;
+      while (c1 < n) {
+        const long long f = s_frame_off[c1 + 1] - s_frame_off[c1];
+        if (c1 > c0 && F + f > cap_frames) break;
+        F += f; ++c1;
+      }
+      {
+        afx::YinArgs ya;
+        ya.audio = d_audio; ya.offsets = d_offsets; ya.lengths = d_lengths; ya.info = d_info;
+        ya.chunk_off = d_ychunk; ya.frame_off = d_frame_off; ya.clip_begin = c0; ya.clip_end = c1; ya.frame_base = s_frame_off[c0];
+        ya.n_fft = h->cfg.frame_length; ya.hop = hop; ya.win = pc.win_length; ya.min_period = pc.min_period; ya.max_period = pc.max_period;
+        ya.n_bins = pc.n_bins; ya.frames_per_chunk = h->yin_frames_per_chunk; ya.lag_pad = h->yin_lag_pad; ya.tile = h->yin_tile;
+        ya.cap = h->yin_cap; ya.rec_bytes = h->yin_rec_bytes; ya.coef = h->cfg.pre_emphasis; ya.sr = (double)h->cfg.sr; ya.fmin = h->cfg.f0_min;
+        ya.tab = h->ptab; ya.obs = d_obs;
+        const int grid_y = s_ychunk[c1] - s_ychunk[c0];
+        PhaseTimer pt(h, stream, AFX_PHASE_YIN);
+        if (grid_y > 0) {
+          if (h->yin_c == 8) afx::yin_obs_kernel<8><<<grid_y, afx::kYinThreads, h->yin_smem, stream>>>(ya);
+          else if (h->yin_c == 11) afx::yin_obs_kernel<11><<<grid_y, afx::kYinThreads, h->yin_smem, stream>>>(ya);
+          else if (h->yin_c == 16) afx::yin_obs_kernel<16><<<grid_y, afx::kYinThreads, h->yin_smem, stream>>>(ya);
+          else afx::yin_obs_kernel<22><<<grid_y, afx::kYinThreads, h->yin_smem, stream>>>(ya);
+          ++g_launches;
+        }
+      }
+      {
+        afx::VitArgs va;
+        va.info = d_info; va.frame_off = d_frame_off; va.clip_begin = c0; va.frame_base = s_frame_off[c0];
+        va.obs = d_obs; va.cap = h->yin_cap; va.rec_bytes = h->yin_rec_bytes; va.n_bins = pc.n_bins; va.half_width = pc.half_width;
+        va.lt_same = h->d_lt_same; va.edge_corr = h->d_edge_corr; va.freqs = h->d_freqs;
+        va.delta_switch = pc.ltrans_sw[pc.half_width] - pc.ltrans_same[pc.half_width];
+        va.log_tiny = pc.log_tiny; va.log_init_unvoiced = pc.log_init_unvoiced;
+        va.ptr = d_ptr; va.states = d_states; va.summaries = d_summaries; va.summary_width = afx_summary_width(h);
+        va.frames_out = d_frames; va.frame_width = afx_frame_width(h); va.n_mfcc = h->cfg.n_mfcc;
+        PhaseTimer pt(h, stream, AFX_PHASE_VITERBI);
+        afx::viterbi_kernel<<<c1 - c0, afx::kVitThreads, h->vit_smem, stream>>>(va);
+        ++g_launches;
+      }
+      c0 = c1;
+    }
   }
   CUDA_TRY(cudaGetLastError());
   return AFX_OK;

@@ -326,7 +326,11 @@ def pyin_transition(n_pitch_bins: int, transition_width: int, switch_prob: float
         row[:max(0, i - w // 2)] = 0
         local[i] = row
     local /= local.sum(axis=1, keepdims=True)
-    t_switch = np.array([[1 - switch_prob, switch_prob], [switch_prob, 1 - switch_prob]])
+    # librosa.sequence.transition_loop(2, 1 - switch_prob): diagonal p, off-diagonal (1 - p) / (n_states - 1)
+    p_stay = 1 - switch_prob
+    t_switch = np.empty((2, 2))
+    t_switch[:] = (1.0 - p_stay) / (2 - 1)
+    t_switch[0, 0] = t_switch[1, 1] = p_stay
     return np.kron(t_switch, local)
 
 

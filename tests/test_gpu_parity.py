@@ -253,3 +253,52 @@ def test_reference_api_files_and_evaluator(torch_cuda, tmp_path):
     assert (tmp_path / "report" / "evaluation_detailed.json").exists()
     assert (tmp_path / "report" / "evaluation_summary.csv").exists()
     assert rep["quality_metrics"]["total_files"] == 3
+
+
+F0_CENTS = 1.0          # BASELINE.json north_star: "F0: within 1 cent on voiced frames"
+F0_VOICING = 0.999      # "voicing decisions matching on at least 99.9% of frames"
+
+
+@pytest.mark.parametrize("cfg,secs", [
+    (dict(sr=22050, frame_length=1024, hop_length=256, n_mfcc=13), [3.0, 2.0, 1.2, 4.0]),      # C1 / C2 geometry
+    (dict(sr=16000, frame_length=512, hop_length=128, n_mfcc=40), [2.5, 1.5]),                  # C3
+    (dict(sr=44100, frame_length=2048, hop_length=512, n_mfcc=13), [2.0, 1.5]),                 # C4
+], ids=["22050-1024-256", "16000-512-128", "44100-2048-512"])
+def test_pyin_f0_track_and_statistics(torch_cuda, cfg, secs):
+    """extract_f0 (core/feature_extractor.py:76-114): the decoded pYIN track frame by frame and the four summary keys."""
+    from audio_feature_extraction_b200 import AudioFeatureExtractor
+    from audio_feature_extraction_b200.synth import make_clip
+    from oracle import OracleFeatureExtractor
+
+    kind = "music" if cfg["sr"] == 44100 else "speech"
+    f_lo, f_hi = (80.0, 400.0) if cfg["sr"] == 16000 else (110.0, 880.0)
+    clips = [make_clip(700 + s, sr=cfg["sr"], seconds=sec, f_lo=f_lo, f_hi=f_hi, kind=kind) for s, sec in enumerate(secs)]
+    rng = np.random.default_rng(3)
+    clips.append((0.05 * rng.standard_normal(int(1.5 * cfg["sr"]))).astype(np.float32))       # noise only: mostly unvoiced
+    ex = AudioFeatureExtractor(**cfg)
+    ora = OracleFeatureExtractor(**cfg)
+    summ, meta, frames, rows = _framewise(ex, clips, groups=("f0", "mfcc", "energy"))
+    n = ex.n_mfcc
+    total = agree = 0
+    for i, y in enumerate(clips):
+        yt = ora.preprocess_audio(y)
+        f0, voiced, vprob = ora.f0_track(yt)
+        T = len(f0)
+        assert meta[i, 3] == T and meta[i, 0] == 0
+        got = frames[rows[i]:rows[i] + T, 3 * n + 1].astype(np.float64)
+        got_v = ~np.isnan(got)
+        total += T; agree += int(np.sum(got_v == voiced))
+        both = got_v & voiced
+        if both.any():
+            cents = 1200.0 * np.abs(np.log2(got[both] / f0[both]))
+            assert cents.max() <= F0_CENTS, (i, cents.max())
+        np.testing.assert_allclose(frames[rows[i]:rows[i] + T, 3 * n + 2], vprob, atol=1e-5)
+        ref = ora.extract_f0(yt)
+        if np.array_equal(got_v, voiced):
+            assert summ[i, 0] == pytest.approx(ref["f0_mean"], rel=1e-5, abs=1e-6)
+            assert summ[i, 1] == pytest.approx(ref["f0_std"], rel=1e-4, abs=1e-4)
+            assert summ[i, 2] == pytest.approx(ref["f0_missing_rate"], abs=1e-6)
+            assert summ[i, 3] == pytest.approx(ref["f0_quality"], abs=1e-6)
+        # the other groups are unaffected by the F0 launches
+        _check_clip(ex, ora, y, summ[i], meta[i], frames, rows[i], n)
+    assert agree / total >= F0_VOICING, (agree, total)
