@@ -168,6 +168,38 @@ class AudioFeatureExtractor:
         m = meta.cpu().numpy()
         return self.rows_to_dicts(s, m, names, features_to_extract, skip_errors=skip_errors)
 
+    def batch_process_sharded(self, audio_dir: str, features_to_extract: Optional[Sequence[str]] = None):
+        """batch_process over the ranks of an initialised torch.distributed job (one process per GPU): the sorted
+        *.wav list is block-partitioned by rank, every rank extracts its shard on its own GPU, the summary rows are
+        gathered to rank 0 (NCCL), which returns the list of dicts; the other ranks return None."""
+        import torch
+        import torch.distributed as dist
+        from ..distributed import extract_sharded
+
+        files = sorted(str(p) for p in Path(audio_dir).glob("*.wav"))
+        dev = torch.device("cuda", self.device)
+        self._h()
+
+        def rows(shard):
+            clips, ok = [], []
+            for f in shard:
+                try:
+                    clips.append(self.load_audio(f)[0]); ok.append(True)
+                except Exception as e:   # unreadable file: reported as a failed row, skipped on rank 0 (reference :233-235)
+                    self.logger.error(f"處理文件 {Path(f).name} 失敗: {str(e)}")
+                    clips.append(np.zeros(0, np.float32)); ok.append(False)
+            if not clips:
+                return (torch.zeros((0, self.summary_width), dtype=torch.float32, device=dev),
+                        torch.zeros((0, 4), dtype=torch.int32, device=dev))
+            buf, offsets, lengths = self.pack_clips(clips)
+            summ, meta, _ = self.extract_batch_device(buf.to(dev, non_blocking=True), offsets, lengths, features_to_extract)
+            return summ, meta
+
+        summ, meta = extract_sharded(rows, files)
+        if summ is None:
+            return None
+        return self.rows_to_dicts(summ.cpu().numpy(), meta.cpu().numpy(), files, features_to_extract, skip_errors=True)
+
     def rows_to_dicts(self, s: np.ndarray, m: np.ndarray, names: Sequence[str], features_to_extract=None,
                       skip_errors: bool = False) -> List[Dict[str, Any]]:
         mask = _mask_of(features_to_extract)

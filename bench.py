@@ -49,6 +49,8 @@ def parse_args():
     ap.add_argument("--cpu-clips", type=int, default=0, help="clips of the CPU baseline sample; 0 = auto")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-f0", action="store_true")
+    ap.add_argument("--f0-clips", type=int, default=1000, help="clips of the full-path (with pYIN) sample")
     return ap.parse_args()
 
 
@@ -227,11 +229,12 @@ def _peak_hbm():
         return 6650.0, "fallback (B200_PROFILING.md)"
 
 
-def _ncu_traffic(kernel: str):
-    """dram bytes per launch of `kernel` from the committed ncu --set full summary, if one exists."""
+def _ncu_traffic(kernel: str, n_clips: int):
+    """dram bytes per launch of `kernel`: bytes per clip from the committed ncu --set full capture (the launch covers
+    the whole batch, so the capture on a smaller batch is scaled by the clip count)."""
     p = ROOT / "profiles" / "ncu_traffic.json"
     try:
-        return json.loads(p.read_text())[kernel]["dram_bytes_per_launch"]
+        return json.loads(p.read_text())[kernel]["dram_bytes_per_clip"] * n_clips
     except Exception:
         return None
 
@@ -314,44 +317,70 @@ def run_native(args):
     kernel_name = {"frames": "clip_kernel", "trim": "trim_kernel", "yin": "yin_kernel", "viterbi": "viterbi_kernel",
                    "pcm": "pcm16_to_f32_kernel"}.get(dom, dom)
     roofline = {"bound": "hbm", "kernel": kernel_name, "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                "traffic": _ncu_traffic(kernel_name), "peak_source": peak_src,
+                "traffic": _ncu_traffic(kernel_name, n), "peak_source": peak_src,
                 "algorithmic_bytes_per_launch": bytes_per_step / max(phases[dom]["launches_per_step"], 1),
                 "avg_launch_ms": dom_ms / max(phases[dom]["launches_per_step"], 1),
                 "whole_path_frac": bytes_per_step / (ms_per_step * 1e-3) / 1e9 / peak, "phases": phases}
 
-    # ---- e2e: the same metric through the C-ABI host entry (pinned host buffer -> H2D waves -> kernels -> D2H rows)
+    # ---- e2e: the same metric through the C-ABI host entry (pinned host buffer -> H2D waves -> kernels -> D2H rows).
+    # Headline: 16-bit PCM as it sits in a WAV data chunk (what load_audio decodes, reference :52), converted on the
+    # device; the float32-buffer variant is reported next to it.
     e2e = None
     if not args.no_e2e:
         ne = args.e2e_clips or max(1, n // 4)
         ne = min(ne, n)
         stride = int(offsets[1] - offsets[0]) if n > 1 else int(audio.numel())
         span = ne * stride
-        host = torch.empty(span, dtype=torch.float32, pin_memory=True)
-        host.copy_(audio[:span]); torch.cuda.synchronize()
-        hs = np.zeros((ne, SS), np.float32); hm = np.zeros((ne, 4), np.int32)
         mask = sum({"f0": 1, "mfcc": 2, "energy": 4}[g] for g in groups)
         off8 = np.ascontiguousarray(offsets[:ne]); len8 = np.ascontiguousarray(lengths[:ne])
         assert (off8 % 8 == 0).all()
+        hs = np.zeros((ne, SS), np.float32); hm = np.zeros((ne, 4), np.int32)
 
-        def e2e_step():
-            N.check(L.afx_extract_host_packed(h, host.data_ptr(), N.SAMPLE_F32, span, off8.ctypes.data, len8.ctypes.data,
-                                              ne, mask, hs.ctypes.data, hm.ctypes.data))
-        for _ in range(max(1, min(args.warmup, 2))):
-            e2e_step()
-        barrier()
-        t0 = time.perf_counter()
-        for _ in range(args.steps):
-            e2e_step()
-        dt = time.perf_counter() - t0
-        t = torch.tensor([dt], dtype=torch.float64, device=dev)
-        if world > 1:
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        dt = float(t.item())
+        def timed(host, fmt):
+            def e2e_step():
+                N.check(L.afx_extract_host_packed(h, host.data_ptr(), fmt, span, off8.ctypes.data, len8.ctypes.data,
+                                                  ne, mask, hs.ctypes.data, hm.ctypes.data))
+            for _ in range(max(1, min(args.warmup, 2))):
+                e2e_step()
+            barrier()
+            t0 = time.perf_counter()
+            for _ in range(args.steps):
+                e2e_step()
+            dt = time.perf_counter() - t0
+            tt = torch.tensor([dt], dtype=torch.float64, device=dev)
+            if world > 1:
+                dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+            return float(tt.item())
+
+        host32 = torch.empty(span, dtype=torch.float32, pin_memory=True)
+        host32.copy_(audio[:span]); torch.cuda.synchronize()
+        dt32 = timed(host32, N.SAMPLE_F32)
         assert np.array_equal(hm[:, 0], meta[:ne, 0].cpu().numpy())
-        e2e = {"value": world * _hours(ne, cfg) * args.steps / dt, "unit": UNIT,
-               "h2d_bytes_per_step": int(4 * span), "d2h_bytes_per_step": int(ne * (4 * SS + 16)),
-               "clips_per_gpu": ne, "api": "afx_extract_host_packed (pinned float32 host buffer)"}
-        del host
+        host16 = torch.empty(span, dtype=torch.int16, pin_memory=True)
+        host16.copy_((audio[:span] * 32768.0).round().clamp_(-32768, 32767).to(torch.int16)); torch.cuda.synchronize()
+        del host32
+        dt16 = timed(host16, N.SAMPLE_S16)
+        ok16 = int((hm[:, 0] == 0).sum())
+        e2e = {"value": world * _hours(ne, cfg) * args.steps / dt16, "unit": UNIT,
+               "h2d_bytes_per_step": int(2 * span), "d2h_bytes_per_step": int(ne * (4 * SS + 16)),
+               "clips_per_gpu": ne, "clips_ok": ok16, "api": "afx_extract_host_packed (pinned 16-bit PCM host buffer, converted on the device)",
+               "float32_buffer": {"value": world * _hours(ne, cfg) * args.steps / dt32, "h2d_bytes_per_step": int(4 * span)}}
+        del host16
+
+    # ---- the full path with pYIN F0 on a bounded sample (compute-bound by construction; reported beside the headline)
+    f0_path = None
+    if "f0" not in groups and not args.no_f0 and rank == 0:
+        nf = min(n, args.f0_clips)
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        allg = ("f0", "mfcc", "energy")
+        ex.extract_batch_device(audio, offsets[:nf], lengths[:nf], allg)
+        torch.cuda.synchronize()
+        ev0.record()
+        s_f0, m_f0, _ = ex.extract_batch_device(audio, offsets[:nf], lengths[:nf], allg)
+        ev1.record(); torch.cuda.synchronize()
+        ms_f0 = ev0.elapsed_time(ev1)
+        f0_path = {"value": _hours(nf, cfg) / (ms_f0 * 1e-3), "unit": UNIT, "clips": nf, "ms": ms_f0,
+                   "features": "f0+mfcc+energy", "voiced_quality_mean": float(s_f0[:, 3].mean().item())}
 
     # ---- CPU baseline beside it (rank 0, N = 1 only): the oracle on a bounded sample of the same clips
     cpu_baseline = None
@@ -374,7 +403,7 @@ def run_native(args):
             "dtype": "f32", "data": "synthetic",
             "config": {"workload": _workload_name(args, cfg, n), "clips_ok": ok, "l2": "inputs (8.8 GB/GPU) larger than L2, no flush",
                        "sharding": f"clips by rank x{world}, NCCL gather of summary rows to rank 0 each step" if world > 1 else "single GPU"},
-            "roofline": roofline, "cpu_baseline": cpu_baseline, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks,
+            "roofline": roofline, "cpu_baseline": cpu_baseline, "e2e": e2e, "f0_path": f0_path, "gpu_launches": int(launches), "clocks": clocks,
         }
         print(json.dumps(line), flush=True)
     if world > 1:
