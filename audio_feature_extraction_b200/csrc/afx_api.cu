@@ -280,11 +280,11 @@ int afx_create(const afx_config_t* cfg, afx_handle_t* out) {
     if (h->f0_ok) {
       std::vector<double> all;
       auto push = [&](const std::vector<double>& v) { const size_t o = all.size(); all.insert(all.end(), v.begin(), v.end()); while (all.size() & 1) all.push_back(0.0); return o; };
-      const size_t o_th = push(pc.thresholds), o_b = push(pc.beta), o_bc = push(pc.beta_cum), o_bf = push(pc.boltz_fact),
+      const size_t o_th = push(pc.thresholds), o_b = push(pc.beta), o_bc = push(pc.beta_cum), o_bs = push(pc.beta_suf), o_bf = push(pc.boltz_fact),
                    o_be = push(pc.boltz_exp), o_lt = push(pc.ltrans_same), o_ec = push(pc.edge_corr), o_fr = push(pc.freqs);
       CUDA_TRY(upload(all, &h->d_pyin));
       h->ptab.thresholds = h->d_pyin + o_th; h->ptab.beta = h->d_pyin + o_b; h->ptab.beta_cum = h->d_pyin + o_bc;
-      h->ptab.boltz_fact = h->d_pyin + o_bf; h->ptab.boltz_exp = h->d_pyin + o_be;
+      h->ptab.boltz_fact = h->d_pyin + o_bf; h->ptab.boltz_exp = h->d_pyin + o_be; h->ptab.beta_suf = h->d_pyin + o_bs;
       h->d_lt_same = h->d_pyin + o_lt; h->d_edge_corr = h->d_pyin + o_ec; h->d_freqs = h->d_pyin + o_fr;
       const int need_c = (pc.max_period + 31) / 32;
       h->yin_c = need_c <= 8 ? 8 : need_c <= 11 ? 11 : need_c <= 16 ? 16 : 22;
@@ -294,9 +294,9 @@ int afx_create(const afx_config_t* cfg, afx_handle_t* out) {
       h->yin_tile = afx::kYinBlocks * cfg->hop_length + h->yin_lag_pad + 8;
       h->yin_frames_per_chunk = afx::kYinBlocks - (cfg->frame_length / (2 * cfg->hop_length) - 1);
       const size_t ph1 = (size_t)h->yin_tile * 4 + (size_t)afx::kYinBlocks * h->yin_lag_pad * 4 + ((size_t)h->yin_tile + 2) * 8;
-      const size_t ph2 = (size_t)afx::kYinWarps * 2 * h->yin_cap * 8;
+      const size_t ph2 = (size_t)afx::kYinWarps * h->yin_cap * (2 * 8 + 4);   // trough heights + periods (double) + packed compact list
       h->yin_smem = align_up(std::max(ph1, ph2), 16);
-      h->vit_smem = align_up(((size_t)7 * pc.n_bins + 2 * pc.half_width + 2) * 8 + (size_t)2 * pc.n_bins * 2, 16);
+      h->vit_smem = align_up(afx::VitGeo(pc.n_bins, pc.half_width).bytes(pc.n_bins), 16);
       if (h->yin_smem > (size_t)prop.sharedMemPerBlockOptin || h->vit_smem > (size_t)prop.sharedMemPerBlockOptin) h->f0_ok = false;
     }
     if (h->f0_ok) {

@@ -30,6 +30,7 @@ struct PyinTables {
   const double* beta_cum;     // [101]
   const double* boltz_fact;   // [cap + 1]
   const double* boltz_exp;    // [cap + 1]
+  const double* beta_suf;     // [102] beta_suf[j] = sum(beta[j - 1:]), j = 1 .. 101 (0 at 101)
 };
 
 struct YinArgs {
@@ -248,89 +249,129 @@ __global__ void __launch_bounds__(kYinThreads, 1) yin_obs_kernel(YinArgs a) {
     }
     return;
   }
-  // lane-per-trough in groups of 32; jmin = first threshold index j (1..100) with h < thresholds[j], 101 if none
-  double prob[kYinMaxGroups];
-  int jmin[kYinMaxGroups];
-  int jlo = 101;
+  // ---- global minimum trough (first index): it gets no_trough_prob * sum(beta[:jmin - 1]) on top of its sweep sum
+  double bh = 1.0e300; int bi = 0x7fffffff;
 #pragma unroll
   for (int g = 0; g < kYinMaxGroups; ++g) {
-    prob[g] = 0.0; jmin[g] = 102;
+    if (32 * g >= n_tr) break;
     const int ai = 32 * g + lane;
-    if (ai < n_tr) {
-      const double h = lh[ai];
-      int j = min(100, max(1, (int)(h * 100.0)));
-      while (j > 1 && h < a.tab.thresholds[j - 1]) --j;
-      while (j <= 100 && !(h < a.tab.thresholds[j])) ++j;
-      jmin[g] = j;
-      jlo = min(jlo, j);
-    }
+    if (ai < n_tr) { const double h = lh[ai]; if (h < bh) { bh = h; bi = ai; } }
   }
 #pragma unroll
-  for (int o = 16; o > 0; o >>= 1) jlo = min(jlo, __shfl_xor_sync(0xffffffffu, jlo, o));
+  for (int o = 16; o > 0; o >>= 1) {
+    const double oh = __shfl_xor_sync(0xffffffffu, bh, o);
+    const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+    if (oh < bh || (oh == bh && oi < bi)) { bh = oh; bi = oi; }
+  }
+  // ---- compaction (order kept): only troughs below some threshold (jmin <= 100; jmin = first j in 1..100 with
+  // h < thresholds[j]) and the global minimum can get a non-zero probability.  packed entry = jmin << 16 | trough index;
+  // am = 128-bit set of the activation points {jmin}
+  unsigned* cpk = reinterpret_cast<unsigned*>(smem_raw + (size_t)kYinWarps * 2 * a.cap * 8) + (size_t)warp * a.cap;
   const unsigned lt_mask = (1u << lane) - 1u;
-  for (int j = jlo; j <= 100; ++j) {
+  unsigned am0 = 0u, am1 = 0u, am2 = 0u, am3 = 0u;
+  int n_c = 0;
+#pragma unroll
+  for (int g = 0; g < kYinMaxGroups; ++g) {
+    if (32 * g >= n_tr) break;
+    const int ai = 32 * g + lane;
+    int j = 102;
+    bool act = false;
+    if (ai < n_tr) {
+      const double h = lh[ai];
+      j = min(100, max(1, (int)(h * 100.0)));
+      while (j > 1 && h < __ldg(a.tab.thresholds + j - 1)) --j;
+      while (j <= 100 && !(h < __ldg(a.tab.thresholds + j))) ++j;
+      act = j <= 100 || ai == bi;
+    }
+    const unsigned bal = __ballot_sync(0xffffffffu, act);
+    if (act) {
+      cpk[n_c + __popc(bal & lt_mask)] = ((unsigned)j << 16) | (unsigned)ai;
+      if (j <= 100) {
+        const unsigned bit = 1u << (j & 31);
+        const int w = j >> 5;
+        am0 |= w == 0 ? bit : 0u; am1 |= w == 1 ? bit : 0u; am2 |= w == 2 ? bit : 0u; am3 |= w == 3 ? bit : 0u;
+      }
+    }
+    n_c += __popc(bal);
+  }
+  am0 = __reduce_or_sync(0xffffffffu, am0); am1 = __reduce_or_sync(0xffffffffu, am1);
+  am2 = __reduce_or_sync(0xffffffffu, am2); am3 = __reduce_or_sync(0xffffffffu, am3);
+  __syncwarp();
+  // first activation point >= from (101 if none); warp-uniform
+  auto next_act = [&](int from) -> int {
+    const unsigned words[4] = {am0, am1, am2, am3};
+#pragma unroll
+    for (int w = 0; w < 4; ++w) {
+      unsigned m = words[w];
+      const int sh = from - 32 * w;
+      if (sh >= 32) m = 0u; else if (sh > 0) m &= 0xffffffffu << sh;
+      if (m) return 32 * w + __ffs(m) - 1;
+    }
+    return 101;
+  };
+  // ---- threshold sweep over the compact list, lane-per-candidate in groups of 32.  Between two activation points the
+  // active set (hence every rank and the Boltzmann normalisation) is constant, so the thresholds of a segment [j, jn)
+  // contribute (sum of their beta weights) * boltzmann.pmf(rank; 2, n_active) in one step.
+  int cjm[kYinMaxGroups], cai[kYinMaxGroups];
+  double prob[kYinMaxGroups];
+#pragma unroll
+  for (int g = 0; g < kYinMaxGroups; ++g) {
+    cjm[g] = 102; cai[g] = -1; prob[g] = 0.0;
+    const int c = 32 * g + lane;
+    if (c < n_c) { const unsigned pk = cpk[c]; cjm[g] = (int)(pk >> 16); cai[g] = (int)(pk & 0xffffu); }
+  }
+  for (int j = next_act(1); j <= 100;) {
+    const int jn = next_act(j + 1);
     unsigned bal[kYinMaxGroups];
     int n_act = 0;
 #pragma unroll
     for (int g = 0; g < kYinMaxGroups; ++g) {
-      bal[g] = (32 * g < n_tr) ? __ballot_sync(0xffffffffu, jmin[g] <= j) : 0u;
+      if (32 * g >= n_c) break;
+      bal[g] = __ballot_sync(0xffffffffu, cjm[g] <= j);
       n_act += __popc(bal[g]);
     }
-    const double cj = a.tab.beta[j - 1] * a.tab.boltz_fact[n_act];
+    const double cj = (__ldg(a.tab.beta_suf + j) - __ldg(a.tab.beta_suf + jn)) * __ldg(a.tab.boltz_fact + n_act);
     int carry = 0;
 #pragma unroll
     for (int g = 0; g < kYinMaxGroups; ++g) {
-      if (jmin[g] <= j) prob[g] = fma(cj, a.tab.boltz_exp[carry + __popc(bal[g] & lt_mask)], prob[g]);
+      if (32 * g >= n_c) break;
+      if (cjm[g] <= j) prob[g] = fma(cj, __ldg(a.tab.boltz_exp + carry + __popc(bal[g] & lt_mask)), prob[g]);
       carry += __popc(bal[g]);
     }
+    j = jn;
   }
-  {  // global minimum (first index): + no_trough_prob * sum(beta[:jmin - 1])
-    double bh = 1.0e300; int bi = 0x7fffffff;
 #pragma unroll
-    for (int g = 0; g < kYinMaxGroups; ++g) {
-      const int ai = 32 * g + lane;
-      if (ai < n_tr) { const double h = lh[ai]; if (h < bh) { bh = h; bi = ai; } }
-    }
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-      const double oh = __shfl_xor_sync(0xffffffffu, bh, o);
-      const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
-      if (oh < bh || (oh == bh && oi < bi)) { bh = oh; bi = oi; }
-    }
-#pragma unroll
-    for (int g = 0; g < kYinMaxGroups; ++g)
-      if (32 * g + lane == bi) prob[g] += 0.01 * a.tab.beta_cum[min(jmin[g], 101) - 1];
-  }
-  __syncwarp();
-  // pitch bins; a later trough (longer period) overwrites an earlier one in the same bin
+  for (int g = 0; g < kYinMaxGroups; ++g)
+    if (cai[g] == bi) prob[g] += 0.01 * __ldg(a.tab.beta_cum + min(cjm[g], 101) - 1);
+  // ---- pitch bins; a later candidate (longer period) overwrites an earlier one in the same bin
   int* lbin = reinterpret_cast<int*>(lh);   // heights are dead: reuse as bin list (-1 = not a candidate)
   int bin_r[kYinMaxGroups];
+  __syncwarp();
 #pragma unroll
   for (int g = 0; g < kYinMaxGroups; ++g) {
-    const int ai = 32 * g + lane;
     bin_r[g] = -1;
-    if (ai < n_tr && prob[g] > 0.0) {
-      const double f0 = a.sr / lp[ai];
+    if (32 * g >= n_c) continue;
+    const int c = 32 * g + lane;
+    if (c < n_c && prob[g] > 0.0) {
+      const double f0 = a.sr / lp[cai[g]];
       double bf = rint(120.0 * log2(f0 / a.fmin));
       bf = fmin(fmax(bf, 0.0), (double)a.n_bins);
       const int b = (int)bf;
       if (b < a.n_bins) bin_r[g] = b;
     }
+    if (c < n_c) lbin[c] = bin_r[g];
   }
-  __syncwarp();
-#pragma unroll
-  for (int g = 0; g < kYinMaxGroups; ++g) { const int ai = 32 * g + lane; if (ai < n_tr) lbin[ai] = bin_r[g]; }
   __syncwarp();
   double vp = 0.0;
   int keep_cnt = 0;
   bool keep[kYinMaxGroups];
 #pragma unroll
   for (int g = 0; g < kYinMaxGroups; ++g) {
-    const int ai = 32 * g + lane;
+    const int c = 32 * g + lane;
     keep[g] = false;
-    if (ai < n_tr && bin_r[g] >= 0) {
+    if (c < n_c && bin_r[g] >= 0) {
       keep[g] = true;
-      for (int q = ai + 1; q < n_tr; ++q) { const int bq = lbin[q]; if (bq >= 0) { keep[g] = bq != bin_r[g]; break; } }
+      for (int q = c + 1; q < n_c; ++q) { const int bq = lbin[q]; if (bq >= 0) { keep[g] = bq != bin_r[g]; break; } }
       if (keep[g]) { vp += prob[g]; ++keep_cnt; }
     }
   }
@@ -357,13 +398,24 @@ __global__ void __launch_bounds__(kYinThreads, 1) yin_obs_kernel(YinArgs a) {
 
 
 // =====================================================================================================
-// pYIN HMM decode (librosa.sequence.viterbi on 2 * n_bins states) + F0 statistics, one CTA per clip.
+// pYIN HMM decode (librosa.sequence.viterbi on 2 * n_bins states) + F0 statistics, one 5-warp CTA per clip, several
+// clips resident per SM (the time recursion is sequential; parallelism comes from co-resident clips).
 //   V_t[j] = logobs_t[j] + max_k (V_{t-1}[k] + logA[k][j]), first index on ties, float64 log domain.
 // Every out-of-band entry of logA is exactly log(tiny) and every in-band entry is larger, so the dense maximum equals
 // max(band maximum in both voicing blocks, G + log(tiny)) with G = max_k V_{t-1}[k] (first index k*).
-// The band maximum is a (max,+) product with the 2*hw+1 triangle log-weights; each thread carries two neighbouring
-// targets so every predecessor value is loaded once for two targets.
-constexpr int kVitThreads = 640;
+// The band maximum h[j] = max_{|k-j|<=hw} (F[k] + lt[j-k+hw]) is a (max,+) product with the log of a triangle, a
+// concave kernel: M[j][k] = F[k] + lt[j-k+hw] is inverse-Monge, so the (leftmost) arg-maxima are non-decreasing in j.
+//   phase A  brute force over the band for every kVitStride-th target (anchors), thread per anchor, four
+//            independent compare chains;
+//   phase B  every other target searches only [argmax(anchor below), argmax(anchor above)] (a handful of entries);
+//   phase C  voicing blocks + global fallback + observation, back-pointers, next F, block arg-max.
+// Declared inexactness: monotonicity holds for exact sums; two band entries whose float64 sums differ by rounding only
+// could in principle be resolved differently from the dense search (never observed; a full-band fallback covers
+// empty search ranges).
+constexpr int kVitThreads = 160;
+constexpr int kVitWarps = kVitThreads / 32;
+constexpr int kVitStride = 8;
+constexpr int kVitMinCtas = 5;
 
 struct VitArgs {
   const ClipInfo* info;
@@ -384,18 +436,36 @@ struct VitArgs {
   float* frames_out; int frame_width, n_mfcc;
 };
 
-__global__ void __launch_bounds__(kVitThreads, 1) viterbi_kernel(VitArgs a) {
+// shared-memory geometry, host and device: F rows are padded by `pad` (multiple of 8 >= hw) on the left and 4 lq + 8
+// on the right (pads hold -1e308) and skewed by one slot per 8 (anchors sit 8 apart: conflict-free 64-bit loads)
+struct VitGeo {
+  int pad, lq, fs, nb_even;
+  __host__ __device__ VitGeo(int nb, int hw) {
+    pad = (hw + 7) & ~7;
+    lq = (2 * hw + 1 + 3) / 4;
+    const int n = pad + nb + 4 * lq + 8;
+    fs = (n + (n >> 3) + 8) & ~1;
+    nb_even = (nb + 1) & ~1;
+  }
+  __host__ __device__ size_t bytes(int nb) const {
+    return (size_t)(2 * fs + 2 * nb_even /*hs*/ + 2 * nb_even /*lobs*/ + nb_even /*corr*/ + 4 * lq + 2 /*ltr*/) * 8 + (size_t)2 * nb_even * 2 /*harg*/;
+  }
+};
+
+__global__ void __launch_bounds__(kVitThreads, kVitMinCtas) viterbi_kernel(VitArgs a) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int nb = a.n_bins, hw = a.half_width, ns = 2 * nb;
-  double* Fp = reinterpret_cast<double*>(smem_raw);   // [2][nb] V_{t-1} + edge_corr
-  double* hs = Fp + ns;                                // [2][nb] band maxima
-  double* lobs = hs + ns;                              // [2][nb] dense log-observation rows (double buffered)
-  double* corr = lobs + ns;                            // [nb]
-  double* lt = corr + nb;                              // [2 hw + 1]
-  unsigned short* harg = reinterpret_cast<unsigned short*>(lt + 2 * hw + 2);   // [2][nb]
-  __shared__ double s_pv[kVitThreads / 32];
-  __shared__ int s_pi[kVitThreads / 32];
-  __shared__ double s_red[3][kVitThreads / 32];
+  const VitGeo geo(nb, hw);
+  const int FS = geo.fs, NBE = geo.nb_even, PAD = geo.pad, LQ = geo.lq;
+  double* Fp = reinterpret_cast<double*>(smem_raw);   // [2][FS] V_{t-1} + edge_corr, padded + skewed
+  double* hs = Fp + 2 * FS;                            // [2][NBE] band maxima
+  double* lobs = hs + 2 * NBE;                         // [2][NBE] dense log-observation rows (double buffered)
+  double* corr = lobs + 2 * NBE;                       // [NBE]
+  double* ltr = corr + NBE;                            // [4 LQ] ltr[d] = lt[2 hw - d]: weight of predecessor j - hw + d
+  unsigned short* harg = reinterpret_cast<unsigned short*>(ltr + 4 * LQ + 2);   // [2][NBE]
+  __shared__ double s_pv[kVitWarps];
+  __shared__ int s_pi[kVitWarps];
+  __shared__ double s_red[3][kVitWarps];
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int clip = a.clip_begin + blockIdx.x;
@@ -406,10 +476,12 @@ __global__ void __launch_bounds__(kVitThreads, 1) viterbi_kernel(VitArgs a) {
   const long long slot0 = a.frame_off[clip] - a.frame_base;
   const unsigned char* rec0 = a.obs + (size_t)slot0 * a.rec_bytes;
   unsigned short* ptr0 = a.ptr + (size_t)slot0 * ns;
+  auto fidx = [PAD](int k) { const int kp = k + PAD; return kp + (kp >> 3); };
 
+  for (int i = tid; i < 2 * FS; i += kVitThreads) Fp[i] = -1.0e308;
   for (int i = tid; i < nb; i += kVitThreads) corr[i] = a.edge_corr[i];
-  for (int i = tid; i < 2 * hw + 1; i += kVitThreads) lt[i] = a.lt_same[i];
-  for (int i = tid; i < ns; i += kVitThreads) lobs[i] = a.log_tiny;
+  for (int i = tid; i < 4 * LQ; i += kVitThreads) ltr[i] = (i <= 2 * hw) ? a.lt_same[2 * hw - i] : -1.0e308;
+  for (int i = tid; i < 2 * NBE; i += kVitThreads) lobs[i] = a.log_tiny;
   __syncthreads();
 
   // block argmax (first index) of per-thread (v, i) pairs -> every thread gets (G, k*)
@@ -423,7 +495,8 @@ __global__ void __launch_bounds__(kVitThreads, 1) viterbi_kernel(VitArgs a) {
     if (lane == 0) { s_pv[warp] = v; s_pi[warp] = i; }
     __syncthreads();
     G = s_pv[0]; ks = s_pi[0];
-    for (int w2 = 1; w2 < kVitThreads / 32; ++w2) {
+#pragma unroll
+    for (int w2 = 1; w2 < kVitWarps; ++w2) {
       const double ov = s_pv[w2]; const int oi = s_pi[w2];
       if (ov > G || (ov == G && oi < ks)) { G = ov; ks = oi; }
     }
@@ -434,63 +507,89 @@ __global__ void __launch_bounds__(kVitThreads, 1) viterbi_kernel(VitArgs a) {
   {
     const int n0c = *reinterpret_cast<const int*>(rec0);
     const double lu0 = *reinterpret_cast<const double*>(rec0 + 8);
-    if (tid < n0c) lobs[rec_bins(const_cast<unsigned char*>(rec0), a.cap)[tid]] = rec_logp(const_cast<unsigned char*>(rec0))[tid];
+    for (int i = tid; i < n0c; i += kVitThreads)
+      lobs[rec_bins(const_cast<unsigned char*>(rec0), a.cap)[i]] = rec_logp(const_cast<unsigned char*>(rec0))[i];
     __syncthreads();
     double bv = -1.0e308; int bi = 0x7fffffff;
-    if (tid < nb) {
-      const double vv = lobs[tid] + a.log_tiny;
+    for (int j = tid; j < nb; j += kVitThreads) {
+      const double vv = lobs[j] + a.log_tiny;
       const double vu = lu0 + a.log_init_unvoiced;
-      Fp[tid] = vv + corr[tid];
-      Fp[nb + tid] = vu + corr[tid];
-      bv = vv; bi = tid;
-      if (vu > bv) { bv = vu; bi = nb + tid; }
+      Fp[fidx(j)] = vv + corr[j];
+      Fp[FS + fidx(j)] = vu + corr[j];
+      if (vv > bv) { bv = vv; bi = j; }          // j ascending within a thread: strict > keeps the first index
     }
+    double bu = -1.0e308; int biu = 0x7fffffff;   // unvoiced states come after every voiced state
+    for (int j = tid; j < nb; j += kVitThreads) { const double vu = lu0 + a.log_init_unvoiced; if (vu > bu) { bu = vu; biu = nb + j; } }
+    if (bu > bv) { bv = bu; bi = biu; }
     block_argmax(bv, bi, G, kstar);
   }
 
+  const int nA = (nb - 1 + kVitStride - 1) / kVitStride + 1;   // anchors per voicing block: 0, S, 2S, ..., nb - 1
   for (int t = 1; t < T; ++t) {
     const unsigned char* rec = rec0 + (size_t)t * a.rec_bytes;
     const unsigned char* recp = rec - a.rec_bytes;
-    double* lob_cur = lobs + (t & 1) * nb;
-    double* lob_old = lobs + ((t - 1) & 1) * nb;
+    double* lob_cur = lobs + (t & 1) * NBE;
+    double* lob_old = lobs + ((t - 1) & 1) * NBE;
     const int nc = *reinterpret_cast<const int*>(rec);
     const double lu = *reinterpret_cast<const double*>(rec + 8);
-    // phase 1: band maxima h_s[j] = max_k (F_s[k] + lt[j - k + hw]); thread <-> (s, two neighbouring targets)
-    {
-      const int half = (nb + 1) >> 1;
-      if (tid < 2 * half) {
-        const int s = tid >= half ? 1 : 0;
-        const int j0 = 2 * (tid - s * half);
-        const double* Fs = Fp + s * nb;
-        double m0 = -1.0e308, m1 = -1.0e308;
-        int a0 = 0, a1 = 0;
-        const int k_lo = max(0, j0 - hw), k_hi = min(nb - 1, j0 + 1 + hw);
-        int idx = j0 - k_lo + hw;               // table index of target j0 at k = k_lo (<= 2 hw)
-        double w1 = (idx + 1 <= 2 * hw) ? lt[idx + 1] : -1.0e308;   // weight of target j0 + 1
-        for (int k = k_lo; k <= k_hi; ++k, --idx) {
-          const double fk = Fs[k];
-          const double w0 = (idx >= 0) ? lt[idx] : -1.0e308;         // weight of target j0
-          const double c0 = fk + w0, c1 = fk + w1;
-          if (idx >= 0 && c0 > m0) { m0 = c0; a0 = k; }
-          if (idx + 1 <= 2 * hw && c1 > m1) { m1 = c1; a1 = k; }
-          w1 = w0;
-        }
-        hs[s * nb + j0] = m0; harg[s * nb + j0] = (unsigned short)a0;
-        if (j0 + 1 < nb) { hs[s * nb + j0 + 1] = m1; harg[s * nb + j0 + 1] = (unsigned short)a1; }
+    // ---- phase A: anchors, full band
+    for (int ax = tid; ax < 2 * nA; ax += kVitThreads) {
+      const int s = ax >= nA ? 1 : 0;
+      const int j = min((ax - s * nA) * kVitStride, nb - 1);
+      const double* Fs = Fp + s * FS;
+      const int kp0 = j - hw + PAD;                 // padded index of predecessor d = 0
+      double b0 = -1.0e308, b1 = -1.0e308, b2 = -1.0e308, b3 = -1.0e308;
+      int a0 = 0, a1 = LQ, a2 = 2 * LQ, a3 = 3 * LQ;
+      for (int i = 0; i < LQ; ++i) {
+        const int k0 = kp0 + i, k1 = k0 + LQ, k2 = k1 + LQ, k3 = k2 + LQ;
+        const double c0 = Fs[k0 + (k0 >> 3)] + ltr[i];
+        const double c1 = Fs[k1 + (k1 >> 3)] + ltr[LQ + i];
+        const double c2 = Fs[k2 + (k2 >> 3)] + ltr[2 * LQ + i];
+        const double c3 = Fs[k3 + (k3 >> 3)] + ltr[3 * LQ + i];
+        if (c0 > b0) { b0 = c0; a0 = i; }
+        if (c1 > b1) { b1 = c1; a1 = LQ + i; }
+        if (c2 > b2) { b2 = c2; a2 = 2 * LQ + i; }
+        if (c3 > b3) { b3 = c3; a3 = 3 * LQ + i; }
       }
-      // this frame's sparse observations into the dense row; the previous frame's entries back to log(tiny)
+      if (b1 > b0) { b0 = b1; a0 = a1; }
+      if (b2 > b0) { b0 = b2; a0 = a2; }
+      if (b3 > b0) { b0 = b3; a0 = a3; }
+      hs[s * NBE + j] = b0;
+      harg[s * NBE + j] = (unsigned short)(j - hw + a0);
+    }
+    // this frame's sparse observations into the dense row; the previous frame's entries back to log(tiny)
+    {
       const int ncp = *reinterpret_cast<const int*>(recp);
-      if (tid < ncp) lob_old[rec_bins(const_cast<unsigned char*>(recp), a.cap)[tid]] = a.log_tiny;
-      if (tid < nc) lob_cur[rec_bins(const_cast<unsigned char*>(rec), a.cap)[tid]] = rec_logp(const_cast<unsigned char*>(rec))[tid];
+      for (int i = tid; i < ncp; i += kVitThreads) lob_old[rec_bins(const_cast<unsigned char*>(recp), a.cap)[i]] = a.log_tiny;
+      for (int i = tid; i < nc; i += kVitThreads) lob_cur[rec_bins(const_cast<unsigned char*>(rec), a.cap)[i]] = rec_logp(const_cast<unsigned char*>(rec))[i];
     }
     __syncthreads();
-    // phase 2: combine the voicing blocks and the global fallback, add the observation, store the back-pointers
-    double bv = -1.0e308; int bi = 0x7fffffff;
+    // ---- phase B: the other targets, restricted to [argmax of the anchor below, argmax of the anchor above]
+    for (int idx = tid; idx < ns; idx += kVitThreads) {
+      const int s = idx >= nb ? 1 : 0;
+      const int j = idx - s * nb;
+      if ((j & (kVitStride - 1)) == 0 || j == nb - 1) continue;
+      const int ja = j & ~(kVitStride - 1), jb = min(ja + kVitStride, nb - 1);
+      int lo = max(j - hw, (int)harg[s * NBE + ja]), hi = min(j + hw, (int)harg[s * NBE + jb]);
+      if (lo > hi) { lo = max(j - hw, 0); hi = min(j + hw, nb - 1); }
+      const double* Fs = Fp + s * FS;
+      double best = -1.0e308; int arg = lo;
+      for (int k = lo; k <= hi; ++k) {
+        const int kp = k + PAD;
+        const double c = Fs[kp + (kp >> 3)] + ltr[k - j + hw];
+        if (c > best) { best = c; arg = k; }
+      }
+      hs[s * NBE + j] = best;
+      harg[s * NBE + j] = (unsigned short)arg;
+    }
+    __syncthreads();
+    // ---- phase C: combine the voicing blocks and the global fallback, add the observation, store the back-pointers
+    double bv = -1.0e308, bu = -1.0e308; int bi = 0x7fffffff, biu = 0x7fffffff;
     const double fb = G + a.log_tiny;   // best out-of-band predecessor: k* through a log(tiny) transition
-    if (tid < nb) {
-      const int j = tid;
-      const double h0 = hs[j], h1 = hs[nb + j];
-      const int k0 = harg[j], k1 = nb + harg[nb + j];
+    unsigned short* pt = ptr0 + (size_t)t * ns;
+    for (int j = tid; j < nb; j += kVitThreads) {
+      const double h0 = hs[j], h1 = hs[NBE + j];
+      const int k0 = harg[j], k1 = nb + harg[NBE + j];
       // voiced target j: predecessors in index order are block 0 (same voicing), then block 1 (switch)
       double mv = h0; int pv = k0;
       { const double c = h1 + a.delta_switch; if (c > mv) { mv = c; pv = k1; } }
@@ -501,23 +600,34 @@ __global__ void __launch_bounds__(kVitThreads, 1) viterbi_kernel(VitArgs a) {
       if (fb > mu || (fb == mu && kstar < pu)) { mu = fb; pu = kstar; }
       const double vv = lob_cur[j] + mv;
       const double vu = lu + mu;
-      unsigned short* pt = ptr0 + (size_t)t * ns;
       pt[j] = (unsigned short)pv; pt[nb + j] = (unsigned short)pu;
-      bv = vv; bi = j;
-      if (vu > bv) { bv = vu; bi = nb + j; }
-      // F for the next step (phase 1 readers are done: the barrier above)
-      Fp[j] = vv + corr[j];
-      Fp[nb + j] = vu + corr[j];
+      if (vv > bv) { bv = vv; bi = j; }
+      if (vu > bu) { bu = vu; biu = nb + j; }
+      // F for the next step (phase A / B readers are done: the barrier above)
+      const int fi = fidx(j);
+      Fp[fi] = vv + corr[j];
+      Fp[FS + fi] = vu + corr[j];
     }
-    block_argmax(bv, bi, G, kstar);   // contains a barrier: Fp complete before the next phase 1
+    if (bu > bv) { bv = bu; bi = biu; }   // every unvoiced index is larger than every voiced one: strict >
+    block_argmax(bv, bi, G, kstar);   // contains a barrier: Fp complete before the next phase A
   }
 
-  // ---- backtrace (thread 0), then statistics over voiced frames (core/feature_extractor.py:97-113)
+  // ---- backtrace (warp 0; the row 8 frames ahead is pulled into L2 around the current state), then statistics over
+  // voiced frames (core/feature_extractor.py:97-113)
   short* st = a.states + slot0;
-  if (tid == 0) {
+  if (warp == 0) {
     int s = kstar;
-    for (int t = T - 1; t >= 1; --t) { st[t] = (short)s; s = ptr0[(size_t)t * ns + s]; }
-    st[0] = (short)s;
+    for (int t = T - 1; t >= 1; --t) {
+      const int tp = t - 8;
+      if (tp >= 1 && lane < 4) {
+        const int jj = s >= nb ? s - nb : s;
+        const int col = (lane >> 1) * nb + min(nb - 1, max(0, jj - 32 + 64 * (lane & 1)));
+        asm volatile("prefetch.global.L2 [%0];" ::"l"(ptr0 + (size_t)tp * ns + col));
+      }
+      if (lane == 0) st[t] = (short)s;
+      s = ptr0[(size_t)t * ns + s];
+    }
+    if (lane == 0) st[0] = (short)s;
   }
   __syncthreads();
   double s1 = 0, s2 = 0, cntv = 0;
@@ -537,7 +647,7 @@ __global__ void __launch_bounds__(kVitThreads, 1) viterbi_kernel(VitArgs a) {
   __syncthreads();
   if (tid == 0) {
     s1 = s2 = cntv = 0;
-    for (int w2 = 0; w2 < kVitThreads / 32; ++w2) { s1 += s_red[0][w2]; s2 += s_red[1][w2]; cntv += s_red[2][w2]; }
+    for (int w2 = 0; w2 < kVitWarps; ++w2) { s1 += s_red[0][w2]; s2 += s_red[1][w2]; cntv += s_red[2][w2]; }
     if (cntv > 0.0) {
       const double mean = s1 / cntv;
       const double var = fmax(s2 / cntv - mean * mean, 0.0);

@@ -20,6 +20,7 @@ struct PyinConsts {
   std::vector<double> thresholds;   // [101] np.linspace(0, 1, 101)
   std::vector<double> beta;         // [100] diff(beta.cdf(thresholds, 2, 18))
   std::vector<double> beta_cum;     // [101] beta_cum[n] = sum(beta[:n])
+  std::vector<double> beta_suf;     // [102] beta_suf[j] = sum(beta[j - 1:]) for j = 1 .. 100, 0 at 101 (index 0 = total)
   std::vector<double> boltz_fact;   // [n] (1 - exp(-2)) / (1 - exp(-2 n)), n = 0 unused
   std::vector<double> boltz_exp;    // [k] exp(-2 k)
   std::vector<double> ltrans_same;  // [2 hw + 1] log(p_stay   * tri[d] / rowsum_interior + tiny)
@@ -83,6 +84,9 @@ inline bool pyin_consts(int sr, int frame_length, int hop_length, double fmin, d
   c.beta.resize(kPyinThresholds);
   c.beta_cum.assign(kPyinThresholds + 1, 0.0);
   for (int j = 0; j < kPyinThresholds; ++j) { c.beta[j] = cdf[j + 1] - cdf[j]; c.beta_cum[j + 1] = c.beta_cum[j] + c.beta[j]; }
+  c.beta_suf.assign(kPyinThresholds + 2, 0.0);   // summed from the small tail upwards
+  for (int j = kPyinThresholds; j >= 1; --j) c.beta_suf[j] = c.beta_suf[j + 1] + c.beta[j - 1];
+  c.beta_suf[0] = c.beta_suf[1];
   // scipy.stats.boltzmann.pmf(k, 2, N) = (1 - exp(-2)) / (1 - exp(-2 N)) * exp(-2 k)
   const int max_troughs = c.n_lags / 2 + 2;
   c.boltz_fact.assign(max_troughs + 1, 0.0);
