@@ -63,7 +63,7 @@ __device__ __forceinline__ double shfl_up_d(double v, int d) { return __shfl_up_
 
 
 template <int C>   // lags per lane in phase 2: 32 * C >= max_period
-__global__ void __launch_bounds__(kYinThreads, 1) yin_obs_kernel(YinArgs a) {
+__global__ void __launch_bounds__(kYinThreads, 2) yin_obs_kernel(YinArgs a) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   // phase 0/1 layout: [ys float tile][A float 16 x lag_pad][S double tile + 1]; phase 2b aliases it with trough lists
   float* ys = reinterpret_cast<float*>(smem_raw);
