@@ -179,7 +179,7 @@ size_t clip_smem_bytes(const afx_handle_s* h, int* tile_floats_out) {
   const int tile_floats = (fpw - 1) * h->cfg.hop_length + n_fft + 8;     // per-warp raw tile, afx::Geo<>::RAWW
   if (tile_floats_out) *tile_floats_out = tile_floats;
   return 128 + 8192 + (n_fft == 2048 ? 4112 : 0) + (size_t)n_fft * 4 + (size_t)(afx::kMoments * afx::kMaxMfcc + 64) * 8 +
-         (size_t)afx::kNMels * (h->n16 + 4) * 4 + (size_t)h->mel_floats * 4 +
+         (size_t)32 * (2 * h->n16 + 4) * 4 + (size_t)h->mel_floats * 4 +
          (size_t)h->clip_warps * (tile_floats + afx::kPlaneFloats) * 4;
 }
 
@@ -237,6 +237,7 @@ int afx_create(const afx_config_t* cfg, afx_handle_t* out) {
   const auto tw = afx::host::twiddle32x32(cfg->frame_length == 512 ? 512 : 1024);
   const auto ptw = afx::host::post_twiddle(2048, 513);
   const auto mel = afx::host::mel_sparse(cfg->sr, cfg->frame_length, cfg->n_mels);
+  if (mel.nnz < 0) { delete h; return fail(AFX_ERR_UNSUPPORTED, "mel filterbank: segment decomposition does not cover every weight"); }
   const auto dct = afx::host::dct_rows(cfg->n_mfcc, cfg->n_mels);
   std::vector<float> dct_t((size_t)cfg->n_mels * h->n16, 0.f);
   for (int c = 0; c < cfg->n_mfcc; ++c)
@@ -254,6 +255,7 @@ int afx_create(const afx_config_t* cfg, afx_handle_t* out) {
   h->tab.mel_w = h->d_mel_w;
   h->tab.mel_k0 = h->d_mel_k0;
   for (int q = 0; q < 4; ++q) { h->tab.mel_cnt[q] = mel.cnt[q]; h->tab.mel_woff[q] = mel.woff[q]; }
+  h->tab.mel_k00 = mel.k00; h->tab.mel_cnt0 = mel.cnt0; h->tab.mel_woff0 = mel.woff0;
   h->tab.dct = nullptr;
 
   CUDA_TRY(cudaFuncSetAttribute(afx::trim_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));

@@ -242,7 +242,7 @@ template <int NFFT, int HOP>
 __global__ void __launch_bounds__(kMaxClipThreads, 1) clip_kernel(ClipArgs a) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   // layout: [16 mbarriers 128B][twiddle 8KB][window NFFT*4][acc 6*64 doubles][red 64 doubles]
-  //         [sDct 128*(n16+4) floats][mel weights][raw tiles 16 x (HOP+NFFT+8) floats][planes 16 x 4224B]
+  //         [sDct 32*(2*n16+4) floats][mel weights][raw tiles 16 x (HOP+NFFT+8) floats][planes 16 x 4224B]
   //         (phase C's sM aliases the raw tiles)
   constexpr int RAWW = Geo<NFFT, HOP>::RAWW;
   Smem sm;
@@ -254,8 +254,8 @@ __global__ void __launch_bounds__(kMaxClipThreads, 1) clip_kernel(ClipArgs a) {
   double* acc = reinterpret_cast<double*>(sm.win + NFFT);
   double* red = acc + kMoments * kMaxMfcc;
   float* sDct = reinterpret_cast<float*>(red + 64);
-  const int dstride = a.n16 + 4;
-  float* sMel = sDct + kNMels * dstride;
+  const int dstride = 2 * a.n16 + 4;   // per lane: DCT rows of band `lane`, then of band 63 - lane (+ pad: conflict-free float4 reads)
+  float* sMel = sDct + 32 * dstride;
   sm.dct = sDct; sm.melw = sMel;
   sm.raw = sMel + a.mel_floats;
   sm.planes = sm.raw + (blockDim.x >> 5) * RAWW;
@@ -266,7 +266,10 @@ __global__ void __launch_bounds__(kMaxClipThreads, 1) clip_kernel(ClipArgs a) {
   for (int i = tid; i < 1024; i += (int)blockDim.x) sm.tw[i] = a.tab.twiddle[i];
   for (int i = tid; i < NFFT; i += (int)blockDim.x) sm.win[i] = a.tab.window_half[i];
   if (NFFT == 2048) for (int i = tid; i <= 512; i += (int)blockDim.x) sm.ptw[i] = a.tab.post_twiddle[i];
-  for (int i = tid; i < kNMels * a.n16; i += (int)blockDim.x) sDct[(i / a.n16) * dstride + (i % a.n16)] = a.dct_t[i];
+  for (int i = tid; i < 64 * a.n16; i += (int)blockDim.x) {
+    const int l = i / (2 * a.n16), rem = i - l * 2 * a.n16, hsel = rem / a.n16, k = rem - hsel * a.n16;
+    sDct[l * dstride + rem] = a.dct_t[(hsel ? 63 - l : l) * a.n16 + k];
+  }
   for (int i = tid; i < a.mel_floats; i += (int)blockDim.x) sMel[i] = a.tab.mel_w[i];
   if (tid < kMaxClipWarps) mbar_init(sm.mbar + tid, 1);
   if (tid == 0) fence_mbar_init();

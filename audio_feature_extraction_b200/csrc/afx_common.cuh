@@ -32,10 +32,11 @@ struct Tables {
   const float*  window_half;   // [n_fft] 0.5 * periodic Hamming (0.5 folds the 1/4 of the two-real-FFT split)
   const float2* twiddle;       // [32][32] W_1024^(row*col) as (cos, -sin)
   const float2* post_twiddle;  // n_fft=2048 only: W_2048^k, k = 0..512
-  const float*  mel_w;         // padded per-quarter weights, [quarter][i][lane]
-  const int*    mel_k0;        // [128] first FFT bin of each band's (padded) run
-  int           mel_cnt[4];    // padded run length per quarter of 32 bands
-  int           mel_woff[4];   // offset of each quarter in mel_w
+  const float*  mel_w;         // float2 (rising-side weight U, falling-side weight D) per entry, padded [quarter][i][lane]
+  const int*    mel_k0;        // [128] first FFT bin of the (padded) run of (q, lane)'s mel segment
+  int           mel_cnt[4];    // padded run length per quarter of 32 segments
+  int           mel_woff[4];   // float2 offset of each quarter in mel_w
+  int           mel_k00, mel_cnt0, mel_woff0;   // segment 0 (below the first mel point): first bin, run, float2 offset
   const float*  dct;           // [n_mfcc][128] ortho DCT-II rows
 };
 

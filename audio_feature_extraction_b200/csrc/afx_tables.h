@@ -50,12 +50,21 @@ inline std::vector<float> post_twiddle(int n, int count) {
   return t;
 }
 
+// Band owned by (quarter q, lane) of the fused kernel: the DCT-II mirror pairs (b, 127 - b) share a lane
+inline int mel_band_of(int q, int lane) { return q == 0 ? lane : q == 1 ? 63 - lane : q == 2 ? 64 + lane : 127 - lane; }
+
+// Sparse Slaney filterbank organised by the 129 SEGMENTS between consecutive mel points instead of by band: every
+// FFT bin lies in exactly one segment s (f_s < f_k <= f_{s+1}), where it feeds the rising side of band s (weight U)
+// and the falling side of band s - 1 (weight D), so each bin is touched once.  The weights are the float32 entries of
+// librosa.filters.mel unchanged.  (q, lane) owns band b = mel_band_of(q, lane) and segment b + 1; segment 0 (below the
+// first mel point, rising side of band 0 only) is kept apart.
 struct MelSparse {
   std::vector<float> dense;   // [128][nbins] float32 weights exactly as librosa.filters.mel builds them
-  std::vector<float> w;       // padded [quarter][i][lane]
-  std::vector<int> k0;        // [128]
-  int cnt[4];
-  int woff[4];
+  std::vector<float> w;       // float2 (U, D) per entry: padded [quarter][i][lane], then segment 0's [cnt0] entries
+  std::vector<int> k0;        // [128] first FFT bin of the (padded) run of (q, lane)'s segment, index 32 q + lane
+  int cnt[4];                 // padded run length per quarter
+  int woff[4];                // float2 offset of each quarter in w
+  int k00, cnt0, woff0;       // segment 0: first bin, run length, float2 offset
   int nnz;
 };
 
@@ -75,7 +84,6 @@ inline MelSparse mel_sparse(int sr, int n_fft, int n_mels = 128) {
   for (int i = 0; i < np_; ++i) mel_f[i] = mel_to_hz(i == np_ - 1 ? max_mel : min_mel + i * step);
   ms.dense.assign((size_t)n_mels * nbins, 0.f);
   ms.nnz = 0;
-  std::vector<int> first(n_mels, nbins), last(n_mels, -1);
   for (int i = 0; i < n_mels; ++i) {
     const double fd0 = mel_f[i + 1] - mel_f[i], fd1 = mel_f[i + 2] - mel_f[i + 1];
     const double enorm = 2.0 / (mel_f[i + 2] - mel_f[i]);
@@ -85,32 +93,51 @@ inline MelSparse mel_sparse(int sr, int n_fft, int n_mels = 128) {
       const float tri = (float)std::fmax(0.0, std::fmin(lower, upper));
       const float wv = (float)((double)tri * enorm);     // weights *= enorm (float32 array, float64 factor)
       ms.dense[(size_t)i * nbins + k] = wv;
-      if (wv != 0.f) { ++ms.nnz; first[i] = std::min(first[i], k); last[i] = std::max(last[i], k); }
+      if (wv != 0.f) ++ms.nnz;
     }
   }
+  // segment of each bin: the s with band s - 1 falling / band s rising there.  A non-zero weight of band m at bin k
+  // means f_m < f_k < f_{m+2}, i.e. s in {m, m + 1}; classify by the dense matrix itself so rounding cannot disagree.
+  std::vector<int> seg(nbins, -1), sfirst(n_mels + 1, nbins), slast(n_mels + 1, -1);
+  for (int k = 0; k < nbins; ++k) {
+    int s = 0;
+    while (s < n_mels && fftfreqs[k] > mel_f[s + 1]) ++s;   // f_s < f_k <= f_{s+1} (s = 0 also takes f_k <= f_0)
+    seg[k] = s;
+    sfirst[s] = std::min(sfirst[s], k); slast[s] = std::max(slast[s], k);
+  }
+  auto wU = [&](int s, int k) -> float { return (s < n_mels && seg[k] == s) ? ms.dense[(size_t)s * nbins + k] : 0.f; };
+  auto wD = [&](int s, int k) -> float { return (s >= 1 && seg[k] == s) ? ms.dense[(size_t)(s - 1) * nbins + k] : 0.f; };
   ms.k0.assign(n_mels, 0);
-  int off = 0;
+  int off = 0;   // float2 units
   for (int q = 0; q < 4; ++q) {
     int cnt = 1;
-    for (int l = 0; l < 32; ++l) {
-      const int m = 32 * q + l;
-      if (last[m] >= first[m]) cnt = std::max(cnt, last[m] - first[m] + 1);
-    }
+    for (int l = 0; l < 32; ++l) { const int s = mel_band_of(q, l) + 1; if (slast[s] >= sfirst[s]) cnt = std::max(cnt, slast[s] - sfirst[s] + 1); }
     ms.cnt[q] = cnt;
     ms.woff[q] = off;
-    ms.w.resize(off + cnt * 32, 0.f);
+    ms.w.resize(2 * (size_t)(off + cnt * 32), 0.f);
     for (int l = 0; l < 32; ++l) {
-      const int m = 32 * q + l;
-      int k0 = (last[m] >= first[m]) ? first[m] : 0;
-      k0 = std::min(k0, nbins - cnt);
-      if (k0 < 0) k0 = 0;
-      ms.k0[m] = k0;
+      const int s = mel_band_of(q, l) + 1;
+      int k0 = (slast[s] >= sfirst[s]) ? sfirst[s] : 0;
+      k0 = std::max(0, std::min(k0, nbins - cnt));
+      ms.k0[32 * q + l] = k0;
       for (int i = 0; i < cnt; ++i) {
         const int k = k0 + i;
-        ms.w[off + i * 32 + l] = (k < nbins) ? ms.dense[(size_t)m * nbins + k] : 0.f;
+        ms.w[2 * (size_t)(off + i * 32 + l)] = k < nbins ? wU(s, k) : 0.f;
+        ms.w[2 * (size_t)(off + i * 32 + l) + 1] = k < nbins ? wD(s, k) : 0.f;
       }
     }
     off += cnt * 32;
+  }
+  ms.cnt0 = (slast[0] >= sfirst[0]) ? slast[0] - sfirst[0] + 1 : 0;
+  ms.k00 = ms.cnt0 ? sfirst[0] : 0;
+  ms.woff0 = off;
+  ms.w.resize(2 * (size_t)(off + ((ms.cnt0 + 1) & ~1)), 0.f);   // keeps the float count a multiple of 4
+  for (int i = 0; i < ms.cnt0; ++i) ms.w[2 * (size_t)(off + i)] = wU(0, ms.k00 + i);
+  // every non-zero weight must be covered exactly once
+  {
+    long covered = 0;
+    for (int k = 0; k < nbins; ++k) { const int s = seg[k]; if (wU(s, k) != 0.f) ++covered; if (wD(s, k) != 0.f) ++covered; }
+    if (covered != ms.nnz) ms.nnz = -1;   // flagged to the caller (afx_create fails)
   }
   return ms;
 }

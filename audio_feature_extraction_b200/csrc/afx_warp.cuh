@@ -26,8 +26,8 @@ struct Smem {
   float2* tw;         // [32][32] W_1024^(row*col) (n_fft 1024, 2048) or [16][32] W_512^(row*col) (n_fft 512)
   float2* ptw;        // n_fft 2048: W_2048^k, k = 0..512
   float* win;         // [NFFT] 0.5 * periodic Hamming
-  const float* dct;   // [128][n16 + 4] DCT-II rows, transposed, padded stride (conflict-free float4 reads)
-  const float* melw;  // copy of Tables::mel_w
+  const float* dct;   // [32][2 n16 + 4] per lane: DCT-II coefficients of band `lane`, then of band 63 - lane (padded stride)
+  const float* melw;  // copy of Tables::mel_w (float2 entries)
   float* raw;         // [warps][RAWW] per-warp raw-sample tiles
   float* planes;      // [warps][32*33]
 };
@@ -52,8 +52,9 @@ struct Geo {
 };
 
 __device__ __forceinline__ float preemph_op(float x, float xm1, float coef) {
-  // scipy.signal.lfilter with b=[1,-c], a=[1] in float32: fl(x + fl(-c * xm1)), no contraction
-  return __fadd_rn(x, __fmul_rn(-coef, xm1));
+  // scipy.signal.lfilter with b=[1,-c], a=[1] in float32 computes fl(x + fl(-c * xm1)); the fused form differs by at
+  // most one rounding of the product (<= 2^-24 |c xm1|), far inside every tolerance of the path, and saves an issue slot
+  return fmaf(-coef, xm1, x);
 }
 
 // pre-emphasised sample at tile offset t (absolute sample gA + t); rp0 = raw + 4.
@@ -128,28 +129,29 @@ __device__ __forceinline__ void fft512x2_core(float (&r)[32], float (&im)[32], c
   fft32_dit(r, im);
 }
 
-// ---- DCT-II (ortho) of two clamped log-mel rows held as 4 bands per lane, 16 coefficients at a time: lane-partial
-// sums over its 4 bands, then a transposed reduction through the plane (lane j sums row j = (frame j/16,
-// coefficient j%16) over the 32 lanes' partials); rows `row` (A) and `row + 1` (B, if vB) of the slab
+// ---- DCT-II (ortho) of two clamped log-mel rows, 16 coefficients at a time.  A lane holds the mirror pairs
+// (lane, 127 - lane) = d[0], d[3] and (63 - lane, 64 + lane) = d[1], d[2]; cos(pi k (2 (127 - b) + 1) / 256) =
+// (-1)^k cos(pi k (2 b + 1) / 256), so even coefficients need only the pair sums and odd ones the pair differences:
+// half the multiplies.  Lane partials, then a transposed reduction through the plane (lane j sums row j =
+// (frame j/16, coefficient j%16) over the 32 lanes' partials); rows `row` (A) and `row + 1` (B, if vB) of the slab
 __device__ __forceinline__ void dct_pair(const ClipArgs& a, const Smem& sm, const Slab& sl, const WarpCtx& wc,
                                          const float (&da)[4], const float (&db)[4], int row, bool vB, int lane) {
   float* plane = wc.plane;
-  const int stride = a.n16 + 4;
+  const int stride = 2 * a.n16 + 4;
+  const float ea0 = da[0] + da[3], oa0 = da[0] - da[3], ea1 = da[1] + da[2], oa1 = da[1] - da[2];
+  const float eb0 = db[0] + db[3], ob0 = db[0] - db[3], eb1 = db[1] + db[2], ob1 = db[1] - db[2];
   for (int kg = 0; kg < a.n16; kg += 16) {
     float pa[16], pb[16];
+    const float* c0row = sm.dct + lane * stride + kg;   // band lane
+    const float* c1row = c0row + a.n16;                 // band 63 - lane
 #pragma unroll
-    for (int k = 0; k < 16; ++k) { pa[k] = 0.f; pb[k] = 0.f; }
-#pragma unroll
-    for (int q = 0; q < 4; ++q) {
-      const float* crow = sm.dct + (32 * q + lane) * stride + kg;
-#pragma unroll
-      for (int k4 = 0; k4 < 4; ++k4) {
-        const float4 c = *reinterpret_cast<const float4*>(crow + 4 * k4);
-        pa[4 * k4 + 0] = fmaf(da[q], c.x, pa[4 * k4 + 0]); pb[4 * k4 + 0] = fmaf(db[q], c.x, pb[4 * k4 + 0]);
-        pa[4 * k4 + 1] = fmaf(da[q], c.y, pa[4 * k4 + 1]); pb[4 * k4 + 1] = fmaf(db[q], c.y, pb[4 * k4 + 1]);
-        pa[4 * k4 + 2] = fmaf(da[q], c.z, pa[4 * k4 + 2]); pb[4 * k4 + 2] = fmaf(db[q], c.z, pb[4 * k4 + 2]);
-        pa[4 * k4 + 3] = fmaf(da[q], c.w, pa[4 * k4 + 3]); pb[4 * k4 + 3] = fmaf(db[q], c.w, pb[4 * k4 + 3]);
-      }
+    for (int k4 = 0; k4 < 4; ++k4) {
+      const float4 c0 = *reinterpret_cast<const float4*>(c0row + 4 * k4);
+      const float4 c1 = *reinterpret_cast<const float4*>(c1row + 4 * k4);
+      pa[4 * k4 + 0] = fmaf(ea0, c0.x, ea1 * c1.x); pb[4 * k4 + 0] = fmaf(eb0, c0.x, eb1 * c1.x);
+      pa[4 * k4 + 1] = fmaf(oa0, c0.y, oa1 * c1.y); pb[4 * k4 + 1] = fmaf(ob0, c0.y, ob1 * c1.y);
+      pa[4 * k4 + 2] = fmaf(ea0, c0.z, ea1 * c1.z); pb[4 * k4 + 2] = fmaf(eb0, c0.z, eb1 * c1.z);
+      pa[4 * k4 + 3] = fmaf(oa0, c0.w, oa1 * c1.w); pb[4 * k4 + 3] = fmaf(ob0, c0.w, ob1 * c1.w);
     }
 #pragma unroll
     for (int k = 0; k < 16; ++k) { plane[k * 33 + lane] = pa[k]; plane[(16 + k) * 33 + lane] = pb[k]; }
@@ -165,6 +167,53 @@ __device__ __forceinline__ void dct_pair(const ClipArgs& a, const Smem& sm, cons
 }
 
 __device__ __forceinline__ float to_db(float m) { return 3.0102999566398120f * __log2f(fmaxf(m, 1e-10f)); }   // 10 log10(max(1e-10, m))
+
+// ---- sparse Slaney mel by SEGMENTS (afx_tables.h): (q, lane) walks the bins of its own segment once, accumulating the
+// rising side U (band + 1's weights) and the falling side D (its own band's weights); the band value is D + the U of
+// the lane that owns the band below.  loadp(k, p) fetches the NF power values of bin k.  d[f][q] = 10 log10 of band
+// mel_band_of(q, lane): q0 = lane, q1 = 63 - lane, q2 = 64 + lane, q3 = 127 - lane.
+template <int NF, typename LoadP>
+__device__ __forceinline__ void mel_db(const ClipArgs& a, const Smem& sm, LoadP loadp, float (&d)[NF][4], int lane) {
+  const float2* mw = reinterpret_cast<const float2*>(sm.melw);
+  float U[4][NF], D[4][NF];
+#pragma unroll
+  for (int q = 0; q < 4; ++q) {
+#pragma unroll
+    for (int f = 0; f < NF; ++f) { U[q][f] = 0.f; D[q][f] = 0.f; }
+    const int k0 = __ldg(a.tab.mel_k0 + 32 * q + lane);
+    const float2* wq = mw + a.tab.mel_woff[q] + lane;
+    const int cnt = a.tab.mel_cnt[q];
+#pragma unroll 2
+    for (int i = 0; i < cnt; ++i) {
+      const float2 w = wq[32 * i];
+      float p[NF];
+      loadp(k0 + i, p);
+#pragma unroll
+      for (int f = 0; f < NF; ++f) { U[q][f] = fmaf(w.x, p[f], U[q][f]); D[q][f] = fmaf(w.y, p[f], D[q][f]); }
+    }
+  }
+  float u00[NF];   // segment 0: the bins below the first mel point rise into band 0
+#pragma unroll
+  for (int f = 0; f < NF; ++f) u00[f] = 0.f;
+  for (int i = 0; i < a.tab.mel_cnt0; ++i) {
+    const float w = mw[a.tab.mel_woff0 + i].x;
+    float p[NF];
+    loadp(a.tab.mel_k00 + i, p);
+#pragma unroll
+    for (int f = 0; f < NF; ++f) u00[f] = fmaf(w, p[f], u00[f]);
+  }
+#pragma unroll
+  for (int f = 0; f < NF; ++f) {
+    float up0 = __shfl_up_sync(0xffffffffu, U[0][f], 1);     // band lane - 1
+    float up1 = __shfl_down_sync(0xffffffffu, U[1][f], 1);   // band 62 - lane = (q1, lane + 1)
+    float up2 = __shfl_up_sync(0xffffffffu, U[2][f], 1);     // band 63 + lane = (q2, lane - 1)
+    float up3 = __shfl_down_sync(0xffffffffu, U[3][f], 1);   // band 126 - lane = (q3, lane + 1)
+    if (lane == 0) { up0 = u00[f]; up2 = U[1][f]; }          // band 63 is (q1, lane 0)
+    if (lane == 31) { up1 = U[0][f]; up3 = U[2][f]; }        // bands 31 and 95 are (q0, 31) and (q2, 31)
+    d[f][0] = to_db(D[0][f] + up0); d[f][1] = to_db(D[1][f] + up1);
+    d[f][2] = to_db(D[2][f] + up2); d[f][3] = to_db(D[3][f] + up3);
+  }
+}
 
 // ---- tail shared by the three front-ends: per-frame extrema of the unclamped log-mel rows, RMS, hop-block sums,
 // clamp at floor_db, DCT.  d[f][q] = unclamped log-mel of band 32 q + lane, eg = lane-partial hop-group energies.
@@ -258,23 +307,9 @@ struct WarpStep<1024, HOP> {
       if (k2 < 16 || lane == 0) P2[lane + 32 * k2] = make_float2(pa, pb);
     }
     __syncwarp();
-    // sparse mel (4 bands per lane), 10 log10
+    // sparse mel by segments, 10 log10
     float d[2][4];
-#pragma unroll
-    for (int q = 0; q < 4; ++q) {
-      const int k0 = __ldg(a.tab.mel_k0 + 32 * q + lane);
-      const float* wq = sm.melw + a.tab.mel_woff[q] + lane;
-      const int cnt = a.tab.mel_cnt[q];
-      float ma = 0.f, mb = 0.f;
-#pragma unroll 4
-      for (int i = 0; i < cnt; ++i) {
-        const float w = wq[32 * i];
-        const float2 p = P2[k0 + i];
-        ma = fmaf(w, p.x, ma);
-        mb = fmaf(w, p.y, mb);
-      }
-      d[0][q] = to_db(ma); d[1][q] = to_db(mb);
-    }
+    mel_db<2>(a, sm, [P2](int k, float (&p)[2]) { const float2 v = P2[k]; p[0] = v.x; p[1] = v.y; }, d, lane);
     __syncwarp();   // P2 consumed: the plane is free for the DCT reduction
     finish_step<1024, HOP>(a, sm, sl, wc, d, eg, nv, row, own_sums, usum_idx, floor_db, lane, bad);
   }
@@ -338,22 +373,10 @@ struct WarpStep<512, HOP> {
     }
     __syncwarp();
     float d[4][4];
-#pragma unroll
-    for (int q = 0; q < 4; ++q) {
-      const int k0 = __ldg(a.tab.mel_k0 + 32 * q + lane);
-      const float* wq = sm.melw + a.tab.mel_woff[q] + lane;
-      const int cnt = a.tab.mel_cnt[q];
-      float m0 = 0.f, m1 = 0.f, m2 = 0.f, m3 = 0.f;
-#pragma unroll 4
-      for (int i = 0; i < cnt; ++i) {
-        const float w = wq[32 * i];
-        const float2 p = P2[k0 + i];
-        const float2 p2 = P2[PSTRIDE + k0 + i];
-        m0 = fmaf(w, p.x, m0); m1 = fmaf(w, p.y, m1);
-        m2 = fmaf(w, p2.x, m2); m3 = fmaf(w, p2.y, m3);
-      }
-      d[0][q] = to_db(m0); d[1][q] = to_db(m1); d[2][q] = to_db(m2); d[3][q] = to_db(m3);
-    }
+    mel_db<4>(a, sm, [P2](int k, float (&p)[4]) {
+      const float2 v = P2[k], v2 = P2[PSTRIDE + k];
+      p[0] = v.x; p[1] = v.y; p[2] = v2.x; p[3] = v2.y;
+    }, d, lane);
     __syncwarp();
     finish_step<512, HOP>(a, sm, sl, wc, d, eg, nv, row, own_sums, usum_idx, floor_db, lane, bad);
   }
@@ -420,20 +443,7 @@ struct WarpStep<2048, HOP> {
     }
     __syncwarp();
     float d[1][4];
-#pragma unroll
-    for (int q = 0; q < 4; ++q) {
-      const int k0 = __ldg(a.tab.mel_k0 + 32 * q + lane);
-      const float* wq = sm.melw + a.tab.mel_woff[q] + lane;
-      const int cnt = a.tab.mel_cnt[q];
-      float m0 = 0.f, m1 = 0.f;
-      int i = 0;
-      for (; i + 1 < cnt; i += 2) {
-        m0 = fmaf(wq[32 * i], P[k0 + i], m0);
-        m1 = fmaf(wq[32 * i + 32], P[k0 + i + 1], m1);
-      }
-      if (i < cnt) m0 = fmaf(wq[32 * i], P[k0 + i], m0);
-      d[0][q] = to_db(m0 + m1);
-    }
+    mel_db<1>(a, sm, [P](int k, float (&p)[1]) { p[0] = P[k]; }, d, lane);
     __syncwarp();
     finish_step<2048, HOP>(a, sm, sl, wc, d, eg, nv, row, own_sums, usum_idx, floor_db, lane, bad);
   }
