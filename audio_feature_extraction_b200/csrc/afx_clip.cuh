@@ -32,6 +32,7 @@ namespace afx {
 constexpr int kMaxClipWarps = 16;                // CTA = 8 warps (two CTAs per SM) or 16 warps (one per SM), chosen by the host
 constexpr int kMaxClipThreads = kMaxClipWarps * 32;
 constexpr int kStatRows = kStatFrames + 2 * kStatHalo;   // frames per sub-chunk incl. halo
+constexpr int kMaxRedo = 1024;                            // listed steps of the top_db redo pass
 constexpr int kMoments = 6;                               // sum x, x^2, x^3, x^4, sum delta, sum delta2
 
 // raw sample range a warp step starting at absolute sample gA needs; tile position p holds sample gA - 4 + p.
@@ -52,18 +53,33 @@ __device__ __forceinline__ unsigned pair_copy_range(const Region& rg, int gA, in
 template <int NFFT, int HOP>
 __device__ __forceinline__ void stream_frames(const ClipArgs& a, const Smem& sm, const Slab& sl, WarpCtx& wc,
                                               const float* __restrict__ clip_audio, int L0, Region rg, int f_begin, int f_end,
-                                              int row_shift, bool own_sums, float floor_db, bool redo, int& bad) {
+                                              int row_shift, bool own_sums, float floor_db, bool redo, int& bad,
+                                              const int* redo_list = nullptr, int n_redo = 0) {
   using G = Geo<NFFT, HOP>;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const int stride = G::FPW * (int)(blockDim.x >> 5);   // frames per CTA step
+  const int nw = (int)(blockDim.x >> 5);
+  const int stride = G::FPW * nw;   // frames per CTA step
   auto need = [&](int f) -> bool {   // warp-uniform
     if (!redo) return true;
     float m = 3.0e38f;
     for (int j = 0; j < G::FPW; ++j) if (f + j < f_end) m = fminf(m, __ldcg(sl.rowmin + row_shift + f + j));
     return m < floor_db;
   };
-  int fA = f_begin + G::FPW * warp;
-  while (fA < f_end && !need(fA)) fA += stride;
+  // redo with a list: the steps to recompute were collected block-wide (redo_list[i] = first frame of a step)
+  int li = warp;
+  auto first_frame = [&]() -> int {
+    if (redo_list) return li < n_redo ? redo_list[li] : f_end;
+    int f = f_begin + G::FPW * warp;
+    while (f < f_end && !need(f)) f += stride;
+    return f;
+  };
+  auto next_frame = [&](int f) -> int {
+    if (redo_list) { li += nw; return li < n_redo ? redo_list[li] : f_end; }
+    f += stride;
+    while (f < f_end && !need(f)) f += stride;
+    return f;
+  };
+  int fA = first_frame();
   if (fA >= f_end) return;
   int gA = rg.origin + fA * HOP - NFFT / 2;
   unsigned cur_bytes;
@@ -77,8 +93,7 @@ __device__ __forceinline__ void stream_frames(const ClipArgs& a, const Smem& sm,
     }
   }
   while (fA < f_end) {
-    int fN = fA + stride;
-    while (fN < f_end && !need(fN)) fN += stride;
+    const int fN = next_frame(fA);
     const int gN = rg.origin + fN * HOP - NFFT / 2;
     unsigned next_bytes = 0;
     int g_lo = 0, s_lo = 0;
@@ -260,7 +275,8 @@ __global__ void __launch_bounds__(kMaxClipThreads, 1) clip_kernel(ClipArgs a) {
   sm.raw = sMel + a.mel_floats;
   sm.planes = sm.raw + (blockDim.x >> 5) * RAWW;
   float* sM = sm.raw;
-  __shared__ int s_clip, s_bad;
+  __shared__ int s_clip, s_bad, s_nredo;
+  __shared__ int s_redo[kMaxRedo];
 
   const int tid = threadIdx.x, warp = tid >> 5;
   for (int i = tid; i < 1024; i += (int)blockDim.x) sm.tw[i] = a.tab.twiddle[i];
@@ -302,6 +318,7 @@ __global__ void __launch_bounds__(kMaxClipThreads, 1) clip_kernel(ClipArgs a) {
     int a0 = 0;          // slab row of trimmed frame 0
     int head_end = 0;
     int bad = 0;
+    int n_redo = 0;
     // pass 0: S (speculative, absolute frame grid) or the whole pretrimmed clip; pass 1 / 2: head / tail fix-ups (F);
     // pass 3: R, redo with the top_db clamp the frames whose log-mel minimum lies below (clip max - top_db)
     float floor_db = -3.0e38f;
@@ -341,9 +358,22 @@ __global__ void __launch_bounds__(kMaxClipThreads, 1) clip_kernel(ClipArgs a) {
           floor_db = mx - a.mfcc_top_db;   // power_to_db(top_db): clamp at the clip-global maximum - top_db
           if (mn >= floor_db) break;       // nothing is clamped: the speculative DCT rows are exact
           fe = ci.n_frames;
+          // collect the steps whose unclamped row minimum lies below the floor (any order)
+          if (tid == 0) s_nredo = 0;
+          __syncthreads();
+          constexpr int FPW = Geo<NFFT, HOP>::FPW;
+          for (int f = FPW * tid; f < fe; f += FPW * (int)blockDim.x) {
+            float m = 3.0e38f;
+            for (int j = 0; j < FPW; ++j) if (f + j < fe) m = fminf(m, __ldcg(sl.rowmin + a0 + f + j));
+            if (m < floor_db) { const int pos = atomicAdd(&s_nredo, 1); if (pos < kMaxRedo) s_redo[pos] = f; }
+          }
+          __syncthreads();
+          n_redo = s_nredo;
         }
       }
-      stream_frames<NFFT, HOP>(a, sm, sl, wc, clip_audio, L0, rg, fb, fe, shift, own, floor_db, pass == 3, bad);
+      const bool listed = pass == 3 && n_redo <= kMaxRedo;   // else (very long clips) every warp filters its own steps
+      stream_frames<NFFT, HOP>(a, sm, sl, wc, clip_audio, L0, rg, fb, fe, shift, own, floor_db, pass == 3, bad,
+                               listed ? s_redo : nullptr, n_redo);
       if (pass == 0 && !a.pretrimmed) {
         if (bad) s_bad = 1;
         __syncthreads();

@@ -216,38 +216,71 @@ __device__ __forceinline__ void mel_db(const ClipArgs& a, const Smem& sm, LoadP 
 }
 
 // ---- tail shared by the three front-ends: per-frame extrema of the unclamped log-mel rows, RMS, hop-block sums,
-// clamp at floor_db, DCT.  d[f][q] = unclamped log-mel of band 32 q + lane, eg = lane-partial hop-group energies.
+// clamp at floor_db, DCT.  d[f][q] = unclamped log-mel of band mel_band_of(q, lane), eg = lane-partial hop-group energies.
+// Reduce M (power of two <= 16) per-lane values over the warp with M - 1 + log2(32 / M) shuffles instead of 5 M:
+// at each of the first log2(M) steps a lane keeps one half of its values and hands the other half to its partner.
+// On return v[0] is the full reduction of value index (lane >> (5 - log2 M)).
+template <int M, typename Op>
+__device__ __forceinline__ void warp_reduce_scatter(float (&v)[M], int lane, Op op) {
+  int dist = 16;
+#pragma unroll
+  for (int half = M / 2; half >= 1; half >>= 1, dist >>= 1) {
+    const bool hi = (lane & dist) != 0;
+#pragma unroll
+    for (int i = 0; i < half; ++i) {
+      const float send = hi ? v[i] : v[i + half];
+      const float keep = hi ? v[i + half] : v[i];
+      v[i] = op(keep, __shfl_xor_sync(0xffffffffu, send, dist));
+    }
+  }
+#pragma unroll
+  for (; dist >= 1; dist >>= 1) v[0] = op(v[0], __shfl_xor_sync(0xffffffffu, v[0], dist));
+}
+
 template <int NFFT, int HOP>
 __device__ __forceinline__ void finish_step(const ClipArgs& a, const Smem& sm, const Slab& sl, const WarpCtx& wc,
                                             float (&d)[Geo<NFFT, HOP>::FPW][4], float (&eg)[Geo<NFFT, HOP>::NG], int nv, int row,
                                             bool own_sums, int usum_idx, float floor_db, int lane, int& bad) {
   using G = Geo<NFFT, HOP>;
   constexpr int GPF = NFFT / HOP;   // hop groups per frame
+  constexpr int FPW = G::FPW;
+  constexpr int M = 2 * FPW;        // values per reduction
+  constexpr int LPV = 32 / M;       // lanes that end up holding one value
+  {  // sums of squares: [frame energies | owned hop blocks (groups G0 + f)]
+    float v[M];
 #pragma unroll
-  for (int g = 0; g < G::NG; ++g) eg[g] = warp_sum(eg[g]);
-  float esum = 0.f;
+    for (int f = 0; f < FPW; ++f) {
+      float e = 0.f;
 #pragma unroll
-  for (int g = 0; g < G::NG; ++g) esum += eg[g];
-  if (!isfinite(esum)) bad = 1;   // a NaN / Inf sample poisons the sums of squares (librosa.util.valid_audio)
+      for (int g = 0; g < GPF; ++g) e += eg[f + g];
+      v[f] = e; v[FPW + f] = eg[G::G0 + f];
+    }
+    warp_reduce_scatter<M>(v, lane, [](float x, float y) { return x + y; });
+    // a NaN / Inf sample poisons the sums of squares (librosa.util.valid_audio); the frame energies cover every group
+    if (__any_sync(0xffffffffu, !isfinite(v[0]))) bad = 1;
+    const int j = lane / LPV;
+    if ((lane & (LPV - 1)) == 0) {
+      if (j < FPW) { if (j < nv) __stcg(sl.rms + row + j, sqrtf(v[0] * (1.0f / NFFT))); }
+      else if (own_sums) __stcg(sl.blk + usum_idx + (j - FPW), v[0]);
+    }
+  }
+  {  // extrema of the unclamped log-mel rows: [row maxima | negated row minima]
+    float v[M];
 #pragma unroll
-  for (int f = 0; f < G::FPW; ++f) {
-    float mx = fmaxf(fmaxf(d[f][0], d[f][1]), fmaxf(d[f][2], d[f][3]));
-    float mn = fminf(fminf(d[f][0], d[f][1]), fminf(d[f][2], d[f][3]));
-    mx = warp_max(mx); mn = warp_min(mn);
-    float e = 0.f;
-#pragma unroll
-    for (int g = 0; g < GPF; ++g) e += eg[f + g];
-    if (lane == 0 && f < nv) {
-      __stcg(sl.rms + row + f, sqrtf(e * (1.0f / NFFT)));
-      __stcg(sl.rowmax + row + f, mx);
-      __stcg(sl.rowmin + row + f, mn);
+    for (int f = 0; f < FPW; ++f) {
+      v[f] = fmaxf(fmaxf(d[f][0], d[f][1]), fmaxf(d[f][2], d[f][3]));
+      v[FPW + f] = -fminf(fminf(d[f][0], d[f][1]), fminf(d[f][2], d[f][3]));
+    }
+    warp_reduce_scatter<M>(v, lane, [](float x, float y) { return fmaxf(x, y); });
+    const int j = lane / LPV;
+    if ((lane & (LPV - 1)) == 0) {
+      if (j < FPW) { if (j < nv) __stcg(sl.rowmax + row + j, v[0]); }
+      else if (j - FPW < nv) __stcg(sl.rowmin + row + (j - FPW), -v[0]);
     }
 #pragma unroll
-    for (int q = 0; q < 4; ++q) d[f][q] = fmaxf(d[f][q], floor_db);
-  }
-  if (own_sums && lane == 0) {   // blocks [(fA + f) hop, + hop) are groups G0 + f
+    for (int f = 0; f < FPW; ++f)
 #pragma unroll
-    for (int f = 0; f < G::FPW; ++f) __stcg(sl.blk + usum_idx + f, eg[G::G0 + f]);
+      for (int q = 0; q < 4; ++q) d[f][q] = fmaxf(d[f][q], floor_db);
   }
   if (G::FPW == 1) {
     dct_pair(a, sm, sl, wc, d[0], d[0], row, false, lane);
