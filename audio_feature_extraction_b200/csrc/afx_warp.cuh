@@ -86,47 +86,49 @@ __device__ __forceinline__ void prefetch_next(WarpCtx& wc, unsigned bytes, const
   }
 }
 
-// transpose (lane a, reg b) -> (lane b, reg a) of a 32 x 32 register tile through the warp's plane,
-// writing the result in bit-reversed register order (the input order of the next 32-point DIT)
-__device__ __forceinline__ void transpose32_bitrev(float (&v)[32], float* plane, int lane) {
+// transpose (lane a, reg b) -> (lane b, reg a) of a 32 x 32 tile of packed complex values through the warp's plane
+// (one half at a time: the plane holds 32 x 33 floats), writing the result in bit-reversed register order (the input
+// order of the next 32-point DIT)
+__device__ __forceinline__ void transpose32_bitrev(c64 (&z)[32], float* plane, int lane) {
+  float t[32];
 #pragma unroll
-  for (int k = 0; k < 32; ++k) plane[k * 33 + lane] = v[k];
+  for (int k = 0; k < 32; ++k) plane[k * 33 + lane] = lo2(z[k]);
   __syncwarp();
 #pragma unroll
-  for (int n = 0; n < 32; ++n) v[bitrev32(n)] = plane[lane * 33 + n];
+  for (int n = 0; n < 32; ++n) t[n] = plane[lane * 33 + n];
+  __syncwarp();
+#pragma unroll
+  for (int k = 0; k < 32; ++k) plane[k * 33 + lane] = hi2(z[k]);
+  __syncwarp();
+#pragma unroll
+  for (int n = 0; n < 32; ++n) z[bitrev32(n)] = pk2(t[n], plane[lane * 33 + n]);
   __syncwarp();
 }
 
-// complex 1024-point FFT of z[32*n1 + lane] held as (r, im)[bitrev32(n1)]; result Z[lane + 32*k2] in (r, im)[k2]
-__device__ __forceinline__ void fft1024_core(float (&r)[32], float (&im)[32], const Smem& sm, float* plane, int lane) {
-  fft32_dit(r, im);
+// complex 1024-point FFT of z[32*n1 + lane] held at register bitrev32(n1); result Z[lane + 32*k2] in z[k2]
+__device__ __forceinline__ void fft1024_core(c64 (&z)[32], const Smem& sm, float* plane, int lane) {
+  fft32_dit2(z);
 #pragma unroll
   for (int k1 = 1; k1 < 32; ++k1) {   // twiddle by W_1024^(k1 * lane)
     const float2 w = sm.tw[k1 * 32 + lane];
-    const float tr = r[k1] * w.x - im[k1] * w.y;
-    const float ti = fmaf(r[k1], w.y, im[k1] * w.x);
-    r[k1] = tr; im[k1] = ti;
+    z[k1] = cmul2(z[k1], w.x, w.y);
   }
-  transpose32_bitrev(r, plane, lane);
-  transpose32_bitrev(im, plane, lane);
-  fft32_dit(r, im);
+  transpose32_bitrev(z, plane, lane);
+  fft32_dit2(z);
 }
 
 // two complex 512-point FFTs: signal s in registers [16 s, 16 s + 16) as z_s[32*n1 + lane] at bitrev16(n1);
-// result: lane 16 s + k1 holds Z_s[k1 + 16*k2] in (r, im)[k2]
-__device__ __forceinline__ void fft512x2_core(float (&r)[32], float (&im)[32], const Smem& sm, float* plane, int lane) {
-  fft16x2_dit(r, im);
+// result: lane 16 s + k1 holds Z_s[k1 + 16*k2] in z[k2]
+__device__ __forceinline__ void fft512x2_core(c64 (&z)[32], const Smem& sm, float* plane, int lane) {
+  fft16x2_dit2(z);
 #pragma unroll
   for (int j = 0; j < 32; ++j) {      // twiddle by W_512^(k1 * lane), k1 = j & 15
     if ((j & 15) == 0) continue;
     const float2 w = sm.tw[(j & 15) * 32 + lane];
-    const float tr = r[j] * w.x - im[j] * w.y;
-    const float ti = fmaf(r[j], w.y, im[j] * w.x);
-    r[j] = tr; im[j] = ti;
+    z[j] = cmul2(z[j], w.x, w.y);
   }
-  transpose32_bitrev(r, plane, lane);
-  transpose32_bitrev(im, plane, lane);
-  fft32_dit(r, im);
+  transpose32_bitrev(z, plane, lane);
+  fft32_dit2(z);
 }
 
 // ---- DCT-II (ortho) of two clamped log-mel rows, 16 coefficients at a time.  A lane holds the mirror pairs
@@ -323,7 +325,12 @@ struct WarpStep<1024, HOP> {
     else load<false>(r, im, eg, wc.raw + 4, gA, rg, L0, a.coef, sm, lane);
     prefetch_next(wc, next_bytes, next_src, next_dst, lane);
     float* plane = wc.plane;
-    fft1024_core(r, im, sm, plane, lane);   // (r[k2], im[k2]) = Z[lane + 32 k2]
+    c64 z[32];
+#pragma unroll
+    for (int k = 0; k < 32; ++k) z[k] = pk2(r[k], im[k]);
+    fft1024_core(z, sm, plane, lane);   // z[k2] = Z[lane + 32 k2]
+#pragma unroll
+    for (int k = 0; k < 32; ++k) { r[k] = lo2(z[k]); im[k] = hi2(z[k]); }
     // split the two real spectra, power -> P2[k] = (|A_k|^2, |B_k|^2), k = 0..512
     float2* P2 = reinterpret_cast<float2*>(plane);
     const int src = (32 - lane) & 31;
@@ -386,7 +393,12 @@ struct WarpStep<512, HOP> {
     else load<false>(r, im, eg, wc.raw + 4, gA, rg, L0, a.coef, sm, lane);
     prefetch_next(wc, next_bytes, next_src, next_dst, lane);
     float* plane = wc.plane;
-    fft512x2_core(r, im, sm, plane, lane);   // lane 16 s + k1: (r[k2], im[k2]) = Z_s[k1 + 16 k2]
+    c64 z[32];
+#pragma unroll
+    for (int k = 0; k < 32; ++k) z[k] = pk2(r[k], im[k]);
+    fft512x2_core(z, sm, plane, lane);   // lane 16 s + k1: z[k2] = Z_s[k1 + 16 k2]
+#pragma unroll
+    for (int k = 0; k < 32; ++k) { r[k] = lo2(z[k]); im[k] = hi2(z[k]); }
     // split each signal's two real spectra, power -> P2[s][k] = (|X_{2s}[k]|^2, |X_{2s+1}[k]|^2), k = 0..256
     float2* P2 = reinterpret_cast<float2*>(plane);
     const int k1 = lane & 15;
@@ -456,7 +468,12 @@ struct WarpStep<2048, HOP> {
     else load<false>(r, im, eg, wc.raw + 4, gA, rg, L0, a.coef, sm, lane);
     prefetch_next(wc, next_bytes, next_src, next_dst, lane);
     float* plane = wc.plane;
-    fft1024_core(r, im, sm, plane, lane);   // (r[k2], im[k2]) = Z[lane + 32 k2]
+    c64 z[32];
+#pragma unroll
+    for (int k = 0; k < 32; ++k) z[k] = pk2(r[k], im[k]);
+    fft1024_core(z, sm, plane, lane);   // z[k2] = Z[lane + 32 k2]
+#pragma unroll
+    for (int k = 0; k < 32; ++k) { r[k] = lo2(z[k]); im[k] = hi2(z[k]); }
     float* P = plane;                        // [1025] power spectrum
     const int src = (32 - lane) & 31;
 #pragma unroll
