@@ -131,6 +131,56 @@ __device__ __forceinline__ void fft512x2_core(c64 (&z)[32], const Smem& sm, floa
   fft32_dit2(z);
 }
 
+__device__ __forceinline__ float to_db(float m) { return 3.0102999566398120f * __log2f(fmaxf(m, 1e-10f)); }   // 10 log10(max(1e-10, m))
+
+// Packed variant: NP pairs of frames per bin (power spectra stored as (frame 2p, frame 2p + 1) pairs): one FFMA2 per
+// (weight, pair).  d[2 p + h][q].
+template <int NP, typename LoadP>
+__device__ __forceinline__ void mel_db2(const ClipArgs& a, const Smem& sm, LoadP loadp, float (&d)[2 * NP][4], int lane) {
+  const float2* mw = reinterpret_cast<const float2*>(sm.melw);
+  c64 U[4][NP], D[4][NP];
+#pragma unroll
+  for (int q = 0; q < 4; ++q) {
+#pragma unroll
+    for (int f = 0; f < NP; ++f) { U[q][f] = 0ull; D[q][f] = 0ull; }
+    const int k0 = __ldg(a.tab.mel_k0 + 32 * q + lane);
+    const float2* wq = mw + a.tab.mel_woff[q] + lane;
+    const int cnt = a.tab.mel_cnt[q];
+#pragma unroll 2
+    for (int i = 0; i < cnt; ++i) {
+      const float2 w = wq[32 * i];
+      c64 p[NP];
+      loadp(k0 + i, p);
+#pragma unroll
+      for (int f = 0; f < NP; ++f) { U[q][f] = fma2(p[f], bc2(w.x), U[q][f]); D[q][f] = fma2(p[f], bc2(w.y), D[q][f]); }
+    }
+  }
+  c64 u00[NP];   // segment 0: the bins below the first mel point rise into band 0
+#pragma unroll
+  for (int f = 0; f < NP; ++f) u00[f] = 0ull;
+  for (int i = 0; i < a.tab.mel_cnt0; ++i) {
+    const float w = mw[a.tab.mel_woff0 + i].x;
+    c64 p[NP];
+    loadp(a.tab.mel_k00 + i, p);
+#pragma unroll
+    for (int f = 0; f < NP; ++f) u00[f] = fma2(p[f], bc2(w), u00[f]);
+  }
+#pragma unroll
+  for (int f = 0; f < NP; ++f) {
+    c64 up0 = __shfl_up_sync(0xffffffffu, U[0][f], 1);     // band lane - 1
+    c64 up1 = __shfl_down_sync(0xffffffffu, U[1][f], 1);   // band 62 - lane = (q1, lane + 1)
+    c64 up2 = __shfl_up_sync(0xffffffffu, U[2][f], 1);     // band 63 + lane = (q2, lane - 1)
+    c64 up3 = __shfl_down_sync(0xffffffffu, U[3][f], 1);   // band 126 - lane = (q3, lane + 1)
+    if (lane == 0) { up0 = u00[f]; up2 = U[1][f]; }        // band 63 is (q1, lane 0)
+    if (lane == 31) { up1 = U[0][f]; up3 = U[2][f]; }      // bands 31 and 95 are (q0, 31) and (q2, 31)
+    const c64 m0 = add2(D[0][f], up0), m1 = add2(D[1][f], up1), m2 = add2(D[2][f], up2), m3 = add2(D[3][f], up3);
+    d[2 * f][0] = to_db(lo2(m0)); d[2 * f + 1][0] = to_db(hi2(m0));
+    d[2 * f][1] = to_db(lo2(m1)); d[2 * f + 1][1] = to_db(hi2(m1));
+    d[2 * f][2] = to_db(lo2(m2)); d[2 * f + 1][2] = to_db(hi2(m2));
+    d[2 * f][3] = to_db(lo2(m3)); d[2 * f + 1][3] = to_db(hi2(m3));
+  }
+}
+
 // ---- DCT-II (ortho) of two clamped log-mel rows, 16 coefficients at a time.  A lane holds the mirror pairs
 // (lane, 127 - lane) = d[0], d[3] and (63 - lane, 64 + lane) = d[1], d[2]; cos(pi k (2 (127 - b) + 1) / 256) =
 // (-1)^k cos(pi k (2 b + 1) / 256), so even coefficients need only the pair sums and odd ones the pair differences:
@@ -140,8 +190,9 @@ __device__ __forceinline__ void dct_pair(const ClipArgs& a, const Smem& sm, cons
                                          const float (&da)[4], const float (&db)[4], int row, bool vB, int lane) {
   float* plane = wc.plane;
   const int stride = 2 * a.n16 + 4;
-  const float ea0 = da[0] + da[3], oa0 = da[0] - da[3], ea1 = da[1] + da[2], oa1 = da[1] - da[2];
-  const float eb0 = db[0] + db[3], ob0 = db[0] - db[3], eb1 = db[1] + db[2], ob1 = db[1] - db[2];
+  // (frame A, frame B) pairs: one FMUL2 + one FFMA2 per coefficient
+  const c64 d0 = pk2(da[0], db[0]), d1 = pk2(da[1], db[1]), d2 = pk2(da[2], db[2]), d3 = pk2(da[3], db[3]);
+  const c64 e0 = add2(d0, d3), o0 = sub2(d0, d3), e1 = add2(d1, d2), o1 = sub2(d1, d2);
   for (int kg = 0; kg < a.n16; kg += 16) {
     float pa[16], pb[16];
     const float* c0row = sm.dct + lane * stride + kg;   // band lane
@@ -150,10 +201,14 @@ __device__ __forceinline__ void dct_pair(const ClipArgs& a, const Smem& sm, cons
     for (int k4 = 0; k4 < 4; ++k4) {
       const float4 c0 = *reinterpret_cast<const float4*>(c0row + 4 * k4);
       const float4 c1 = *reinterpret_cast<const float4*>(c1row + 4 * k4);
-      pa[4 * k4 + 0] = fmaf(ea0, c0.x, ea1 * c1.x); pb[4 * k4 + 0] = fmaf(eb0, c0.x, eb1 * c1.x);
-      pa[4 * k4 + 1] = fmaf(oa0, c0.y, oa1 * c1.y); pb[4 * k4 + 1] = fmaf(ob0, c0.y, ob1 * c1.y);
-      pa[4 * k4 + 2] = fmaf(ea0, c0.z, ea1 * c1.z); pb[4 * k4 + 2] = fmaf(eb0, c0.z, eb1 * c1.z);
-      pa[4 * k4 + 3] = fmaf(oa0, c0.w, oa1 * c1.w); pb[4 * k4 + 3] = fmaf(ob0, c0.w, ob1 * c1.w);
+      const c64 p0 = fma2(e0, bc2(c0.x), mul2(e1, bc2(c1.x)));
+      const c64 p1 = fma2(o0, bc2(c0.y), mul2(o1, bc2(c1.y)));
+      const c64 p2 = fma2(e0, bc2(c0.z), mul2(e1, bc2(c1.z)));
+      const c64 p3 = fma2(o0, bc2(c0.w), mul2(o1, bc2(c1.w)));
+      pa[4 * k4 + 0] = lo2(p0); pb[4 * k4 + 0] = hi2(p0);
+      pa[4 * k4 + 1] = lo2(p1); pb[4 * k4 + 1] = hi2(p1);
+      pa[4 * k4 + 2] = lo2(p2); pb[4 * k4 + 2] = hi2(p2);
+      pa[4 * k4 + 3] = lo2(p3); pb[4 * k4 + 3] = hi2(p3);
     }
 #pragma unroll
     for (int k = 0; k < 16; ++k) { plane[k * 33 + lane] = pa[k]; plane[(16 + k) * 33 + lane] = pb[k]; }
@@ -168,7 +223,6 @@ __device__ __forceinline__ void dct_pair(const ClipArgs& a, const Smem& sm, cons
   }
 }
 
-__device__ __forceinline__ float to_db(float m) { return 3.0102999566398120f * __log2f(fmaxf(m, 1e-10f)); }   // 10 log10(max(1e-10, m))
 
 // ---- sparse Slaney mel by SEGMENTS (afx_tables.h): (q, lane) walks the bins of its own segment once, accumulating the
 // rising side U (band + 1's weights) and the falling side D (its own band's weights); the band value is D + the U of
@@ -329,27 +383,25 @@ struct WarpStep<1024, HOP> {
 #pragma unroll
     for (int k = 0; k < 32; ++k) z[k] = pk2(r[k], im[k]);
     fft1024_core(z, sm, plane, lane);   // z[k2] = Z[lane + 32 k2]
-#pragma unroll
-    for (int k = 0; k < 32; ++k) { r[k] = lo2(z[k]); im[k] = hi2(z[k]); }
-    // split the two real spectra, power -> P2[k] = (|A_k|^2, |B_k|^2), k = 0..512
-    float2* P2 = reinterpret_cast<float2*>(plane);
+    // split the two real spectra, power -> P2[k] = (|A_k|^2, |B_k|^2), k = 0..512.  With the partner Q = Z[1024 - k]:
+    // X = Z + Q = (sr, si), Y = Z - Q = (dr, di); |A|^2 = sr^2 + di^2, |B|^2 = si^2 + dr^2, i.e. X^2 + swap(Y^2) on pairs
+    c64* P2 = reinterpret_cast<c64*>(plane);
     const int src = (32 - lane) & 31;
 #pragma unroll
     for (int k2 = 0; k2 <= 16; ++k2) {
       const int pk = (k2 < 16) ? 31 - k2 : 15;
-      float pr = __shfl_sync(0xffffffffu, r[pk], src);
-      float pi = __shfl_sync(0xffffffffu, im[pk], src);
-      if (lane == 0) { pr = r[(32 - k2) & 31]; pi = im[(32 - k2) & 31]; }
-      const float sr = r[k2] + pr, di = im[k2] - pi;
-      const float si = im[k2] + pi, dr = r[k2] - pr;
-      const float pa = fmaf(sr, sr, di * di);
-      const float pb = fmaf(si, si, dr * dr);
-      if (k2 < 16 || lane == 0) P2[lane + 32 * k2] = make_float2(pa, pb);
+      float pr = __shfl_sync(0xffffffffu, lo2(z[pk]), src);
+      float pi = __shfl_sync(0xffffffffu, hi2(z[pk]), src);
+      if (lane == 0) { pr = lo2(z[(32 - k2) & 31]); pi = hi2(z[(32 - k2) & 31]); }
+      const c64 q = pk2(pr, pi);
+      const c64 x = add2(z[k2], q), y = sub2(z[k2], q);
+      const c64 pw = fma2(x, x, swap2(mul2(y, y)));
+      if (k2 < 16 || lane == 0) P2[lane + 32 * k2] = pw;
     }
     __syncwarp();
     // sparse mel by segments, 10 log10
     float d[2][4];
-    mel_db<2>(a, sm, [P2](int k, float (&p)[2]) { const float2 v = P2[k]; p[0] = v.x; p[1] = v.y; }, d, lane);
+    mel_db2<1>(a, sm, [P2](int k, c64 (&p)[1]) { p[0] = P2[k]; }, d, lane);
     __syncwarp();   // P2 consumed: the plane is free for the DCT reduction
     finish_step<1024, HOP>(a, sm, sl, wc, d, eg, nv, row, own_sums, usum_idx, floor_db, lane, bad);
   }
@@ -397,31 +449,25 @@ struct WarpStep<512, HOP> {
 #pragma unroll
     for (int k = 0; k < 32; ++k) z[k] = pk2(r[k], im[k]);
     fft512x2_core(z, sm, plane, lane);   // lane 16 s + k1: z[k2] = Z_s[k1 + 16 k2]
-#pragma unroll
-    for (int k = 0; k < 32; ++k) { r[k] = lo2(z[k]); im[k] = hi2(z[k]); }
     // split each signal's two real spectra, power -> P2[s][k] = (|X_{2s}[k]|^2, |X_{2s+1}[k]|^2), k = 0..256
-    float2* P2 = reinterpret_cast<float2*>(plane);
+    c64* P2 = reinterpret_cast<c64*>(plane);
     const int k1 = lane & 15;
     const int src = (lane & 16) | ((16 - k1) & 15);
-    float2* Ps = P2 + (lane >> 4) * PSTRIDE + k1;
+    c64* Ps = P2 + (lane >> 4) * PSTRIDE + k1;
 #pragma unroll
     for (int k2 = 0; k2 <= 16; ++k2) {
       const int pk = (k2 < 16) ? 31 - k2 : 15;
-      float pr = __shfl_sync(0xffffffffu, r[pk], src);
-      float pi = __shfl_sync(0xffffffffu, im[pk], src);
-      if (k1 == 0) { pr = r[(32 - k2) & 31]; pi = im[(32 - k2) & 31]; }
-      const float sr = r[k2] + pr, di = im[k2] - pi;
-      const float si = im[k2] + pi, dr = r[k2] - pr;
-      const float pa = fmaf(sr, sr, di * di);
-      const float pb = fmaf(si, si, dr * dr);
-      if (k2 < 16 || k1 == 0) Ps[16 * k2] = make_float2(pa, pb);
+      float pr = __shfl_sync(0xffffffffu, lo2(z[pk]), src);
+      float pi = __shfl_sync(0xffffffffu, hi2(z[pk]), src);
+      if (k1 == 0) { pr = lo2(z[(32 - k2) & 31]); pi = hi2(z[(32 - k2) & 31]); }
+      const c64 q = pk2(pr, pi);
+      const c64 x = add2(z[k2], q), y = sub2(z[k2], q);
+      const c64 pw = fma2(x, x, swap2(mul2(y, y)));
+      if (k2 < 16 || k1 == 0) Ps[16 * k2] = pw;
     }
     __syncwarp();
     float d[4][4];
-    mel_db<4>(a, sm, [P2](int k, float (&p)[4]) {
-      const float2 v = P2[k], v2 = P2[PSTRIDE + k];
-      p[0] = v.x; p[1] = v.y; p[2] = v2.x; p[3] = v2.y;
-    }, d, lane);
+    mel_db2<2>(a, sm, [P2](int k, c64 (&p)[2]) { p[0] = P2[k]; p[1] = P2[PSTRIDE + k]; }, d, lane);
     __syncwarp();
     finish_step<512, HOP>(a, sm, sl, wc, d, eg, nv, row, own_sums, usum_idx, floor_db, lane, bad);
   }
