@@ -13,6 +13,7 @@ _PKG = Path(__file__).resolve().parent
 LIB_PATH = _PKG / "lib" / "libafx_b200.so"
 
 AFX_FEAT_F0, AFX_FEAT_MFCC, AFX_FEAT_ENERGY, AFX_FEAT_ALL = 0x1, 0x2, 0x4, 0x7
+AFX_FEAT_PREPROCESSED = 0x100   # clips are outputs of preprocess_audio: no filter, no trim
 CLIP_OK, CLIP_EMPTY, CLIP_NONFINITE, CLIP_TOO_SHORT = 0, 1, 2, 3
 ABI_VERSION = 1
 ERR_INVALID_ARG, ERR_CUDA, ERR_WORKSPACE, ERR_UNSUPPORTED = 1, 2, 3, 4
@@ -21,7 +22,7 @@ EXPORTS = [
     "afx_config_default", "afx_abi_version", "afx_last_error", "afx_create", "afx_destroy",
     "afx_summary_width", "afx_frame_width", "afx_max_frames", "afx_workspace_bytes",
     "afx_workspace_min_bytes", "afx_extract", "afx_extract_host", "afx_extract_host_packed",
-    "afx_launch_count", "afx_profile_enable", "afx_profile_read",
+    "afx_launch_count", "afx_profile_enable", "afx_profile_read", "afx_preprocess",
 ]
 PHASES = ("trim", "frames", "mfcc", "finalize", "pcm", "yin", "viterbi", "reserved")
 N_PHASES = 8
@@ -69,6 +70,7 @@ def lib():
     L.afx_workspace_bytes.argtypes = [vp, i64, vp]; L.afx_workspace_bytes.restype = sz
     L.afx_workspace_min_bytes.argtypes = [vp, i64, vp]; L.afx_workspace_min_bytes.restype = sz
     L.afx_extract.argtypes = [vp, vp, vp, vp, i64, u32, vp, vp, vp, vp, sz, vp]; L.afx_extract.restype = C.c_int
+    L.afx_preprocess.argtypes = [vp, vp, vp, vp, i64, vp, vp, vp, vp, sz, vp]; L.afx_preprocess.restype = C.c_int
     L.afx_extract_host.argtypes = [vp, vp, vp, i64, u32, vp, vp]; L.afx_extract_host.restype = C.c_int
     L.afx_extract_host_packed.argtypes = [vp, vp, C.c_int, i64, vp, vp, i64, u32, vp, vp]
     L.afx_extract_host_packed.restype = C.c_int

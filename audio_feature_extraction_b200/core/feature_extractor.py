@@ -42,6 +42,9 @@ def _mask_of(features_to_extract: Optional[Sequence[str]]) -> int:
         return N.AFX_FEAT_ALL
     m = 0
     for f in features_to_extract:
+        if f == "preprocessed":   # modifier: the waveforms are outputs of preprocess_audio
+            m |= N.AFX_FEAT_PREPROCESSED
+            continue
         if f not in _MASKS:
             raise ValueError(f"unknown feature group {f!r}; expected a subset of {FEATURE_GROUPS}")
         m |= _MASKS[f]
@@ -233,6 +236,55 @@ class AudioFeatureExtractor:
         return out
 
     # ------------------------------------------------------------------ reference API
+    def _to_device(self, y: np.ndarray):
+        import torch
+        buf, offsets, lengths = self.pack_clips([np.asarray(y, dtype=np.float32)])
+        return buf.to(torch.device("cuda", self.device), non_blocking=True), offsets, lengths
+
+    def preprocess_audio(self, y: np.ndarray) -> np.ndarray:
+        """音頻預處理 (reference :58-74): librosa.effects.preemphasis(coef=self.pre_emphasis) then
+        librosa.effects.trim(top_db=30), both on the device (afx_preprocess)."""
+        import torch
+        L = N.lib()
+        h = self._h()
+        audio, offsets, lengths = self._to_device(y)
+        out = torch.zeros_like(audio)
+        meta = torch.empty((1, 4), dtype=torch.int32, device=audio.device)
+        scratch = torch.empty((1, self.summary_width), dtype=torch.float32, device=audio.device)
+        need = L.afx_workspace_bytes(h, 1, lengths.ctypes.data)
+        if self._ws is None or self._ws.numel() < need or self._ws.device != audio.device:
+            self._ws = torch.empty(int(need), dtype=torch.uint8, device=audio.device)
+        N.check(L.afx_preprocess(h, audio.data_ptr(), offsets.ctypes.data, lengths.ctypes.data, 1, out.data_ptr(),
+                                 meta.data_ptr(), scratch.data_ptr(), self._ws.data_ptr(), self._ws.numel(),
+                                 torch.cuda.current_stream(audio.device).cuda_stream))
+        m = meta.cpu().numpy()[0]
+        if int(m[0]) == N.CLIP_NONFINITE:   # librosa.util.valid_audio raises ParameterError
+            raise FeatureExtractionError(_STATUS_MSG[N.CLIP_NONFINITE])
+        return out[int(m[1]):int(m[2])].cpu().numpy()   # empty when every frame is silent, as librosa returns
+
+    def _extract_preprocessed(self, y: np.ndarray, group: str) -> Dict[str, Any]:
+        audio, offsets, lengths = self._to_device(y)
+        feats = (group, "preprocessed")
+        summaries, meta, _ = self.extract_batch_device(audio, offsets, lengths, feats)
+        d = self.rows_to_dicts(summaries.cpu().numpy(), meta.cpu().numpy(), ["<array>"], feats)[0]
+        d.pop("file_path")
+        return d
+
+    def extract_f0(self, y: np.ndarray) -> Dict[str, Any]:
+        """提取F0特徵 (reference :76-114): librosa.pyin on an already preprocessed waveform ->
+        f0_mean, f0_std, f0_missing_rate, f0_quality."""
+        return self._extract_preprocessed(y, "f0")
+
+    def extract_mfcc(self, y: np.ndarray) -> Dict[str, Any]:
+        """提取MFCC特徵 (reference :116-151) on an already preprocessed waveform ->
+        mfcc_mean, mfcc_std, mfcc_delta_mean, mfcc_delta2_mean."""
+        return self._extract_preprocessed(y, "mfcc")
+
+    def extract_energy(self, y: np.ndarray) -> Dict[str, Any]:
+        """提取能量特徵 (reference :153-179) on an already preprocessed waveform ->
+        energy_mean, energy_std, energy_range."""
+        return self._extract_preprocessed(y, "energy")
+
     def load_audio(self, audio_path: str) -> Tuple[np.ndarray, int]:
         """載入音頻文件 (reference :41-56): float32 mono at self.sr."""
         try:

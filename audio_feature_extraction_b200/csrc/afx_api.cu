@@ -355,7 +355,13 @@ int afx_extract(afx_handle_t h, const float* d_audio, const int64_t* h_offsets, 
   if (n_clips < 0 || n_clips > 0x7fffff00LL) return fail(AFX_ERR_INVALID_ARG, "afx_extract: bad n_clips");
   if (!d_audio || !h_offsets || !h_lengths || !d_summaries || !d_meta || !d_workspace)
     return fail(AFX_ERR_INVALID_ARG, "afx_extract: null pointer argument");
-  if ((feature_mask & ~AFX_FEAT_ALL) != 0) return fail(AFX_ERR_INVALID_ARG, "afx_extract: unknown feature bits 0x%x", feature_mask);
+  if ((feature_mask & ~(AFX_FEAT_ALL | AFX_FEAT_PREPROCESSED)) != 0) return fail(AFX_ERR_INVALID_ARG, "afx_extract: unknown feature bits 0x%x", feature_mask);
+  // AFX_FEAT_PREPROCESSED: the clips are outputs of preprocess_audio (already pre-emphasised and trimmed), the way the
+  // reference's extract_f0 / extract_mfcc / extract_energy receive them: no filter, no first-sample rule, no trim
+  const bool raw = (feature_mask & AFX_FEAT_PREPROCESSED) != 0;
+  feature_mask &= AFX_FEAT_ALL;
+  const float coef = raw ? 0.f : h->cfg.pre_emphasis;
+  const float trim_top_db = raw ? 3.0e38f : h->cfg.trim_top_db;
   if ((feature_mask & AFX_FEAT_F0) && !h->f0_ok)
     return fail(AFX_ERR_UNSUPPORTED, "afx_extract: the F0 (pYIN) group does not support this f0_min / f0_max / frame geometry");
   if ((reinterpret_cast<uintptr_t>(d_audio) & 15u) != 0) return fail(AFX_ERR_INVALID_ARG, "afx_extract: d_audio must be 16-byte aligned");
@@ -418,7 +424,7 @@ int afx_extract(afx_handle_t h, const float* d_audio, const int64_t* h_offsets, 
   if (!one_pass) {  // hop does not divide 512: the trim decision needs its own pass over the batch first
     afx::TrimArgs ta;
     ta.audio = d_audio; ta.offsets = d_offsets; ta.lengths = d_lengths; ta.info = d_info;
-    ta.clip_begin = 0; ta.hop = hop; ta.coef = h->cfg.pre_emphasis; ta.top_db = h->cfg.trim_top_db;
+    ta.clip_begin = 0; ta.hop = hop; ta.coef = coef; ta.top_db = trim_top_db; ta.raw = raw ? 1 : 0;
     const size_t smem = (size_t)(ceil_div(max_len, afx::kTrimHop) + 4) * sizeof(float);
     PhaseTimer pt(h, stream, AFX_PHASE_TRIM);
     afx::trim_kernel<<<n, afx::kTrimThreads, smem, stream>>>(ta);
@@ -432,7 +438,7 @@ int afx_extract(afx_handle_t h, const float* d_audio, const int64_t* h_offsets, 
     ca.counter = reinterpret_cast<int*>(ws + L.off_counter); ca.n_clips = n;
     ca.slabs = ws + L.header_bytes; ca.slab_bytes = slab_bytes; ca.a_max = slab_rows(h, max_len);
     ca.tab = h->tab; ca.dct_t = h->d_dct_t; ca.hop = hop; ca.mel_floats = h->mel_floats;
-    ca.coef = h->cfg.pre_emphasis; ca.trim_top_db = h->cfg.trim_top_db; ca.mfcc_top_db = h->cfg.mfcc_top_db;
+    ca.coef = coef; ca.trim_top_db = trim_top_db; ca.mfcc_top_db = h->cfg.mfcc_top_db; ca.raw = raw ? 1 : 0;
     ca.n_mfcc = h->cfg.n_mfcc; ca.n16 = h->n16; ca.summary_width = afx_summary_width(h); ca.frame_width = afx_frame_width(h);
     ca.mask = feature_mask; ca.summaries = d_summaries; ca.meta = d_meta; ca.frames_out = d_frames;
     ca.pretrimmed = one_pass ? 0 : 1;
@@ -476,7 +482,7 @@ int afx_extract(afx_handle_t h, const float* d_audio, const int64_t* h_offsets, 
         ya.chunk_off = d_ychunk; ya.frame_off = d_frame_off; ya.clip_begin = c0; ya.clip_end = c1; ya.frame_base = s_frame_off[c0];
         ya.n_fft = h->cfg.frame_length; ya.hop = hop; ya.win = pc.win_length; ya.min_period = pc.min_period; ya.max_period = pc.max_period;
         ya.n_bins = pc.n_bins; ya.frames_per_chunk = h->yin_frames_per_chunk; ya.lag_pad = h->yin_lag_pad; ya.tile = h->yin_tile;
-        ya.cap = h->yin_cap; ya.rec_bytes = h->yin_rec_bytes; ya.coef = h->cfg.pre_emphasis; ya.sr = (double)h->cfg.sr; ya.fmin = h->cfg.f0_min;
+        ya.cap = h->yin_cap; ya.rec_bytes = h->yin_rec_bytes; ya.coef = coef; ya.raw = raw ? 1 : 0; ya.sr = (double)h->cfg.sr; ya.fmin = h->cfg.f0_min;
         ya.tab = h->ptab; ya.obs = d_obs;
         const int grid_y = s_ychunk[c1] - s_ychunk[c0];
         PhaseTimer pt(h, stream, AFX_PHASE_YIN);
@@ -504,6 +510,47 @@ int afx_extract(afx_handle_t h, const float* d_audio, const int64_t* h_offsets, 
       c0 = c1;
     }
   }
+  CUDA_TRY(cudaGetLastError());
+  return AFX_OK;
+}
+
+// y[n] = x[n] - c x[n-1] (librosa's first-sample rule at n = 0) for the samples of the trimmed range, same packing as x
+__global__ void preemph_kernel(const float* __restrict__ x, float* __restrict__ y, const long long* __restrict__ offsets,
+                               const int* __restrict__ lengths, const int* __restrict__ meta, float coef) {
+  const int clip = blockIdx.y;
+  const int L0 = lengths[clip];
+  const int start = meta[4 * clip + 1], end = meta[4 * clip + 2];
+  const float* xc = x + offsets[clip];
+  float* yc = y + offsets[clip];
+  for (int n = blockIdx.x * blockDim.x + threadIdx.x; n < L0; n += gridDim.x * blockDim.x) {
+    float v = 0.f;
+    if (n >= start && n < end) {
+      const float xv = xc[n];
+      if (n == 0) v = xv + (2.f * xv - (L0 > 1 ? xc[1] : 0.f));
+      else v = __fadd_rn(xv, __fmul_rn(-coef, xc[n - 1]));   // scipy.signal.lfilter in float32
+    }
+    yc[n] = v;
+  }
+}
+
+int afx_preprocess(afx_handle_t h, const float* d_audio, const int64_t* h_offsets, const int32_t* h_lengths, int64_t n_clips,
+                   float* d_out, int32_t* d_meta, float* d_summaries_scratch, void* d_workspace, size_t workspace_bytes, void* stream_v) {
+  if (!h || !d_out || !d_summaries_scratch) return fail(AFX_ERR_INVALID_ARG, "afx_preprocess: null argument");
+  if (n_clips == 0) return AFX_OK;
+  // the trim decision comes from the fused kernel run with no feature group (it still streams the clip once)
+  const int rc = afx_extract(h, d_audio, h_offsets, h_lengths, n_clips, 0u, d_summaries_scratch, d_meta, nullptr, d_workspace,
+                             workspace_bytes, stream_v);
+  if (rc != AFX_OK) return rc;
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_v);
+  const Layout L = header_layout(n_clips);
+  const char* ws = static_cast<const char*>(d_workspace);
+  long long max_len = 1;
+  for (int64_t i = 0; i < n_clips; ++i) max_len = std::max<long long>(max_len, h_lengths[i]);
+  const dim3 grid((unsigned)std::min<long long>(ceil_div(max_len, 256), 1024), (unsigned)n_clips);
+  if (n_clips > 65535) return fail(AFX_ERR_UNSUPPORTED, "afx_preprocess: at most 65535 clips per call");
+  preemph_kernel<<<grid, 256, 0, stream>>>(d_audio, d_out, reinterpret_cast<const long long*>(ws + L.off_offsets),
+                                           reinterpret_cast<const int*>(ws + L.off_lengths), d_meta, h->cfg.pre_emphasis);
+  ++g_launches;
   CUDA_TRY(cudaGetLastError());
   return AFX_OK;
 }

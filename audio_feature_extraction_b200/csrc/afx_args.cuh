@@ -26,6 +26,7 @@ struct ClipArgs {
   int* meta;                    // [n_clips][4]
   float* frames_out;            // nullable
   int pretrimmed;
+  int raw;                      // clips are already pre-emphasised and trimmed (AFX_FEAT_PREPROCESSED)
 };
 
 struct Slab {

@@ -324,12 +324,14 @@ __global__ void __launch_bounds__(kMaxClipThreads, 1) clip_kernel(ClipArgs a) {
     float floor_db = -3.0e38f;
     for (int pass = 0; pass < 4; ++pass) {
       Region rg{0, 0, L0};
+      rg.raw = a.raw;
       int fb = 0, fe = 0, shift = 0;
       bool own = false;
       if (pass == 0) {
         if (a.pretrimmed) {
           ci = a.info[clip];
           rg = Region{ci.start, ci.start, ci.end};
+          rg.raw = a.raw;
           fe = (ci.status == 0 && want_frames) ? ci.n_frames : 0;
         } else {
           fe = L0 > 0 ? 1 + L0 / hop : 0;
@@ -338,6 +340,7 @@ __global__ void __launch_bounds__(kMaxClipThreads, 1) clip_kernel(ClipArgs a) {
       } else {
         if (ci.status != 0 || !want_frames) break;
         rg = Region{ci.start, ci.start, ci.end};
+        rg.raw = a.raw;
         shift = a0;                // 0 when pretrimmed
         if (pass == 1) {           // frames t with t*hop < n_fft/2 reach in front of the trimmed signal
           if (!a.pretrimmed && ci.start > 0) { head_end = min(ci.n_frames, (NFFT / 2 + hop - 1) / hop); fe = head_end; }

@@ -49,6 +49,7 @@ struct YinArgs {
   int cap;                     // candidate slots per frame record
   int rec_bytes;               // bytes per frame record
   float coef;
+  int raw;                     // input already pre-emphasised: no first-sample rule
   double sr, fmin;
   PyinTables tab;
   unsigned char* obs;          // [wave frames][rec_bytes]
@@ -102,7 +103,7 @@ __global__ void __launch_bounds__(kYinThreads, 2) yin_obs_kernel(YinArgs a) {
       const float xv = __ldg(x + g);
       if (g == 0) {
         const float x1 = (L0 > 1) ? __ldg(x + 1) : 0.f;
-        y = xv + (2.f * xv - x1);
+        y = a.raw ? xv : xv + (2.f * xv - x1);
       } else {
         y = __fadd_rn(xv, __fmul_rn(-a.coef, __ldg(x + g - 1)));
       }

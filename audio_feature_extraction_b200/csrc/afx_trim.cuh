@@ -24,6 +24,7 @@ struct TrimArgs {
   int hop;                    // feature hop (for n_frames)
   float coef;                 // pre-emphasis
   float top_db;
+  int raw;                    // input already pre-emphasised: no first-sample rule
 };
 
 __device__ __forceinline__ float preemph_sample(float x, float xm1, float coef) {
@@ -50,7 +51,7 @@ __global__ void __launch_bounds__(kTrimThreads) trim_kernel(TrimArgs a) {
   float x0 = 0.f, x1 = 0.f;
   if (L0 > 0) x0 = x[0];
   if (L0 > 1) x1 = x[1];
-  const float y_first = x0 + (2.f * x0 - x1);  // zi = 2*y[0]-y[1] handed to lfilter as state
+  const float y_first = a.raw ? x0 : x0 + (2.f * x0 - x1);  // zi = 2*y[0]-y[1] handed to lfilter as state
 
   int bad = 0;
   for (int j = warp; j < nb; j += kTrimThreads / 32) {

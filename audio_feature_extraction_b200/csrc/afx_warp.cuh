@@ -18,7 +18,7 @@ constexpr int kPlaneFloats = 32 * 33;
 
 // where a streaming step reads: frames f (relative to `origin`) cover origin + f*hop - n_fft/2 + [0, n_fft),
 // samples outside [lo, hi) count as zero (librosa centre padding of the trimmed signal)
-struct Region { int origin, lo, hi; };
+struct Region { int origin, lo, hi; int raw = 0; };   // raw: the input is already pre-emphasised (no first-sample rule)
 
 // shared-memory tables + per-warp buffers
 struct Smem {
@@ -68,7 +68,7 @@ __device__ __forceinline__ float load_y(const float* rp0, int t, int gA, const R
     const float xv = rp0[t];
     if (g == 0) {
       const float x1 = (L0 > 1) ? rp0[t + 1] : 0.f;
-      y = xv + (2.f * xv - x1);          // zi = 2*y[0]-y[1] handed to lfilter as state (librosa.effects.preemphasis)
+      y = rg.raw ? xv : xv + (2.f * xv - x1);   // zi = 2*y[0]-y[1] handed to lfilter as state (librosa.effects.preemphasis)
     } else {
       y = preemph_op(xv, rp0[t - 1], coef);
     }

@@ -38,6 +38,9 @@ typedef enum {
 #define AFX_FEAT_MFCC    0x2u
 #define AFX_FEAT_ENERGY  0x4u
 #define AFX_FEAT_ALL     0x7u
+/* modifier: the clips are outputs of preprocess_audio (:58-74) -- already pre-emphasised and trimmed -- which is what
+ * the reference's extract_f0(y) / extract_mfcc(y) / extract_energy(y) receive: no filter, no trim */
+#define AFX_FEAT_PREPROCESSED 0x100u
 
 /* per-clip status written to meta[clip][0]; mirrors the librosa exceptions that make the
  * reference's extract_features raise (:211-213) and batch_process skip (:233-235) */
@@ -120,6 +123,16 @@ size_t afx_workspace_min_bytes(afx_handle_t h, int64_t n_clips, const int32_t* h
 int afx_extract(afx_handle_t h, const float* d_audio, const int64_t* h_offsets, const int32_t* h_lengths,
                 int64_t n_clips, uint32_t feature_mask, float* d_summaries, int32_t* d_meta,
                 float* d_frames, void* d_workspace, size_t workspace_bytes, void* stream);
+
+/*
+ * preprocess_audio (core/feature_extractor.py:58-74) on its own: librosa.effects.preemphasis (:69) followed by
+ * librosa.effects.trim(top_db=30) (:72).  d_out has the packing of d_audio; clip i's result is
+ * d_out[h_offsets[i] + meta[i][1] .. h_offsets[i] + meta[i][2]) (zeros elsewhere inside the clip).
+ * d_summaries_scratch: device float32 [n_clips, SS] scratch (the fused kernel zeroes its rows).
+ */
+int afx_preprocess(afx_handle_t h, const float* d_audio, const int64_t* h_offsets, const int32_t* h_lengths, int64_t n_clips,
+                   float* d_out, int32_t* d_meta, float* d_summaries_scratch, void* d_workspace, size_t workspace_bytes,
+                   void* stream);
 
 /*
  * Same computation from HOST memory (what a caller holding decoded files has): clips are staged

@@ -302,3 +302,41 @@ def test_pyin_f0_track_and_statistics(torch_cuda, cfg, secs):
         # the other groups are unaffected by the F0 launches
         _check_clip(ex, ora, y, summ[i], meta[i], frames, rows[i], n)
     assert agree / total >= F0_VOICING, (agree, total)
+
+
+def test_reference_method_api_on_preprocessed_waveforms(torch_cuda):
+    """The reference's public per-stage methods (core/feature_extractor.py:58-179): preprocess_audio(y) returns the
+    pre-emphasised + trimmed waveform; extract_f0 / extract_mfcc / extract_energy take THAT waveform (no second
+    filter, no second trim) and return the reference's keys."""
+    from audio_feature_extraction_b200 import AudioFeatureExtractor
+    from audio_feature_extraction_b200.synth import make_clip
+    from oracle import OracleFeatureExtractor
+    ex, ora = AudioFeatureExtractor(), OracleFeatureExtractor()
+    for seed in (3, 11):
+        y = make_clip(seed, seconds=2.5)
+        yt = ex.preprocess_audio(y)
+        ref = ora.preprocess_audio(y)
+        assert yt.dtype == np.float32 and yt.shape == ref.shape          # trim indices: bit-exact
+        np.testing.assert_array_equal(yt, ref.astype(np.float32))         # float32 lfilter arithmetic: bit-exact
+        got_m, ref_m = ex.extract_mfcc(yt), ora.extract_mfcc(ref)
+        assert list(got_m) == ["mfcc_mean", "mfcc_std", "mfcc_delta_mean", "mfcc_delta2_mean"]
+        for k in got_m:
+            assert np.max(np.abs(np.asarray(got_m[k]) - np.asarray(ref_m[k]))) <= MFCC_ATOL, k
+        got_e, ref_e = ex.extract_energy(yt), ora.extract_energy(ref)
+        assert list(got_e) == ["energy_mean", "energy_std", "energy_range"]
+        for k in got_e:
+            assert got_e[k] == pytest.approx(ref_e[k], rel=ENERGY_RTOL), k
+    # F0 on one clip (the pYIN oracle takes seconds)
+    y = make_clip(5, seconds=2.0)
+    yt = ex.preprocess_audio(y)
+    got_f, ref_f = ex.extract_f0(yt), ora.extract_f0(ora.preprocess_audio(y))
+    assert list(got_f) == ["f0_mean", "f0_std", "f0_missing_rate", "f0_quality"]
+    assert got_f["f0_missing_rate"] == pytest.approx(ref_f["f0_missing_rate"], abs=1e-6)   # float32 summary row
+    assert got_f["f0_mean"] == pytest.approx(ref_f["f0_mean"], rel=1e-5)
+    assert got_f["f0_std"] == pytest.approx(ref_f["f0_std"], rel=1e-4, abs=1e-3)
+
+
+def test_preprocess_audio_of_silence_is_empty(torch_cuda):
+    from audio_feature_extraction_b200 import AudioFeatureExtractor
+    ex = AudioFeatureExtractor()
+    assert ex.preprocess_audio(np.zeros(22050, np.float32)).shape == (0,)
