@@ -93,7 +93,8 @@ struct afx_handle_s {
   int* d_meta = nullptr;      size_t d_meta_bytes = 0;
   cudaStream_t copy_stream = nullptr, compute_stream = nullptr;
   cudaEvent_t copied[2] = {nullptr, nullptr}, computed[2] = {nullptr, nullptr};
-  long long host_wave_samples = 16ll << 20;   // samples per host->device wave (AFX_HOST_WAVE_SAMPLES)
+  long long host_wave_samples = 96ll << 20;   // samples per host->device wave (AFX_HOST_WAVE_SAMPLES): several clips per
+                                              // resident CTA of the fused kernel; the first waves are shorter (pipeline fill)
   // per-phase device-time accounting (afx_profile_enable / afx_profile_read)
   bool profiling = false;
   struct Span { cudaEvent_t a, b; int phase; };
@@ -232,6 +233,7 @@ int afx_create(const afx_config_t* cfg, afx_handle_t* out) {
   h->cfg = *cfg;
   h->n16 = (cfg->n_mfcc + 15) & ~15;
   h->sm_count = prop.multiProcessorCount;
+  if (const char* e = getenv("AFX_HOST_WAVE_SAMPLES")) { const long long v = atoll(e); if (v >= (1 << 16)) h->host_wave_samples = v; }
 
   const auto win = afx::host::window_half(cfg->frame_length);
   const auto tw = afx::host::twiddle32x32(cfg->frame_length == 512 ? 512 : 1024);
@@ -689,7 +691,7 @@ int run_host_waves(afx_handle_s* h, const std::vector<HostWave>& waves, const st
 }
 
 // split clips [0,n) with (4-aligned) sample offsets `off` into waves of at most `cap` samples (a longer clip gets its own wave)
-int plan_waves(const int64_t* off, const int32_t* len, int64_t n, long long cap, std::vector<HostWave>& waves,
+int plan_waves(const int64_t* off, const int32_t* len, int64_t n, long long cap_full, std::vector<HostWave>& waves,
                std::vector<long long>& rel_off, long long* max_span) {
   rel_off.resize(n);
   *max_span = 0;
@@ -698,6 +700,8 @@ int plan_waves(const int64_t* off, const int32_t* len, int64_t n, long long cap,
     const long long base = off[c0];
     int64_t c1 = c0;
     long long end = base;
+    // ramp: the first copy cannot overlap any compute, so it is kept short; sizes then double up to `cap_full`
+    const long long cap = waves.size() == 0 ? cap_full / 8 : waves.size() == 1 ? cap_full / 4 : waves.size() == 2 ? cap_full / 2 : cap_full;
     while (c1 < n) {
       if (c1 > c0 && off[c1] < off[c1 - 1] + len[c1 - 1]) return fail(AFX_ERR_INVALID_ARG, "host path: clip offsets must be ascending and non-overlapping (clip %lld)", (long long)c1);
       const long long e = (off[c1] + len[c1] + 7) & ~7LL;   // 8-sample granularity (s16 conversion, TMA tail reads)
@@ -759,7 +763,7 @@ int afx_extract_host(afx_handle_t h, const float* const* h_clips, const int32_t*
   std::vector<HostWave> waves;
   std::vector<long long> rel_off;
   long long max_span = 0;
-  if (int rc = plan_waves(reinterpret_cast<const int64_t*>(off.data()), h_lengths, n_clips, h->host_wave_samples, waves, rel_off, &max_span)) return rc;
+  if (int rc = plan_waves(reinterpret_cast<const int64_t*>(off.data()), h_lengths, n_clips, std::min<long long>(h->host_wave_samples, 32ll << 20) /* pinned staging slots */, waves, rel_off, &max_span)) return rc;
   if (int rc = ensure_host_path(h, (size_t)max_span + 8, false, true, n_clips)) return rc;
   // pack each wave into a pinned slot with a few host threads (the gather is a plain memcpy per clip)
   auto fill = [&](int slot, const HostWave& w) -> const void* {

@@ -336,7 +336,12 @@ def test_reference_method_api_on_preprocessed_waveforms(torch_cuda):
     assert got_f["f0_std"] == pytest.approx(ref_f["f0_std"], rel=1e-4, abs=1e-3)
 
 
-def test_preprocess_audio_of_silence_is_empty(torch_cuda):
+def test_preprocess_audio_of_digital_silence_matches_librosa_semantics(torch_cuda):
+    """All-zero input: every RMS frame sits at 0 dB re the (zero) maximum, so librosa.effects.trim keeps everything."""
     from audio_feature_extraction_b200 import AudioFeatureExtractor
-    ex = AudioFeatureExtractor()
-    assert ex.preprocess_audio(np.zeros(22050, np.float32)).shape == (0,)
+    from oracle import OracleFeatureExtractor
+    ex, ora = AudioFeatureExtractor(), OracleFeatureExtractor()
+    y = np.zeros(22050, np.float32)
+    got, ref = ex.preprocess_audio(y), ora.preprocess_audio(y)
+    assert got.shape == ref.shape
+    np.testing.assert_array_equal(got, ref.astype(np.float32))
