@@ -235,6 +235,71 @@ class AudioFeatureExtractor:
             out.append(d)
         return out
 
+    # ------------------------------------------------------------------ framewise feature set (.npz of the experiment pipeline)
+    def extract_framewise(self, clips: Sequence[np.ndarray], names: Optional[Sequence[str]] = None,
+                          skip_errors: bool = False) -> List[Dict[str, Any]]:
+        """Framewise features of a batch in the layout the reference's experiment pipeline saves with np.savez
+        (04_feature_extraction_experiment/feature_extraction.py:191-292, :340-353) and its DTW stage loads:
+        'mfcc' [3 n_mfcc, T] (MFCC / delta / delta2), 'f0' [2, T] (nan_to_num(pyin f0) / delta), 'energy' [2, T]
+        (rms / delta), 'zcr' [2, T] (zero-crossing rate / delta), computed on the preprocessed (pre-emphasised,
+        trimmed) waveform of this class.  One batched device pass + one small kernel (afx_frame_extras)."""
+        import torch
+
+        if len(clips) == 0:
+            return []
+        names = list(names) if names is not None else [f"<clip {i}>" for i in range(len(clips))]
+        L = N.lib()
+        buf, offsets, lengths = self.pack_clips(clips)
+        dev = torch.device("cuda", self.device)
+        audio = buf.to(dev, non_blocking=True)
+        summaries, meta, frames = self.extract_batch_device(audio, offsets, lengths, None, return_frames=True)
+        extras = torch.zeros((frames.shape[0], N.EXTRAS_WIDTH), dtype=torch.float32, device=dev)
+        N.check(L.afx_frame_extras(self._h(), audio.data_ptr(), len(clips), meta.data_ptr(), frames.data_ptr(),
+                                   extras.data_ptr(), self._ws.data_ptr(), torch.cuda.current_stream(dev).cuda_stream))
+        fr, ex, m = frames.cpu().numpy(), extras.cpu().numpy(), meta.cpu().numpy()
+        rows = np.concatenate([[0], np.cumsum([self.max_frames(int(l)) for l in lengths])])
+        n = self.n_mfcc
+        out = []
+        for i, name in enumerate(names):
+            st = int(m[i, 0])
+            if st != N.CLIP_OK:
+                err = FeatureExtractionError(f"{name}: {_STATUS_MSG.get(st, 'status %d' % st)}")
+                if skip_errors:
+                    self.logger.error(f"處理文件 {Path(str(name)).name} 失敗: {err}")
+                    continue
+                raise err
+            T = int(m[i, 3])
+            f, e = fr[rows[i]:rows[i] + T], ex[rows[i]:rows[i] + T]
+            out.append({"file_path": name,
+                        "mfcc": np.ascontiguousarray(f[:, :3 * n].T),
+                        "f0": np.stack([np.nan_to_num(f[:, 3 * n + 1]), e[:, 3]]),
+                        "energy": np.stack([f[:, 3 * n], e[:, 2]]),
+                        "zcr": np.stack([e[:, 0], e[:, 1]])})
+        return out
+
+    @staticmethod
+    def save_features_npz(features: Dict[str, Any], npz_path: str) -> str:
+        """np.savez of one clip's framewise features under the reference's keys (feature_extraction.py:351-352)."""
+        np.savez(npz_path, **{k: v for k, v in features.items() if k != "file_path"})
+        return npz_path
+
+    def batch_export_npz(self, audio_dir: str, out_dir: str) -> List[str]:
+        """Every *.wav of a directory -> <out_dir>/<stem>_processed_features.npz (the file-name pattern of
+        feature_extraction.py:350, without the timestamp prefix); unreadable / failing files are logged and skipped."""
+        out_dir_p = Path(out_dir)
+        out_dir_p.mkdir(parents=True, exist_ok=True)
+        clips, names = [], []
+        for audio_file in sorted(Path(audio_dir).glob("*.wav")):
+            try:
+                clips.append(self.load_audio(str(audio_file))[0]); names.append(str(audio_file))
+            except Exception as e:
+                self.logger.error(f"處理文件 {audio_file.name} 失敗: {str(e)}")
+        paths = []
+        for feats in self.extract_framewise(clips, names, skip_errors=True):
+            stem = Path(feats["file_path"]).stem
+            paths.append(self.save_features_npz(feats, str(out_dir_p / f"{stem}_processed_features.npz")))
+        return paths
+
     # ------------------------------------------------------------------ reference API
     def _to_device(self, y: np.ndarray):
         import torch

@@ -17,6 +17,7 @@
 
 #include "afx_common.cuh"
 #include "afx_clip.cuh"
+#include "afx_extras.cuh"
 #include "afx_pyin.cuh"
 #include "afx_pyin_tables.h"
 #include "afx_tables.h"
@@ -552,6 +553,27 @@ int afx_preprocess(afx_handle_t h, const float* d_audio, const int64_t* h_offset
   if (n_clips > 65535) return fail(AFX_ERR_UNSUPPORTED, "afx_preprocess: at most 65535 clips per call");
   preemph_kernel<<<grid, 256, 0, stream>>>(d_audio, d_out, reinterpret_cast<const long long*>(ws + L.off_offsets),
                                            reinterpret_cast<const int*>(ws + L.off_lengths), d_meta, h->cfg.pre_emphasis);
+  ++g_launches;
+  CUDA_TRY(cudaGetLastError());
+  return AFX_OK;
+}
+
+int afx_frame_extras(afx_handle_t h, const float* d_audio, int64_t n_clips, const int32_t* d_meta, const float* d_frames,
+                     float* d_extras, const void* d_workspace, void* stream_v) {
+  if (!h || !d_audio || !d_meta || !d_frames || !d_extras || !d_workspace) return fail(AFX_ERR_INVALID_ARG, "afx_frame_extras: null argument");
+  if (n_clips <= 0) return AFX_OK;
+  CUDA_TRY(cudaSetDevice(h->cfg.device));
+  const Layout L = header_layout(n_clips);
+  const char* ws = static_cast<const char*>(d_workspace);
+  afx::ExtrasArgs ea;
+  ea.audio = d_audio;
+  ea.offsets = reinterpret_cast<const long long*>(ws + L.off_offsets);
+  ea.lengths = reinterpret_cast<const int*>(ws + L.off_lengths);
+  ea.frame_off = reinterpret_cast<const long long*>(ws + L.off_frame_off);
+  ea.meta = d_meta; ea.frames = d_frames; ea.extras = d_extras;
+  ea.frame_width = afx_frame_width(h); ea.n_mfcc = h->cfg.n_mfcc; ea.n_fft = h->cfg.frame_length; ea.hop = h->cfg.hop_length;
+  ea.coef = h->cfg.pre_emphasis;
+  afx::frame_extras_kernel<<<(unsigned)n_clips, afx::kExtrasThreads, 0, static_cast<cudaStream_t>(stream_v)>>>(ea);
   ++g_launches;
   CUDA_TRY(cudaGetLastError());
   return AFX_OK;

@@ -135,6 +135,18 @@ int afx_preprocess(afx_handle_t h, const float* d_audio, const int64_t* h_offset
                    void* stream);
 
 /*
+ * Framewise extras of the .npz feature set the reference's experiment pipeline stores
+ * (04_feature_extraction_experiment/feature_extraction.py:191-292, np.savez :340-353): per frame
+ *   [0] zero-crossing rate (librosa.feature.zero_crossing_rate, :279-283)  [1] its delta (:286)
+ *   [2] delta of the RMS energy (:265)   [3] delta of nan_to_num(f0) (:241-244)
+ * Call right after afx_extract(..., d_frames != NULL, ...) on the same stream with the SAME d_audio, d_meta, d_frames
+ * and d_workspace (the batch header afx_extract left there is reused).  d_extras: float32 [rows of d_frames, 4].
+ */
+#define AFX_EXTRAS_WIDTH 4
+int afx_frame_extras(afx_handle_t h, const float* d_audio, int64_t n_clips, const int32_t* d_meta, const float* d_frames,
+                     float* d_extras, const void* d_workspace, void* stream);
+
+/*
  * Same computation from HOST memory (what a caller holding decoded files has): clips are staged
  * through pinned buffers, copied host->device in waves on a copy stream that overlaps the compute
  * stream, and the summaries / meta rows are copied back.  Blocks until the results are in

@@ -98,3 +98,17 @@ class OracleFeatureExtractor:
         if "energy" in features_to_extract:
             feats.update(self.extract_energy(y_processed))
         return feats
+
+    def framewise(self, y):
+        """The framewise feature set the reference's experiment pipeline stores as .npz
+        (04_feature_extraction_experiment/feature_extraction.py:191-292, saved :340-353), computed on this class's
+        preprocessed waveform: 'mfcc' [3 n_mfcc, T] = MFCC / delta / delta2, 'f0' [2, T] = nan_to_num(pyin f0) / delta,
+        'energy' [2, T] = rms / delta, 'zcr' [2, T] = zero-crossing rate / delta."""
+        yt = self.preprocess_audio(y)
+        m, d1, d2 = self.mfcc_frames(yt)
+        f0, _, _ = self.f0_track(yt)
+        f0 = np.nan_to_num(f0).reshape(1, -1)
+        r = self.rms_frames(yt)
+        z = L.zero_crossing_rate(yt, frame_length=self.frame_length, hop_length=self.hop_length)
+        return {"mfcc": np.vstack([m, d1, d2]), "f0": np.vstack([f0, L.delta(f0)]),
+                "energy": np.vstack([r, L.delta(r)]), "zcr": np.vstack([z, L.delta(z)])}

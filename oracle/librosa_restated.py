@@ -27,7 +27,7 @@ except Exception:  # pragma: no cover
 __all__ = [
     "note_c2_hz", "note_c7_hz", "preemphasis", "frame", "rms", "trim_indices", "trim",
     "hamming_periodic", "stft_power", "hz_to_mel", "mel_to_hz", "mel_filterbank",
-    "power_to_db", "dct_ortho", "melspectrogram", "mfcc", "delta", "pyin_constants",
+    "power_to_db", "dct_ortho", "melspectrogram", "mfcc", "delta", "zero_crossing_rate", "pyin_constants",
     "yin_cmnd", "parabolic_shifts", "pyin_observations", "pyin_transition", "viterbi",
     "pyin", "beta_probs", "TINY",
 ]
@@ -208,6 +208,21 @@ def delta(data: np.ndarray, order: int = 1, width: int = 9) -> np.ndarray:
     if width > data.shape[-1]:
         raise ValueError("when mode='interp', width=%d cannot exceed data.shape[axis]=%d" % (width, data.shape[-1]))
     return scipy.signal.savgol_filter(data, width, polyorder=order, deriv=order, axis=-1, mode="interp")
+
+
+def zero_crossing_rate(y: np.ndarray, frame_length: int = 2048, hop_length: int = 512, threshold: float = 1e-10) -> np.ndarray:
+    """librosa.feature.zero_crossing_rate(y, frame_length, hop_length) (center=True): edge padding by frame_length // 2,
+    frames, librosa.zero_crossings(pad=False, zero_pos=True, threshold=1e-10) down each frame, mean over the frame's
+    frame_length entries (the first entry of a frame is `pad` = False).  Samples with |x| <= threshold count as +0.
+    Called by 04_feature_extraction_experiment/feature_extraction.py:279-283 (the framewise .npz features).  [A9]"""
+    y = np.asarray(y)
+    yp = np.pad(y, (frame_length // 2, frame_length // 2), mode="edge")
+    fr = frame(yp, frame_length, hop_length)                      # [frame_length, T]
+    z = np.where(np.abs(fr) <= threshold, 0.0, fr)
+    sb = np.signbit(z)
+    cross = np.zeros(fr.shape, dtype=bool)
+    cross[1:] = sb[1:] != sb[:-1]
+    return np.mean(cross, axis=0, keepdims=True)                  # [1, T] float64
 
 
 # --------------------------------------------------------------------------- pYIN

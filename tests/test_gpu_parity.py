@@ -345,3 +345,36 @@ def test_preprocess_audio_of_digital_silence_matches_librosa_semantics(torch_cud
     got, ref = ex.preprocess_audio(y), ora.preprocess_audio(y)
     assert got.shape == ref.shape
     np.testing.assert_array_equal(got, ref.astype(np.float32))
+
+
+def test_framewise_npz_feature_set(torch_cuda, tmp_path):
+    """The framewise .npz feature set (04_feature_extraction_experiment/feature_extraction.py:191-292,:340-353):
+    mfcc 39 x T, f0 / energy / zcr with their deltas, against the oracle on the same clips; then the writer."""
+    from audio_feature_extraction_b200 import AudioFeatureExtractor
+    from audio_feature_extraction_b200.synth import make_clip
+    from audio_feature_extraction_b200.wav import write_wav
+    from oracle import OracleFeatureExtractor
+    ex, ora = AudioFeatureExtractor(), OracleFeatureExtractor()
+    clips = [make_clip(s, seconds=1.5) for s in (2, 9)]
+    got = ex.extract_framewise(clips)
+    for y, g in zip(clips, got):
+        ref = ora.framewise(y)
+        assert g["mfcc"].shape == ref["mfcc"].shape and g["mfcc"].shape[0] == 39          # frame counts: bit-exact
+        assert np.max(np.abs(g["mfcc"] - ref["mfcc"])) <= MFCC_ATOL
+        np.testing.assert_allclose(g["energy"][0], ref["energy"][0], rtol=ENERGY_RTOL, atol=1e-12)
+        np.testing.assert_allclose(g["energy"][1], ref["energy"][1], rtol=1e-4, atol=1e-7)
+        np.testing.assert_array_equal(g["zcr"][0], ref["zcr"][0].astype(np.float32))       # integer counts / n_fft: exact
+        np.testing.assert_allclose(g["zcr"][1], ref["zcr"][1], rtol=1e-5, atol=1e-7)
+        voiced = (ref["f0"][0] > 0)
+        assert np.mean((g["f0"][0] > 0) == voiced) >= 0.999                                 # voicing decisions
+        both = voiced & (g["f0"][0] > 0)
+        cents = 1200 * np.abs(np.log2(g["f0"][0][both] / ref["f0"][0][both]))
+        assert cents.size == 0 or cents.max() <= 1.0                                        # F0 within 1 cent
+        if np.array_equal(g["f0"][0] > 0, voiced):
+            np.testing.assert_allclose(g["f0"][1], ref["f0"][1], rtol=1e-4, atol=1e-3)
+    for i, y in enumerate(clips):
+        write_wav(str(tmp_path / f"clip{i}.wav"), y, 22050)
+    paths = ex.batch_export_npz(str(tmp_path), str(tmp_path / "features"))
+    assert [p.split("/")[-1] for p in paths] == ["clip0_processed_features.npz", "clip1_processed_features.npz"]
+    z = np.load(paths[0])
+    assert sorted(z.files) == ["energy", "f0", "mfcc", "zcr"] and z["mfcc"].shape[0] == 39
