@@ -216,7 +216,7 @@ def run_reference(args):
         "gpu_launches": 0,
         "note": "librosa (the reference's arithmetic) is not installable offline: this is the numpy/scipy restatement in oracle/",
     }
-    print(json.dumps(line), flush=True)
+    _emit(line)
     return 0
 
 
@@ -405,14 +405,29 @@ def run_native(args):
                        "sharding": f"clips by rank x{world}, NCCL gather of summary rows to rank 0 each step" if world > 1 else "single GPU"},
             "roofline": roofline, "cpu_baseline": cpu_baseline, "e2e": e2e, "f0_path": f0_path, "gpu_launches": int(launches), "clocks": clocks,
         }
-        print(json.dumps(line), flush=True)
+        _emit(line)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
     return 0
 
 
+_JSON_OUT = None
+
+
+def _emit(line):
+    """The one JSON line goes to the process's ORIGINAL stdout; everything else written to fd 1 during the run (NCCL's
+    version banner, library chatter) was diverted to stderr by main()."""
+    out = _JSON_OUT or sys.stdout
+    out.write(json.dumps(line) + "\n")
+    out.flush()
+
+
 def main():
+    global _JSON_OUT
+    _JSON_OUT = os.fdopen(os.dup(1), "w")
+    sys.stdout.flush()
+    os.dup2(2, 1)
     args = parse_args()
     if args.impl == "reference":
         return run_reference(args)
