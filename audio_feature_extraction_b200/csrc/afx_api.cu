@@ -73,6 +73,7 @@ struct afx_handle_s {
   int mel_floats = 0;      // floats in the padded sparse mel weight table
   int sm_count;
   void (*clip_fn)(afx::ClipArgs) = nullptr;   // clip_kernel<frame_length, hop_length>
+  void (*vit_fn)(afx::VitArgs) = nullptr;     // viterbi_kernel<half width or 0>
   // device tables
   float* d_window = nullptr;
   float* d_twiddle = nullptr;
@@ -308,7 +309,14 @@ int afx_create(const afx_config_t* cfg, afx_handle_t* out) {
       const void* yk = h->yin_c == 8 ? (const void*)afx::yin_obs_kernel<8> : h->yin_c == 11 ? (const void*)afx::yin_obs_kernel<11>
                      : h->yin_c == 16 ? (const void*)afx::yin_obs_kernel<16> : (const void*)afx::yin_obs_kernel<22>;
       CUDA_TRY(cudaFuncSetAttribute(yk, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->yin_smem));
-      CUDA_TRY(cudaFuncSetAttribute(afx::viterbi_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->vit_smem));
+      // Viterbi band search: the int32-filtered variant for the half widths of the stock geometries, else the generic one
+      h->vit_fn = afx::viterbi_kernel<0>;
+      const char* vsel = getenv("AFX_VITERBI");
+      if (!(vsel && !strcmp(vsel, "generic"))) {
+        if (pc.half_width == 25) h->vit_fn = afx::viterbi_kernel<25>;
+        else if (pc.half_width == 15) h->vit_fn = afx::viterbi_kernel<15>;
+      }
+      CUDA_TRY(cudaFuncSetAttribute(h->vit_fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->vit_smem));
     }
   }
   CUDA_TRY(cudaEventCreateWithFlags(&h->stage_ev, cudaEventDisableTiming));
@@ -507,7 +515,11 @@ int afx_extract(afx_handle_t h, const float* d_audio, const int64_t* h_offsets, 
         va.ptr = d_ptr; va.states = d_states; va.summaries = d_summaries; va.summary_width = afx_summary_width(h);
         va.frames_out = d_frames; va.frame_width = afx_frame_width(h); va.n_mfcc = h->cfg.n_mfcc;
         PhaseTimer pt(h, stream, AFX_PHASE_VITERBI);
-        afx::viterbi_kernel<<<c1 - c0, afx::kVitThreads, h->vit_smem, stream>>>(va);
+        for (int d = 0; d < 64; ++d) {
+          const int w = 2 * pc.half_width + 1;
+          va.wk[d] = d < w ? (int)std::floor(pc.ltrans_same[w - 1 - d] * 16384.0) * 64 + (63 - d) : -(1 << 30);
+        }
+        h->vit_fn<<<c1 - c0, afx::kVitThreads, h->vit_smem, stream>>>(va);
         ++g_launches;
       }
       c0 = c1;

@@ -435,24 +435,34 @@ struct VitArgs {
   short* states;                // [wave frames] decoded state per frame
   float* summaries; int summary_width;
   float* frames_out; int frame_width, n_mfcc;
+  int wk[64];                   // filter path: (floor(ltr[d] * 2^14) << 6) | (63 - d), d = 0 .. 2 hw
 };
 
 // shared-memory geometry, host and device: F rows are padded by `pad` (multiple of 8 >= hw) on the left and 4 lq + 8
 // on the right (pads hold -1e308) and skewed by one slot per 8 (anchors sit 8 apart: conflict-free 64-bit loads)
 struct VitGeo {
-  int pad, lq, fs, nb_even;
+  int pad, lq, fs, nb_even, ks;
   __host__ __device__ VitGeo(int nb, int hw) {
     pad = (hw + 7) & ~7;
     lq = (2 * hw + 1 + 3) / 4;
     const int n = pad + nb + 4 * lq + 8;
     fs = (n + (n >> 3) + 8) & ~1;
     nb_even = (nb + 1) & ~1;
+    ks = (2 * hw + nb + 16 + 3) & ~3;   // int32 key row of the filter path: index hw + k, k = -hw .. nb + hw + 12
   }
   __host__ __device__ size_t bytes(int nb) const {
-    return (size_t)(2 * fs + 2 * nb_even /*hs*/ + 2 * nb_even /*lobs*/ + nb_even /*corr*/ + 4 * lq + 2 /*ltr*/) * 8 + (size_t)2 * nb_even * 2 /*harg*/;
+    return (size_t)(2 * fs + 2 * nb_even /*hs*/ + 2 * nb_even /*lobs*/ + nb_even /*corr*/ + 4 * lq + 8 /*ltr*/) * 8 +
+           (size_t)2 * ks * 4 /*keys*/ + (size_t)2 * nb_even * 2 /*harg*/;
   }
 };
 
+// HW = 0: generic band search (anchors + monotone ranges).  HW > 0 (compile-time half width, 2 HW + 1 <= 63): the band
+// maximum is found by an exact two-stage search -- an int32 fixed-point pre-filter (keys floor((F - G) 2^14) << 6 with
+// the band offset in the low bits, one VIADDMNMX per (target, predecessor), maxima kept per chunk of kVitChunk
+// predecessors), then the float64 scan of only those chunks whose filtered maximum lies within 3 quantisation steps of
+// the best one (any chunk that could hold the true float64 maximum: the filter's error is < 2 steps per entry).
+constexpr int kVitChunk = 8;
+template <int HW>
 __global__ void __launch_bounds__(kVitThreads, kVitMinCtas) viterbi_kernel(VitArgs a) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int nb = a.n_bins, hw = a.half_width, ns = 2 * nb;
@@ -462,8 +472,10 @@ __global__ void __launch_bounds__(kVitThreads, kVitMinCtas) viterbi_kernel(VitAr
   double* hs = Fp + 2 * FS;                            // [2][NBE] band maxima
   double* lobs = hs + 2 * NBE;                         // [2][NBE] dense log-observation rows (double buffered)
   double* corr = lobs + 2 * NBE;                       // [NBE]
-  double* ltr = corr + NBE;                            // [4 LQ] ltr[d] = lt[2 hw - d]: weight of predecessor j - hw + d
-  unsigned short* harg = reinterpret_cast<unsigned short*>(ltr + 4 * LQ + 2);   // [2][NBE]
+  double* ltr = corr + NBE;                            // [4 LQ + 8] ltr[d] = lt[2 hw - d]: weight of predecessor j - hw + d
+  int* Kq = reinterpret_cast<int*>(ltr + 4 * LQ + 8);  // [2][KS] filter keys, index hw + k
+  const int KS = geo.ks;
+  unsigned short* harg = reinterpret_cast<unsigned short*>(Kq + 2 * KS);   // [2][NBE]
   __shared__ double s_pv[kVitWarps];
   __shared__ int s_pi[kVitWarps];
   __shared__ double s_red[3][kVitWarps];
@@ -477,11 +489,12 @@ __global__ void __launch_bounds__(kVitThreads, kVitMinCtas) viterbi_kernel(VitAr
   const long long slot0 = a.frame_off[clip] - a.frame_base;
   const unsigned char* rec0 = a.obs + (size_t)slot0 * a.rec_bytes;
   unsigned short* ptr0 = a.ptr + (size_t)slot0 * ns;
-  auto fidx = [PAD](int k) { const int kp = k + PAD; return kp + (kp >> 3); };
+  auto fidx = [PAD](int k) { const int kp = k + PAD; return HW > 0 ? kp : kp + (kp >> 3); };   // the filter path needs no skew
 
   for (int i = tid; i < 2 * FS; i += kVitThreads) Fp[i] = -1.0e308;
   for (int i = tid; i < nb; i += kVitThreads) corr[i] = a.edge_corr[i];
-  for (int i = tid; i < 4 * LQ; i += kVitThreads) ltr[i] = (i <= 2 * hw) ? a.lt_same[2 * hw - i] : -1.0e308;
+  for (int i = tid; i < 4 * LQ + 8; i += kVitThreads) ltr[i] = (i <= 2 * hw) ? a.lt_same[2 * hw - i] : -1.0e308;
+  if (HW > 0) for (int i = tid; i < 2 * KS; i += kVitThreads) Kq[i] = -(1 << 30);   // pads never win
   for (int i = tid; i < 2 * NBE; i += kVitThreads) lobs[i] = a.log_tiny;
   __syncthreads();
 
@@ -523,6 +536,12 @@ __global__ void __launch_bounds__(kVitThreads, kVitMinCtas) viterbi_kernel(VitAr
     for (int j = tid; j < nb; j += kVitThreads) { const double vu = lu0 + a.log_init_unvoiced; if (vu > bu) { bu = vu; biu = nb + j; } }
     if (bu > bv) { bv = bu; bi = biu; }
     block_argmax(bv, bi, G, kstar);
+    if (HW > 0) {   // filter keys of F_0 relative to G_0 (later steps: relative to the G of the step before, in phase C)
+      for (int j = tid; j < nb; j += kVitThreads) {
+        Kq[HW + j] = max(__double2int_rd((Fp[fidx(j)] - G) * 16384.0), -33554431) * 64;
+        Kq[KS + HW + j] = max(__double2int_rd((Fp[FS + fidx(j)] - G) * 16384.0), -33554431) * 64;
+      }
+    }
   }
 
   const int nA = (nb - 1 + kVitStride - 1) / kVitStride + 1;   // anchors per voicing block: 0, S, 2S, ..., nb - 1
@@ -533,6 +552,60 @@ __global__ void __launch_bounds__(kVitThreads, kVitMinCtas) viterbi_kernel(VitAr
     double* lob_old = lobs + ((t - 1) & 1) * NBE;
     const int nc = *reinterpret_cast<const int*>(rec);
     const double lu = *reinterpret_cast<const double*>(rec + 8);
+    if constexpr (HW > 0) {
+      // ---- filter path: thread <-> 4 consecutive targets of one voicing block
+      constexpr int W = 2 * HW + 1, NCH = (W + kVitChunk - 1) / kVitChunk, NI4 = (W + 3 + 3) / 4;
+      const int NT = (nb + 3) >> 2;
+      for (int task = tid; task < 2 * NT; task += kVitThreads) {
+        const int s = task >= NT ? 1 : 0;
+        const int j0 = 4 * (task - s * NT);
+        const int4* kp = reinterpret_cast<const int4*>(Kq + s * KS + j0);   // keys of predecessors j0 - HW + i, i = 0, 1, ...
+        int acc[4][NCH];
+#pragma unroll
+        for (int r = 0; r < 4; ++r)
+#pragma unroll
+          for (int c = 0; c < NCH; ++c) acc[r][c] = -2147483647;
+#pragma unroll
+        for (int i4 = 0; i4 < NI4; ++i4) {
+          const int4 kv = kp[i4];
+          const int keys[4] = {kv.x, kv.y, kv.z, kv.w};
+#pragma unroll
+          for (int u = 0; u < 4; ++u)
+#pragma unroll
+            for (int r = 0; r < 4; ++r) {
+              const int d = 4 * i4 + u - r;
+              if (d >= 0 && d < W) acc[r][d / kVitChunk] = __viaddmax_s32(keys[u], a.wk[d], acc[r][d / kVitChunk]);
+            }
+        }
+        const double* Fs = Fp + s * FS + PAD - HW;   // Fs[j + d] = F[j - HW + d]
+#pragma unroll
+        for (int r = 0; r < 4; ++r) {
+          const int j = j0 + r;
+          if (j >= nb) break;
+          int m = acc[r][0];
+#pragma unroll
+          for (int c = 1; c < NCH; ++c) m = max(m, acc[r][c]);
+          const int thr = ((m >> 6) - 3) * 64;      // every chunk that could hold the true float64 maximum
+          unsigned cmask = 0u;
+#pragma unroll
+          for (int c = 0; c < NCH; ++c) cmask |= (acc[r][c] >= thr) ? (1u << c) : 0u;
+          double best = -1.0e308; int arg = 0;
+          while (cmask) {                           // ascending chunks, strict >: first index on float64 ties
+            const int c = __ffs(cmask) - 1;
+            cmask &= cmask - 1;
+            const double* fc = Fs + j + c * kVitChunk;
+            const double* wc = ltr + c * kVitChunk;   // ltr is -1e308 beyond d = 2 HW: those entries never win
+#pragma unroll
+            for (int dd = 0; dd < kVitChunk; ++dd) {
+              const double cand = fc[dd] + wc[dd];
+              if (cand > best) { best = cand; arg = c * kVitChunk + dd; }
+            }
+          }
+          hs[s * NBE + j] = best;
+          harg[s * NBE + j] = (unsigned short)(j - HW + arg);
+        }
+      }
+    } else {
     // ---- phase A: anchors, full band
     for (int ax = tid; ax < 2 * nA; ax += kVitThreads) {
       const int s = ax >= nA ? 1 : 0;
@@ -558,6 +631,7 @@ __global__ void __launch_bounds__(kVitThreads, kVitMinCtas) viterbi_kernel(VitAr
       hs[s * NBE + j] = b0;
       harg[s * NBE + j] = (unsigned short)(j - hw + a0);
     }
+    }
     // this frame's sparse observations into the dense row; the previous frame's entries back to log(tiny)
     {
       const int ncp = *reinterpret_cast<const int*>(recp);
@@ -565,6 +639,7 @@ __global__ void __launch_bounds__(kVitThreads, kVitMinCtas) viterbi_kernel(VitAr
       for (int i = tid; i < nc; i += kVitThreads) lob_cur[rec_bins(const_cast<unsigned char*>(rec), a.cap)[i]] = rec_logp(const_cast<unsigned char*>(rec))[i];
     }
     __syncthreads();
+    if constexpr (HW == 0) {
     // ---- phase B: the other targets, restricted to [argmax of the anchor below, argmax of the anchor above]
     for (int idx = tid; idx < ns; idx += kVitThreads) {
       const int s = idx >= nb ? 1 : 0;
@@ -584,6 +659,7 @@ __global__ void __launch_bounds__(kVitThreads, kVitMinCtas) viterbi_kernel(VitAr
       harg[s * NBE + j] = (unsigned short)arg;
     }
     __syncthreads();
+    }
     // ---- phase C: combine the voicing blocks and the global fallback, add the observation, store the back-pointers
     double bv = -1.0e308, bu = -1.0e308; int bi = 0x7fffffff, biu = 0x7fffffff;
     const double fb = G + a.log_tiny;   // best out-of-band predecessor: k* through a log(tiny) transition
@@ -606,8 +682,13 @@ __global__ void __launch_bounds__(kVitThreads, kVitMinCtas) viterbi_kernel(VitAr
       if (vu > bu) { bu = vu; biu = nb + j; }
       // F for the next step (phase A / B readers are done: the barrier above)
       const int fi = fidx(j);
-      Fp[fi] = vv + corr[j];
-      Fp[FS + fi] = vu + corr[j];
+      const double fv = vv + corr[j], fu = vu + corr[j];
+      Fp[fi] = fv;
+      Fp[FS + fi] = fu;
+      if (HW > 0) {   // filter keys relative to the previous step's maximum (G still holds it here)
+        Kq[HW + j] = max(__double2int_rd((fv - G) * 16384.0), -33554431) * 64;
+        Kq[KS + HW + j] = max(__double2int_rd((fu - G) * 16384.0), -33554431) * 64;
+      }
     }
     if (bu > bv) { bv = bu; bi = biu; }   // every unvoiced index is larger than every voiced one: strict >
     block_argmax(bv, bi, G, kstar);   // contains a barrier: Fp complete before the next phase A
