@@ -22,6 +22,7 @@
 #include "afx_pyin_tables.h"
 #include "afx_tables.h"
 #include "afx_trim.cuh"
+#include "afx_wav.h"
 
 namespace {
 
@@ -588,6 +589,32 @@ int afx_frame_extras(afx_handle_t h, const float* d_audio, int64_t n_clips, cons
   afx::frame_extras_kernel<<<(unsigned)n_clips, afx::kExtrasThreads, 0, static_cast<cudaStream_t>(stream_v)>>>(ea);
   ++g_launches;
   CUDA_TRY(cudaGetLastError());
+  return AFX_OK;
+}
+
+int afx_wav_probe_batch(const char* const* paths, int64_t n, int threads, int32_t* sr, int32_t* channels, int64_t* frames,
+                        int32_t* format, int32_t* status) {
+  if (n < 0 || (n > 0 && (!paths || !sr || !channels || !frames || !format || !status)))
+    return fail(AFX_ERR_INVALID_ARG, "afx_wav_probe_batch: null argument");
+  afx::wav::parallel_for(n, threads, [&](int64_t i) {
+    afx::wav::Info info;
+    status[i] = paths[i] ? afx::wav::probe(paths[i], info) : afx::wav::OPEN_FAILED;
+    sr[i] = info.sr; channels[i] = info.channels; frames[i] = info.frames; format[i] = (info.tag << 8) | info.bits;
+  });
+  return AFX_OK;
+}
+
+int afx_wav_load_batch(const char* const* paths, int64_t n, int threads, int sample_format, void* h_out,
+                       const int64_t* h_offsets, const int64_t* h_frames, int32_t* status) {
+  if (n < 0 || (n > 0 && (!paths || !h_out || !h_offsets || !h_frames || !status)))
+    return fail(AFX_ERR_INVALID_ARG, "afx_wav_load_batch: null argument");
+  if (sample_format != AFX_SAMPLE_F32 && sample_format != AFX_SAMPLE_S16)
+    return fail(AFX_ERR_INVALID_ARG, "afx_wav_load_batch: unknown sample format %d", sample_format);
+  afx::wav::parallel_for(n, threads, [&](int64_t i) {
+    if (!paths[i] || h_offsets[i] < 0 || h_frames[i] < 0) { status[i] = afx::wav::OPEN_FAILED; return; }
+    if (sample_format == AFX_SAMPLE_S16) status[i] = afx::wav::load(paths[i], h_frames[i], nullptr, static_cast<int16_t*>(h_out) + h_offsets[i]);
+    else status[i] = afx::wav::load(paths[i], h_frames[i], static_cast<float*>(h_out) + h_offsets[i], nullptr);
+  });
   return AFX_OK;
 }
 

@@ -11,7 +11,7 @@ import struct
 
 import numpy as np
 
-__all__ = ["read_wav", "write_wav"]
+__all__ = ["read_wav", "write_wav", "probe_batch", "load_batch"]
 
 
 def read_wav(path):
@@ -75,3 +75,45 @@ def write_wav(path, y, sr, subtype="PCM_16"):
         "<IHHIIHH", 16, tag, 1, sr, sr * block, block, bits) + b"data" + struct.pack("<I", len(pcm))
     with open(path, "wb") as f:
         f.write(hdr + pcm)
+
+
+WAV_STATUS = {1: "cannot open", 2: "not a RIFF/WAVE file", 3: "missing fmt or data chunk", 4: "unsupported WAVE encoding",
+              5: "length changed between probe and load", 6: "not 16-bit mono PCM"}
+
+
+def _c_paths(paths):
+    import ctypes as C
+    arr = (C.c_char_p * len(paths))(*[str(p).encode() for p in paths])
+    return arr
+
+
+def probe_batch(paths, threads: int = 0):
+    """Headers of many WAV files at once (native, threaded: afx_wav_probe_batch).  Returns dict of numpy arrays
+    sr, channels, frames, tag, bits, status (0 = ok, else a WAV_STATUS key)."""
+    from . import _native as N
+    n = len(paths)
+    sr = np.zeros(n, np.int32); ch = np.zeros(n, np.int32); fr = np.zeros(n, np.int64)
+    fmt = np.zeros(n, np.int32); st = np.zeros(n, np.int32)
+    if n:
+        cp = _c_paths(paths)
+        N.check(N.lib().afx_wav_probe_batch(cp, n, threads, sr.ctypes.data, ch.ctypes.data, fr.ctypes.data,
+                                            fmt.ctypes.data, st.ctypes.data))
+    return {"sr": sr, "channels": ch, "frames": fr, "tag": fmt >> 8, "bits": fmt & 0xFF, "status": st}
+
+
+def load_batch(paths, frames, out, offsets, as_pcm16: bool = False, threads: int = 0):
+    """Decode many WAV files in parallel straight into `out` (a torch tensor or numpy array, ideally pinned):
+    file i -> out[offsets[i] : offsets[i] + frames[i]] as float32 mono, or as raw int16 when as_pcm16 (16-bit mono
+    PCM files only).  Returns the per-file status array."""
+    from . import _native as N
+    n = len(paths)
+    st = np.zeros(n, np.int32)
+    if n == 0:
+        return st
+    offsets = np.ascontiguousarray(offsets, dtype=np.int64)
+    frames = np.ascontiguousarray(frames, dtype=np.int64)
+    ptr = out.data_ptr() if hasattr(out, "data_ptr") else out.ctypes.data
+    cp = _c_paths(paths)
+    N.check(N.lib().afx_wav_load_batch(cp, n, threads, N.SAMPLE_S16 if as_pcm16 else N.SAMPLE_F32, ptr,
+                                       offsets.ctypes.data, frames.ctypes.data, st.ctypes.data))
+    return st

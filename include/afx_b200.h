@@ -173,6 +173,21 @@ int afx_extract_host_packed(afx_handle_t h, const void* h_audio, int sample_form
                             const int64_t* h_offsets, const int32_t* h_lengths, int64_t n_clips,
                             uint32_t feature_mask, float* h_summaries, int32_t* h_meta);
 
+/*
+ * Host ingest for batch_process (core/feature_extractor.py:215-237): the decode half of librosa.load (:52) for a list of
+ * RIFF/WAVE files on `threads` host threads (<= 0: all cores).  PCM 8/16/24/32 and IEEE float32/64, mono mix by channel
+ * mean, no resampling.  Two steps so the caller can size ONE packed (pinned) buffer for afx_extract_host_packed:
+ *   afx_wav_probe_batch  headers only: sample rate, channels, frames per channel, format = (format tag << 8) | bits
+ *   afx_wav_load_batch   decodes file i into h_out[h_offsets[i] .. + h_frames[i]) as float32 (AFX_SAMPLE_F32), or copies
+ *                        its raw samples (AFX_SAMPLE_S16; 16-bit mono PCM files only -- converted on the device later)
+ * status[i]: 0 ok, 1 cannot open, 2 not RIFF/WAVE, 3 fmt/data chunk missing, 4 unsupported encoding,
+ *            5 length differs from h_frames[i], 6 not 16-bit mono PCM (S16 requested).  Pure host code (no GPU needed).
+ */
+int afx_wav_probe_batch(const char* const* paths, int64_t n, int threads, int32_t* sr, int32_t* channels, int64_t* frames,
+                        int32_t* format, int32_t* status);
+int afx_wav_load_batch(const char* const* paths, int64_t n, int threads, int sample_format, void* h_out,
+                       const int64_t* h_offsets, const int64_t* h_frames, int32_t* status);
+
 /* Per-phase device-time accounting, for bench.py's roofline line: when enabled, every kernel launch
  * of afx_extract is bracketed by two CUDA events on the launching stream.  afx_profile_read
  * synchronises on the recorded events and returns, per phase, the accumulated milliseconds and the

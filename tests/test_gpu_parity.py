@@ -378,3 +378,29 @@ def test_framewise_npz_feature_set(torch_cuda, tmp_path):
     assert [p.split("/")[-1] for p in paths] == ["clip0_processed_features.npz", "clip1_processed_features.npz"]
     z = np.load(paths[0])
     assert sorted(z.files) == ["energy", "f0", "mfcc", "zcr"] and z["mfcc"].shape[0] == 39
+
+
+def test_batch_process_native_ingest_pcm16_and_mixed(torch_cuda, tmp_path):
+    """batch_process through the native threaded WAV reader: a directory of 16-bit mono PCM files takes the raw-PCM
+    path (converted on the device), a directory with another encoding the float32 path; both equal extract_features on
+    the same file, and unreadable / wrong-rate files are skipped (core/feature_extractor.py:233-235)."""
+    from audio_feature_extraction_b200 import AudioFeatureExtractor
+    from audio_feature_extraction_b200.synth import make_clip
+    from audio_feature_extraction_b200.wav import write_wav
+    ex = AudioFeatureExtractor()
+    d16 = tmp_path / "pcm16"; d16.mkdir()
+    for i in range(5):
+        write_wav(str(d16 / f"c{i}.wav"), make_clip(40 + i, seconds=1.0 + 0.3 * i), 22050, subtype="PCM_16")
+    (d16 / "broken.wav").write_bytes(b"RIFF\x00\x00\x00\x00JUNK")
+    write_wav(str(d16 / "rate.wav"), make_clip(1, seconds=1.0), 16000, subtype="PCM_16")
+    res = ex.batch_process(str(d16), features_to_extract=["mfcc", "energy"])
+    assert sorted(r["file_path"].split("/")[-1] for r in res) == [f"c{i}.wav" for i in range(5)]
+    for r in res:
+        one = ex.extract_features(r["file_path"], features_to_extract=["mfcc", "energy"])
+        np.testing.assert_allclose(r["mfcc_mean"], one["mfcc_mean"], atol=1e-5)
+        assert r["energy_mean"] == pytest.approx(one["energy_mean"], rel=1e-6)
+    dmix = tmp_path / "mixed"; dmix.mkdir()
+    write_wav(str(dmix / "a.wav"), make_clip(50, seconds=1.2), 22050, subtype="PCM_16")
+    write_wav(str(dmix / "b.wav"), make_clip(51, seconds=1.4), 22050, subtype="FLOAT")
+    res = ex.batch_process(str(dmix))
+    assert len(res) == 2 and all("f0_mean" in r and "mfcc_mean" in r for r in res)
