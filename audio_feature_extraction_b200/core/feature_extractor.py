@@ -277,6 +277,44 @@ class AudioFeatureExtractor:
                         "zcr": np.stack([e[:, 0], e[:, 1]])})
         return out
 
+    # ------------------------------------------------------------------ F0 post-processing (README "中值濾波平滑" / "F0範圍約束")
+    def extract_f0_smoothed(self, clips: Sequence[np.ndarray]) -> List[Dict[str, Any]]:
+        """pYIN F0 of a batch followed, on the device, by the post-processing the reference advertises (README.md:12-15;
+        recipe 04_feature_extraction_experiment/feature_extractor.py:283-301): the voiced frames' F0 through
+        scipy.signal.medfilt(5) and savgol_filter(11, 3), clamped to [f0_min, f0_max].  Per clip: 'f0' [T] float32 (NaN
+        where unvoiced), 'f0_smoothed' [T] (smoothed values at the voiced frames, NaN elsewhere), 'voiced_flag' [T], and
+        the recipe's statistics 'f0_mean', 'f0_global_rmse', 'f0_local_rmse', 'f0_stability', 'f0_missing_rate'."""
+        import torch
+
+        if len(clips) == 0:
+            return []
+        L = N.lib()
+        buf, offsets, lengths = self.pack_clips(clips)
+        dev = torch.device("cuda", self.device)
+        audio = buf.to(dev, non_blocking=True)
+        summaries, meta, frames = self.extract_batch_device(audio, offsets, lengths, ("f0",), return_frames=True)
+        track = torch.full((frames.shape[0],), float("nan"), dtype=torch.float32, device=dev)
+        stats = torch.zeros((len(clips), 4), dtype=torch.float32, device=dev)
+        h_len = np.ascontiguousarray(lengths, dtype=np.int32)
+        N.check(L.afx_f0_postprocess(self._h(), len(clips), h_len.ctypes.data, meta.data_ptr(), frames.data_ptr(),
+                                     track.data_ptr(), stats.data_ptr(), self._ws.data_ptr(),
+                                     torch.cuda.current_stream(dev).cuda_stream))
+        fr, tr, st, m = frames.cpu().numpy(), track.cpu().numpy(), stats.cpu().numpy(), meta.cpu().numpy()
+        rows = np.concatenate([[0], np.cumsum([self.max_frames(int(l)) for l in lengths])])
+        c_f0 = 3 * self.n_mfcc + 1
+        out = []
+        for i in range(len(clips)):
+            if int(m[i, 0]) != N.CLIP_OK:
+                raise FeatureExtractionError(f"<clip {i}>: {_STATUS_MSG.get(int(m[i, 0]), 'status %d' % int(m[i, 0]))}")
+            T = int(m[i, 3])
+            f0 = fr[rows[i]:rows[i] + T, c_f0].copy()
+            voiced = ~np.isnan(f0)
+            out.append({"f0": f0, "f0_smoothed": tr[rows[i]:rows[i] + T].copy(), "voiced_flag": voiced,
+                        "f0_mean": float(st[i, 0]), "f0_global_rmse": float(st[i, 1]), "f0_local_rmse": float(st[i, 2]),
+                        "f0_stability": float(st[i, 3]),
+                        "f0_missing_rate": float(np.sum(~voiced) / T) if T else 1.0})
+        return out
+
     @staticmethod
     def save_features_npz(features: Dict[str, Any], npz_path: str) -> str:
         """np.savez of one clip's framewise features under the reference's keys (feature_extraction.py:351-352)."""

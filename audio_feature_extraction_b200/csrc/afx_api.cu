@@ -618,6 +618,48 @@ int afx_wav_load_batch(const char* const* paths, int64_t n, int threads, int sam
   return AFX_OK;
 }
 
+int afx_f0_postprocess(afx_handle_t h, int64_t n_clips, const int32_t* h_lengths, const int32_t* d_meta, const float* d_frames,
+                       float* d_track, float* d_stats, const void* d_workspace, void* stream_v) {
+  if (!h || !h_lengths || !d_meta || !d_frames || !d_stats || !d_workspace) return fail(AFX_ERR_INVALID_ARG, "afx_f0_postprocess: null argument");
+  if (n_clips <= 0) return AFX_OK;
+  CUDA_TRY(cudaSetDevice(h->cfg.device));
+  const Layout L = header_layout(n_clips);
+  const char* ws = static_cast<const char*>(d_workspace);
+  afx::F0PostArgs fa;
+  fa.frame_off = reinterpret_cast<const long long*>(ws + L.off_frame_off);
+  fa.meta = d_meta; fa.frames = d_frames; fa.track = d_track; fa.stats = d_stats;
+  fa.frame_width = afx_frame_width(h); fa.n_mfcc = h->cfg.n_mfcc;
+  long long max_f = 16;
+  for (int64_t i = 0; i < n_clips; ++i) max_f = std::max<long long>(max_f, frames_ub(h, h_lengths[i]));
+  fa.max_frames = (int)((max_f + 1) & ~1LL);
+  fa.fmin = h->cfg.f0_min; fa.fmax = h->cfg.f0_max;
+  // Savitzky-Golay(11, 3) as a least-squares hat matrix H = V (V^T V)^-1 V^T on x = -5 .. 5 (centred: the fit is shift
+  // invariant): row 5 is the interior filter, rows 0 .. 4 scipy's mode='interp' edge fit evaluated at the first 5 points
+  {
+    double V[11][4], G[4][8];
+    for (int i = 0; i < 11; ++i) { const double x = i - 5; V[i][0] = 1; V[i][1] = x; V[i][2] = x * x; V[i][3] = x * x * x; }
+    for (int r = 0; r < 4; ++r) for (int c = 0; c < 4; ++c) { double acc = 0; for (int i = 0; i < 11; ++i) acc += V[i][r] * V[i][c]; G[r][c] = acc; G[r][4 + c] = r == c; }
+    for (int p = 0; p < 4; ++p) {   // Gauss-Jordan with partial pivoting on [V^T V | I]
+      int best = p; for (int r = p + 1; r < 4; ++r) if (std::fabs(G[r][p]) > std::fabs(G[best][p])) best = r;
+      for (int c = 0; c < 8; ++c) std::swap(G[p][c], G[best][c]);
+      const double piv = G[p][p]; for (int c = 0; c < 8; ++c) G[p][c] /= piv;
+      for (int r = 0; r < 4; ++r) if (r != p) { const double f = G[r][p]; for (int c = 0; c < 8; ++c) G[r][c] -= f * G[p][c]; }
+    }
+    for (int i = 0; i < 6; ++i) for (int j = 0; j < 11; ++j) {
+      double acc = 0;
+      for (int r = 0; r < 4; ++r) for (int c = 0; c < 4; ++c) acc += V[i][r] * G[r][4 + c] * V[j][c];
+      fa.hat[i][j] = acc;
+    }
+  }
+  const size_t smem = (size_t)fa.max_frames * (8 + 8 + 4);
+  if (smem > 200 * 1024) return fail(AFX_ERR_UNSUPPORTED, "afx_f0_postprocess: clips of more than %d frames are not supported", (200 * 1024) / 20);
+  CUDA_TRY(cudaFuncSetAttribute(afx::f0_post_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  afx::f0_post_kernel<<<(unsigned)n_clips, afx::kF0PostThreads, smem, static_cast<cudaStream_t>(stream_v)>>>(fa);
+  ++g_launches;
+  CUDA_TRY(cudaGetLastError());
+  return AFX_OK;
+}
+
 int afx_profile_enable(afx_handle_t h, int on) {
   if (!h) return fail(AFX_ERR_INVALID_ARG, "afx_profile_enable: null handle");
   h->profiling = on != 0;

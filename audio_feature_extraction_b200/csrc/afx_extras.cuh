@@ -76,3 +76,131 @@ __global__ void __launch_bounds__(kExtrasThreads) frame_extras_kernel(ExtrasArgs
 }
 
 }  // namespace afx
+
+// =====================================================================================================
+// F0 post-processing the reference advertises (README.md:12-15: median smoothing, range constraint, outlier handling;
+// concrete recipe 04_feature_extraction_experiment/feature_extractor.py:283-301): on the VOICED frames of the pYIN
+// track, scipy.signal.medfilt(kernel 5, zero padded) -> scipy.signal.savgol_filter(11, 3, mode='interp') when at least
+// 11 voiced frames -> clip to [f0_min, f0_max] -> mean, std (= the recipe's global RMSE), local RMSE
+// sqrt(mean(diff^2)) and stability std / (mean + 1e-8).  One CTA per clip; the voiced track sits in shared memory.
+namespace afx {
+
+constexpr int kF0PostThreads = 256;
+
+struct F0PostArgs {
+  const long long* frame_off;   // device [n_clips + 1]
+  const int* meta;              // [n_clips][4]
+  const float* frames;          // [rows][frame_width]; column 3 n_mfcc + 1 = f0 (NaN when unvoiced)
+  float* track;                 // [rows] smoothed f0 at voiced frames (other rows untouched)
+  float* stats;                 // [n_clips][4] mean, std, local_rmse, stability
+  int frame_width, n_mfcc, max_frames;
+  double fmin, fmax;
+  double hat[6][11];            // rows 0..4: edge fit (cubic through the first 11 points, evaluated at 0..4); row 5: interior
+};
+
+__device__ __forceinline__ void cswap(double& x, double& y) { const double lo = fmin(x, y), hi = fmax(x, y); x = lo; y = hi; }
+
+__global__ void __launch_bounds__(kF0PostThreads) f0_post_kernel(F0PostArgs a) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  double* A = reinterpret_cast<double*>(smem_raw);          // [max_frames]
+  double* B = A + a.max_frames;                              // [max_frames]
+  int* P = reinterpret_cast<int*>(B + a.max_frames);         // [max_frames] frame index of each voiced entry
+  __shared__ int s_wcnt[kF0PostThreads / 32];
+  __shared__ int s_base;
+  __shared__ double s_red[3][kF0PostThreads / 32];
+  const int clip = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int* m = a.meta + 4 * clip;
+  const int T = m[3];
+  float* st = a.stats + 4 * clip;
+  if (m[0] != 0 || T <= 0) { if (tid < 4) st[tid] = 0.f; return; }
+  const long long row0 = a.frame_off[clip];
+  const int c_f0 = 3 * a.n_mfcc + 1;
+  // ---- compact the voiced frames, order kept
+  if (tid == 0) s_base = 0;
+  __syncthreads();
+  for (int t0 = 0; t0 < T; t0 += kF0PostThreads) {
+    const int t = t0 + tid;
+    float f = __int_as_float(0x7fc00000);
+    if (t < T) f = a.frames[(size_t)(row0 + t) * a.frame_width + c_f0];
+    const bool v = !isnan(f);
+    const unsigned bal = __ballot_sync(0xffffffffu, v);
+    if (lane == 0) s_wcnt[warp] = __popc(bal);
+    __syncthreads();
+    int pos = s_base + __popc(bal & ((1u << lane) - 1u));
+    for (int w = 0; w < warp; ++w) pos += s_wcnt[w];
+    if (v) { A[pos] = (double)f; P[pos] = t; }
+    __syncthreads();
+    if (tid == 0) { int s = 0; for (int w = 0; w < kF0PostThreads / 32; ++w) s += s_wcnt[w]; s_base += s; }
+    __syncthreads();
+  }
+  const int nv = s_base;
+  if (nv == 0) {
+    if (tid == 0) { st[0] = 0.f; st[1] = st[2] = st[3] = __int_as_float(0x7f800000); }   // the recipe's np.inf branch
+    return;
+  }
+  // ---- medfilt(kernel min(5, len)), zero padded: 5 from 5 voiced frames on, 3 for exactly 3, identity for 1; scipy
+  // rejects the even kernels of 2 and 4 voiced frames (the recipe's except branch), which pass through here
+  double* cur = A; double* nxt = B;
+  if (nv >= 5) {
+    for (int i = tid; i < nv; i += kF0PostThreads) {
+      double v0 = i >= 2 ? cur[i - 2] : 0.0, v1 = i >= 1 ? cur[i - 1] : 0.0, v2 = cur[i];
+      double v3 = i + 1 < nv ? cur[i + 1] : 0.0, v4 = i + 2 < nv ? cur[i + 2] : 0.0;
+      cswap(v0, v1); cswap(v3, v4); cswap(v0, v3); cswap(v1, v4); cswap(v1, v2); cswap(v2, v3); cswap(v1, v2);   // median in v2
+      nxt[i] = v2;
+    }
+    __syncthreads();
+    double* tmp = cur; cur = nxt; nxt = tmp;
+  } else if (nv == 3) {
+    if (tid < 3) {
+      const double lo = tid >= 1 ? cur[tid - 1] : 0.0, mid = cur[tid], hi = tid + 1 < nv ? cur[tid + 1] : 0.0;
+      nxt[tid] = fmax(fmin(lo, mid), fmin(fmax(lo, mid), hi));
+    }
+    __syncthreads();
+    double* tmp = cur; cur = nxt; nxt = tmp;
+  }
+  // ---- savgol_filter(11, 3, mode='interp')
+  if (nv >= 11) {
+    for (int i = tid; i < nv; i += kF0PostThreads) {
+      double acc = 0.0;
+      if (i < 5) { for (int j = 0; j < 11; ++j) acc += a.hat[i][j] * cur[j]; }
+      else if (i >= nv - 5) { const int r = nv - 1 - i; for (int j = 0; j < 11; ++j) acc += a.hat[r][j] * cur[nv - 1 - j]; }
+      else { for (int j = 0; j < 11; ++j) acc += a.hat[5][j] * cur[i - 5 + j]; }
+      nxt[i] = acc;
+    }
+    __syncthreads();
+    double* tmp = cur; cur = nxt; nxt = tmp;
+  }
+  // ---- range constraint, output track, statistics
+  double s1 = 0.0, s2 = 0.0, sd = 0.0;
+  for (int i = tid; i < nv; i += kF0PostThreads) {
+    const double v = fmin(fmax(cur[i], a.fmin), a.fmax);
+    nxt[i] = v;
+    if (a.track) a.track[row0 + P[i]] = (float)v;
+    s1 += v;
+  }
+  __syncthreads();   // nxt holds the clipped track
+  s1 = warp_sum(s1);
+  if (lane == 0) s_red[0][warp] = s1;
+  __syncthreads();
+  double mean = 0.0;
+  for (int w = 0; w < kF0PostThreads / 32; ++w) mean += s_red[0][w];
+  mean /= (double)nv;
+  for (int i = tid; i < nv; i += kF0PostThreads) {
+    const double d = nxt[i] - mean;
+    s2 += d * d;
+    if (i + 1 < nv) { const double e = nxt[i + 1] - nxt[i]; sd += e * e; }
+  }
+  s2 = warp_sum(s2); sd = warp_sum(sd);
+  if (lane == 0) { s_red[1][warp] = s2; s_red[2][warp] = sd; }
+  __syncthreads();
+  if (tid == 0) {
+    double v2 = 0.0, d2 = 0.0;
+    for (int w = 0; w < kF0PostThreads / 32; ++w) { v2 += s_red[1][w]; d2 += s_red[2][w]; }
+    const double sdev = sqrt(v2 / (double)nv);
+    st[0] = (float)mean; st[1] = (float)sdev;
+    st[2] = nv >= 2 ? (float)sqrt(d2 / (double)(nv - 1)) : __int_as_float(0x7fc00000);   // np.mean of an empty diff is NaN
+    st[3] = (float)(sdev / (mean + 1e-8));
+  }
+}
+
+}  // namespace afx

@@ -147,6 +147,17 @@ int afx_frame_extras(afx_handle_t h, const float* d_audio, int64_t n_clips, cons
                      float* d_extras, const void* d_workspace, void* stream);
 
 /*
+ * F0 post-processing the reference advertises (README.md:12-15; recipe 04_feature_extraction_experiment/
+ * feature_extractor.py:283-301) on the voiced frames of the pYIN track in d_frames: scipy.signal.medfilt(5) ->
+ * scipy.signal.savgol_filter(11, 3) (>= 11 voiced frames) -> clip to [f0_min, f0_max].  Call after
+ * afx_extract(AFX_FEAT_F0, d_frames != NULL) with the same d_meta / d_frames / d_workspace.
+ *   d_track  float32 [rows of d_frames] or NULL: smoothed F0 at the voiced rows (other rows untouched)
+ *   d_stats  float32 [n_clips, 4]: mean, std (global RMSE), local RMSE sqrt(mean(diff^2)), stability std / (mean + 1e-8)
+ */
+int afx_f0_postprocess(afx_handle_t h, int64_t n_clips, const int32_t* h_lengths, const int32_t* d_meta, const float* d_frames,
+                       float* d_track, float* d_stats, const void* d_workspace, void* stream);
+
+/*
  * Same computation from HOST memory (what a caller holding decoded files has): clips are staged
  * through pinned buffers, copied host->device in waves on a copy stream that overlaps the compute
  * stream, and the summaries / meta rows are copied back.  Blocks until the results are in

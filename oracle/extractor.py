@@ -112,3 +112,25 @@ class OracleFeatureExtractor:
         z = L.zero_crossing_rate(yt, frame_length=self.frame_length, hop_length=self.hop_length)
         return {"mfcc": np.vstack([m, d1, d2]), "f0": np.vstack([f0, L.delta(f0)]),
                 "energy": np.vstack([r, L.delta(r)]), "zcr": np.vstack([z, L.delta(z)])}
+
+    def f0_postprocess(self, f0, voiced_flag):
+        """F0 post-processing of the reference's experiment recipe (04_feature_extraction_experiment/
+        feature_extractor.py:283-301; README.md:12-15 'median smoothing', 'F0 range constraint'), with scipy itself:
+        medfilt(min(5, len)) -> savgol_filter(11, 3) from 11 voiced frames on -> clip to [f0_min, f0_max]; returns the
+        smoothed voiced values and (mean, global RMSE, local RMSE, stability).  scipy rejects the even kernels of
+        2 and 4 voiced frames; the values pass through there."""
+        import scipy.signal
+        v = np.asarray(f0, dtype=np.float64)[np.asarray(voiced_flag, dtype=bool)]
+        if v.size == 0:
+            return v, (0.0, np.inf, np.inf, np.inf)
+        k = min(5, v.size)
+        if k % 2 == 1:
+            v = scipy.signal.medfilt(v, kernel_size=k)
+        if v.size >= 11:
+            v = scipy.signal.savgol_filter(v, window_length=11, polyorder=3)
+        v = np.clip(v, self.f0_min, self.f0_max)
+        with np.errstate(invalid="ignore"), __import__("warnings").catch_warnings():
+            __import__("warnings").simplefilter("ignore")
+            local = float(np.sqrt(np.mean(np.diff(v) ** 2)))
+        glob = float(np.sqrt(np.mean((v - np.mean(v)) ** 2)))
+        return v, (float(np.mean(v)), glob, local, float(np.std(v) / (np.mean(v) + 1e-8)))

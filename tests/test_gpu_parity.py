@@ -404,3 +404,61 @@ def test_batch_process_native_ingest_pcm16_and_mixed(torch_cuda, tmp_path):
     write_wav(str(dmix / "b.wav"), make_clip(51, seconds=1.4), 22050, subtype="FLOAT")
     res = ex.batch_process(str(dmix))
     assert len(res) == 2 and all("f0_mean" in r and "mfcc_mean" in r for r in res)
+
+
+def test_f0_postprocess_matches_scipy(torch_cuda):
+    """F0 post-processing (README.md:12-15; 04_feature_extraction_experiment/feature_extractor.py:283-301): medfilt(5) ->
+    savgol_filter(11, 3) -> clip on the voiced frames, against scipy through the oracle.  First on the device's own
+    pYIN track, then on planted tracks with 0 .. 12 and many voiced frames (every branch of the recipe)."""
+    import torch
+    from audio_feature_extraction_b200 import AudioFeatureExtractor, _native as N
+    from audio_feature_extraction_b200.synth import make_clip
+    from oracle import OracleFeatureExtractor
+    ex, ora = AudioFeatureExtractor(), OracleFeatureExtractor()
+    clips = [make_clip(s, seconds=1.0 + 0.25 * s) for s in range(16)]
+    got = ex.extract_f0_smoothed(clips)
+    for g in got:
+        ref, st = ora.f0_postprocess(g["f0"], g["voiced_flag"])
+        np.testing.assert_allclose(g["f0_smoothed"][g["voiced_flag"]], ref, rtol=2e-7, atol=0)
+        assert np.all(np.isnan(g["f0_smoothed"][~g["voiced_flag"]]))
+        np.testing.assert_allclose([g["f0_mean"], g["f0_global_rmse"], g["f0_local_rmse"], g["f0_stability"]], st, rtol=1e-6)
+    # planted tracks: overwrite the F0 column of the frame matrix, then post-process again
+    buf, offsets, lengths = ex.pack_clips(clips)
+    dev = torch.device("cuda", ex.device)
+    audio = buf.to(dev)
+    _, meta, frames = ex.extract_batch_device(audio, offsets, lengths, ("f0",), return_frames=True)
+    m = meta.cpu().numpy()
+    rows = np.concatenate([[0], np.cumsum([ex.max_frames(int(l)) for l in lengths])])
+    rng = np.random.default_rng(5)
+    fr = frames.cpu().numpy().copy()
+    c_f0 = 3 * ex.n_mfcc + 1
+    planted = []
+    for i, nv in enumerate([0, 1, 2, 3, 4, 5, 6, 10, 11, 12, 13, 21, 30, 40, None, None]):
+        T = int(m[i, 3])
+        nv = T if nv is None else nv
+        f0 = np.full(T, np.nan, dtype=np.float32)
+        idx = np.sort(rng.choice(T, size=nv, replace=False))
+        walk = 220.0 * 2.0 ** np.cumsum(rng.normal(0, 0.02, size=nv))
+        walk[rng.random(nv) < 0.1] *= 2.0                          # octave jumps for the median filter
+        if i == 15:
+            walk *= 12.0                                           # beyond f0_max: the range clamp
+        f0[idx] = walk.astype(np.float32)
+        fr[rows[i]:rows[i] + T, c_f0] = f0
+        planted.append(f0)
+    frames.copy_(torch.from_numpy(fr))
+    track = torch.full((frames.shape[0],), float("nan"), dtype=torch.float32, device=dev)
+    stats = torch.zeros((len(clips), 4), dtype=torch.float32, device=dev)
+    h_len = np.ascontiguousarray(lengths, dtype=np.int32)
+    N.check(N.lib().afx_f0_postprocess(ex._h(), len(clips), h_len.ctypes.data, meta.data_ptr(), frames.data_ptr(),
+                                       track.data_ptr(), stats.data_ptr(), ex._ws.data_ptr(),
+                                       torch.cuda.current_stream(dev).cuda_stream))
+    tr, st = track.cpu().numpy(), stats.cpu().numpy()
+    for i, f0 in enumerate(planted):
+        T = f0.size
+        voiced = ~np.isnan(f0)
+        ref, rst = ora.f0_postprocess(f0, voiced)
+        g = tr[rows[i]:rows[i] + T]
+        np.testing.assert_allclose(g[voiced], ref, rtol=2e-7, atol=0)
+        assert np.all(np.isnan(g[~voiced]))
+        np.testing.assert_allclose(st[i], np.asarray(rst, dtype=np.float64), rtol=1e-6, equal_nan=True)
+    assert tr[rows[15]:rows[15] + planted[15].size].max() <= np.float32(ex.f0_max)
