@@ -27,7 +27,7 @@ EXPORTS = [
 PHASES = ("trim", "frames", "mfcc", "finalize", "pcm", "yin", "viterbi", "reserved")
 N_PHASES = 8
 SAMPLE_F32, SAMPLE_S16 = 0, 1
-EXTRAS_WIDTH = 4
+EXTRAS_WIDTH = 5
 
 
 class AfxConfig(C.Structure):

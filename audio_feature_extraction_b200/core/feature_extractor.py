@@ -242,7 +242,8 @@ class AudioFeatureExtractor:
         (04_feature_extraction_experiment/feature_extraction.py:191-292, :340-353) and its DTW stage loads:
         'mfcc' [3 n_mfcc, T] (MFCC / delta / delta2), 'f0' [2, T] (nan_to_num(pyin f0) / delta), 'energy' [2, T]
         (rms / delta), 'zcr' [2, T] (zero-crossing rate / delta), computed on the preprocessed (pre-emphasised,
-        trimmed) waveform of this class.  One batched device pass + one small kernel (afx_frame_extras)."""
+        trimmed) waveform of this class; plus 'short_time_energy' [1 + (L - frame_length) // hop] = sum(frame ** 2) over
+        librosa.util.frame's unpadded frames (README.md:33), which is not part of the stored .npz.  One batched device pass + one small kernel (afx_frame_extras)."""
         import torch
 
         if len(clips) == 0:
@@ -270,11 +271,13 @@ class AudioFeatureExtractor:
                 raise err
             T = int(m[i, 3])
             f, e = fr[rows[i]:rows[i] + T], ex[rows[i]:rows[i] + T]
+            n_ste = max(0, 1 + (int(m[i, 2]) - int(m[i, 1]) - self.frame_length) // self.hop_length)
             out.append({"file_path": name,
                         "mfcc": np.ascontiguousarray(f[:, :3 * n].T),
                         "f0": np.stack([np.nan_to_num(f[:, 3 * n + 1]), e[:, 3]]),
                         "energy": np.stack([f[:, 3 * n], e[:, 2]]),
-                        "zcr": np.stack([e[:, 0], e[:, 1]])})
+                        "zcr": np.stack([e[:, 0], e[:, 1]]),
+                        "short_time_energy": e[:n_ste, 4].copy()})
         return out
 
     # ------------------------------------------------------------------ F0 post-processing (README "中值濾波平滑" / "F0範圍約束")
@@ -318,7 +321,7 @@ class AudioFeatureExtractor:
     @staticmethod
     def save_features_npz(features: Dict[str, Any], npz_path: str) -> str:
         """np.savez of one clip's framewise features under the reference's keys (feature_extraction.py:351-352)."""
-        np.savez(npz_path, **{k: v for k, v in features.items() if k != "file_path"})
+        np.savez(npz_path, **{k: features[k] for k in ("mfcc", "f0", "energy", "zcr")})
         return npz_path
 
     def batch_export_npz(self, audio_dir: str, out_dir: str) -> List[str]:

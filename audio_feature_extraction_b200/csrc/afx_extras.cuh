@@ -1,7 +1,10 @@
 // Framewise extras for the .npz feature set of the reference's experiment pipeline
 // (04_feature_extraction_experiment/feature_extraction.py:191-292, stored :340-353): zero-crossing rate per frame
 // (librosa.feature.zero_crossing_rate: edge padding, |x| <= 1e-10 counts as +0, first entry of a frame never a
-// crossing) and the SavGol(9) deltas of the one-row features zcr, rms and nan_to_num(f0).
+// crossing), the SavGol(9) deltas of the one-row features zcr, rms and nan_to_num(f0), and the short-time energy
+// sum(frame^2) over the UNPADDED frames of librosa.util.frame (README.md:33; 04_feature_extraction_experiment/
+// 'audio_feature_extraction 2'/audio_feature_extraction/feature_extractor.py:234-238): unpadded frame t is the centred
+// frame t + n_fft / (2 hop), so its energy is n_fft * rms^2 of that row.
 // Runs after afx_extract on the same batch: it reads the trim decision (meta), the frame rows (rms, f0) and
 // recomputes the pre-emphasised samples on the fly.
 #pragma once
@@ -10,7 +13,7 @@
 namespace afx {
 
 constexpr int kExtrasThreads = 256;
-constexpr int kExtrasWidth = 4;   // zcr, delta(zcr), delta(rms), delta(nan_to_num(f0))
+constexpr int kExtrasWidth = 5;   // zcr, delta(zcr), delta(rms), delta(nan_to_num(f0)), short-time energy
 
 struct ExtrasArgs {
   const float* audio;
@@ -72,6 +75,12 @@ __global__ void __launch_bounds__(kExtrasThreads) frame_extras_kernel(ExtrasArgs
     }
     float* e = a.extras + (size_t)(row0 + t) * kExtrasWidth;
     e[1] = (float)(dz / 60.0); e[2] = (float)(dr / 60.0); e[3] = (float)(df / 60.0);
+    float ste = 0.f;
+    if (L >= a.n_fft && t <= (L - a.n_fft) / a.hop) {
+      const float r = a.frames[(size_t)(row0 + t + a.n_fft / (2 * a.hop)) * a.frame_width + c_rms];
+      ste = (float)a.n_fft * r * r;
+    }
+    e[4] = ste;
   }
 }
 

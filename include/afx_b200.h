@@ -139,10 +139,12 @@ int afx_preprocess(afx_handle_t h, const float* d_audio, const int64_t* h_offset
  * (04_feature_extraction_experiment/feature_extraction.py:191-292, np.savez :340-353): per frame
  *   [0] zero-crossing rate (librosa.feature.zero_crossing_rate, :279-283)  [1] its delta (:286)
  *   [2] delta of the RMS energy (:265)   [3] delta of nan_to_num(f0) (:241-244)
+ *   [4] short-time energy sum(frame^2) of the UNPADDED frame t (README.md:33; librosa.util.frame, '04_.../audio_feature_
+ *       extraction 2/audio_feature_extraction/feature_extractor.py:234-238'): 1 + (L - n_fft) / hop values, then zeros
  * Call right after afx_extract(..., d_frames != NULL, ...) on the same stream with the SAME d_audio, d_meta, d_frames
- * and d_workspace (the batch header afx_extract left there is reused).  d_extras: float32 [rows of d_frames, 4].
+ * and d_workspace (the batch header afx_extract left there is reused).  d_extras: float32 [rows of d_frames, 5].
  */
-#define AFX_EXTRAS_WIDTH 4
+#define AFX_EXTRAS_WIDTH 5
 int afx_frame_extras(afx_handle_t h, const float* d_audio, int64_t n_clips, const int32_t* d_meta, const float* d_frames,
                      float* d_extras, const void* d_workspace, void* stream);
 

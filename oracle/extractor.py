@@ -110,8 +110,16 @@ class OracleFeatureExtractor:
         f0 = np.nan_to_num(f0).reshape(1, -1)
         r = self.rms_frames(yt)
         z = L.zero_crossing_rate(yt, frame_length=self.frame_length, hop_length=self.hop_length)
+        # short-time energy of the variant extractor (README.md:33; '04_.../audio_feature_extraction 2/
+        # audio_feature_extraction/feature_extractor.py:234-238'): np.sum(librosa.util.frame(y, N, hop) ** 2, axis=0)
+        N, hop = self.frame_length, self.hop_length
+        if yt.size >= N:
+            fr = np.lib.stride_tricks.sliding_window_view(yt, N)[::hop]
+            ste = np.sum(fr.astype(np.float64) ** 2, axis=1)
+        else:
+            ste = np.zeros(0)
         return {"mfcc": np.vstack([m, d1, d2]), "f0": np.vstack([f0, L.delta(f0)]),
-                "energy": np.vstack([r, L.delta(r)]), "zcr": np.vstack([z, L.delta(z)])}
+                "energy": np.vstack([r, L.delta(r)]), "zcr": np.vstack([z, L.delta(z)]), "short_time_energy": ste}
 
     def f0_postprocess(self, f0, voiced_flag):
         """F0 post-processing of the reference's experiment recipe (04_feature_extraction_experiment/

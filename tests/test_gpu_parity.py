@@ -365,6 +365,8 @@ def test_framewise_npz_feature_set(torch_cuda, tmp_path):
         np.testing.assert_allclose(g["energy"][1], ref["energy"][1], rtol=1e-4, atol=1e-7)
         np.testing.assert_array_equal(g["zcr"][0], ref["zcr"][0].astype(np.float32))       # integer counts / n_fft: exact
         np.testing.assert_allclose(g["zcr"][1], ref["zcr"][1], rtol=1e-5, atol=1e-7)
+        assert g["short_time_energy"].shape == ref["short_time_energy"].shape              # 1 + (L - N) // hop
+        np.testing.assert_allclose(g["short_time_energy"], ref["short_time_energy"], rtol=ENERGY_RTOL, atol=1e-12)
         voiced = (ref["f0"][0] > 0)
         assert np.mean((g["f0"][0] > 0) == voiced) >= 0.999                                 # voicing decisions
         both = voiced & (g["f0"][0] > 0)
