@@ -391,15 +391,46 @@ class AudioFeatureExtractor:
         energy_mean, energy_std, energy_range."""
         return self._extract_preprocessed(y, "energy")
 
+    def resample_batch_device(self, audio, offsets, lengths, native_sr: int, stream=None):
+        """Sample-rate conversion native_sr -> self.sr of device-resident clips (afx_resample): librosa.load's resampling
+        step (reference :52) with res_type='polyphase' (scipy.signal.resample_poly defaults; 'soxr_hq' is a C library
+        that cannot be restated).  Returns (audio_out cuda f32, offsets int64, lengths int32) in pack_clips' layout."""
+        import torch
+
+        L = N.lib()
+        h = self._h()
+        offsets = np.ascontiguousarray(offsets, dtype=np.int64)
+        lengths = np.ascontiguousarray(lengths, dtype=np.int32)
+        n = int(lengths.shape[0])
+        out_len = np.asarray([L.afx_resample_length(h, int(native_sr), int(l)) for l in lengths], dtype=np.int64)
+        strides = (out_len + 3) // 4 * 4
+        out_off = np.zeros(n, dtype=np.int64)
+        if n > 1:
+            out_off[1:] = np.cumsum(strides)[:-1]
+        out = torch.zeros(int(strides.sum()) + 4, dtype=torch.float32, device=audio.device)
+        s = stream if stream is not None else torch.cuda.current_stream(audio.device)
+        N.check(L.afx_resample(h, audio.data_ptr(), offsets.ctypes.data, lengths.ctypes.data, n, int(native_sr),
+                               out.data_ptr(), out_off.ctypes.data, s.cuda_stream))
+        return out, out_off, out_len.astype(np.int32)
+
+    def resample(self, y: np.ndarray, native_sr: int) -> np.ndarray:
+        """One waveform native_sr -> self.sr on the device; float32 numpy in, float32 numpy out."""
+        import torch
+
+        if int(native_sr) == self.sr:
+            return np.asarray(y, dtype=np.float32)
+        buf, offsets, lengths = self.pack_clips([np.asarray(y, dtype=np.float32)])
+        dev = torch.device("cuda", self.device)
+        out, _, out_len = self.resample_batch_device(buf.to(dev, non_blocking=True), offsets, lengths, native_sr)
+        return out[:int(out_len[0])].cpu().numpy()
+
     def load_audio(self, audio_path: str) -> Tuple[np.ndarray, int]:
-        """載入音頻文件 (reference :41-56): float32 mono at self.sr."""
+        """載入音頻文件 (reference :41-56): float32 mono at self.sr; a file at another rate is resampled on the device."""
         try:
             y, sr = read_wav(audio_path)
             if sr != self.sr:
-                raise FeatureExtractionError(
-                    f"{audio_path}: native sample rate {sr} != {self.sr}; resampling (librosa.load's soxr path) "
-                    "is outside the B200 hot path")
-            return y, sr
+                y = self.resample(y, sr)
+            return y, self.sr
         except Exception as e:
             self.logger.error(f"載入音頻文件失敗: {str(e)}")
             raise
@@ -412,6 +443,53 @@ class AudioFeatureExtractor:
         except Exception as e:
             self.logger.error(f"特徵提取失敗: {str(e)}")
             raise
+
+    def _batch_process_mixed_rates(self, files, info, keep, other, features_to_extract):
+        """batch_process for a directory that holds files at other sample rates: every readable file is decoded to
+        float32 by the native reader, the groups at another rate are converted on the device (afx_resample) and all
+        clips go through one device pass, in the enumeration order."""
+        import torch
+        from ..wav import load_batch, WAV_STATUS
+
+        dev = torch.device("cuda", self.device)
+        order = sorted(keep + other)
+        names = [files[i] for i in order]
+        frames = info["frames"][order].astype(np.int64)
+        rates = info["sr"][order].astype(np.int64)
+        strides = (frames + 7) // 8 * 8
+        offsets = np.zeros(len(order), dtype=np.int64)
+        offsets[1:] = np.cumsum(strides)[:-1]
+        host = torch.zeros(int(strides.sum()) + 8, dtype=torch.float32, pin_memory=True)
+        st = load_batch(names, frames, host, offsets, as_pcm16=False)
+        for i in np.nonzero(st)[0]:
+            self.logger.error(f"載入音頻文件失敗: {names[i]}: {WAV_STATUS.get(int(st[i]), 'unreadable')}")
+        lengths = np.where(st == 0, frames, 0).astype(np.int32)
+        raw = host.to(dev, non_blocking=True)
+        # target layout: every clip at self.sr
+        L = N.lib()
+        h = self._h()
+        out_len = np.asarray([int(l) if int(r) == self.sr else L.afx_resample_length(h, int(r), int(l))
+                              for l, r in zip(lengths, rates)], dtype=np.int64)
+        ostr = (out_len + 3) // 4 * 4
+        ooff = np.zeros(len(order), dtype=np.int64)
+        ooff[1:] = np.cumsum(ostr)[:-1]
+        audio = torch.zeros(int(ostr.sum()) + 4, dtype=torch.float32, device=dev)
+        s = torch.cuda.current_stream(dev)
+        for r in np.unique(rates):
+            idx = np.nonzero(rates == r)[0]
+            if int(r) == self.sr:
+                for i in idx:   # same rate: plain device copies
+                    audio[ooff[i]:ooff[i] + out_len[i]].copy_(raw[offsets[i]:offsets[i] + lengths[i]])
+                continue
+            io, il, oo = (np.ascontiguousarray(offsets[idx]), np.ascontiguousarray(lengths[idx]),
+                          np.ascontiguousarray(ooff[idx]))
+            N.check(L.afx_resample(h, raw.data_ptr(), io.ctypes.data, il.ctypes.data, len(idx), int(r),
+                                   audio.data_ptr(), oo.ctypes.data, s.cuda_stream))
+        summ, meta, _ = self.extract_batch_device(audio, ooff, out_len.astype(np.int32), features_to_extract)
+        results = self.rows_to_dicts(summ.cpu().numpy(), meta.cpu().numpy(), names, features_to_extract, skip_errors=True)
+        for r in results:
+            self.logger.info(f"成功處理文件: {Path(r['file_path']).name}")
+        return results
 
     def batch_process(self, audio_dir: str, features_to_extract: Optional[Sequence[str]] = None) -> List[Dict[str, Any]]:
         """批量處理音頻文件 (reference :215-237): every *.wav of the directory in one batched pass.
@@ -428,19 +506,18 @@ class AudioFeatureExtractor:
         L = N.lib()
         h = self._h()
         info = probe_batch(files)
-        keep = []
+        keep, other = [], []
         for i, f in enumerate(files):
-            msg = None
             if info["status"][i] != 0:
                 msg = WAV_STATUS.get(int(info["status"][i]), "unreadable")
-            elif int(info["sr"][i]) != self.sr:
-                msg = (f"native sample rate {int(info['sr'][i])} != {self.sr}; resampling (librosa.load's soxr path) "
-                       "is outside the B200 hot path")
-            if msg is None:
-                keep.append(i)
-            else:
                 self.logger.error(f"載入音頻文件失敗: {f}: {msg}")
                 self.logger.error(f"處理文件 {Path(f).name} 失敗: {msg}")
+            elif int(info["sr"][i]) != self.sr:
+                other.append(i)
+            else:
+                keep.append(i)
+        if other:
+            return self._batch_process_mixed_rates(files, info, keep, other, features_to_extract)
         if not keep:
             return []
         names = [files[i] for i in keep]

@@ -13,6 +13,8 @@
 #include <cstring>
 #include <string>
 #include <thread>
+#include <map>
+#include <numeric>
 #include <vector>
 
 #include "afx_common.cuh"
@@ -23,6 +25,7 @@
 #include "afx_tables.h"
 #include "afx_trim.cuh"
 #include "afx_wav.h"
+#include "afx_resample.cuh"
 
 namespace {
 
@@ -98,6 +101,10 @@ struct afx_handle_s {
   cudaEvent_t copied[2] = {nullptr, nullptr}, computed[2] = {nullptr, nullptr};
   long long host_wave_samples = 96ll << 20;   // samples per host->device wave (AFX_HOST_WAVE_SAMPLES): several clips per
                                               // resident CTA of the fused kernel; the first waves are shorter (pipeline fill)
+  // sample-rate conversion (afx_resample): one phase-ordered filter per native rate, header arrays of the last call
+  struct ResampleDev { afx::ResampleFilter f; float* d_taps = nullptr; };
+  std::map<int, ResampleDev> resamplers;
+  void* d_rs_hdr = nullptr; size_t d_rs_hdr_bytes = 0;
   // per-phase device-time accounting (afx_profile_enable / afx_profile_read)
   bool profiling = false;
   struct Span { cudaEvent_t a, b; int phase; };
@@ -336,6 +343,8 @@ int afx_destroy(afx_handle_t h) {
   for (auto& sp : h->spans) { cudaEventDestroy(sp.a); cudaEventDestroy(sp.b); }
   for (auto e : h->ev_pool) cudaEventDestroy(e);
   cudaFree(h->d_pcm[0]); cudaFree(h->d_pcm[1]);
+  for (auto& kv : h->resamplers) cudaFree(kv.second.d_taps);
+  cudaFree(h->d_rs_hdr);
   if (h->h_pin[0]) cudaFreeHost(h->h_pin[0]);
   if (h->h_pin[1]) cudaFreeHost(h->h_pin[1]);
   for (int i = 0; i < 2; ++i) { if (h->copied[i]) cudaEventDestroy(h->copied[i]); if (h->computed[i]) cudaEventDestroy(h->computed[i]); }
@@ -656,6 +665,70 @@ int afx_f0_postprocess(afx_handle_t h, int64_t n_clips, const int32_t* h_lengths
   CUDA_TRY(cudaFuncSetAttribute(afx::f0_post_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   afx::f0_post_kernel<<<(unsigned)n_clips, afx::kF0PostThreads, smem, static_cast<cudaStream_t>(stream_v)>>>(fa);
   ++g_launches;
+  CUDA_TRY(cudaGetLastError());
+  return AFX_OK;
+}
+
+int64_t afx_resample_length(afx_handle_t h, int32_t native_sr, int64_t n_in) {
+  if (!h || native_sr < 1 || n_in < 0) return -1;
+  const int g = std::gcd(h->cfg.sr, native_sr);
+  return afx::resample_out_len(n_in, h->cfg.sr / g, native_sr / g);
+}
+
+int afx_resample(afx_handle_t h, const float* d_in, const int64_t* h_in_offsets, const int32_t* h_in_lengths, int64_t n_clips,
+                 int32_t native_sr, float* d_out, const int64_t* h_out_offsets, void* stream_v) {
+  if (!h || !d_in || !d_out || !h_in_offsets || !h_in_lengths || !h_out_offsets) return fail(AFX_ERR_INVALID_ARG, "afx_resample: null argument");
+  if (native_sr < 1 || native_sr > (1 << 22)) return fail(AFX_ERR_INVALID_ARG, "afx_resample: bad native sample rate %d", native_sr);
+  if (n_clips < 0 || n_clips > 0x7fffff00LL) return fail(AFX_ERR_INVALID_ARG, "afx_resample: bad n_clips");
+  if (n_clips == 0) return AFX_OK;
+  CUDA_TRY(cudaSetDevice(h->cfg.device));
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_v);
+  auto it = h->resamplers.find(native_sr);
+  if (it == h->resamplers.end()) {
+    afx_handle_s::ResampleDev rd;
+    rd.f = afx::design_resample_filter(h->cfg.sr, native_sr);
+    if ((size_t)rd.f.up * rd.f.J > (64u << 20)) return fail(AFX_ERR_UNSUPPORTED, "afx_resample: %d -> %d Hz needs a %d-phase filter", native_sr, h->cfg.sr, rd.f.up);
+    CUDA_TRY(cudaMalloc(&rd.d_taps, rd.f.taps.size() * sizeof(float)));
+    CUDA_TRY(cudaMemcpy(rd.d_taps, rd.f.taps.data(), rd.f.taps.size() * sizeof(float), cudaMemcpyHostToDevice));
+    it = h->resamplers.emplace(native_sr, std::move(rd)).first;
+  }
+  const afx::ResampleFilter& f = it->second.f;
+  // header: in_off | out_off (long long), in_len | out_len (int)
+  const size_t n = (size_t)n_clips, bytes = n * (2 * sizeof(long long) + 2 * sizeof(int));
+  std::vector<unsigned char> hdr(bytes);
+  long long* ho = reinterpret_cast<long long*>(hdr.data());
+  int* hl = reinterpret_cast<int*>(hdr.data() + 2 * n * sizeof(long long));
+  long long max_out = 0;
+  for (size_t i = 0; i < n; ++i) {
+    if (h_in_lengths[i] < 0 || h_in_offsets[i] < 0 || h_out_offsets[i] < 0) return fail(AFX_ERR_INVALID_ARG, "afx_resample: clip %zu has a negative length or offset", i);
+    const long long no = afx::resample_out_len(h_in_lengths[i], f.up, f.down);
+    if (no > 0x7fffffffLL) return fail(AFX_ERR_UNSUPPORTED, "afx_resample: clip %zu is too long", i);
+    ho[i] = h_in_offsets[i]; ho[n + i] = h_out_offsets[i]; hl[i] = h_in_lengths[i]; hl[n + i] = (int)no;
+    max_out = std::max(max_out, no);
+  }
+  if (max_out == 0) return AFX_OK;
+  if (h->d_rs_hdr_bytes < bytes) {
+    CUDA_TRY(cudaFree(h->d_rs_hdr)); h->d_rs_hdr = nullptr; h->d_rs_hdr_bytes = 0;
+    CUDA_TRY(cudaMalloc(&h->d_rs_hdr, bytes * 2));
+    h->d_rs_hdr_bytes = bytes * 2;
+  }
+  CUDA_TRY(cudaStreamSynchronize(stream));   // a previous call on this stream may still read the header
+  CUDA_TRY(cudaMemcpyAsync(h->d_rs_hdr, hdr.data(), bytes, cudaMemcpyHostToDevice, stream));
+  afx::ResampleArgs ra;
+  ra.in = d_in; ra.out = d_out;
+  ra.in_off = reinterpret_cast<const long long*>(h->d_rs_hdr);
+  ra.out_off = ra.in_off + n;
+  ra.in_len = reinterpret_cast<const int*>(static_cast<const unsigned char*>(h->d_rs_hdr) + 2 * n * sizeof(long long));
+  ra.out_len = ra.in_len + n;
+  ra.taps = it->second.d_taps; ra.up = f.up; ra.down = f.down; ra.J = f.J; ra.n_pre_remove = f.n_pre_remove;
+  const long long tile = afx::kResampleThreads * afx::kResamplePerThread;
+  const unsigned gx = (unsigned)std::min<long long>((max_out + tile - 1) / tile, 1 << 16);
+  for (int64_t c0 = 0; c0 < n_clips; c0 += 65535) {
+    ra.clip0 = (int)c0;
+    const unsigned gy = (unsigned)std::min<int64_t>(65535, n_clips - c0);
+    afx::resample_kernel<<<dim3(gx, gy), afx::kResampleThreads, 0, stream>>>(ra);
+    ++g_launches;
+  }
   CUDA_TRY(cudaGetLastError());
   return AFX_OK;
 }

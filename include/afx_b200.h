@@ -160,6 +160,19 @@ int afx_f0_postprocess(afx_handle_t h, int64_t n_clips, const int32_t* h_lengths
                        float* d_track, float* d_stats, const void* d_workspace, void* stream);
 
 /*
+ * Sample-rate conversion of a batch to the handle's `sr`: the resampling half of librosa.load(path, sr=self.sr)
+ * (core/feature_extractor.py:52) for files whose native rate differs.  librosa's default res_type 'soxr_hq' is the soxr
+ * C library (absent from the reference tree); this is librosa's res_type='polyphase', i.e.
+ * scipy.signal.resample_poly(y, sr / g, native_sr / g) with scipy's default Kaiser(5) design, float32, bit-exact.
+ *   afx_resample_length   ceil(n_in * sr / native_sr): samples clip of n_in samples resamples to (-1 on bad arguments)
+ *   d_in / d_out          device float32; clip i at d_in[h_in_offsets[i] .. + h_in_lengths[i]) -> d_out[h_out_offsets[i] ..)
+ * Only enqueues work on `stream` (after waiting for a previous afx_resample on the same handle).
+ */
+int64_t afx_resample_length(afx_handle_t h, int32_t native_sr, int64_t n_in);
+int afx_resample(afx_handle_t h, const float* d_in, const int64_t* h_in_offsets, const int32_t* h_in_lengths, int64_t n_clips,
+                 int32_t native_sr, float* d_out, const int64_t* h_out_offsets, void* stream);
+
+/*
  * Same computation from HOST memory (what a caller holding decoded files has): clips are staged
  * through pinned buffers, copied host->device in waves on a copy stream that overlaps the compute
  * stream, and the summaries / meta rows are copied back.  Blocks until the results are in

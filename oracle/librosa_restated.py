@@ -408,3 +408,22 @@ def pyin(y, fmin, fmax, sr=22050, frame_length=2048, hop_length=None, switch_pro
     if return_details:
         return f0, voiced_flag, voiced_prob, dict(yin=yin_frames, shifts=shifts, obs=obs, states=states, consts=c)
     return f0, voiced_flag, voiced_prob
+
+
+def resample_polyphase(y, orig_sr, target_sr):
+    """librosa.resample(y, orig_sr=, target_sr=, res_type='polyphase') (librosa 0.11 core/audio.py): scipy.signal.
+    resample_poly(y, target_sr // gcd, orig_sr // gcd) on the float32 signal, fixed to ceil(len * target / orig) samples.
+    Stands in for librosa.load's default 'soxr_hq' (the soxr C library, not restatable) on files whose rate != sr."""
+    import math
+    import scipy.signal
+    y = np.asarray(y, dtype=np.float32)
+    if int(orig_sr) == int(target_sr):
+        return y
+    g = math.gcd(int(orig_sr), int(target_sr))
+    out = scipy.signal.resample_poly(y, int(target_sr) // g, int(orig_sr) // g)
+    n = int(np.ceil(y.shape[-1] * float(target_sr) / float(orig_sr)))
+    if out.shape[-1] > n:
+        out = out[:n]
+    elif out.shape[-1] < n:
+        out = np.pad(out, (0, n - out.shape[-1]))
+    return np.asarray(out, dtype=np.float32)

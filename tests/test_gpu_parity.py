@@ -385,7 +385,8 @@ def test_framewise_npz_feature_set(torch_cuda, tmp_path):
 def test_batch_process_native_ingest_pcm16_and_mixed(torch_cuda, tmp_path):
     """batch_process through the native threaded WAV reader: a directory of 16-bit mono PCM files takes the raw-PCM
     path (converted on the device), a directory with another encoding the float32 path; both equal extract_features on
-    the same file, and unreadable / wrong-rate files are skipped (core/feature_extractor.py:233-235)."""
+    the same file; unreadable files are skipped (core/feature_extractor.py:233-235) and a file at another sample rate
+    is resampled on the device (librosa.load's resampling step, :52)."""
     from audio_feature_extraction_b200 import AudioFeatureExtractor
     from audio_feature_extraction_b200.synth import make_clip
     from audio_feature_extraction_b200.wav import write_wav
@@ -394,9 +395,9 @@ def test_batch_process_native_ingest_pcm16_and_mixed(torch_cuda, tmp_path):
     for i in range(5):
         write_wav(str(d16 / f"c{i}.wav"), make_clip(40 + i, seconds=1.0 + 0.3 * i), 22050, subtype="PCM_16")
     (d16 / "broken.wav").write_bytes(b"RIFF\x00\x00\x00\x00JUNK")
-    write_wav(str(d16 / "rate.wav"), make_clip(1, seconds=1.0), 16000, subtype="PCM_16")
+    write_wav(str(d16 / "rate.wav"), make_clip(1, sr=16000, seconds=1.0), 16000, subtype="PCM_16")
     res = ex.batch_process(str(d16), features_to_extract=["mfcc", "energy"])
-    assert sorted(r["file_path"].split("/")[-1] for r in res) == [f"c{i}.wav" for i in range(5)]
+    assert sorted(r["file_path"].split("/")[-1] for r in res) == [f"c{i}.wav" for i in range(5)] + ["rate.wav"]
     for r in res:
         one = ex.extract_features(r["file_path"], features_to_extract=["mfcc", "energy"])
         np.testing.assert_allclose(r["mfcc_mean"], one["mfcc_mean"], atol=1e-5)
@@ -464,3 +465,55 @@ def test_f0_postprocess_matches_scipy(torch_cuda):
         assert np.all(np.isnan(g[~voiced]))
         np.testing.assert_allclose(st[i], np.asarray(rst, dtype=np.float64), rtol=1e-6, equal_nan=True)
     assert tr[rows[15]:rows[15] + planted[15].size].max() <= np.float32(ex.f0_max)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("native_sr,target_sr", [(16000, 22050), (44100, 22050), (48000, 22050), (8000, 22050),
+                                                 (11025, 22050), (22050, 16000), (32000, 22050)])
+def test_resample_matches_scipy_resample_poly(torch_cuda, native_sr, target_sr):
+    """afx_resample against scipy.signal.resample_poly (= librosa.resample(res_type='polyphase'), the restatable
+    stand-in for librosa.load's soxr path, core/feature_extractor.py:52): same filter, same float32 operation order, so
+    the comparison is bit for bit; ragged lengths down to 0 and 1 samples."""
+    import torch
+    from audio_feature_extraction_b200 import AudioFeatureExtractor
+    from audio_feature_extraction_b200.synth import make_clip
+    from oracle import librosa_restated as LR
+    ex = AudioFeatureExtractor(sr=target_sr)
+    rng = np.random.default_rng(native_sr)
+    clips = [make_clip(90 + i, sr=native_sr, seconds=0.4 + 0.35 * i) for i in range(4)]
+    clips += [rng.standard_normal(n).astype(np.float32) * 0.2 for n in (0, 1, 2, 37, 1000)]
+    buf, offsets, lengths = ex.pack_clips(clips)
+    out, ooff, olen = ex.resample_batch_device(buf.to(torch.device("cuda", ex.device)), offsets, lengths, native_sr)
+    out = out.cpu().numpy()
+    for y, o, l in zip(clips, ooff, olen):
+        ref = LR.resample_polyphase(y, native_sr, target_sr)
+        assert int(l) == ref.shape[0] == int(np.ceil(y.shape[0] * target_sr / native_sr))     # lengths: bit-exact
+        np.testing.assert_array_equal(out[o:o + l], ref)
+
+
+@pytest.mark.gpu
+def test_load_audio_and_batch_process_resample_other_rates(torch_cuda, tmp_path):
+    """load_audio returns (y at self.sr, self.sr) for a file at another rate (reference :52 `librosa.load(path,
+    sr=self.sr)`), and batch_process on a mixed-rate directory equals the oracle on the resampled waveforms."""
+    from audio_feature_extraction_b200 import AudioFeatureExtractor
+    from audio_feature_extraction_b200.synth import make_clip
+    from audio_feature_extraction_b200.wav import write_wav
+    from oracle import OracleFeatureExtractor, librosa_restated as LR
+    ex, ora = AudioFeatureExtractor(), OracleFeatureExtractor()
+    specs = [("a.wav", 16000, "FLOAT"), ("b.wav", 22050, "PCM_16"), ("c.wav", 44100, "FLOAT"), ("d.wav", 48000, "PCM_16")]
+    waves = {}
+    for i, (name, sr, sub) in enumerate(specs):
+        y = make_clip(300 + i, sr=sr, seconds=1.5)
+        write_wav(str(tmp_path / name), y, sr, subtype=sub)
+        if sub == "PCM_16":
+            y = (np.clip(np.round(y * 32768.0), -32768, 32767) / 32768.0).astype(np.float32)
+        waves[name] = LR.resample_polyphase(y, sr, 22050)
+    y, sr = ex.load_audio(str(tmp_path / "a.wav"))
+    assert sr == 22050
+    np.testing.assert_array_equal(y, waves["a.wav"])
+    res = ex.batch_process(str(tmp_path), features_to_extract=["mfcc", "energy"])
+    assert len(res) == 4
+    for r in res:
+        ref = ora.extract_features_array(waves[r["file_path"].split("/")[-1]], features_to_extract=("mfcc", "energy"))
+        assert np.max(np.abs(np.asarray(r["mfcc_mean"]) - np.asarray(ref["mfcc_mean"]))) <= MFCC_ATOL
+        assert r["energy_mean"] == pytest.approx(ref["energy_mean"], rel=ENERGY_RTOL)
