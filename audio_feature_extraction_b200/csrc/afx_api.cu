@@ -26,6 +26,7 @@
 #include "afx_trim.cuh"
 #include "afx_wav.h"
 #include "afx_resample.cuh"
+#include "afx_dtw.cuh"
 
 namespace {
 
@@ -669,6 +670,8 @@ int afx_f0_postprocess(afx_handle_t h, int64_t n_clips, const int32_t* h_lengths
   return AFX_OK;
 }
 
+static int upload_small_header(afx_handle_t h, const void* host, size_t bytes, cudaStream_t stream);
+
 int64_t afx_resample_length(afx_handle_t h, int32_t native_sr, int64_t n_in) {
   if (!h || native_sr < 1 || n_in < 0) return -1;
   const int g = std::gcd(h->cfg.sr, native_sr);
@@ -707,13 +710,7 @@ int afx_resample(afx_handle_t h, const float* d_in, const int64_t* h_in_offsets,
     max_out = std::max(max_out, no);
   }
   if (max_out == 0) return AFX_OK;
-  if (h->d_rs_hdr_bytes < bytes) {
-    CUDA_TRY(cudaFree(h->d_rs_hdr)); h->d_rs_hdr = nullptr; h->d_rs_hdr_bytes = 0;
-    CUDA_TRY(cudaMalloc(&h->d_rs_hdr, bytes * 2));
-    h->d_rs_hdr_bytes = bytes * 2;
-  }
-  CUDA_TRY(cudaStreamSynchronize(stream));   // a previous call on this stream may still read the header
-  CUDA_TRY(cudaMemcpyAsync(h->d_rs_hdr, hdr.data(), bytes, cudaMemcpyHostToDevice, stream));
+  if (int rc = upload_small_header(h, hdr.data(), bytes, stream)) return rc;
   afx::ResampleArgs ra;
   ra.in = d_in; ra.out = d_out;
   ra.in_off = reinterpret_cast<const long long*>(h->d_rs_hdr);
@@ -727,6 +724,93 @@ int afx_resample(afx_handle_t h, const float* d_in, const int64_t* h_in_offsets,
     ra.clip0 = (int)c0;
     const unsigned gy = (unsigned)std::min<int64_t>(65535, n_clips - c0);
     afx::resample_kernel<<<dim3(gx, gy), afx::kResampleThreads, 0, stream>>>(ra);
+    ++g_launches;
+  }
+  CUDA_TRY(cudaGetLastError());
+  return AFX_OK;
+}
+
+// header arrays of the small batched entry points (afx_resample, afx_dtw_*): one handle-owned device buffer
+static int upload_small_header(afx_handle_t h, const void* host, size_t bytes, cudaStream_t stream) {
+  if (h->d_rs_hdr_bytes < bytes) {
+    CUDA_TRY(cudaFree(h->d_rs_hdr)); h->d_rs_hdr = nullptr; h->d_rs_hdr_bytes = 0;
+    CUDA_TRY(cudaMalloc(&h->d_rs_hdr, bytes * 2));
+    h->d_rs_hdr_bytes = bytes * 2;
+  }
+  CUDA_TRY(cudaStreamSynchronize(stream));   // a previous call on this stream may still read the header
+  CUDA_TRY(cudaMemcpyAsync(h->d_rs_hdr, host, bytes, cudaMemcpyHostToDevice, stream));
+  return AFX_OK;
+}
+
+int afx_dtw_frame_distance(afx_handle_t h, const double* d_x, const int64_t* h_x_off, const int32_t* h_n, const double* d_y,
+                           const int64_t* h_y_off, const int32_t* h_m, int32_t dim, int64_t n_pairs, double* d_D,
+                           const int64_t* h_D_off, void* stream_v) {
+  if (!h || !d_x || !d_y || !d_D || !h_x_off || !h_y_off || !h_D_off || !h_n || !h_m) return fail(AFX_ERR_INVALID_ARG, "afx_dtw_frame_distance: null argument");
+  if (dim < 1 || dim > 1024) return fail(AFX_ERR_INVALID_ARG, "afx_dtw_frame_distance: feature dimension %d out of range [1, 1024]", dim);
+  if (n_pairs < 0 || n_pairs > 0x7fffff00LL) return fail(AFX_ERR_INVALID_ARG, "afx_dtw_frame_distance: bad n_pairs");
+  if (n_pairs == 0) return AFX_OK;
+  CUDA_TRY(cudaSetDevice(h->cfg.device));
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_v);
+  const size_t n = (size_t)n_pairs, bytes = n * (3 * sizeof(long long) + 2 * sizeof(int));
+  std::vector<unsigned char> hdr(bytes);
+  long long* ho = reinterpret_cast<long long*>(hdr.data());
+  int* hl = reinterpret_cast<int*>(hdr.data() + 3 * n * sizeof(long long));
+  long long max_tiles = 0;
+  for (size_t i = 0; i < n; ++i) {
+    if (h_n[i] < 0 || h_m[i] < 0 || h_x_off[i] < 0 || h_y_off[i] < 0 || h_D_off[i] < 0) return fail(AFX_ERR_INVALID_ARG, "afx_dtw_frame_distance: pair %zu has a negative size or offset", i);
+    ho[i] = h_x_off[i]; ho[n + i] = h_y_off[i]; ho[2 * n + i] = h_D_off[i]; hl[i] = h_n[i]; hl[n + i] = h_m[i];
+    const long long ti = (h_n[i] + afx::kDtwTile - 1) / afx::kDtwTile, tj = (h_m[i] + afx::kDtwTile - 1) / afx::kDtwTile;
+    max_tiles = std::max(max_tiles, ti * tj);
+  }
+  if (max_tiles == 0) return AFX_OK;
+  if (int rc = upload_small_header(h, hdr.data(), bytes, stream)) return rc;
+  afx::DtwDistArgs da;
+  da.x = d_x; da.y = d_y; da.D = d_D;
+  da.x_off = reinterpret_cast<const long long*>(h->d_rs_hdr); da.y_off = da.x_off + n; da.D_off = da.y_off + n;
+  da.n = reinterpret_cast<const int*>(static_cast<const unsigned char*>(h->d_rs_hdr) + 3 * n * sizeof(long long)); da.m = da.n + n;
+  da.dim = dim;
+  const size_t smem = ((size_t)2 * afx::kDtwTile * (dim | 1) + 2 * afx::kDtwTile * 3) * sizeof(double);
+  CUDA_TRY(cudaFuncSetAttribute(afx::dtw_distance_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  // a few thousand CTAs in flight are plenty: the tiles of a pair are strided over gridDim.x
+  const unsigned gx = (unsigned)std::min<long long>(max_tiles, std::max<long long>(1, (long long)h->sm_count * 16 / std::min<int64_t>(n_pairs, 65535) + 1));
+  for (int64_t c0 = 0; c0 < n_pairs; c0 += 65535) {
+    da.pair0 = (int)c0;
+    const unsigned gy = (unsigned)std::min<int64_t>(65535, n_pairs - c0);
+    afx::dtw_distance_kernel<<<dim3(gx, gy), afx::kDtwDistThreads, smem, stream>>>(da);
+    ++g_launches;
+  }
+  CUDA_TRY(cudaGetLastError());
+  return AFX_OK;
+}
+
+int afx_dtw_accumulated_cost(afx_handle_t h, const double* d_D, const int64_t* h_D_off, const int32_t* h_n, const int32_t* h_m,
+                             int64_t n_pairs, double* d_A, void* stream_v) {
+  if (!h || !d_D || !d_A || !h_D_off || !h_n || !h_m) return fail(AFX_ERR_INVALID_ARG, "afx_dtw_accumulated_cost: null argument");
+  if (n_pairs < 0 || n_pairs > 0x7fffff00LL) return fail(AFX_ERR_INVALID_ARG, "afx_dtw_accumulated_cost: bad n_pairs");
+  if (n_pairs == 0) return AFX_OK;
+  CUDA_TRY(cudaSetDevice(h->cfg.device));
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_v);
+  const size_t n = (size_t)n_pairs, bytes = n * (sizeof(long long) + 2 * sizeof(int));
+  std::vector<unsigned char> hdr(bytes);
+  long long* ho = reinterpret_cast<long long*>(hdr.data());
+  int* hl = reinterpret_cast<int*>(hdr.data() + n * sizeof(long long));
+  int max_n = 0;
+  for (size_t i = 0; i < n; ++i) {
+    if (h_n[i] < 0 || h_m[i] < 0 || h_D_off[i] < 0) return fail(AFX_ERR_INVALID_ARG, "afx_dtw_accumulated_cost: pair %zu has a negative size or offset", i);
+    ho[i] = h_D_off[i]; hl[i] = h_n[i]; hl[n + i] = h_m[i];
+    max_n = std::max(max_n, h_n[i]);
+  }
+  if (int rc = upload_small_header(h, hdr.data(), bytes, stream)) return rc;
+  afx::DtwAccArgs aa;
+  aa.D = d_D; aa.A = d_A;
+  aa.D_off = reinterpret_cast<const long long*>(h->d_rs_hdr);
+  aa.n = reinterpret_cast<const int*>(static_cast<const unsigned char*>(h->d_rs_hdr) + n * sizeof(long long)); aa.m = aa.n + n;
+  for (int64_t c0 = 0; c0 < n_pairs; c0 += (1 << 30)) {
+    aa.pair0 = (int)c0;
+    const unsigned g = (unsigned)std::min<int64_t>(1 << 30, n_pairs - c0);
+    if (max_n <= 257) afx::dtw_accumulate_kernel<256><<<g, 256, 0, stream>>>(aa);
+    else if (max_n <= 513) afx::dtw_accumulate_kernel<512><<<g, 512, 0, stream>>>(aa);
+    else afx::dtw_accumulate_kernel<1024><<<g, 1024, 0, stream>>>(aa);
     ++g_launches;
   }
   CUDA_TRY(cudaGetLastError());

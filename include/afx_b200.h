@@ -173,6 +173,22 @@ int afx_resample(afx_handle_t h, const float* d_in, const int64_t* h_in_offsets,
                  int32_t native_sr, float* d_out, const int64_t* h_out_offsets, void* stream);
 
 /*
+ * DTW stage downstream of the extractor, batched over pairs of feature sequences, float64:
+ *   afx_dtw_frame_distance    FastDTWAligner.compute_distance_matrix, 05_dtw_alignment_experiment/dtw_alignment.py:532-552
+ *                             (0.6 euclid - 0.25 (1 + cos) cos - 0.15 (1 + |corr|) corr; without the serial positional
+ *                             penalties of _apply_local_constraints :559-668)
+ *   afx_dtw_accumulated_cost  FastDTWAligner._compute_accumulated_cost :930-969 (bit-exact operation order); the DTW
+ *                             distance of align_features :847 is the last element of each matrix
+ * Pair p: x rows at d_x[h_x_off[p] ..) as [h_n[p], dim] row-major, y at d_y[h_y_off[p] ..) as [h_m[p], dim], matrices
+ * at d_D / d_A[h_D_off[p] ..) as [h_n[p], h_m[p]] row-major (offsets in elements).  Only enqueue work on `stream`.
+ */
+int afx_dtw_frame_distance(afx_handle_t h, const double* d_x, const int64_t* h_x_off, const int32_t* h_n, const double* d_y,
+                           const int64_t* h_y_off, const int32_t* h_m, int32_t dim, int64_t n_pairs, double* d_D,
+                           const int64_t* h_D_off, void* stream);
+int afx_dtw_accumulated_cost(afx_handle_t h, const double* d_D, const int64_t* h_D_off, const int32_t* h_n, const int32_t* h_m,
+                             int64_t n_pairs, double* d_A, void* stream);
+
+/*
  * Same computation from HOST memory (what a caller holding decoded files has): clips are staged
  * through pinned buffers, copied host->device in waves on a copy stream that overlaps the compute
  * stream, and the summaries / meta rows are copied back.  Blocks until the results are in

@@ -20,3 +20,11 @@ def built_lib():
     g.build()
     from audio_feature_extraction_b200 import _native
     return _native.lib()
+
+
+@pytest.fixture(scope="module")
+def torch_cuda(built_lib):
+    import torch
+    if not torch.cuda.is_available():
+        pytest.fail("-m gpu tests need a CUDA device (there is no CPU fallback)")
+    return torch

@@ -14,14 +14,6 @@ ENERGY_RTOL = 1e-5    # "energy: within 1e-5 relative"
 GROUPS = ("mfcc", "energy")
 
 
-@pytest.fixture(scope="module")
-def torch_cuda(built_lib):
-    import torch
-    if not torch.cuda.is_available():
-        pytest.fail("-m gpu tests need a CUDA device (there is no CPU fallback)")
-    return torch
-
-
 def _framewise(ex, clips, groups=GROUPS):
     import torch
     buf, offsets, lengths = ex.pack_clips(clips)
