@@ -746,7 +746,7 @@ int afx_dtw_frame_distance(afx_handle_t h, const double* d_x, const int64_t* h_x
                            const int64_t* h_y_off, const int32_t* h_m, int32_t dim, int64_t n_pairs, double* d_D,
                            const int64_t* h_D_off, void* stream_v) {
   if (!h || !d_x || !d_y || !d_D || !h_x_off || !h_y_off || !h_D_off || !h_n || !h_m) return fail(AFX_ERR_INVALID_ARG, "afx_dtw_frame_distance: null argument");
-  if (dim < 1 || dim > 1024) return fail(AFX_ERR_INVALID_ARG, "afx_dtw_frame_distance: feature dimension %d out of range [1, 1024]", dim);
+  if (dim < 1 || dim > 200) return fail(AFX_ERR_INVALID_ARG, "afx_dtw_frame_distance: feature dimension %d out of range [1, 200]", dim);
   if (n_pairs < 0 || n_pairs > 0x7fffff00LL) return fail(AFX_ERR_INVALID_ARG, "afx_dtw_frame_distance: bad n_pairs");
   if (n_pairs == 0) return AFX_OK;
   CUDA_TRY(cudaSetDevice(h->cfg.device));
@@ -769,7 +769,9 @@ int afx_dtw_frame_distance(afx_handle_t h, const double* d_x, const int64_t* h_x
   da.x_off = reinterpret_cast<const long long*>(h->d_rs_hdr); da.y_off = da.x_off + n; da.D_off = da.y_off + n;
   da.n = reinterpret_cast<const int*>(static_cast<const unsigned char*>(h->d_rs_hdr) + 3 * n * sizeof(long long)); da.m = da.n + n;
   da.dim = dim;
-  const size_t smem = ((size_t)2 * afx::kDtwTile * (dim | 1) + 2 * afx::kDtwTile * 3) * sizeof(double);
+  int ld = (dim + 3) & ~3; while ((ld & 7) != 4) ld += 4;   // DMMA fragment reads (8 rows x 4 columns) hit distinct banks
+  da.ld = ld;
+  const size_t smem = ((size_t)2 * afx::kDtwTile * ld + 2 * afx::kDtwTile * 4) * sizeof(double);
   CUDA_TRY(cudaFuncSetAttribute(afx::dtw_distance_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   // a few thousand CTAs in flight are plenty: the tiles of a pair are strided over gridDim.x
   const unsigned gx = (unsigned)std::min<long long>(max_tiles, std::max<long long>(1, (long long)h->sm_count * 16 / std::min<int64_t>(n_pairs, 65535) + 1));
@@ -805,14 +807,12 @@ int afx_dtw_accumulated_cost(afx_handle_t h, const double* d_D, const int64_t* h
   aa.D = d_D; aa.A = d_A;
   aa.D_off = reinterpret_cast<const long long*>(h->d_rs_hdr);
   aa.n = reinterpret_cast<const int*>(static_cast<const unsigned char*>(h->d_rs_hdr) + n * sizeof(long long)); aa.m = aa.n + n;
-  for (int64_t c0 = 0; c0 < n_pairs; c0 += (1 << 30)) {
-    aa.pair0 = (int)c0;
-    const unsigned g = (unsigned)std::min<int64_t>(1 << 30, n_pairs - c0);
-    if (max_n <= 257) afx::dtw_accumulate_kernel<256><<<g, 256, 0, stream>>>(aa);
-    else if (max_n <= 513) afx::dtw_accumulate_kernel<512><<<g, 512, 0, stream>>>(aa);
-    else afx::dtw_accumulate_kernel<1024><<<g, 1024, 0, stream>>>(aa);
-    ++g_launches;
-  }
+  (void)max_n;
+  CUDA_TRY(cudaFuncSetAttribute(afx::dtw_accumulate_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, afx::kDtwAccSmem));
+  aa.pair0 = 0;
+  const unsigned g = (unsigned)((n_pairs + afx::kDtwAccWarps - 1) / afx::kDtwAccWarps);
+  afx::dtw_accumulate_kernel<<<g, afx::kDtwAccWarps * 32, afx::kDtwAccSmem, stream>>>(aa, (int)n_pairs);
+  ++g_launches;
   CUDA_TRY(cudaGetLastError());
   return AFX_OK;
 }

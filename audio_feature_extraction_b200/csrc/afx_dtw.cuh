@@ -1,6 +1,7 @@
 // DTW stage downstream of the extractor, batched over (teacher, student) pairs of feature sequences
 // (/root/reference/05_dtw_alignment_experiment/dtw_alignment.py):
 //   dtw_distance_kernel    :532-552  composite frame distance 0.6 euclid - 0.25 (1 + cos) cos - 0.15 (1 + |corr|) corr
+//                                    (one float64 tensor-core product per tile + a per-cell epilogue)
 //   dtw_accumulate_kernel  :930-969  accumulated cost, D + min(1.2 up, 0.8 diagonal, 1.2 left), weighted borders
 // float64 throughout, as numpy computes them.  The accumulated cost keeps the reference's operation order (no fused
 // multiply-add), so it is bit-exact; the distance sums over the feature dimension in index order (numpy's pairwise /
@@ -10,70 +11,113 @@
 
 namespace afx {
 
-constexpr int kDtwTile = 32;
-constexpr int kDtwDistThreads = 256;
+constexpr int kDtwTile = 64;            // output tile of one CTA: 64 x 64 cells, one 32 x 32 quadrant per warp
+constexpr int kDtwDistThreads = 128;
 
 struct DtwDistArgs {
   const double* x; const double* y; double* D;
   const long long* x_off; const long long* y_off; const long long* D_off;   // device [pairs], element offsets
   const int* n; const int* m;                                               // device [pairs]
-  int dim, pair0;
+  int dim, ld, pair0;                                                       // ld: shared-memory row pitch (doubles), ld % 8 == 4
 };
 
-// one CTA per 32 x 32 tile of one pair's matrix (blockIdx.y = pair, blockIdx.x strides over the tiles)
+// D = A * B + C on one 8 x 8 x 4 float64 tensor-core tile (DMMA): lane l holds A[l / 4][l % 4], B[l % 4][l / 4] and
+// C[l / 4][2 (l % 4) + {0, 1}]
+__device__ __forceinline__ void dmma884(double& c0, double& c1, double a, double b) {
+  asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0, %1}, {%2}, {%3}, {%0, %1};\n" : "+d"(c0), "+d"(c1) : "d"(a), "d"(b));
+}
+
+// One CTA per 64 x 64 tile of one pair's matrix (blockIdx.y = pair, blockIdx.x strides over the tiles).  The three sums
+// over the feature dimension collapse into ONE float64 matrix product on the tensor cores, cov = Xc Yc^T of the
+// mean-centred rows: dot = cov + dim mean_x mean_y, |x - y|^2 = |x|^2 + |y|^2 - 2 dot.  Where that difference cancels
+// (frames closer than 10 % of their norms: near-identical teacher / student frames) the cell recomputes sum (x - y)^2
+// directly from global memory, so an exactly equal pair of frames still gives exactly 0.
 __global__ void __launch_bounds__(kDtwDistThreads) dtw_distance_kernel(DtwDistArgs a) {
   extern __shared__ __align__(16) double dsm[];
-  const int dim = a.dim, ld = dim | 1;                       // odd leading dimension: conflict-free row reads
-  double* xs = dsm;                                           // [32][ld]
-  double* ys = xs + kDtwTile * ld;                            // [32][ld]
-  double* st = ys + kDtwTile * ld;                            // [64][3]: mean, |v|, sqrt(sum centred^2)
+  const int dim = a.dim, ld = a.ld;
+  double* xs = dsm;                                           // [64][ld] x rows (centred in place)
+  double* ys = xs + kDtwTile * ld;                            // [64][ld] y rows
+  double* st = ys + kDtwTile * ld;                            // [128][4]: mean, |v|^2, |v|, 1 / sqrt(sum centred^2)
   const int pair = a.pair0 + blockIdx.y;
   const int n = a.n[pair], m = a.m[pair];
   const double* __restrict__ X = a.x + a.x_off[pair];
   const double* __restrict__ Y = a.y + a.y_off[pair];
   double* __restrict__ D = a.D + a.D_off[pair];
   const int ti_n = (n + kDtwTile - 1) / kDtwTile, tj_n = (m + kDtwTile - 1) / kDtwTile;
-  const int tid = threadIdx.x, tx = tid & 31, ty = tid >> 5;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int ksteps = (dim + 3) >> 2;
   for (int tile = blockIdx.x; tile < ti_n * tj_n; tile += gridDim.x) {
     const int i0 = (tile / tj_n) * kDtwTile, j0 = (tile % tj_n) * kDtwTile;
     __syncthreads();
-    for (int e = tid; e < kDtwTile * dim; e += kDtwDistThreads) {
-      const int r = e / dim, k = e - r * dim;
-      xs[r * ld + k] = i0 + r < n ? X[(size_t)(i0 + r) * dim + k] : 0.0;
-      ys[r * ld + k] = j0 + r < m ? Y[(size_t)(j0 + r) * dim + k] : 0.0;
+    for (int e = tid; e < kDtwTile * ld; e += kDtwDistThreads) {
+      const int r = e / ld, k = e - r * ld;
+      xs[e] = (k < dim && i0 + r < n) ? X[(size_t)(i0 + r) * dim + k] : 0.0;
+      ys[e] = (k < dim && j0 + r < m) ? Y[(size_t)(j0 + r) * dim + k] : 0.0;
     }
     __syncthreads();
-    if (tid < 2 * kDtwTile) {                                // per-row statistics
-      const double* v = (tid < kDtwTile ? xs : ys) + (tid & (kDtwTile - 1)) * ld;
+    {                                                         // per-row statistics, rows centred in place
+      double* v = (tid < kDtwTile ? xs : ys) + (tid & (kDtwTile - 1)) * ld;
       double s = 0.0, q = 0.0;
       for (int k = 0; k < dim; ++k) { s += v[k]; q = fma(v[k], v[k], q); }
       const double mean = s / (double)dim;
       double c = 0.0;
-      for (int k = 0; k < dim; ++k) { const double d = v[k] - mean; c = fma(d, d, c); }
-      st[tid * 3 + 0] = mean; st[tid * 3 + 1] = sqrt(q); st[tid * 3 + 2] = sqrt(c);
+      for (int k = 0; k < dim; ++k) { const double d = v[k] - mean; v[k] = d; c = fma(d, d, c); }
+      st[tid * 4 + 0] = mean; st[tid * 4 + 1] = q; st[tid * 4 + 2] = sqrt(q); st[tid * 4 + 3] = 1.0 / sqrt(c);
     }
     __syncthreads();
-    const double* yv = ys + tx * ld;
-    const double my = st[(kDtwTile + tx) * 3], ny = st[(kDtwTile + tx) * 3 + 1], sy = st[(kDtwTile + tx) * 3 + 2];
+    // ---- cov = Xc Yc^T for this warp's 32 x 32 quadrant: 4 x 4 DMMA tiles, k in steps of 4
+    const int wi = (warp >> 1) * 32, wj = (warp & 1) * 32;
+    double acc[4][4][2];
 #pragma unroll
-    for (int u = 0; u < kDtwTile / 8; ++u) {
-      const int r = ty + 8 * u;
-      const double* xv = xs + r * ld;
-      const double mx = st[r * 3], nx = st[r * 3 + 1], sx = st[r * 3 + 2];
-      double e2 = 0.0, dot = 0.0, cov = 0.0;
-      for (int k = 0; k < dim; ++k) {
-        const double p = xv[k], q = yv[k], d = p - q;
-        e2 = fma(d, d, e2);
-        dot = fma(p, q, dot);
-        cov = fma(p - mx, q - my, cov);
+    for (int mb = 0; mb < 4; ++mb)
+#pragma unroll
+      for (int nb = 0; nb < 4; ++nb) acc[mb][nb][0] = acc[mb][nb][1] = 0.0;
+    const double* xa = xs + (wi + (lane >> 2)) * ld + (lane & 3);
+    const double* yb = ys + (wj + (lane >> 2)) * ld + (lane & 3);
+    for (int ks = 0; ks < ksteps; ++ks) {
+      double af[4], bf[4];
+#pragma unroll
+      for (int q = 0; q < 4; ++q) { af[q] = xa[q * 8 * ld + 4 * ks]; bf[q] = yb[q * 8 * ld + 4 * ks]; }
+#pragma unroll
+      for (int mb = 0; mb < 4; ++mb)
+#pragma unroll
+        for (int nb = 0; nb < 4; ++nb) dmma884(acc[mb][nb][0], acc[mb][nb][1], af[mb], bf[nb]);
+    }
+    // ---- epilogue: lane holds rows wi + 8 mb + lane / 4, columns wj + 8 nb + 2 (lane % 4) + {0, 1}
+#pragma unroll
+    for (int mb = 0; mb < 4; ++mb) {
+      const int r = wi + 8 * mb + (lane >> 2);
+      const double mx = st[r * 4], qx = st[r * 4 + 1], nx = st[r * 4 + 2], rsx = st[r * 4 + 3];
+#pragma unroll
+      for (int nb = 0; nb < 4; ++nb) {
+        double out[2];
+#pragma unroll
+        for (int e = 0; e < 2; ++e) {
+          const int c = wj + 8 * nb + 2 * (lane & 3) + e;
+          const double* sy = st + (kDtwTile + c) * 4;
+          const double cov = acc[mb][nb][e];
+          const double dot = fma((double)dim * mx, sy[0], cov);
+          double e2 = fma(-2.0, dot, qx + sy[1]);
+          if (e2 < 1e-2 * (qx + sy[1]) && i0 + r < n && j0 + c < m) {     // cancellation: sum the differences themselves
+            const double* xr = X + (size_t)(i0 + r) * dim;
+            const double* yr = Y + (size_t)(j0 + c) * dim;
+            e2 = 0.0;
+            for (int k = 0; k < dim; ++k) { const double d = xr[k] - yr[k]; e2 = fma(d, d, e2); }
+          }
+          const double cosv = dot * __drcp_rn(fma(nx, sy[2], 1e-8));
+          double corr = cov * rsx * sy[3];                    // np.corrcoef; 0 * inf = NaN for a constant frame, as 0 / 0 there
+          if (corr > 1.0) corr = 1.0;                         // np.clip keeps NaN, as these do
+          if (corr < -1.0) corr = -1.0;
+          const double w2 = 0.25 * (1.0 + cosv), w3 = 0.15 * (1.0 + fabs(corr));
+          out[e] = 0.6 * sqrt(fmax(e2, 0.0)) - w2 * cosv - w3 * corr;
+        }
+        const int c0 = j0 + wj + 8 * nb + 2 * (lane & 3);
+        if (i0 + r < n) {
+          double* dst = D + (size_t)(i0 + r) * m + c0;
+          if (c0 < m) dst[0] = out[0];
+          if (c0 + 1 < m) dst[1] = out[1];
+        }
       }
-      const double cosv = dot / (nx * ny + 1e-8);
-      double corr = cov / sx / sy;                            // np.corrcoef: one division per standard deviation
-      if (corr > 1.0) corr = 1.0;                             // np.clip keeps NaN (constant frame), as these do
-      if (corr < -1.0) corr = -1.0;
-      const double w2 = 0.25 * (1.0 + cosv), w3 = 0.15 * (1.0 + fabs(corr));
-      const double val = 0.6 * sqrt(e2) - w2 * cosv - w3 * corr;
-      if (i0 + r < n && j0 + tx < m) D[(size_t)(i0 + r) * m + j0 + tx] = val;
     }
   }
 }
@@ -94,64 +138,96 @@ __device__ __forceinline__ double dtw_step(double d, double up, double diag, dou
   return __dadd_rn(d, mn);
 }
 
-// one CTA per pair; strips of THREADS rows, thread r owns row s0 + r and walks the anti-diagonals: at step d it is at
-// column d - r + 1, takes `up` from the thread above (shared memory, written one step earlier), keeps `diag` and
-// `left` in registers.  One barrier per anti-diagonal.
-template <int THREADS>
-__global__ void __launch_bounds__(THREADS) dtw_accumulate_kernel(DtwAccArgs a) {
-  __shared__ double sh[2][THREADS];
-  const int pair = a.pair0 + blockIdx.x;
+// One WARP per pair.  The warp sweeps the matrix in bands of 32 rows; lane r owns row i0 + r and at step t sits at
+// column t - r (an anti-diagonal of the band), takes `up` from lane r - 1 by shuffle (the value that lane produced one
+// step earlier), keeps `diag` and `left` in registers: no barrier on the dependency chain.  D enters and A leaves
+// through a 3-slot ring of 32-column tiles in shared memory: cp.async fills tile cb + 1 while tile cb is walked, each
+// cell is overwritten in place by its accumulated cost and finished tiles are written back row by row (256-byte rows
+// both ways, where a lane-per-row walk of global memory would touch one sector per lane per step).  Row 0 of a tile
+// holds the boundary row A[i0 - 1] for lane 0.  The weighted borders (:936-945) are the i == 0 / j == 0 cases of the
+// same step, so the whole matrix is one sweep.
+constexpr int kDtwAccWarps = 4;
+constexpr int kDtwLd = 34;                                    // doubles per tile row: lane r at column s - r -> bank pairs all distinct
+constexpr int kDtwTileDoubles = 33 * kDtwLd;
+constexpr int kDtwAccSmem = kDtwAccWarps * 3 * kDtwTileDoubles * (int)sizeof(double);
+
+__device__ __forceinline__ void cp_async8(double* dst_smem, const double* src) {
+  const unsigned d = (unsigned)__cvta_generic_to_shared(dst_smem);
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 8;\n" ::"r"(d), "l"(src) : "memory");
+}
+
+__global__ void __launch_bounds__(kDtwAccWarps * 32) dtw_accumulate_kernel(DtwAccArgs a, int n_pairs) {
+  extern __shared__ __align__(16) double dtw_sm[];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int pair = a.pair0 + blockIdx.x * kDtwAccWarps + warp;
+  if (pair >= n_pairs) return;
   const int n = a.n[pair], m = a.m[pair];
   if (n <= 0 || m <= 0) return;
   const double* __restrict__ D = a.D + a.D_off[pair];
   double* A = a.A + a.D_off[pair];
-  const int tid = threadIdx.x;
-  // borders (:936-945): serial prefix sums with the 1 + 0.1 k weight; column 0 by warp 0, row 0 by warp 1
-  if (tid == 0) {
-    double acc = D[0];
-    A[0] = acc;
-    for (int i = 1; i < n; ++i) {
-      acc = __dadd_rn(acc, __dmul_rn(D[(size_t)i * m], __dadd_rn(1.0, __dmul_rn(0.1, (double)i))));
-      A[(size_t)i * m] = acc;
-    }
-  } else if (tid == 32) {
-    double acc = D[0];
-    for (int j = 1; j < m; ++j) {
-      acc = __dadd_rn(acc, __dmul_rn(D[j], __dadd_rn(1.0, __dmul_rn(0.1, (double)j))));
-      A[j] = acc;
-    }
-  }
-  __syncthreads();
-  for (int s0 = 1; s0 < n; s0 += THREADS) {
-    const int rows = min(THREADS, n - s0);
-    const int i = s0 + tid;
-    const bool mine = tid < rows;
-    const double* Drow = D + (size_t)i * m;
-    double* Arow = A + (size_t)i * m;
-    const double* Aup = A + (size_t)(i - 1) * m;              // read by thread 0 only: the finished row above the strip
-    double left = mine ? Arow[0] : 0.0;
-    double diag = mine ? Aup[0] : 0.0;
-    const int steps = (m - 1) + rows - 1;
-    double d_next = (mine && tid == 0 && m > 1) ? Drow[1] : 0.0;
-    double up_next = (mine && tid == 0 && m > 1) ? Aup[1] : 0.0;
-    for (int d = 0; d < steps; ++d) {
-      const int j = d - tid + 1;
-      const bool active = mine && j >= 1 && j < m;
-      const double dv = d_next, upg = up_next;
-      // prefetch the next step's operands off the dependency chain
-      const int jn = j + 1;
-      if (mine && jn >= 1 && jn < m) { d_next = Drow[jn]; if (tid == 0) up_next = Aup[jn]; }
-      if (active) {
-        const double up = tid == 0 ? upg : sh[(d + 1) & 1][tid - 1];
-        const double v = dtw_step(dv, up, diag, left);
-        Arow[j] = v;
-        sh[d & 1][tid] = v;
-        left = v; diag = up;
+  double* ring = dtw_sm + (size_t)warp * 3 * kDtwTileDoubles;
+  const int nb = (m + 31) >> 5;
+  for (int i0 = 0; i0 < n; i0 += 32) {
+    const int i = i0 + lane;
+    const bool row_ok = i < n;
+    const int rows = min(32, n - i0);
+    const double wi = __dadd_rn(1.0, __dmul_rn(0.1, (double)i));
+    double left = 0.0, diag = 0.0, v = 0.0;
+    // fill of tile cb: rows 1..rows from D, row 0 from the finished row above the band
+    auto fill = [&](int cb) {
+      double* tile = ring + (cb % 3) * kDtwTileDoubles;
+      const int j = (cb << 5) + lane;
+      if (cb < nb && j < m) {
+        if (i0 > 0) cp_async8(tile + lane, A + (size_t)(i0 - 1) * m + j);
+        for (int rr = 0; rr < rows; ++rr) cp_async8(tile + (rr + 1) * kDtwLd + lane, D + (size_t)(i0 + rr) * m + j);
       }
-      __syncthreads();
+      asm volatile("cp.async.commit_group;\n" ::: "memory");
+    };
+    __syncwarp();
+    fill(0);
+    for (int cb = 0; cb < nb + 2; ++cb) {
+      __syncwarp();
+      if (cb >= 2) {                                          // tile cb - 2 is complete: write it back
+        const double* tile = ring + ((cb - 2) % 3) * kDtwTileDoubles;
+        const int j = ((cb - 2) << 5) + lane;
+        if (j < m) for (int rr = 0; rr < rows; ++rr) A[(size_t)(i0 + rr) * m + j] = tile[(rr + 1) * kDtwLd + lane];
+      }
+      __syncwarp();
+      fill(cb + 1);                                           // into the slot just written back
+      asm volatile("cp.async.wait_group 1;\n" ::: "memory");  // tile cb has landed
+      __syncwarp();
+      if (cb >= nb + 1) continue;                             // only write-backs left
+#pragma unroll 4
+      for (int s = 0; s < 32; ++s) {
+        // branch-free step: the three border cases and the interior are selects around ONE add, so a warp whose lanes sit
+        // on different cases does not serialise the float64 chain
+        const int t = (cb << 5) + s, j = t - lane;
+        const double vup = __shfl_up_sync(0xffffffffu, v, 1);
+        const bool active = row_ok && j >= 0 && j < m;
+        const int jc = active ? j : 0;
+        double* tile = ring + ((jc >> 5) % 3) * kDtwTileDoubles;
+        const int c = jc & 31;
+        const double d = tile[(lane + 1) * kDtwLd + c];
+        const double up = lane == 0 ? tile[c] : vup;
+        const bool top = i == 0, border = top || j == 0;
+        // interior: min(up * 1.2, diag * 0.8, left * 1.2), first of equal / unordered values kept (Python's min):
+        // the two comparisons against up * 1.2 are independent, the third does not wait for the shuffle
+        const double u12 = __dmul_rn(up, 1.2), dg = __dmul_rn(diag, 0.8), hz = __dmul_rn(left, 1.2);
+        const double p = hz < dg ? hz : dg;
+        const double q = hz < u12 ? hz : u12;
+        const double mn = dg < u12 ? p : q;
+        // borders (:936-945): previous cell along the border + D * (1 + 0.1 k)
+        const double wj = __dadd_rn(1.0, __dmul_rn(0.1, (double)j));
+        const double base = top ? left : up;
+        const double dw = __dmul_rn(d, top ? wj : wi);
+        double nv = __dadd_rn(border ? base : d, border ? dw : mn);
+        if (top && j == 0) nv = d;
+        if (active) { tile[(lane + 1) * kDtwLd + c] = nv; v = nv; left = nv; diag = up; }
+      }
     }
+    asm volatile("cp.async.wait_group 0;\n" ::: "memory");
     __threadfence_block();
-    __syncthreads();   // the strip's last row is read from global memory by the next strip
+    __syncwarp();   // the band's last row is the next band's boundary row
   }
 }
 
