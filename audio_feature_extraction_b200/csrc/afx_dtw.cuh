@@ -27,6 +27,42 @@ __device__ __forceinline__ void dmma884(double& c0, double& c1, double a, double
   asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0, %1}, {%2}, {%3}, {%0, %1};\n" : "+d"(c0), "+d"(c1) : "d"(a), "d"(b));
 }
 
+// per-cell arithmetic of the distance on one lane's two accumulators of an 8 x 8 DMMA tile (kept out of line: 16 inlined
+// copies of the float64 sqrt / reciprocal sequences overflow the instruction cache)
+__device__ __noinline__ void dtw_distance_epilogue(double cov0, double cov1, const double* st, int r, int cl, int i0, int j0,
+                                                   int n, int m, int dim, const double* __restrict__ X,
+                                                   const double* __restrict__ Y, double* __restrict__ D) {
+  const double mx = st[r * 4], qx = st[r * 4 + 1], nx = st[r * 4 + 2], rsx = st[r * 4 + 3];
+  double out[2];
+#pragma unroll
+  for (int e = 0; e < 2; ++e) {
+    const int c = cl + e;
+    const double* sy = st + (kDtwTile + c) * 4;
+    const double cov = e ? cov1 : cov0;
+    const double dot = fma((double)dim * mx, sy[0], cov);
+    double e2 = fma(-2.0, dot, qx + sy[1]);
+    if (e2 < 1e-2 * (qx + sy[1]) && i0 + r < n && j0 + c < m) {     // cancellation: sum the differences themselves
+      const double* xr = X + (size_t)(i0 + r) * dim;
+      const double* yr = Y + (size_t)(j0 + c) * dim;
+      e2 = 0.0;
+#pragma unroll 1
+      for (int k = 0; k < dim; ++k) { const double d = xr[k] - yr[k]; e2 = fma(d, d, e2); }
+    }
+    const double cosv = dot * __drcp_rn(fma(nx, sy[2], 1e-8));
+    double corr = cov * rsx * sy[3];                    // np.corrcoef; 0 * inf = NaN for a constant frame, as 0 / 0 there
+    if (corr > 1.0) corr = 1.0;                         // np.clip keeps NaN, as these do
+    if (corr < -1.0) corr = -1.0;
+    const double w2 = 0.25 * (1.0 + cosv), w3 = 0.15 * (1.0 + fabs(corr));
+    out[e] = 0.6 * sqrt(fmax(e2, 0.0)) - w2 * cosv - w3 * corr;
+  }
+  const int c0 = j0 + cl;
+  if (i0 + r < n) {
+    double* dst = D + (size_t)(i0 + r) * m + c0;
+    if (c0 < m) dst[0] = out[0];
+    if (c0 + 1 < m) dst[1] = out[1];
+  }
+}
+
 // One CTA per 64 x 64 tile of one pair's matrix (blockIdx.y = pair, blockIdx.x strides over the tiles).  The three sums
 // over the feature dimension collapse into ONE float64 matrix product on the tensor cores, cov = Xc Yc^T of the
 // mean-centred rows: dot = cov + dim mean_x mean_y, |x - y|^2 = |x|^2 + |y|^2 - 2 dot.  Where that difference cancels
@@ -57,11 +93,28 @@ __global__ void __launch_bounds__(kDtwDistThreads) dtw_distance_kernel(DtwDistAr
     __syncthreads();
     {                                                         // per-row statistics, rows centred in place
       double* v = (tid < kDtwTile ? xs : ys) + (tid & (kDtwTile - 1)) * ld;
-      double s = 0.0, q = 0.0;
-      for (int k = 0; k < dim; ++k) { s += v[k]; q = fma(v[k], v[k], q); }
-      const double mean = s / (double)dim;
-      double c = 0.0;
-      for (int k = 0; k < dim; ++k) { const double d = v[k] - mean; v[k] = d; c = fma(d, d, c); }
+      // the row is zero beyond dim (ld is a multiple of 4): four independent chains per sum
+      double s4[4] = {0, 0, 0, 0}, q4[4] = {0, 0, 0, 0}, c4[4] = {0, 0, 0, 0};
+      const int k4 = (dim + 3) & ~3;
+      // each thread starts at its own column (rows are ld = 4 mod 8 doubles apart: the same column would be a 4-way
+      // bank conflict)
+      const int rot = (tid & 15) < k4 ? (tid & 15) : 0;
+      for (int kk = 0; kk < k4; kk += 4)
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          int k = kk + u + rot; k -= k >= k4 ? k4 : 0;
+          const double x = v[k]; s4[u] += x; q4[u] = fma(x, x, q4[u]);
+        }
+      const double mean = ((s4[0] + s4[1]) + (s4[2] + s4[3])) / (double)dim;
+      const double q = (q4[0] + q4[1]) + (q4[2] + q4[3]);
+      for (int kk = 0; kk < k4; kk += 4)
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          int k = kk + u + rot; k -= k >= k4 ? k4 : 0;
+          const double d = k < dim ? v[k] - mean : 0.0;
+          v[k] = d; c4[u] = fma(d, d, c4[u]);
+        }
+      const double c = (c4[0] + c4[1]) + (c4[2] + c4[3]);
       st[tid * 4 + 0] = mean; st[tid * 4 + 1] = q; st[tid * 4 + 2] = sqrt(q); st[tid * 4 + 3] = 1.0 / sqrt(c);
     }
     __syncthreads();
@@ -85,40 +138,11 @@ __global__ void __launch_bounds__(kDtwDistThreads) dtw_distance_kernel(DtwDistAr
     }
     // ---- epilogue: lane holds rows wi + 8 mb + lane / 4, columns wj + 8 nb + 2 (lane % 4) + {0, 1}
 #pragma unroll
-    for (int mb = 0; mb < 4; ++mb) {
-      const int r = wi + 8 * mb + (lane >> 2);
-      const double mx = st[r * 4], qx = st[r * 4 + 1], nx = st[r * 4 + 2], rsx = st[r * 4 + 3];
+    for (int mb = 0; mb < 4; ++mb)
 #pragma unroll
-      for (int nb = 0; nb < 4; ++nb) {
-        double out[2];
-#pragma unroll
-        for (int e = 0; e < 2; ++e) {
-          const int c = wj + 8 * nb + 2 * (lane & 3) + e;
-          const double* sy = st + (kDtwTile + c) * 4;
-          const double cov = acc[mb][nb][e];
-          const double dot = fma((double)dim * mx, sy[0], cov);
-          double e2 = fma(-2.0, dot, qx + sy[1]);
-          if (e2 < 1e-2 * (qx + sy[1]) && i0 + r < n && j0 + c < m) {     // cancellation: sum the differences themselves
-            const double* xr = X + (size_t)(i0 + r) * dim;
-            const double* yr = Y + (size_t)(j0 + c) * dim;
-            e2 = 0.0;
-            for (int k = 0; k < dim; ++k) { const double d = xr[k] - yr[k]; e2 = fma(d, d, e2); }
-          }
-          const double cosv = dot * __drcp_rn(fma(nx, sy[2], 1e-8));
-          double corr = cov * rsx * sy[3];                    // np.corrcoef; 0 * inf = NaN for a constant frame, as 0 / 0 there
-          if (corr > 1.0) corr = 1.0;                         // np.clip keeps NaN, as these do
-          if (corr < -1.0) corr = -1.0;
-          const double w2 = 0.25 * (1.0 + cosv), w3 = 0.15 * (1.0 + fabs(corr));
-          out[e] = 0.6 * sqrt(fmax(e2, 0.0)) - w2 * cosv - w3 * corr;
-        }
-        const int c0 = j0 + wj + 8 * nb + 2 * (lane & 3);
-        if (i0 + r < n) {
-          double* dst = D + (size_t)(i0 + r) * m + c0;
-          if (c0 < m) dst[0] = out[0];
-          if (c0 + 1 < m) dst[1] = out[1];
-        }
-      }
-    }
+      for (int nb = 0; nb < 4; ++nb)
+        dtw_distance_epilogue(acc[mb][nb][0], acc[mb][nb][1], st, wi + 8 * mb + (lane >> 2), wj + 8 * nb + 2 * (lane & 3),
+                              i0, j0, n, m, dim, X, Y, D);
   }
 }
 
