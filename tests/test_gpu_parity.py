@@ -509,3 +509,98 @@ def test_load_audio_and_batch_process_resample_other_rates(torch_cuda, tmp_path)
         ref = ora.extract_features_array(waves[r["file_path"].split("/")[-1]], features_to_extract=("mfcc", "energy"))
         assert np.max(np.abs(np.asarray(r["mfcc_mean"]) - np.asarray(ref["mfcc_mean"]))) <= MFCC_ATOL
         assert r["energy_mean"] == pytest.approx(ref["energy_mean"], rel=ENERGY_RTOL)
+
+
+def test_full_size_c2_batch_properties(torch_cuda):
+    """BASELINE.json configs[1] at its full size (10 000 clips x 10 s @ 22.05 kHz, 8.82 GB resident) through properties
+    that do not need the oracle at that size: the batch is 625 copies of 16 distinct clips, so (1) every copy must give
+    bit-identical rows wherever it sits in the batch and whichever CTA picks it up (a checksum of checksums), (2) the
+    rows equal those of the 16 clips extracted alone, which (3) match the oracle; (4) scaling the audio by 1/2 (exact in
+    binary floating point) halves the energy rows bit for bit, leaves the trim decisions and frame counts alone and
+    shifts MFCC 0 by sqrt(128) * 10 log10(1/4) with every other coefficient unchanged."""
+    import torch
+    from audio_feature_extraction_b200 import AudioFeatureExtractor
+    from audio_feature_extraction_b200.synth import make_clip
+    from oracle import OracleFeatureExtractor
+    ex = AudioFeatureExtractor()
+    n_base, copies, L = 16, 625, 220500
+    base = [make_clip(1000 + s, seconds=10.0) for s in range(n_base)]
+    assert all(b.shape[0] == L for b in base)
+    dev = torch.device("cuda", ex.device)
+    base_dev = torch.from_numpy(np.concatenate(base)).to(dev)
+    audio = torch.empty(n_base * copies * L + 8, dtype=torch.float32, device=dev)
+    audio[:n_base * copies * L].view(copies, n_base * L).copy_(base_dev.unsqueeze(0).expand(copies, -1))
+    n = n_base * copies
+    offsets = np.arange(n, dtype=np.int64) * L
+    lengths = np.full(n, L, dtype=np.int32)
+    groups = ("mfcc", "energy")
+    summ, meta, _ = ex.extract_batch_device(audio, offsets, lengths, groups)
+    torch.cuda.synchronize()
+    assert int(meta[:, 0].abs().max()) == 0
+    s3, m3 = summ.view(copies, n_base, -1), meta.view(copies, n_base, 4)
+    assert torch.equal(s3, s3[:1].expand_as(s3)) and torch.equal(m3, m3[:1].expand_as(m3))          # (1)
+    small_s, small_m, _ = ex.extract_batch_device(base_dev, offsets[:n_base], lengths[:n_base], groups)
+    assert torch.equal(small_s, s3[0]) and torch.equal(small_m, m3[0])                               # (2)
+    T = m3[0, :, 3].cpu().numpy()
+    trimmed = (m3[0, :, 2] - m3[0, :, 1]).cpu().numpy()
+    np.testing.assert_array_equal(T, 1 + trimmed // ex.hop_length)                                   # frame counts
+    ora = OracleFeatureExtractor()
+    rows = s3[0].cpu().numpy()
+    nm = ex.n_mfcc
+    for i in (0, 9):                                                                                 # (3)
+        ref = ora.extract_features_array(base[i], features_to_extract=groups)
+        assert np.max(np.abs(rows[i, 4:4 + nm] - np.asarray(ref["mfcc_mean"]))) <= MFCC_ATOL
+        assert np.max(np.abs(rows[i, 4 + nm:4 + 2 * nm] - np.asarray(ref["mfcc_std"]))) <= MFCC_ATOL
+        assert rows[i, 4 + 4 * nm] == pytest.approx(ref["energy_mean"], rel=ENERGY_RTOL)
+    audio.mul_(0.5)                                                                                  # (4)
+    summ2, meta2, _ = ex.extract_batch_device(audio, offsets, lengths, groups)
+    torch.cuda.synchronize()
+    assert torch.equal(meta2, meta)
+    e0 = 4 + 4 * nm
+    assert torch.equal(summ2[:, e0:e0 + 3], summ[:, e0:e0 + 3] * 0.5)
+    shift = float(np.sqrt(128.0) * 10.0 * np.log10(0.25))
+    d = (summ2[:, 4:4 + nm] - summ[:, 4:4 + nm]).cpu().numpy()
+    assert np.max(np.abs(d[:, 0] - shift)) <= MFCC_ATOL and np.max(np.abs(d[:, 1:])) <= MFCC_ATOL
+    dstd = (summ2[:, 4 + nm:4 + 4 * nm] - summ[:, 4 + nm:4 + 4 * nm]).abs().max().item()
+    assert dstd <= MFCC_ATOL
+
+
+@pytest.mark.parametrize("cfg,n_clips,kind,f_lo,f_hi", [
+    (dict(sr=16000, frame_length=512, hop_length=128, n_mfcc=40, extended_stats=True), 4096, "speech", 80.0, 400.0),  # C3
+    (dict(sr=44100, frame_length=2048, hop_length=512, n_mfcc=13), 2048, "music", 110.0, 880.0),                      # C4
+], ids=["C3-full", "C4-full"])
+def test_full_size_c3_c4_all_features_batch_invariance(torch_cuda, cfg, n_clips, kind, f_lo, f_hi):
+    """BASELINE.json configs[2] / configs[3] at SURVEY.md section 8(d)'s full sizes (4 096 x 10 s @ 16 kHz with the
+    skew / kurtosis extension and F0; 2 048 x 10 s @ 44.1 kHz, all features): the batch repeats 8 distinct clips, every
+    copy must produce bit-identical rows (pYIN, its chunked scratch and the Viterbi included) and those rows must equal
+    the 8 clips extracted alone; frame counts follow 1 + L / hop of the trimmed length."""
+    import torch
+    from audio_feature_extraction_b200 import AudioFeatureExtractor
+    from audio_feature_extraction_b200.synth import make_clip
+    ex = AudioFeatureExtractor(**cfg)
+    n_base = 8
+    copies = n_clips // n_base
+    base = [make_clip(2000 + s, sr=cfg["sr"], seconds=10.0, f_lo=f_lo, f_hi=f_hi, kind=kind) for s in range(n_base)]
+    L = base[0].shape[0]
+    assert L % 4 == 0 and all(b.shape[0] == L for b in base)
+    dev = torch.device("cuda", ex.device)
+    base_dev = torch.from_numpy(np.concatenate(base)).to(dev)
+    audio = torch.empty(n_clips * L + 8, dtype=torch.float32, device=dev)
+    audio[:n_clips * L].view(copies, n_base * L).copy_(base_dev.unsqueeze(0).expand(copies, -1))
+    offsets = np.arange(n_clips, dtype=np.int64) * L
+    lengths = np.full(n_clips, L, dtype=np.int32)
+    summ, meta, _ = ex.extract_batch_device(audio, offsets, lengths, None)
+    torch.cuda.synchronize()
+    assert int(meta[:, 0].abs().max()) == 0
+    s3, m3 = summ.view(copies, n_base, -1), meta.view(copies, n_base, 4)
+    same = (s3 == s3[:1]) | (torch.isnan(s3) & torch.isnan(s3[:1]))
+    assert bool(same.all()) and torch.equal(m3, m3[:1].expand_as(m3))
+    small_s, small_m, _ = ex.extract_batch_device(base_dev, offsets[:n_base], lengths[:n_base], None)
+    assert torch.equal(small_m, m3[0])
+    assert bool(((small_s == s3[0]) | (torch.isnan(small_s) & torch.isnan(s3[0]))).all())
+    T = m3[0, :, 3].cpu().numpy()
+    np.testing.assert_array_equal(T, 1 + (m3[0, :, 2] - m3[0, :, 1]).cpu().numpy() // ex.hop_length)
+    f0 = s3[0, :, 0].cpu().numpy()
+    # mean F0 inside [f0_min, f0_max], or 0 for a clip without a voiced frame (reference :103-107; the low-pitched
+    # speech-like clips at frame_length 512 and the three-note music clips are all-unvoiced for the oracle as well)
+    assert np.all(((f0 >= ex.f0_min) & (f0 <= ex.f0_max)) | (f0 == 0))
