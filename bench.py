@@ -56,52 +56,85 @@ def parse_args():
 
 # ----------------------------------------------------------------------------- clocks sampler
 class ClockSampler:
-    """nvidia-smi clocks + throttle reasons sampled every 200 ms while the timed region runs."""
-    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
-         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+    """SM clock, power and throttle reasons of one GPU polled through NVML every ~2 ms by a thread while the timed
+    region runs (the region is tens of milliseconds: an `nvidia-smi -lms` child process would deliver its first sample
+    after it has ended).  Only samples taken between mark_begin() and mark_end() are reported; nvidia-smi is the
+    fallback when the NVML binding is missing."""
+    REASONS = ((0x8, "hw_slowdown"), (0x40, "hw_thermal_slowdown"), (0x20, "sw_thermal_slowdown"), (0x4, "sw_power_cap"))
 
     def __init__(self, index: int):
         self.index = index
-        self.proc = None
-        self.lines = []
+        self.samples = []          # (t, sm_mhz, power_w, reasons bitmask)
+        self.t0 = self.t1 = None
+        self.stop_flag = threading.Event()
+        self.thread = None
+        self.sm_max = None
+        self.err = None
+
+    def _run(self):
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            visible = os.environ.get("CUDA_VISIBLE_DEVICES")
+            idx = self.index
+            if visible:   # NVML enumerates every GPU of the box, CUDA only the visible ones
+                ids = [v.strip() for v in visible.split(",") if v.strip()]
+                if idx < len(ids) and ids[idx].isdigit():
+                    idx = int(ids[idx])
+            h = pynvml.nvmlDeviceGetHandleByIndex(idx)
+            self.sm_max = float(pynvml.nvmlDeviceGetMaxClockInfo(h, pynvml.NVML_CLOCK_SM))
+            get_reasons = getattr(pynvml, "nvmlDeviceGetCurrentClocksEventReasons", None) or pynvml.nvmlDeviceGetCurrentClocksThrottleReasons
+            while not self.stop_flag.is_set():
+                try:
+                    sm = float(pynvml.nvmlDeviceGetClockInfo(h, pynvml.NVML_CLOCK_SM))
+                    pw = pynvml.nvmlDeviceGetPowerUsage(h) / 1000.0
+                    rs = int(get_reasons(h))
+                    self.samples.append((time.perf_counter(), sm, pw, rs))
+                except Exception as e:   # a single failed query: keep polling
+                    self.err = repr(e)
+                time.sleep(0.002)
+        except Exception as e:
+            self.err = repr(e)
 
     def start(self):
-        try:
-            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
-                                          "--format=csv,noheader,nounits", "-lms", "200"],
-                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
-            self.thread = threading.Thread(target=self._pump, daemon=True)
-            self.thread.start()
-        except Exception:
-            self.proc = None
+        self.thread = threading.Thread(target=self._run, daemon=True)
+        self.thread.start()
 
-    def _pump(self):
-        for ln in self.proc.stdout:
-            self.lines.append(ln.strip())
+    def mark_begin(self):
+        self.t0 = time.perf_counter()
+
+    def mark_end(self):
+        self.t1 = time.perf_counter()
 
     def stop(self):
-        if self.proc is None:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        self.proc.terminate()
+        self.stop_flag.set()
+        if self.thread is not None:
+            self.thread.join(timeout=5)
+        if not self.samples:
+            return self._smi_fallback()
+        t0 = self.t0 if self.t0 is not None else -1e30
+        t1 = self.t1 if self.t1 is not None else 1e30
+        inside = [x for x in self.samples if t0 <= x[0] <= t1] or self.samples[-1:]
+        bits = 0
+        for x in inside:
+            bits |= x[3]
+        return {"sm_mhz": float(np.median([x[1] for x in inside])), "sm_max_mhz": self.sm_max,
+                "power_w_max": max(x[2] for x in inside), "samples": len(inside),
+                "reasons": sorted(nm for b, nm in self.REASONS if bits & b), "source": "nvml, 2 ms poll inside the timed region"}
+
+    def _smi_fallback(self):
+        q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+             "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
         try:
-            self.proc.wait(timeout=5)
+            out = subprocess.run(["nvidia-smi", "-i", str(self.index), f"--query-gpu={q}", "--format=csv,noheader,nounits"],
+                                 capture_output=True, text=True, timeout=20).stdout.strip().splitlines()[0]
+            f = [x.strip() for x in out.split(",")]
+            names = ("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap")
+            return {"sm_mhz": float(f[0]), "sm_max_mhz": float(f[1]), "power_w_max": float(f[2]), "samples": 1,
+                    "reasons": sorted(nm for nm, v in zip(names, f[3:7]) if v.lower().startswith("active")),
+                    "source": "nvidia-smi after the timed region (NVML binding unavailable: %s)" % self.err}
         except Exception:
-            self.proc.kill()
-        sm, smax, reasons, power = [], [], set(), []
-        names = ("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap")
-        for ln in self.lines:
-            f = [x.strip() for x in ln.split(",")]
-            if len(f) < 7:
-                continue
-            try:
-                sm.append(float(f[0])); smax.append(float(f[1])); power.append(float(f[2]))
-            except ValueError:
-                continue
-            for nm, v in zip(names, f[3:7]):
-                if v.lower().startswith("active"):
-                    reasons.add(nm)
-        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(smax) if smax else None,
-                "power_w_max": max(power) if power else None, "samples": len(sm), "reasons": sorted(reasons)}
+            return {"sm_mhz": None, "sm_max_mhz": None, "samples": 0, "reasons": ["nvidia-smi unavailable"]}
 
 
 # ----------------------------------------------------------------------------- CPU (oracle) leg
@@ -276,22 +309,24 @@ def run_native(args):
             dist.barrier()
         torch.cuda.synchronize()
 
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()   # NVML comes up during the warm-up; only samples inside the timed region are reported
     for _ in range(args.warmup):
         step()
     barrier()
     L.afx_profile_read(h, None, None, 1)
     L.afx_profile_enable(h, 1)
     launches0 = L.afx_launch_count()
-    sampler = ClockSampler(local)
-    if rank == 0:
-        sampler.start()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
+    sampler.mark_begin()
     e0.record()
     for _ in range(args.steps):
         summ, meta = step()
     e1.record()
     barrier()
+    sampler.mark_end()
     ms_total = e0.elapsed_time(e1)
     clocks = sampler.stop() if rank == 0 else None
     launches = L.afx_launch_count() - launches0
