@@ -162,23 +162,26 @@ __device__ __forceinline__ double dtw_step(double d, double up, double diag, dou
   return __dadd_rn(d, mn);
 }
 
-// One WARP per pair.  The warp sweeps the matrix in bands of 32 rows; lane r owns row i0 + r and at step t sits at
-// column t - r (an anti-diagonal of the band), takes `up` from lane r - 1 by shuffle (the value that lane produced one
-// step earlier), keeps `diag` and `left` in registers: no barrier on the dependency chain.  D enters and A leaves
-// through a 3-slot ring of 32-column tiles in shared memory: cp.async fills tile cb + 1 while tile cb is walked, each
-// cell is overwritten in place by its accumulated cost and finished tiles are written back row by row (256-byte rows
-// both ways, where a lane-per-row walk of global memory would touch one sector per lane per step).  Row 0 of a tile
-// holds the boundary row A[i0 - 1] for lane 0.  The weighted borders (:936-945) are the i == 0 / j == 0 cases of the
-// same step, so the whole matrix is one sweep.
+// One WARP per pair.  Row 0 is a serial prefix (:942-945).  The rest of the matrix is swept in bands of 32 rows; lane r
+// owns row i0 + r and at step t sits at column t - r + 1 (an anti-diagonal of the band), takes `up` from lane r - 1 by
+// shuffle (the value that lane produced one step earlier) and keeps `diag` and `left` in registers: no barrier on the
+// dependency chain, and only the interior recurrence inside the loop (column 0, :936-940, is a 32-step prefix over
+// the lanes at the head of each band).  D enters and A leaves through a circular buffer of 96 columns per row in shared
+// memory: cp.async fills the 32-column block after the one lane 0 is in, each cell is overwritten in place by its
+// accumulated cost and finished blocks are written back row by row (256-byte rows both ways, where a lane-per-row walk of
+// global memory would touch one sector per lane per step).  Row 0 of the buffer holds the boundary row A[i0 - 1].
 constexpr int kDtwAccWarps = 4;
-constexpr int kDtwLd = 34;                                    // doubles per tile row: lane r at column s - r -> bank pairs all distinct
-constexpr int kDtwTileDoubles = 33 * kDtwLd;
-constexpr int kDtwAccSmem = kDtwAccWarps * 3 * kDtwTileDoubles * (int)sizeof(double);
+constexpr int kDtwRing = 96;                                  // columns in the circular buffer: blocks cb - 1, cb, cb + 1
+constexpr int kDtwLd = 98;                                    // doubles per buffer row: lane r at column c - r -> 97 r + c, distinct bank pairs
+constexpr int kDtwRingDoubles = 33 * kDtwLd;
+constexpr int kDtwAccSmem = kDtwAccWarps * kDtwRingDoubles * (int)sizeof(double);
 
 __device__ __forceinline__ void cp_async8(double* dst_smem, const double* src) {
   const unsigned d = (unsigned)__cvta_generic_to_shared(dst_smem);
   asm volatile("cp.async.ca.shared.global [%0], [%1], 8;\n" ::"r"(d), "l"(src) : "memory");
 }
+
+__device__ __forceinline__ double dtw_border_weight(int k) { return __dadd_rn(1.0, __dmul_rn(0.1, (double)k)); }
 
 __global__ void __launch_bounds__(kDtwAccWarps * 32) dtw_accumulate_kernel(DtwAccArgs a, int n_pairs) {
   extern __shared__ __align__(16) double dtw_sm[];
@@ -189,64 +192,98 @@ __global__ void __launch_bounds__(kDtwAccWarps * 32) dtw_accumulate_kernel(DtwAc
   if (n <= 0 || m <= 0) return;
   const double* __restrict__ D = a.D + a.D_off[pair];
   double* A = a.A + a.D_off[pair];
-  double* ring = dtw_sm + (size_t)warp * 3 * kDtwTileDoubles;
+  double* ring = dtw_sm + (size_t)warp * kDtwRingDoubles;
   const int nb = (m + 31) >> 5;
-  for (int i0 = 0; i0 < n; i0 += 32) {
+  // ---- row 0: A[0][j] = A[0][j - 1] + D[0][j] (1 + 0.1 j), additions strictly in column order
+  double carry = 0.0;
+  for (int j0 = 0; j0 < m; j0 += 32) {
+    const int j = j0 + lane;
+    double term = 0.0;
+    if (j < m) { const double d = D[j]; term = j == 0 ? d : __dmul_rn(d, dtw_border_weight(j)); }
+    double mine = 0.0;
+#pragma unroll 8
+    for (int l = 0; l < 32; ++l) {
+      const double tl = __shfl_sync(0xffffffffu, term, l);
+      carry = (j0 + l == 0) ? tl : __dadd_rn(carry, tl);
+      if (lane == l) mine = carry;
+    }
+    if (j < m) A[j] = mine;
+  }
+  double col0 = __shfl_sync(0xffffffffu, D[0], 0);            // A[i0 - 1][0] of the first band = A[0][0] = D[0][0]
+  __threadfence_block();
+  __syncwarp();
+  for (int i0 = 1; i0 < n; i0 += 32) {
     const int i = i0 + lane;
     const bool row_ok = i < n;
     const int rows = min(32, n - i0);
-    const double wi = __dadd_rn(1.0, __dmul_rn(0.1, (double)i));
-    double left = 0.0, diag = 0.0, v = 0.0;
-    // fill of tile cb: rows 1..rows from D, row 0 from the finished row above the band
-    auto fill = [&](int cb) {
-      double* tile = ring + (cb % 3) * kDtwTileDoubles;
+    // fill of block cb: buffer rows 1..rows from D, row 0 from the finished row above the band
+    auto fill = [&](int cb, int rc) {
       const int j = (cb << 5) + lane;
       if (cb < nb && j < m) {
-        if (i0 > 0) cp_async8(tile + lane, A + (size_t)(i0 - 1) * m + j);
-        for (int rr = 0; rr < rows; ++rr) cp_async8(tile + (rr + 1) * kDtwLd + lane, D + (size_t)(i0 + rr) * m + j);
+        double* dst = ring + rc + lane;
+        cp_async8(dst, A + (size_t)(i0 - 1) * m + j);
+        const double* src = D + (size_t)i0 * m + j;
+        for (int rr = 0; rr < rows; ++rr) { dst += kDtwLd; cp_async8(dst, src); src += m; }
       }
       asm volatile("cp.async.commit_group;\n" ::: "memory");
     };
+    fill(0, 0);
+    asm volatile("cp.async.wait_group 0;\n" ::: "memory");
     __syncwarp();
-    fill(0);
+    // ---- column 0 of the band: A[i][0] = A[i - 1][0] + D[i][0] (1 + 0.1 i), serial over the lanes
+    double left, diag;
+    {
+      const double term = row_ok ? __dmul_rn(ring[(lane + 1) * kDtwLd], dtw_border_weight(i)) : 0.0;
+      double mine = 0.0, acc = col0;
+#pragma unroll 8
+      for (int l = 0; l < 32; ++l) {
+        acc = __dadd_rn(acc, __shfl_sync(0xffffffffu, term, l));
+        if (lane == l) mine = acc;
+      }
+      const double above = __shfl_up_sync(0xffffffffu, mine, 1);
+      left = mine;
+      diag = lane == 0 ? col0 : above;
+      if (row_ok) ring[(lane + 1) * kDtwLd] = mine;
+      col0 = __shfl_sync(0xffffffffu, mine, rows - 1);        // boundary of the next band
+    }
+    __syncwarp();
+    double v = left;
+    int j = -lane;                                            // lane r's column at the step where lane 0 is at column 0
+    int jm = (kDtwRing - lane) % kDtwRing;                    // j mod 96
+    double* cell = ring + (lane + 1) * kDtwLd;                // this lane's buffer row
+    int rc_fill = 32, rc_back = 0;                            // buffer columns of block cb + 1 / block cb - 2
     for (int cb = 0; cb < nb + 2; ++cb) {
       __syncwarp();
-      if (cb >= 2) {                                          // tile cb - 2 is complete: write it back
-        const double* tile = ring + ((cb - 2) % 3) * kDtwTileDoubles;
-        const int j = ((cb - 2) << 5) + lane;
-        if (j < m) for (int rr = 0; rr < rows; ++rr) A[(size_t)(i0 + rr) * m + j] = tile[(rr + 1) * kDtwLd + lane];
+      if (cb >= 2) {                                          // block cb - 2 is complete: write it back
+        const int jb = ((cb - 2) << 5) + lane;
+        if (jb < m) {
+          const double* src = ring + kDtwLd + rc_back + lane;
+          double* dst = A + (size_t)i0 * m + jb;
+          for (int rr = 0; rr < rows; ++rr) { *dst = *src; src += kDtwLd; dst += m; }
+        }
+        rc_back = rc_back == 64 ? 0 : rc_back + 32;
       }
       __syncwarp();
-      fill(cb + 1);                                           // into the slot just written back
-      asm volatile("cp.async.wait_group 1;\n" ::: "memory");  // tile cb has landed
+      fill(cb + 1, rc_fill);                                  // into the columns just written back
+      rc_fill = rc_fill == 64 ? 0 : rc_fill + 32;
+      asm volatile("cp.async.wait_group 1;\n" ::: "memory");  // block cb has landed
       __syncwarp();
       if (cb >= nb + 1) continue;                             // only write-backs left
 #pragma unroll 4
       for (int s = 0; s < 32; ++s) {
-        // branch-free step: the three border cases and the interior are selects around ONE add, so a warp whose lanes sit
-        // on different cases does not serialise the float64 chain
-        const int t = (cb << 5) + s, j = t - lane;
         const double vup = __shfl_up_sync(0xffffffffu, v, 1);
-        const bool active = row_ok && j >= 0 && j < m;
-        const int jc = active ? j : 0;
-        double* tile = ring + ((jc >> 5) % 3) * kDtwTileDoubles;
-        const int c = jc & 31;
-        const double d = tile[(lane + 1) * kDtwLd + c];
-        const double up = lane == 0 ? tile[c] : vup;
-        const bool top = i == 0, border = top || j == 0;
-        // interior: min(up * 1.2, diag * 0.8, left * 1.2), first of equal / unordered values kept (Python's min):
-        // the two comparisons against up * 1.2 are independent, the third does not wait for the shuffle
+        const bool active = row_ok && j >= 1 && j < m;
+        const double d = cell[jm];
+        const double up = lane == 0 ? ring[jm] : vup;
+        // min(up * 1.2, diag * 0.8, left * 1.2), first of equal / unordered values kept (Python's min): the two comparisons
+        // against up * 1.2 are independent, the third does not wait for the shuffle
         const double u12 = __dmul_rn(up, 1.2), dg = __dmul_rn(diag, 0.8), hz = __dmul_rn(left, 1.2);
         const double p = hz < dg ? hz : dg;
         const double q = hz < u12 ? hz : u12;
-        const double mn = dg < u12 ? p : q;
-        // borders (:936-945): previous cell along the border + D * (1 + 0.1 k)
-        const double wj = __dadd_rn(1.0, __dmul_rn(0.1, (double)j));
-        const double base = top ? left : up;
-        const double dw = __dmul_rn(d, top ? wj : wi);
-        double nv = __dadd_rn(border ? base : d, border ? dw : mn);
-        if (top && j == 0) nv = d;
-        if (active) { tile[(lane + 1) * kDtwLd + c] = nv; v = nv; left = nv; diag = up; }
+        const double nv = __dadd_rn(d, dg < u12 ? p : q);
+        if (active) { cell[jm] = nv; v = nv; left = nv; diag = up; }
+        ++j;
+        jm = jm == kDtwRing - 1 ? 0 : jm + 1;
       }
     }
     asm volatile("cp.async.wait_group 0;\n" ::: "memory");

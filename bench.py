@@ -50,7 +50,7 @@ def parse_args():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-f0", action="store_true")
-    ap.add_argument("--f0-clips", type=int, default=1000, help="clips of the full-path (with pYIN) sample")
+    ap.add_argument("--f0-clips", type=int, default=2960, help="clips of the full-path (with pYIN) sample; 2960 = 4 resident waves of the Viterbi kernel (5 CTAs x 148 SMs)")
     return ap.parse_args()
 
 
