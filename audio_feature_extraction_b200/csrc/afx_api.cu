@@ -672,6 +672,19 @@ int afx_f0_postprocess(afx_handle_t h, int64_t n_clips, const int32_t* h_lengths
 
 static int upload_small_header(afx_handle_t h, const void* host, size_t bytes, cudaStream_t stream);
 
+int64_t afx_resample_filter(int32_t sr, int32_t native_sr, float* taps, int64_t taps_capacity, int32_t* up, int32_t* down,
+                            int32_t* taps_per_phase, int32_t* n_pre_remove) {
+  if (sr < 1 || native_sr < 1 || sr > (1 << 22) || native_sr > (1 << 22)) { fail(AFX_ERR_INVALID_ARG, "afx_resample_filter: bad sample rates %d, %d", sr, native_sr); return -1; }
+  const afx::ResampleFilter f = afx::design_resample_filter(sr, native_sr);
+  if (up) *up = f.up;
+  if (down) *down = f.down;
+  if (taps_per_phase) *taps_per_phase = f.J;
+  if (n_pre_remove) *n_pre_remove = f.n_pre_remove;
+  const int64_t count = (int64_t)f.taps.size();
+  if (taps && taps_capacity >= count) std::memcpy(taps, f.taps.data(), f.taps.size() * sizeof(float));
+  return count;
+}
+
 int64_t afx_resample_length(afx_handle_t h, int32_t native_sr, int64_t n_in) {
   if (!h || native_sr < 1 || n_in < 0) return -1;
   const int g = std::gcd(h->cfg.sr, native_sr);

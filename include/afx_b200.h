@@ -169,6 +169,11 @@ int afx_f0_postprocess(afx_handle_t h, int64_t n_clips, const int32_t* h_lengths
  * Only enqueues work on `stream` (after waiting for a previous afx_resample on the same handle).
  */
 int64_t afx_resample_length(afx_handle_t h, int32_t native_sr, int64_t n_in);
+/* host only (no device needed): the phase-ordered filter afx_resample uses for native_sr -> sr, taps[up][taps_per_phase] =
+ * h_padded[p + up * j] of scipy.signal.resample_poly's padded Kaiser design; returns up * taps_per_phase (-1 on bad
+ * arguments) and copies the taps when taps_capacity is large enough */
+int64_t afx_resample_filter(int32_t sr, int32_t native_sr, float* taps, int64_t taps_capacity, int32_t* up, int32_t* down,
+                            int32_t* taps_per_phase, int32_t* n_pre_remove);
 int afx_resample(afx_handle_t h, const float* d_in, const int64_t* h_in_offsets, const int32_t* h_in_lengths, int64_t n_clips,
                  int32_t native_sr, float* d_out, const int64_t* h_out_offsets, void* stream);
 

@@ -74,3 +74,28 @@ def test_raw_pcm16_delivery_and_its_guard(built_lib, wav_files):
     np.testing.assert_array_equal(out[:3001].astype(np.float32) / 32768.0, y)
     st = load_batch(paths[:1], [3000], np.zeros(3008, np.float32), [0])
     assert st.tolist() == [5]                                                              # length mismatch is reported
+
+
+@pytest.mark.parametrize("sr,native", [(22050, 16000), (22050, 44100), (22050, 48000), (22050, 8000), (16000, 22050), (22050, 11025)])
+def test_resample_filter_design_equals_scipy_firwin(built_lib, sr, native):
+    """The host half of afx_resample (no GPU needed): the phase-ordered Kaiser-sinc filter equals, bit for bit, what
+    scipy.signal.resample_poly builds (firwin(2 * 10 * max(up, down) + 1, 1 / max(up, down), window=('kaiser', 5.0)) cast
+    to float32, times up, zero-padded in front so that the output is centred)."""
+    import ctypes as C
+    import math
+    from scipy.signal import firwin
+    up, down, J, npr = C.c_int32(), C.c_int32(), C.c_int32(), C.c_int32()
+    count = built_lib.afx_resample_filter(sr, native, None, 0, C.byref(up), C.byref(down), C.byref(J), C.byref(npr))
+    g = math.gcd(sr, native)
+    assert (up.value, down.value) == (sr // g, native // g) and count == up.value * J.value
+    taps = np.zeros(count, dtype=np.float32)
+    assert built_lib.afx_resample_filter(sr, native, taps.ctypes.data, count, None, None, None, None) == count
+    mr = max(up.value, down.value)
+    half = 10 * mr
+    h = firwin(2 * half + 1, 1.0 / mr, window=("kaiser", 5.0)).astype(np.float32)
+    h *= up.value
+    n_pre_pad = down.value - half % down.value
+    assert npr.value == (half + n_pre_pad) // down.value
+    hp = np.concatenate([np.zeros(n_pre_pad, np.float32), h])
+    hp = np.concatenate([hp, np.zeros((-len(hp)) % up.value, np.float32)])
+    np.testing.assert_array_equal(taps.reshape(up.value, J.value), hp.reshape(-1, up.value).T)
