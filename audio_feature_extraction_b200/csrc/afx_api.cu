@@ -135,6 +135,16 @@ struct PhaseTimer {
   }
 };
 
+// The batch header travels from the pinned staging buffer to the workspace through a kernel that reads host memory
+// directly (unified addressing), not through a copy engine: on the host-buffer paths the host->device engine is busy
+// with the NEXT wave's samples, and a header memcpy queued behind that 100+ MB transfer delayed this wave's kernels until
+// the next wave had landed, which serialised compute with the copies.  Also zeroes the work counter.
+__global__ void header_fetch_kernel(int* __restrict__ dst, const int* __restrict__ src_host, long long words, int* __restrict__ counter) {
+  const long long i0 = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  for (long long i = i0; i < words; i += (long long)gridDim.x * blockDim.x) dst[i] = src_host[i];
+  if (i0 < 64) counter[i0] = 0;
+}
+
 struct Layout {   // carve-up of the caller's workspace
   size_t off_offsets, off_frame_off, off_lengths, off_yin_chunk, off_info, off_counter, header_bytes;
 };
@@ -435,9 +445,14 @@ int afx_extract(afx_handle_t h, const float* d_audio, const int64_t* h_offsets, 
     return fail(AFX_ERR_WORKSPACE, "afx_extract: workspace of %zu bytes is below afx_workspace_bytes", workspace_bytes);
   char* ws = static_cast<char*>(d_workspace);
   if ((reinterpret_cast<uintptr_t>(ws) & 255u) != 0) return fail(AFX_ERR_INVALID_ARG, "afx_extract: workspace must be 256-byte aligned");
-  CUDA_TRY(cudaMemcpyAsync(ws, st, staged_bytes, cudaMemcpyHostToDevice, stream));
+  {
+    const long long words = (long long)((staged_bytes + 3) / 4);
+    const int blocks = (int)std::min<long long>((words + 255) / 256, 4LL * h->sm_count);
+    header_fetch_kernel<<<std::max(blocks, 1), 256, 0, stream>>>(reinterpret_cast<int*>(ws), reinterpret_cast<const int*>(st), words,
+                                                                 reinterpret_cast<int*>(ws + L.off_counter));
+    ++g_launches;
+  }
   CUDA_TRY(cudaEventRecord(h->stage_ev, stream));
-  CUDA_TRY(cudaMemsetAsync(ws + L.off_counter, 0, 256, stream));
   const long long* d_offsets = reinterpret_cast<const long long*>(ws + L.off_offsets);
   const long long* d_frame_off = reinterpret_cast<const long long*>(ws + L.off_frame_off);
   const int* d_lengths = reinterpret_cast<const int*>(ws + L.off_lengths);

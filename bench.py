@@ -45,7 +45,7 @@ def parse_args():
     ap.add_argument("--config", default="c2", help="synth.CONFIGS key (c2 = the headline workload)")
     ap.add_argument("--clips", type=int, default=10000, help="clips per GPU")
     ap.add_argument("--features", default="mfcc,energy")
-    ap.add_argument("--e2e-clips", type=int, default=0, help="clips of the host-buffer (e2e) leg; 0 = clips/4")
+    ap.add_argument("--e2e-clips", type=int, default=0, help="clips of the host-buffer (e2e) leg; 0 = all clips on one GPU, clips/4 per rank otherwise")
     ap.add_argument("--cpu-clips", type=int, default=0, help="clips of the CPU baseline sample; 0 = auto")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
@@ -362,7 +362,7 @@ def run_native(args):
     # device; the float32-buffer variant is reported next to it.
     e2e = None
     if not args.no_e2e:
-        ne = args.e2e_clips or max(1, n // 4)
+        ne = args.e2e_clips or (n if world == 1 else max(1, n // 4))   # the whole workload on one GPU; a quarter per rank when 8 ranks pin host memory at once
         ne = min(ne, n)
         stride = int(offsets[1] - offsets[0]) if n > 1 else int(audio.numel())
         span = ne * stride
