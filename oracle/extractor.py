@@ -142,3 +142,14 @@ class OracleFeatureExtractor:
             local = float(np.sqrt(np.mean(np.diff(v) ** 2)))
         glob = float(np.sqrt(np.mean((v - np.mean(v)) ** 2)))
         return v, (float(np.mean(v)), glob, local, float(np.std(v) / (np.mean(v) + 1e-8)))
+
+
+def f0_track_task(task):
+    """(constructor kwargs, waveform) -> (f0, voiced_flag, voiced_prob) of the preprocessed waveform; a module-level
+    function so that multiprocessing pools (tools/f0_parity_sweep.py, tests) can ship it to worker processes."""
+    import os
+    for k in ("OMP_NUM_THREADS", "MKL_NUM_THREADS", "OPENBLAS_NUM_THREADS"):
+        os.environ[k] = "1"
+    cfg, y = task
+    ora = OracleFeatureExtractor(**cfg)
+    return ora.f0_track(ora.preprocess_audio(y))

@@ -604,3 +604,40 @@ def test_full_size_c3_c4_all_features_batch_invariance(torch_cuda, cfg, n_clips,
     # mean F0 inside [f0_min, f0_max], or 0 for a clip without a voiced frame (reference :103-107; the low-pitched
     # speech-like clips at frame_length 512 and the three-note music clips are all-unvoiced for the oracle as well)
     assert np.all(((f0 >= ex.f0_min) & (f0 <= ex.f0_max)) | (f0 == 0))
+
+
+@pytest.mark.parametrize("cfg,kind,f_lo,f_hi", [
+    (dict(sr=22050, frame_length=1024, hop_length=256, n_mfcc=13), "speech", 110.0, 880.0),    # C1 / C2
+    (dict(sr=16000, frame_length=512, hop_length=128, n_mfcc=40), "speech", 80.0, 400.0),      # C3
+    (dict(sr=44100, frame_length=2048, hop_length=512, n_mfcc=13), "music", 110.0, 880.0),     # C4
+], ids=["C2", "C3", "C4"])
+def test_parity_set_of_64_seeded_clips(torch_cuda, cfg, kind, f_lo, f_hi):
+    """SURVEY.md section 8(d)'s parity set: 64 clips per configuration, seeds 0 .. 63 (lengths 0.6 .. 5 s), compared with
+    the oracle stage by stage - trim indices and frame counts bit-exact, framewise MFCC / delta / delta2 within 1e-3,
+    RMS within 1e-5 relative, and the summary row."""
+    from audio_feature_extraction_b200 import AudioFeatureExtractor
+    from audio_feature_extraction_b200.synth import make_clip
+    from oracle import OracleFeatureExtractor
+    ex, ora = AudioFeatureExtractor(**cfg), OracleFeatureExtractor(**cfg)
+    rng = np.random.default_rng(64)
+    secs = np.round(rng.uniform(0.6, 5.0, size=64), 3)
+    clips = [make_clip(s, sr=cfg["sr"], seconds=float(sec), f_lo=f_lo, f_hi=f_hi, kind=kind) for s, sec in enumerate(secs)]
+    summ, meta, frames, rows = _framewise(ex, clips)
+    for i, y in enumerate(clips):
+        _check_clip(ex, ora, y, summ[i], meta[i], frames, rows[i], ex.n_mfcc)
+
+
+def test_pyin_parity_sweep_over_seeded_clips(torch_cuda):
+    """tools/f0_parity_sweep.py with 20 + 4 clips per configuration (C2, C3, C4 geometry; the oracle tracks are computed
+    on all host cores): BASELINE.json's F0 bar over a few thousand frames per configuration - voicing decisions equal on
+    >= 99.9 % of the frames, F0 within 1 cent wherever both are voiced.  The 64-clip run of the same tool is stored in
+    profiles/r01h_f0_parity_sweep.jsonl (100 % agreement, 1e-4 cents)."""
+    import importlib.util
+    from pathlib import Path
+    spec = importlib.util.spec_from_file_location("f0_parity_sweep", Path(__file__).resolve().parents[1] / "tools" / "f0_parity_sweep.py")
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    for res in mod.sweep(20):
+        assert res["voicing_agreement"] >= F0_VOICING, res
+        assert res["worst_cents"] <= F0_CENTS, res
+        assert res["frames"] > 1500
