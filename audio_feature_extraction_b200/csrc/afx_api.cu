@@ -747,11 +747,16 @@ int afx_resample(afx_handle_t h, const float* d_in, const int64_t* h_in_offsets,
   ra.out_len = ra.in_len + n;
   ra.taps = it->second.d_taps; ra.up = f.up; ra.down = f.down; ra.J = f.J; ra.n_pre_remove = f.n_pre_remove;
   const long long tile = afx::kResampleThreads * afx::kResamplePerThread;
-  const unsigned gx = (unsigned)std::min<long long>((max_out + tile - 1) / tile, 1 << 16);
+  const long long tiles = (max_out + tile - 1) / tile;
+  const unsigned gx = (unsigned)((tiles + afx::kResampleTilesPerCta - 1) / afx::kResampleTilesPerCta);
+  const size_t smem = (size_t)f.up * (f.J | 1) * sizeof(float);
+  const bool smem_taps = smem <= 200 * 1024;
+  if (smem_taps) CUDA_TRY(cudaFuncSetAttribute(afx::resample_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   for (int64_t c0 = 0; c0 < n_clips; c0 += 65535) {
     ra.clip0 = (int)c0;
     const unsigned gy = (unsigned)std::min<int64_t>(65535, n_clips - c0);
-    afx::resample_kernel<<<dim3(gx, gy), afx::kResampleThreads, 0, stream>>>(ra);
+    if (smem_taps) afx::resample_kernel<true><<<dim3(gx, gy), afx::kResampleThreads, smem, stream>>>(ra, (int)n_clips);
+    else afx::resample_kernel<false><<<dim3(gx, gy), afx::kResampleThreads, 0, stream>>>(ra, (int)n_clips);
     ++g_launches;
   }
   CUDA_TRY(cudaGetLastError());

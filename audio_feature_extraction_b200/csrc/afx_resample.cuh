@@ -20,6 +20,7 @@ namespace afx {
 
 constexpr int kResampleThreads = 256;
 constexpr int kResamplePerThread = 4;
+constexpr int kResampleTilesPerCta = 8;
 
 struct ResampleArgs {
   const float* in;
@@ -33,29 +34,49 @@ struct ResampleArgs {
   int clip0;
 };
 
-// one thread per output sample; products and sums rounded to float32 one by one, oldest input sample first, which is
-// the order of scipy's upfirdn inner loop
-__global__ void __launch_bounds__(kResampleThreads) resample_kernel(ResampleArgs a) {
-  const int clip = a.clip0 + blockIdx.y;
-  const int n_in = a.in_len[clip], n_out = a.out_len[clip];
-  const float* __restrict__ x = a.in + a.in_off[clip];
-  float* __restrict__ y = a.out + a.out_off[clip];
+// One thread per output sample; products and sums rounded to float32 one by one, oldest input sample first, which is
+// the order of scipy's upfirdn inner loop.  The phase table sits in shared memory (a row per phase, odd row length:
+// the lanes' rows fall on different banks; from global memory every lane's row would be its own cache line and a warp
+// load 32 wavefronts); a CTA loads it once for kResampleTilesPerCta consecutive tiles of 1024 outputs of clip blockIdx.y
+// (CTAs in launch order walk one clip after the other: neighbours in time are neighbours in memory).
+template <bool SMEM_TAPS>
+__global__ void __launch_bounds__(kResampleThreads) resample_kernel(ResampleArgs a, int n_clips) {
+  extern __shared__ float rs_taps[];
+  const int Jp = a.J | 1;                                   // padded row length in shared memory
+  if (SMEM_TAPS) {
+    for (int e = threadIdx.x; e < a.up * a.J; e += kResampleThreads) {
+      const int p = e / a.J, j = e - p * a.J;
+      rs_taps[p * Jp + j] = a.taps[e];
+    }
+    __syncthreads();
+  }
   const int tile = kResampleThreads * kResamplePerThread;
-  for (long long base = (long long)blockIdx.x * tile; base < n_out; base += (long long)gridDim.x * tile) {
+  {
+    const int clip = a.clip0 + blockIdx.y;
+    if (clip >= n_clips) return;
+    const int n_in = a.in_len[clip], n_out = a.out_len[clip];
+    if ((long long)blockIdx.x * kResampleTilesPerCta * tile >= n_out) return;
+    const float* __restrict__ x = a.in + a.in_off[clip];
+    float* __restrict__ y = a.out + a.out_off[clip];
+    for (int tt = 0; tt < kResampleTilesPerCta; ++tt) {
+      const long long base = ((long long)blockIdx.x * kResampleTilesPerCta + tt) * tile;
+      if (base >= n_out) break;
 #pragma unroll
-    for (int u = 0; u < kResamplePerThread; ++u) {
-      const long long n = base + u * kResampleThreads + threadIdx.x;
-      if (n >= n_out) continue;
-      const long long t = (n + a.n_pre_remove) * (long long)a.down;
-      const long long q = t / a.up;
-      const int p = (int)(t - q * a.up);
-      const float* __restrict__ w = a.taps + (size_t)p * a.J;
-      float acc = 0.f;
-      int j_hi = a.J - 1, j_lo = 0;
-      if (q - j_hi < 0) j_hi = (int)q;                         // x index >= 0
-      if (q >= n_in) j_lo = (int)(q - (n_in - 1));             // x index < n_in
-      for (int j = j_hi; j >= j_lo; --j) acc = __fadd_rn(acc, __fmul_rn(__ldg(x + (q - j)), __ldg(w + j)));
-      y[n] = acc;
+      for (int u = 0; u < kResamplePerThread; ++u) {
+        const long long n = base + u * kResampleThreads + threadIdx.x;
+        if (n >= n_out) continue;
+        const long long t = (n + a.n_pre_remove) * (long long)a.down;
+        const long long q = t / a.up;
+        const int p = (int)(t - q * a.up);
+        const float* __restrict__ w = SMEM_TAPS ? rs_taps + p * Jp : a.taps + (size_t)p * a.J;
+        float acc = 0.f;
+        int j_hi = a.J - 1, j_lo = 0;
+        if (q - j_hi < 0) j_hi = (int)q;                         // x index >= 0
+        if (q >= n_in) j_lo = (int)(q - (n_in - 1));             // x index < n_in
+        const float* xq = x + q;
+        for (int j = j_hi; j >= j_lo; --j) acc = __fadd_rn(acc, __fmul_rn(__ldg(xq - j), w[j]));
+        y[n] = acc;
+      }
     }
   }
 }
