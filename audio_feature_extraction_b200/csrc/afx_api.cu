@@ -611,7 +611,9 @@ int afx_frame_extras(afx_handle_t h, const float* d_audio, int64_t n_clips, cons
   ea.meta = d_meta; ea.frames = d_frames; ea.extras = d_extras;
   ea.frame_width = afx_frame_width(h); ea.n_mfcc = h->cfg.n_mfcc; ea.n_fft = h->cfg.frame_length; ea.hop = h->cfg.hop_length;
   ea.coef = h->cfg.pre_emphasis;
-  afx::frame_extras_kernel<<<(unsigned)n_clips, afx::kExtrasThreads, 0, static_cast<cudaStream_t>(stream_v)>>>(ea);
+  const int ex_smem = 2 * (afx::kExtrasMaxBlocks + 1) * (int)sizeof(int);
+  CUDA_TRY(cudaFuncSetAttribute(afx::frame_extras_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, ex_smem));
+  afx::frame_extras_kernel<<<(unsigned)n_clips, afx::kExtrasThreads, ex_smem, static_cast<cudaStream_t>(stream_v)>>>(ea);
   ++g_launches;
   CUDA_TRY(cudaGetLastError());
   return AFX_OK;

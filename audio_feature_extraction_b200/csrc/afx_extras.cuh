@@ -13,6 +13,8 @@
 namespace afx {
 
 constexpr int kExtrasThreads = 256;
+constexpr int kExtrasMaxBlocks = 2560;    // hop blocks whose crossing counts fit the shared-memory tables (2 ints each): 20 KB,
+                                          // 8 CTAs per SM; 29 s at hop 256 / 22.05 kHz, longer clips take the per-frame count
 constexpr int kExtrasWidth = 5;   // zcr, delta(zcr), delta(rms), delta(nan_to_num(f0)), short-time energy
 
 struct ExtrasArgs {
@@ -47,6 +49,58 @@ __global__ void __launch_bounds__(kExtrasThreads) frame_extras_kernel(ExtrasArgs
     if (fabsf(y) <= 1e-10f) y = 0.f;
     return signbit(y);
   };
+  // Zero crossings of frame t are the crossings of the sample pairs (i - 1, i), i = s + 1 .. s + n_fft - 1 (s = t hop -
+  // n_fft / 2; edge padding adds none).  Counted once per hop block - cin[b]: pairs inside block b, cb[b]: the pair
+  // across its lower border - a frame is the sum of its n_fft / hop blocks and of the borders between them: every sample
+  // is read once (one ballot per 32 samples) instead of once per frame it belongs to.
+  extern __shared__ int ex_cnt[];
+  const int nblk = (L + a.hop - 1) / a.hop;
+  if (nblk <= kExtrasMaxBlocks && (a.hop & 31) == 0) {
+    int* cin = ex_cnt;
+    int* cb = ex_cnt + nblk + 1;
+    for (int b = tid; b <= nblk; b += kExtrasThreads) { cin[b] = 0; cb[b] = 0; }
+    __syncthreads();
+    const int nwords = (L + 31) >> 5;
+    constexpr int NW = kExtrasThreads / 32, UN = 4;             // 4 words per warp in flight: the loads overlap
+    for (int w0 = warp; w0 < nwords; w0 += NW * UN) {
+      unsigned bits[UN], valid[UN]; bool below[UN];
+#pragma unroll
+      for (int u = 0; u < UN; ++u) {
+        const int w = w0 + u * NW;
+        const int i = 32 * w + lane;
+        const bool ok = w < nwords && i < L;
+        bits[u] = __ballot_sync(0xffffffffu, ok && neg(i));
+        valid[u] = __ballot_sync(0xffffffffu, ok);
+        below[u] = (w > 0 && w < nwords) ? neg(32 * w - 1) : false;
+      }
+#pragma unroll
+      for (int u = 0; u < UN; ++u) {
+        const int w = w0 + u * NW;
+        if (w >= nwords) break;
+        unsigned prev = bits[u] << 1;                             // sign of sample i - 1 at bit position i
+        prev |= w > 0 ? (below[u] ? 1u : 0u) : (bits[u] & 1u);    // sample 0 has no pair below it
+        const unsigned cross = (bits[u] ^ prev) & valid[u];
+        if (lane == 0) {
+          const int b = (32 * w) / a.hop;
+          const bool first = (32 * w) % a.hop == 0;               // bit 0 of a block's first word is its border pair
+          const int inner = __popc(first ? (cross & ~1u) : cross);
+          if (inner) atomicAdd(&cin[b], inner);
+          if (first && (cross & 1u)) cb[b] = 1;
+        }
+      }
+    }
+    __syncthreads();
+    const int K = a.n_fft / a.hop;
+    for (int t = tid; t < T; t += kExtrasThreads) {
+      const int b0 = t - K / 2;
+      int cnt = 0;
+      for (int k = 0; k < K; ++k) {
+        const int b = b0 + k;
+        if (b >= 0 && b < nblk) cnt += cin[b] + (k > 0 ? cb[b] : 0);
+      }
+      a.extras[(size_t)(row0 + t) * kExtrasWidth] = (float)cnt / (float)a.n_fft;
+    }
+  } else {
   for (int t = warp; t < T; t += kExtrasThreads / 32) {
     const int s = t * a.hop - a.n_fft / 2;
     int cnt = 0;
@@ -54,6 +108,7 @@ __global__ void __launch_bounds__(kExtrasThreads) frame_extras_kernel(ExtrasArgs
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
     if (lane == 0) a.extras[(size_t)(row0 + t) * kExtrasWidth] = (float)cnt / (float)a.n_fft;
+  }
   }
   __threadfence_block();
   __syncthreads();
