@@ -436,7 +436,7 @@ def run_native(args):
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f32", "data": "synthetic",
-            "config": {"workload": _workload_name(args, cfg, n), "clips_ok": ok, "l2": "inputs (8.8 GB/GPU) larger than L2, no flush",
+            "config": {"workload": _workload_name(args, cfg, n), "clips_ok": ok, "l2": "inputs (%.1f GB/GPU) larger than L2, no flush" % (audio.numel() * 4 / 1e9),
                        "sharding": f"clips by rank x{world}, NCCL gather of summary rows to rank 0 each step" if world > 1 else "single GPU"},
             "roofline": roofline, "cpu_baseline": cpu_baseline, "e2e": e2e, "f0_path": f0_path, "gpu_launches": int(launches), "clocks": clocks,
         }

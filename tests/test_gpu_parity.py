@@ -565,6 +565,39 @@ def test_full_size_c2_batch_properties(torch_cuda):
     assert dstd <= MFCC_ATOL
 
 
+def test_full_size_c5_shard_past_2_32_samples(torch_cuda):
+    """BASELINE.json configs[4]: 1000 audio-hours = 360 000 clips of C2 sharded by clip over 8 GPUs, i.e. 45 000 clips
+    (39.7 GB, 9.9e9 samples: more than 2^32, so every 32-bit sample index on the path would show) resident on ONE GPU.
+    The shard is 2 812 copies of 16 distinct clips + 8: every copy must give bit-identical rows wherever it sits, and the
+    rows of the clips extracted alone."""
+    import torch
+    from audio_feature_extraction_b200 import AudioFeatureExtractor
+    from audio_feature_extraction_b200.synth import make_clip
+    ex = AudioFeatureExtractor()
+    n_base, n, L = 16, 45000, 220500
+    dev = torch.device("cuda", ex.device)
+    free, _ = torch.cuda.mem_get_info(dev)
+    if free < 48 * 2 ** 30:
+        pytest.skip("needs 48 GB of free device memory")
+    base_dev = torch.from_numpy(np.concatenate([make_clip(1000 + s, seconds=10.0) for s in range(n_base)])).to(dev)
+    assert base_dev.numel() == n_base * L
+    audio = torch.empty(n * L + 8, dtype=torch.float32, device=dev)
+    copies, rest = divmod(n, n_base)
+    audio[:copies * n_base * L].view(copies, n_base * L).copy_(base_dev.unsqueeze(0).expand(copies, -1))
+    audio[copies * n_base * L:n * L].copy_(base_dev[:rest * L])
+    offsets = np.arange(n, dtype=np.int64) * L
+    lengths = np.full(n, L, dtype=np.int32)
+    groups = ("mfcc", "energy")
+    summ, meta, _ = ex.extract_batch_device(audio, offsets, lengths, groups)
+    torch.cuda.synchronize()
+    assert int(meta[:, 0].abs().max()) == 0
+    small_s, small_m, _ = ex.extract_batch_device(base_dev, offsets[:n_base], lengths[:n_base], groups)
+    idx = torch.arange(n, device=dev) % n_base
+    assert torch.equal(summ, small_s[idx]) and torch.equal(meta, small_m[idx])
+    del audio
+    torch.cuda.empty_cache()
+
+
 @pytest.mark.parametrize("cfg,n_clips,kind,f_lo,f_hi", [
     (dict(sr=16000, frame_length=512, hop_length=128, n_mfcc=40, extended_stats=True), 4096, "speech", 80.0, 400.0),  # C3
     (dict(sr=44100, frame_length=2048, hop_length=512, n_mfcc=13), 2048, "music", 110.0, 880.0),                      # C4
