@@ -13,7 +13,7 @@ from typing import Callable, List, Optional, Sequence, Tuple
 
 import numpy as np
 
-__all__ = ["shard_range", "gather_rows", "extract_sharded"]
+__all__ = ["shard_range", "gather_rows", "extract_sharded", "bind_host_to_gpu_node", "parse_cpulist"]
 
 
 def shard_range(n: int, rank: int, world: int) -> Tuple[int, int]:
@@ -62,3 +62,58 @@ def extract_sharded(extract_rows: Callable[[Sequence], Tuple["torch.Tensor", "to
     if world == 1:
         return summ, meta
     return gather_rows(summ, dst, group), gather_rows(meta, dst, group)
+
+
+def parse_cpulist(text: str) -> List[int]:
+    """'0-3,8,10-11' (the sysfs cpulist format) -> [0, 1, 2, 3, 8, 10, 11]"""
+    out: List[int] = []
+    for part in text.strip().split(","):
+        part = part.strip()
+        if not part:
+            continue
+        if "-" in part:
+            a, b = part.split("-", 1)
+            out.extend(range(int(a), int(b) + 1))
+        else:
+            out.append(int(part))
+    return out
+
+
+def bind_host_to_gpu_node(device_index: int, sysfs: str = "/sys") -> dict:
+    """Place this rank's host side next to its GPU: with one process per GPU on a multi-socket box, the pinned staging
+    buffers of the host path (afx_extract_host_packed) must live on the NUMA node the GPU's PCIe root hangs off, or half
+    the ranks pull their waves across the socket interconnect.  Sets the CPU affinity to that node's CPUs (when the
+    process is allowed any of them) and the memory policy to MPOL_PREFERRED(node) so that pinned allocations made
+    afterwards are node-local.  Call it BEFORE allocating pinned memory.  Returns what it found and did (never raises:
+    a box without NUMA information is left as it is)."""
+    import ctypes
+    import os
+    info = {"device": device_index, "node": None, "cpus_bound": None, "mempolicy": False}
+    try:
+        import torch
+        pr = torch.cuda.get_device_properties(device_index)
+        bdf = "%04x:%02x:%02x.0" % (pr.pci_domain_id, pr.pci_bus_id, pr.pci_device_id)
+        info["pci"] = bdf
+        with open(f"{sysfs}/bus/pci/devices/{bdf}/numa_node") as f:
+            node = int(f.read().strip())
+        info["node"] = node
+        if node < 0:
+            return info
+        with open(f"{sysfs}/devices/system/node/node{node}/cpulist") as f:
+            cpus = set(parse_cpulist(f.read()))
+        allowed = os.sched_getaffinity(0)
+        mine = sorted(cpus & allowed)
+        if mine:
+            os.sched_setaffinity(0, mine)
+            info["cpus_bound"] = len(mine)
+        libc = ctypes.CDLL(None, use_errno=True)
+        maxnode = 1024
+        mask = (ctypes.c_ulong * (maxnode // (8 * ctypes.sizeof(ctypes.c_ulong))))()
+        mask[node // (8 * ctypes.sizeof(ctypes.c_ulong))] = 1 << (node % (8 * ctypes.sizeof(ctypes.c_ulong)))
+        MPOL_PREFERRED, SYS_set_mempolicy = 1, 238   # x86_64
+        if os.uname().machine == "x86_64":
+            rc = libc.syscall(SYS_set_mempolicy, MPOL_PREFERRED, ctypes.byref(mask), maxnode)
+            info["mempolicy"] = rc == 0
+    except Exception as e:   # no sysfs entry, no NUMA, restricted container: stay as we are
+        info["error"] = repr(e)
+    return info

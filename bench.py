@@ -284,6 +284,11 @@ def run_native(args):
         raise SystemExit("bench.py (native arm) needs a CUDA device: there is no CPU fallback")
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
+    numa = None
+    if world > 1 and os.environ.get("AFX_NUMA_BIND", "1") != "0":   # before any pinned allocation
+        from audio_feature_extraction_b200.distributed import bind_host_to_gpu_node
+        numa = bind_host_to_gpu_node(local)
+        print(f"[bench] rank {rank}: {numa}", file=sys.stderr)
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
     L = N.lib()
@@ -399,7 +404,8 @@ def run_native(args):
         e2e = {"value": world * _hours(ne, cfg) * args.steps / dt16, "unit": UNIT,
                "h2d_bytes_per_step": int(2 * span), "d2h_bytes_per_step": int(ne * (4 * SS + 16)),
                "clips_per_gpu": ne, "clips_ok": ok16, "api": "afx_extract_host_packed (pinned 16-bit PCM host buffer, converted on the device)",
-               "float32_buffer": {"value": world * _hours(ne, cfg) * args.steps / dt32, "h2d_bytes_per_step": int(4 * span)}}
+               "float32_buffer": {"value": world * _hours(ne, cfg) * args.steps / dt32, "h2d_bytes_per_step": int(4 * span)},
+               "host_numa_binding": numa}
         del host16
 
     # ---- the full path with pYIN F0 on a bounded sample (compute-bound by construction; reported beside the headline)

@@ -62,3 +62,14 @@ def test_two_rank_gloo_gather_matches_single_process(tmp_path, n_items):
     mp.spawn(_worker, args=(2, port, n_items, str(out)), nprocs=2, join=True)
     res = torch.load(out)
     assert res["ok"] and res["rows"] == n_items
+
+
+def test_parse_cpulist_and_numa_binding_is_harmless_without_a_gpu():
+    from audio_feature_extraction_b200.distributed import bind_host_to_gpu_node, parse_cpulist
+    assert parse_cpulist("0-3,8,10-11\n") == [0, 1, 2, 3, 8, 10, 11]
+    assert parse_cpulist("") == [] and parse_cpulist("5") == [5]
+    import os
+    before = os.sched_getaffinity(0)
+    info = bind_host_to_gpu_node(0)          # no GPU / no sysfs entry here: reports, never raises, changes nothing
+    assert isinstance(info, dict) and info["device"] == 0
+    assert os.sched_getaffinity(0) == before or info.get("cpus_bound")
