@@ -178,7 +178,17 @@ inline bool single_pass(const afx_handle_s* h) { return afx::kTrimHop % h->cfg.h
 
 // the fused kernel is instantiated per (frame_length, hop_length): hop = frame_length / 2, / 4, / 8
 typedef void (*clip_fn_t)(afx::ClipArgs);
-clip_fn_t clip_kernel_for(int n_fft, int hop) {
+// stock: the mel tables have MelCnt<n_fft, true>'s run lengths -> the variant with the unrolled segment walk
+// (instantiated for the stock hop of each frame length: 1024/256, 512/128, 2048/512)
+template <int NFFT>
+bool mel_counts_are_stock(const afx::host::MelSparse& m) {
+  using MC = afx::MelCnt<NFFT, true>;
+  return m.cnt[0] == MC::c0 && m.cnt[1] == MC::c1 && m.cnt[2] == MC::c2 && m.cnt[3] == MC::c3 && m.cnt0 == MC::cz;
+}
+clip_fn_t clip_kernel_for(int n_fft, int hop, const afx::host::MelSparse& mel) {
+  if (n_fft == 1024 && hop == 256 && mel_counts_are_stock<1024>(mel)) return afx::clip_kernel<1024, 256, true>;
+  if (n_fft == 512 && hop == 128 && mel_counts_are_stock<512>(mel)) return afx::clip_kernel<512, 128, true>;
+  if (n_fft == 2048 && hop == 512 && mel_counts_are_stock<2048>(mel)) return afx::clip_kernel<2048, 512, true>;
   if (n_fft == 1024) {
     if (hop == 512) return afx::clip_kernel<1024, 512>;
     if (hop == 256) return afx::clip_kernel<1024, 256>;
@@ -235,7 +245,7 @@ int afx_create(const afx_config_t* cfg, afx_handle_t* out) {
     return fail(AFX_ERR_UNSUPPORTED, "frame_length %d not supported (512, 1024 or 2048)", cfg->frame_length);
   if (cfg->hop_length < 1 || cfg->hop_length > cfg->frame_length / 2)
     return fail(AFX_ERR_INVALID_ARG, "hop_length %d out of range [1, frame_length/2]", cfg->hop_length);
-  if (!clip_kernel_for(cfg->frame_length, cfg->hop_length))
+  if (!clip_kernel_for(cfg->frame_length, cfg->hop_length, afx::host::MelSparse{}))
     return fail(AFX_ERR_UNSUPPORTED, "frame_length %d / hop_length %d: this build has kernels for hop = frame_length/2, /4, /8",
                 cfg->frame_length, cfg->hop_length);
   if (cfg->n_mfcc < 1 || cfg->n_mfcc > afx::kMaxMfcc) return fail(AFX_ERR_INVALID_ARG, "n_mfcc %d out of range [1,64]", cfg->n_mfcc);
@@ -282,7 +292,7 @@ int afx_create(const afx_config_t* cfg, afx_handle_t* out) {
   h->tab.dct = nullptr;
 
   CUDA_TRY(cudaFuncSetAttribute(afx::trim_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-  h->clip_fn = clip_kernel_for(cfg->frame_length, cfg->hop_length);
+  h->clip_fn = clip_kernel_for(cfg->frame_length, cfg->hop_length, mel);
   // two 8-warp CTAs per SM (one clip each: the serial trim / fix-up / statistics phases of one hide behind the
   // streaming phase of the other) when their shared memory fits twice; else one 16-warp CTA
   {

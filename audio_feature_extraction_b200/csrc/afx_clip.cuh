@@ -50,7 +50,7 @@ __device__ __forceinline__ unsigned pair_copy_range(const Region& rg, int gA, in
 // f_begin + 2w, + 2*16, ...; no CTA-wide barrier inside.  own_sums: rg.origin == 0 and the hop-block sums are wanted.
 // floor_db: power_to_db clamp applied before the DCT (-3e38 = none, the speculative pass).  redo: only pairs whose
 // unclamped row minimum lies below floor_db are (re)computed -- the pass that makes the speculation exact.
-template <int NFFT, int HOP>
+template <int NFFT, int HOP, bool STOCK>
 __device__ __forceinline__ void stream_frames(const ClipArgs& a, const Smem& sm, const Slab& sl, WarpCtx& wc,
                                               const float* __restrict__ clip_audio, int L0, Region rg, int f_begin, int f_end,
                                               int row_shift, bool own_sums, float floor_db, bool redo, int& bad,
@@ -99,7 +99,7 @@ __device__ __forceinline__ void stream_frames(const ClipArgs& a, const Smem& sm,
     int g_lo = 0, s_lo = 0;
     if (fN < f_end) next_bytes = pair_copy_range(rg, gN, G::SPAN, L0, g_lo, s_lo);
     if (cur_bytes) { mbar_wait(wc.mbar, wc.parity); wc.parity ^= 1u; }
-    WarpStep<NFFT, HOP>::run(a, sm, sl, wc, rg, gA, L0, min(G::FPW, f_end - fA), row_shift + fA, own_sums, fA, floor_db,
+    WarpStep<NFFT, HOP>::template run<MelCnt<NFFT, STOCK>>(a, sm, sl, wc, rg, gA, L0, min(G::FPW, f_end - fA), row_shift + fA, own_sums, fA, floor_db,
                              next_bytes, clip_audio + g_lo, wc.raw + s_lo, bad);
     fA = fN; gA = gN; cur_bytes = next_bytes;
   }
@@ -253,7 +253,8 @@ __device__ __forceinline__ void mfcc_phase(const ClipArgs& a, const Slab& sl, in
 }
 
 // ---- the kernel
-template <int NFFT, int HOP>
+// STOCK: the mel tables carry the stock run lengths of this frame length (MelCnt<NFFT, true>), checked by the host
+template <int NFFT, int HOP, bool STOCK = false>
 __global__ void __launch_bounds__(kMaxClipThreads, 1) clip_kernel(ClipArgs a) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   // layout: [16 mbarriers 128B][twiddle 8KB][window NFFT*4][acc 6*64 doubles][red 64 doubles]
@@ -380,7 +381,7 @@ __global__ void __launch_bounds__(kMaxClipThreads, 1) clip_kernel(ClipArgs a) {
         }
       }
       const bool listed = pass == 3 && n_redo <= kMaxRedo;   // else (very long clips) every warp filters its own steps
-      stream_frames<NFFT, HOP>(a, sm, sl, wc, clip_audio, L0, rg, fb, fe, shift, own, floor_db, pass == 3, bad,
+      stream_frames<NFFT, HOP, STOCK>(a, sm, sl, wc, clip_audio, L0, rg, fb, fe, shift, own, floor_db, pass == 3, bad,
                                listed ? s_redo : nullptr, n_redo);
       if (pass == 0 && !a.pretrimmed) {
         if (bad) s_bad = 1;

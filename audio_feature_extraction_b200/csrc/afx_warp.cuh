@@ -133,9 +133,22 @@ __device__ __forceinline__ void fft512x2_core(c64 (&z)[32], const Smem& sm, floa
 
 __device__ __forceinline__ float to_db(float m) { return 3.0102999566398120f * __log2f(fmaxf(m, 1e-10f)); }   // 10 log10(max(1e-10, m))
 
+// Run lengths of the mel segment walk.  MelCnt<NFFT, false>: read from the tables (any sample rate).  MelCnt<NFFT, true>:
+// the stock pairing of this frame length (22.05 kHz / 1024, 16 kHz / 512, 44.1 kHz / 2048; the host checks that the
+// tables it built carry exactly these counts before it picks the variant): compile-time trip counts, the walk is
+// fully unrolled and every shared-memory offset becomes an immediate.
+template <int NFFT, bool STOCK> struct MelCnt { static constexpr bool kStatic = false; };
+template <> struct MelCnt<1024, true> { static constexpr bool kStatic = true; static constexpr int c0 = 2, c1 = 3, c2 = 6, c3 = 14, cz = 2; };
+template <> struct MelCnt<512, true>  { static constexpr bool kStatic = true; static constexpr int c0 = 1, c1 = 2, c2 = 3, c3 = 7, cz = 1; };
+template <> struct MelCnt<2048, true> { static constexpr bool kStatic = true; static constexpr int c0 = 2, c1 = 4, c2 = 12, c3 = 33, cz = 2; };
+template <typename MC> __device__ __forceinline__ constexpr int mel_cnt_static(int q) {
+  if constexpr (MC::kStatic) return q == 0 ? MC::c0 : q == 1 ? MC::c1 : q == 2 ? MC::c2 : MC::c3;
+  else return -1;
+}
+
 // Packed variant: NP pairs of frames per bin (power spectra stored as (frame 2p, frame 2p + 1) pairs): one FFMA2 per
 // (weight, pair).  d[2 p + h][q].
-template <int NP, typename LoadP>
+template <int NP, typename MC, typename LoadP>
 __device__ __forceinline__ void mel_db2(const ClipArgs& a, const Smem& sm, LoadP loadp, float (&d)[2 * NP][4], int lane) {
   const float2* mw = reinterpret_cast<const float2*>(sm.melw);
   c64 U[4][NP], D[4][NP];
@@ -145,25 +158,40 @@ __device__ __forceinline__ void mel_db2(const ClipArgs& a, const Smem& sm, LoadP
     for (int f = 0; f < NP; ++f) { U[q][f] = 0ull; D[q][f] = 0ull; }
     const int k0 = __ldg(a.tab.mel_k0 + 32 * q + lane);
     const float2* wq = mw + a.tab.mel_woff[q] + lane;
-    const int cnt = a.tab.mel_cnt[q];
-#pragma unroll 2
-    for (int i = 0; i < cnt; ++i) {
+    auto body = [&](int i) {
       const float2 w = wq[32 * i];
       c64 p[NP];
       loadp(k0 + i, p);
 #pragma unroll
       for (int f = 0; f < NP; ++f) { U[q][f] = fma2(p[f], bc2(w.x), U[q][f]); D[q][f] = fma2(p[f], bc2(w.y), D[q][f]); }
+    };
+    if constexpr (MC::kStatic) {
+      constexpr int kCnt[4] = {mel_cnt_static<MC>(0), mel_cnt_static<MC>(1), mel_cnt_static<MC>(2), mel_cnt_static<MC>(3)};
+#pragma unroll
+      for (int i = 0; i < kCnt[q]; ++i) body(i);
+    } else {
+      const int cnt = a.tab.mel_cnt[q];
+#pragma unroll 2
+      for (int i = 0; i < cnt; ++i) body(i);
     }
   }
   c64 u00[NP];   // segment 0: the bins below the first mel point rise into band 0
 #pragma unroll
   for (int f = 0; f < NP; ++f) u00[f] = 0ull;
-  for (int i = 0; i < a.tab.mel_cnt0; ++i) {
-    const float w = mw[a.tab.mel_woff0 + i].x;
-    c64 p[NP];
-    loadp(a.tab.mel_k00 + i, p);
+  {
+    auto body0 = [&](int i) {
+      const float w = mw[a.tab.mel_woff0 + i].x;
+      c64 p[NP];
+      loadp(a.tab.mel_k00 + i, p);
 #pragma unroll
-    for (int f = 0; f < NP; ++f) u00[f] = fma2(p[f], bc2(w), u00[f]);
+      for (int f = 0; f < NP; ++f) u00[f] = fma2(p[f], bc2(w), u00[f]);
+    };
+    if constexpr (MC::kStatic) {
+#pragma unroll
+      for (int i = 0; i < MC::cz; ++i) body0(i);
+    } else {
+      for (int i = 0; i < a.tab.mel_cnt0; ++i) body0(i);
+    }
   }
 #pragma unroll
   for (int f = 0; f < NP; ++f) {
@@ -228,7 +256,7 @@ __device__ __forceinline__ void dct_pair(const ClipArgs& a, const Smem& sm, cons
 // rising side U (band + 1's weights) and the falling side D (its own band's weights); the band value is D + the U of
 // the lane that owns the band below.  loadp(k, p) fetches the NF power values of bin k.  d[f][q] = 10 log10 of band
 // mel_band_of(q, lane): q0 = lane, q1 = 63 - lane, q2 = 64 + lane, q3 = 127 - lane.
-template <int NF, typename LoadP>
+template <int NF, typename MC, typename LoadP>
 __device__ __forceinline__ void mel_db(const ClipArgs& a, const Smem& sm, LoadP loadp, float (&d)[NF][4], int lane) {
   const float2* mw = reinterpret_cast<const float2*>(sm.melw);
   float U[4][NF], D[4][NF];
@@ -238,25 +266,40 @@ __device__ __forceinline__ void mel_db(const ClipArgs& a, const Smem& sm, LoadP 
     for (int f = 0; f < NF; ++f) { U[q][f] = 0.f; D[q][f] = 0.f; }
     const int k0 = __ldg(a.tab.mel_k0 + 32 * q + lane);
     const float2* wq = mw + a.tab.mel_woff[q] + lane;
-    const int cnt = a.tab.mel_cnt[q];
-#pragma unroll 2
-    for (int i = 0; i < cnt; ++i) {
+    auto body = [&](int i) {
       const float2 w = wq[32 * i];
       float p[NF];
       loadp(k0 + i, p);
 #pragma unroll
       for (int f = 0; f < NF; ++f) { U[q][f] = fmaf(w.x, p[f], U[q][f]); D[q][f] = fmaf(w.y, p[f], D[q][f]); }
+    };
+    if constexpr (MC::kStatic) {
+      constexpr int kCnt[4] = {mel_cnt_static<MC>(0), mel_cnt_static<MC>(1), mel_cnt_static<MC>(2), mel_cnt_static<MC>(3)};
+#pragma unroll
+      for (int i = 0; i < kCnt[q]; ++i) body(i);
+    } else {
+      const int cnt = a.tab.mel_cnt[q];
+#pragma unroll 2
+      for (int i = 0; i < cnt; ++i) body(i);
     }
   }
   float u00[NF];   // segment 0: the bins below the first mel point rise into band 0
 #pragma unroll
   for (int f = 0; f < NF; ++f) u00[f] = 0.f;
-  for (int i = 0; i < a.tab.mel_cnt0; ++i) {
-    const float w = mw[a.tab.mel_woff0 + i].x;
-    float p[NF];
-    loadp(a.tab.mel_k00 + i, p);
+  {
+    auto body0 = [&](int i) {
+      const float w = mw[a.tab.mel_woff0 + i].x;
+      float p[NF];
+      loadp(a.tab.mel_k00 + i, p);
 #pragma unroll
-    for (int f = 0; f < NF; ++f) u00[f] = fmaf(w, p[f], u00[f]);
+      for (int f = 0; f < NF; ++f) u00[f] = fmaf(w, p[f], u00[f]);
+    };
+    if constexpr (MC::kStatic) {
+#pragma unroll
+      for (int i = 0; i < MC::cz; ++i) body0(i);
+    } else {
+      for (int i = 0; i < a.tab.mel_cnt0; ++i) body0(i);
+    }
   }
 #pragma unroll
   for (int f = 0; f < NF; ++f) {
@@ -366,6 +409,7 @@ struct WarpStep<1024, HOP> {
       if (n1 >= SH) im[bitrev32(n1 - SH)] = sm.win[32 * (n1 - SH) + lane] * y;
     }
   }
+  template <typename MC>
   static __device__ __forceinline__ void run(const ClipArgs& a, const Smem& sm, const Slab& sl, WarpCtx& wc, const Region& rg,
                                              int gA, int L0, int nv, int row, bool own_sums, int usum_idx, float floor_db,
                                              unsigned next_bytes, const float* next_src, float* next_dst, int& bad) {
@@ -401,7 +445,7 @@ struct WarpStep<1024, HOP> {
     __syncwarp();
     // sparse mel by segments, 10 log10
     float d[2][4];
-    mel_db2<1>(a, sm, [P2](int k, c64 (&p)[1]) { p[0] = P2[k]; }, d, lane);
+    mel_db2<1, MC>(a, sm, [P2](int k, c64 (&p)[1]) { p[0] = P2[k]; }, d, lane);
     __syncwarp();   // P2 consumed: the plane is free for the DCT reduction
     finish_step<1024, HOP>(a, sm, sl, wc, d, eg, nv, row, own_sums, usum_idx, floor_db, lane, bad);
   }
@@ -432,6 +476,7 @@ struct WarpStep<512, HOP> {
       }
     }
   }
+  template <typename MC>
   static __device__ __forceinline__ void run(const ClipArgs& a, const Smem& sm, const Slab& sl, WarpCtx& wc, const Region& rg,
                                              int gA, int L0, int nv, int row, bool own_sums, int usum_idx, float floor_db,
                                              unsigned next_bytes, const float* next_src, float* next_dst, int& bad) {
@@ -467,7 +512,7 @@ struct WarpStep<512, HOP> {
     }
     __syncwarp();
     float d[4][4];
-    mel_db2<2>(a, sm, [P2](int k, c64 (&p)[2]) { p[0] = P2[k]; p[1] = P2[PSTRIDE + k]; }, d, lane);
+    mel_db2<2, MC>(a, sm, [P2](int k, c64 (&p)[2]) { p[0] = P2[k]; p[1] = P2[PSTRIDE + k]; }, d, lane);
     __syncwarp();
     finish_step<512, HOP>(a, sm, sl, wc, d, eg, nv, row, own_sums, usum_idx, floor_db, lane, bad);
   }
@@ -501,6 +546,7 @@ struct WarpStep<2048, HOP> {
       im[bitrev32(n1)] = w.y * y1;
     }
   }
+  template <typename MC>
   static __device__ __forceinline__ void run(const ClipArgs& a, const Smem& sm, const Slab& sl, WarpCtx& wc, const Region& rg,
                                              int gA, int L0, int nv, int row, bool own_sums, int usum_idx, float floor_db,
                                              unsigned next_bytes, const float* next_src, float* next_dst, int& bad) {
@@ -539,7 +585,7 @@ struct WarpStep<2048, HOP> {
     }
     __syncwarp();
     float d[1][4];
-    mel_db<1>(a, sm, [P](int k, float (&p)[1]) { p[0] = P[k]; }, d, lane);
+    mel_db<1, MC>(a, sm, [P](int k, float (&p)[1]) { p[0] = P[k]; }, d, lane);
     __syncwarp();
     finish_step<2048, HOP>(a, sm, sl, wc, d, eg, nv, row, own_sums, usum_idx, floor_db, lane, bad);
   }
