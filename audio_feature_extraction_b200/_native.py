@@ -23,6 +23,7 @@ EXPORTS = [
     "afx_summary_width", "afx_frame_width", "afx_max_frames", "afx_workspace_bytes",
     "afx_workspace_min_bytes", "afx_extract", "afx_extract_host", "afx_extract_host_packed",
     "afx_launch_count", "afx_profile_enable", "afx_profile_read", "afx_preprocess", "afx_frame_extras", "afx_wav_probe_batch", "afx_wav_load_batch", "afx_f0_postprocess", "afx_resample_length", "afx_resample_filter", "afx_resample", "afx_dtw_frame_distance", "afx_dtw_accumulated_cost",
+    "afx_clip_kernel_variant",
 ]
 PHASES = ("trim", "frames", "mfcc", "finalize", "pcm", "yin", "viterbi", "reserved")
 N_PHASES = 8
@@ -77,6 +78,7 @@ def lib():
     L.afx_wav_load_batch.argtypes = [vp, i64, C.c_int, C.c_int, vp, vp, vp, vp]; L.afx_wav_load_batch.restype = C.c_int
     L.afx_f0_postprocess.argtypes = [vp, i64, vp, vp, vp, vp, vp, vp, vp]; L.afx_f0_postprocess.restype = C.c_int
     L.afx_resample_length.argtypes = [vp, C.c_int32, i64]; L.afx_resample_length.restype = i64
+    L.afx_clip_kernel_variant.argtypes = [C.c_int32, C.c_int32, C.c_int32, vp]; L.afx_clip_kernel_variant.restype = C.c_int
     L.afx_resample_filter.argtypes = [C.c_int32, C.c_int32, vp, i64, vp, vp, vp, vp]; L.afx_resample_filter.restype = i64
     L.afx_resample.argtypes = [vp, vp, vp, vp, i64, C.c_int32, vp, vp, vp]; L.afx_resample.restype = C.c_int
     L.afx_dtw_frame_distance.argtypes = [vp, vp, vp, vp, vp, vp, vp, C.c_int32, i64, vp, vp, vp]; L.afx_dtw_frame_distance.restype = C.c_int

@@ -699,6 +699,15 @@ int afx_f0_postprocess(afx_handle_t h, int64_t n_clips, const int32_t* h_lengths
 
 static int upload_small_header(afx_handle_t h, const void* host, size_t bytes, cudaStream_t stream);
 
+int afx_clip_kernel_variant(int32_t sr, int32_t frame_length, int32_t hop_length, int32_t* mel_runs) {
+  if (sr < 1 || (frame_length != 512 && frame_length != 1024 && frame_length != 2048)) return -1;
+  const auto mel = afx::host::mel_sparse(sr, frame_length, afx::kNMels);
+  if (mel_runs) { for (int q = 0; q < 4; ++q) mel_runs[q] = mel.cnt[q]; mel_runs[4] = mel.cnt0; }
+  const clip_fn_t fn = clip_kernel_for(frame_length, hop_length, mel);
+  if (!fn) return -1;
+  return fn == clip_kernel_for(frame_length, hop_length, afx::host::MelSparse{}) ? 0 : 1;
+}
+
 int64_t afx_resample_filter(int32_t sr, int32_t native_sr, float* taps, int64_t taps_capacity, int32_t* up, int32_t* down,
                             int32_t* taps_per_phase, int32_t* n_pre_remove) {
   if (sr < 1 || native_sr < 1 || sr > (1 << 22) || native_sr > (1 << 22)) { fail(AFX_ERR_INVALID_ARG, "afx_resample_filter: bad sample rates %d, %d", sr, native_sr); return -1; }

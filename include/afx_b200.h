@@ -168,6 +168,11 @@ int afx_f0_postprocess(afx_handle_t h, int64_t n_clips, const int32_t* h_lengths
  *   d_in / d_out          device float32; clip i at d_in[h_in_offsets[i] .. + h_in_lengths[i]) -> d_out[h_out_offsets[i] ..)
  * Only enqueues work on `stream` (after waiting for a previous afx_resample on the same handle).
  */
+/* host only (no device needed): which instantiation of the fused kernel afx_create picks for (sr, frame_length, hop_length):
+ * 1 = the stock variant (compile-time run lengths of the mel segment walk: 22.05 kHz / 1024 / 256, 16 kHz / 512 / 128,
+ * 44.1 kHz / 2048 / 512), 0 = the table-driven variant, -1 = no kernel for this frame / hop pairing.  mel_runs (nullable)
+ * receives the five run lengths of the mel tables built for (sr, frame_length): quarters 0..3 and segment 0. */
+int afx_clip_kernel_variant(int32_t sr, int32_t frame_length, int32_t hop_length, int32_t* mel_runs);
 int64_t afx_resample_length(afx_handle_t h, int32_t native_sr, int64_t n_in);
 /* host only (no device needed): the phase-ordered filter afx_resample uses for native_sr -> sr, taps[up][taps_per_phase] =
  * h_padded[p + up * j] of scipy.signal.resample_poly's padded Kaiser design; returns up * taps_per_phase (-1 on bad

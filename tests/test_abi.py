@@ -70,3 +70,18 @@ def test_product_never_imports_the_oracle():
     for p in list(pkg.rglob("*.py")) + list(pkg.rglob("*.cu")) + list(pkg.rglob("*.cuh")) + list((ROOT / "audio_feature_extraction_toolkit").rglob("*.py")):
         txt = p.read_text()
         assert not re.search(r"^\s*(from|import)\s+oracle\b", txt, flags=re.M), p
+
+
+def test_stock_configurations_select_the_unrolled_kernel_variant(built_lib):
+    """MelCnt<NFFT, true> (csrc/afx_warp.cuh) must carry the run lengths of the mel tables the host builds for the stock
+    pairings; any other sample rate or hop takes the table-driven variant, unsupported pairings none."""
+    runs = (C.c_int32 * 5)()
+    for sr, n_fft, hop, expect in ((22050, 1024, 256, (2, 3, 6, 14, 2)), (16000, 512, 128, (1, 2, 3, 7, 1)),
+                                   (44100, 2048, 512, (2, 4, 12, 33, 2))):
+        assert built_lib.afx_clip_kernel_variant(sr, n_fft, hop, runs) == 1, (sr, n_fft, hop, list(runs))
+        assert tuple(runs) == expect
+    assert built_lib.afx_clip_kernel_variant(22050, 1024, 512, None) == 0     # stock tables, other hop
+    assert built_lib.afx_clip_kernel_variant(16000, 1024, 256, None) == 0     # other sample rate: table-driven walk
+    assert built_lib.afx_clip_kernel_variant(8000, 512, 128, None) == 0
+    assert built_lib.afx_clip_kernel_variant(22050, 1024, 100, None) == -1
+    assert built_lib.afx_clip_kernel_variant(22050, 1000, 250, None) == -1
