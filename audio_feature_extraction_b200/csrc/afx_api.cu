@@ -19,6 +19,7 @@
 
 #include "afx_common.cuh"
 #include "afx_clip.cuh"
+#include "afx_stream.cuh"
 #include "afx_extras.cuh"
 #include "afx_pyin.cuh"
 #include "afx_pyin_tables.h"
@@ -77,7 +78,11 @@ struct afx_handle_s {
   int ctas_per_sm = 1;
   int mel_floats = 0;      // floats in the padded sparse mel weight table
   int sm_count;
-  void (*clip_fn)(afx::ClipArgs) = nullptr;   // clip_kernel<frame_length, hop_length>
+  void (*clip_fn)(afx::ClipArgs) = nullptr;   // clip_kernel<frame_length, hop_length> (AFX_CLIP_IMPL=cta: the round-1 CTA-per-clip kernel)
+  void (*stream_fn)(afx::StreamArgs) = nullptr;   // stream_kernel<frame_length, hop_length>: warp-autonomous streaming kernel
+  bool use_stream = true;
+  int stream_warps = 16;   // warps per CTA of the streaming kernel (one CTA per SM)
+  int item_steps = 8;      // warp steps per work item
   void (*vit_fn)(afx::VitArgs) = nullptr;     // viterbi_kernel<half width or 0>
   // device tables
   float* d_window = nullptr;
@@ -146,8 +151,9 @@ __global__ void header_fetch_kernel(int* __restrict__ dst, const int* __restrict
 }
 
 struct Layout {   // carve-up of the caller's workspace
-  size_t off_offsets, off_frame_off, off_lengths, off_yin_chunk, off_info, off_counter, header_bytes;
+  size_t off_offsets, off_frame_off, off_lengths, off_yin_chunk, off_item_off, off_info, off_counter, off_slots, header_bytes;
 };
+constexpr int kMaxSlots = 4096;   // slab ring of the streaming kernel
 
 Layout header_layout(int64_t n) {
   Layout L;
@@ -156,8 +162,10 @@ Layout header_layout(int64_t n) {
   L.off_frame_off = o; o += align_up(sizeof(long long) * (n + 1), 16);
   L.off_lengths = o;   o += align_up(sizeof(int) * n, 16);
   L.off_yin_chunk = o; o += align_up(sizeof(int) * (n + 1), 16);   // prefix of pYIN frame chunks per clip
+  L.off_item_off = o;  o += align_up(sizeof(int) * (n + 1), 16);   // prefix of work items per clip (streaming kernel)
   L.off_info = o;      o += align_up(sizeof(afx::ClipInfo) * n, 16);   // produced on device; not staged from the host
   L.off_counter = o;   o += 256;
+  L.off_slots = o;     o += 2 * sizeof(int) * kMaxSlots;              // slot owner / arrival counters (device-initialised)
   L.header_bytes = align_up(o, 256);
   return L;
 }
@@ -213,6 +221,53 @@ size_t clip_smem_bytes(const afx_handle_s* h, int* tile_floats_out) {
   return 128 + 8192 + (n_fft == 2048 ? 4112 : 0) + (size_t)n_fft * 4 + (size_t)(afx::kMoments * afx::kMaxMfcc + 64) * 8 +
          (size_t)32 * (2 * h->n16 + 4) * 4 + (size_t)h->mel_floats * 4 +
          (size_t)h->clip_warps * (tile_floats + afx::kPlaneFloats) * 4;
+}
+
+typedef void (*stream_fn_t)(afx::StreamArgs);
+stream_fn_t stream_kernel_for(int n_fft, int hop, const afx::host::MelSparse& mel) {
+  if (n_fft == 1024 && hop == 256 && mel_counts_are_stock<1024>(mel)) return afx::stream_kernel<1024, 256, true>;
+  if (n_fft == 512 && hop == 128 && mel_counts_are_stock<512>(mel)) return afx::stream_kernel<512, 128, true>;
+  if (n_fft == 2048 && hop == 512 && mel_counts_are_stock<2048>(mel)) return afx::stream_kernel<2048, 512, true>;
+  if (n_fft == 1024) {
+    if (hop == 512) return afx::stream_kernel<1024, 512>;
+    if (hop == 256) return afx::stream_kernel<1024, 256>;
+    if (hop == 128) return afx::stream_kernel<1024, 128>;
+  } else if (n_fft == 512) {
+    if (hop == 256) return afx::stream_kernel<512, 256>;
+    if (hop == 128) return afx::stream_kernel<512, 128>;
+    if (hop == 64) return afx::stream_kernel<512, 64>;
+  } else if (n_fft == 2048) {
+    if (hop == 1024) return afx::stream_kernel<2048, 1024>;
+    if (hop == 512) return afx::stream_kernel<2048, 512>;
+    if (hop == 256) return afx::stream_kernel<2048, 256>;
+  }
+  return nullptr;
+}
+
+inline int frames_per_step(const afx_handle_s* h) { return h->cfg.frame_length == 2048 ? 1 : (h->cfg.frame_length == 1024 ? 2 : 4); }
+
+// bytes of one warp's buffer of the streaming kernel (afx::WarpBuf<>::kBytes)
+inline size_t stream_warp_bytes(const afx_handle_s* h) {
+  const size_t tile = (size_t)((frames_per_step(h) - 1) * h->cfg.hop_length + h->cfg.frame_length + 8) * 4;
+  return align_up(std::max<size_t>(tile + afx::kPlaneBFloats * 4, afx::kPlaneTBytes), 16);
+}
+size_t stream_smem_bytes(const afx_handle_s* h, int warps) {
+  const int n_fft = h->cfg.frame_length;
+  return 256 + (size_t)afx::kStreamMaxWarps * sizeof(afx::WarpScratch) + 8192 + (n_fft == 2048 ? 4112 : 0) + (size_t)n_fft * 4 +
+         (size_t)32 * (2 * h->n16 + 4) * 4 + (size_t)h->mel_floats * 4 + (size_t)warps * stream_warp_bytes(h);
+}
+
+// work items of the streaming kernel: runs of item_steps warp steps over the frames of the untrimmed clip (an upper
+// bound of the trimmed frames when the trim runs first); every clip has at least one item, whose completion
+// triggers the clip's finishing phases
+inline long long items_of(const afx_handle_s* h, long long len) {
+  const long long fpi = (long long)frames_per_step(h) * h->item_steps;
+  return std::max<long long>(1, ceil_div(len > 0 ? frames_ub(h, len) : 0, fpi));
+}
+inline int slots_for(const afx_handle_s* h, long long n_clips, long long max_len) {
+  const size_t sb = slab_bytes_for(h, max_len);
+  const long long by_l2 = std::max<long long>(64, (long long)((size_t)(48u << 20) / sb));
+  return (int)std::max<long long>(1, std::min<long long>({n_clips, by_l2, (long long)kMaxSlots}));
 }
 
 }  // namespace
@@ -308,6 +363,17 @@ int afx_create(const afx_config_t* cfg, afx_handle_t* out) {
     if (!found) { delete h; return fail(AFX_ERR_UNSUPPORTED, "no CTA shape of the fused kernel fits this device's shared memory"); }
   }
   CUDA_TRY(cudaFuncSetAttribute(h->clip_fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)clip_smem_bytes(h, nullptr)));
+  {  // the warp-autonomous streaming kernel: one CTA per SM with as many warps as shared memory (and 128 registers) allow
+    h->stream_fn = stream_kernel_for(cfg->frame_length, cfg->hop_length, mel);
+    if (const char* e = getenv("AFX_CLIP_IMPL")) h->use_stream = strcmp(e, "cta") != 0;
+    if (const char* e = getenv("AFX_ITEM_STEPS")) { const int v = atoi(e); if (v >= 1 && v * frames_per_step(h) <= 255) h->item_steps = v; }
+    int w = afx::kStreamMaxWarps;
+    if (const char* e = getenv("AFX_STREAM_WARPS")) { const int v = atoi(e); if (v >= 1 && v <= afx::kStreamMaxWarps) w = v; }
+    while (w > 1 && stream_smem_bytes(h, w) + 1024 > (size_t)prop.sharedMemPerBlockOptin) --w;
+    if (stream_smem_bytes(h, w) + 1024 > (size_t)prop.sharedMemPerBlockOptin) { delete h; return fail(AFX_ERR_UNSUPPORTED, "the streaming kernel does not fit this device's shared memory"); }
+    h->stream_warps = w;
+    CUDA_TRY(cudaFuncSetAttribute(h->stream_fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)stream_smem_bytes(h, w)));
+  }
   {  // pYIN constants and tables (F0 group); an unsupported f0 range only disables that group
     afx::host::PyinConsts& pc = h->pc;
     h->f0_ok = afx::host::pyin_consts(cfg->sr, cfg->frame_length, cfg->hop_length, cfg->f0_min, cfg->f0_max, pc) &&
@@ -381,11 +447,13 @@ int64_t afx_max_frames(afx_handle_t h, int64_t length) { return h ? frames_ub(h,
 
 static size_t workspace_bytes_impl(afx_handle_t h, int64_t n_clips, const int32_t* h_lengths) {
   if (!h || n_clips < 0 || (n_clips > 0 && !h_lengths)) return 0;
-  long long max_len = 0;
-  for (int64_t i = 0; i < n_clips; ++i) max_len = std::max<long long>(max_len, h_lengths[i]);
-  return header_layout(n_clips).header_bytes + (size_t)grid_for(h, n_clips) * slab_bytes_for(h, max_len) + 1024;
+  long long max_len = 0, items = 0;
+  for (int64_t i = 0; i < n_clips; ++i) { max_len = std::max<long long>(max_len, h_lengths[i]); items += items_of(h, h_lengths[i]); }
+  const size_t cta = (size_t)grid_for(h, n_clips) * slab_bytes_for(h, max_len);
+  const size_t stream = align_up((size_t)items * sizeof(afx::WorkItem), 256) + (size_t)slots_for(h, n_clips, max_len) * slab_bytes_for(h, max_len);
+  return header_layout(n_clips).header_bytes + std::max(cta, stream) + 1024;
 }
-// one private slab per resident CTA (at most one per SM); there is no smaller configuration, so both agree
+// header + work-item table + the ring of per-clip slabs; there is no smaller configuration, so both agree
 size_t afx_workspace_bytes(afx_handle_t h, int64_t n_clips, const int32_t* h_lengths) { return workspace_bytes_impl(h, n_clips, h_lengths); }
 size_t afx_workspace_min_bytes(afx_handle_t h, int64_t n_clips, const int32_t* h_lengths) { return workspace_bytes_impl(h, n_clips, h_lengths); }
 
@@ -428,8 +496,9 @@ int afx_extract(afx_handle_t h, const float* d_audio, const int64_t* h_offsets, 
   long long* s_frame_off = reinterpret_cast<long long*>(st + L.off_frame_off);
   int* s_lengths = reinterpret_cast<int*>(st + L.off_lengths);
   int* s_ychunk = reinterpret_cast<int*>(st + L.off_yin_chunk);
+  int* s_item_off = reinterpret_cast<int*>(st + L.off_item_off);
   const int yF = std::max(1, h->yin_frames_per_chunk);
-  long long fo = 0, max_len = 0, yc = 0;
+  long long fo = 0, max_len = 0, yc = 0, n_items = 0;
   for (int i = 0; i < n; ++i) {
     if (h_lengths[i] < 0) return fail(AFX_ERR_INVALID_ARG, "afx_extract: clip %d has negative length", i);
     if (h_offsets[i] < 0 || (h_offsets[i] & 3) != 0) return fail(AFX_ERR_INVALID_ARG, "afx_extract: clip %d offset %lld is not a multiple of 4 samples", i, (long long)h_offsets[i]);
@@ -437,6 +506,9 @@ int afx_extract(afx_handle_t h, const float* d_audio, const int64_t* h_offsets, 
     s_lengths[i] = h_lengths[i];
     s_frame_off[i] = fo;
     s_ychunk[i] = (int)yc;
+    s_item_off[i] = (int)n_items;
+    n_items += items_of(h, h_lengths[i]);
+    if (n_items > 0x7fffff00LL) return fail(AFX_ERR_UNSUPPORTED, "afx_extract: batch too large");
     yc += ceil_div(frames_ub(h, h_lengths[i]), yF);
     if (yc > 0x7fffff00LL) return fail(AFX_ERR_UNSUPPORTED, "afx_extract: batch too large");
     fo += frames_ub(h, h_lengths[i]);
@@ -444,6 +516,7 @@ int afx_extract(afx_handle_t h, const float* d_audio, const int64_t* h_offsets, 
   }
   s_frame_off[n] = fo;
   s_ychunk[n] = (int)yc;
+  s_item_off[n] = (int)n_items;
   const bool one_pass = single_pass(h);
   const long long max_trim_blocks = (200 * 1024) / 4 - 8;
   if (!one_pass && ceil_div(max_len, afx::kTrimHop) > max_trim_blocks)
@@ -451,7 +524,9 @@ int afx_extract(afx_handle_t h, const float* d_audio, const int64_t* h_offsets, 
 
   const int grid = grid_for(h, n);
   const size_t slab_bytes = slab_bytes_for(h, max_len);
-  if (workspace_bytes < L.header_bytes + (size_t)grid * slab_bytes)
+  const int n_slots = slots_for(h, n, max_len);
+  const size_t items_bytes = align_up((size_t)n_items * sizeof(afx::WorkItem), 256);
+  if (workspace_bytes < L.header_bytes + (h->use_stream ? items_bytes + (size_t)n_slots * slab_bytes : (size_t)grid * slab_bytes))
     return fail(AFX_ERR_WORKSPACE, "afx_extract: workspace of %zu bytes is below afx_workspace_bytes", workspace_bytes);
   char* ws = static_cast<char*>(d_workspace);
   if ((reinterpret_cast<uintptr_t>(ws) & 255u) != 0) return fail(AFX_ERR_INVALID_ARG, "afx_extract: workspace must be 256-byte aligned");
@@ -490,8 +565,24 @@ int afx_extract(afx_handle_t h, const float* d_audio, const int64_t* h_offsets, 
     ca.mask = feature_mask; ca.summaries = d_summaries; ca.meta = d_meta; ca.frames_out = d_frames;
     ca.pretrimmed = one_pass ? 0 : 1;
     PhaseTimer pt(h, stream, AFX_PHASE_FRAMES);
-    h->clip_fn<<<grid, h->clip_warps * 32, smem, stream>>>(ca);
-    ++g_launches;
+    if (!h->use_stream) {
+      h->clip_fn<<<grid, h->clip_warps * 32, smem, stream>>>(ca);
+      ++g_launches;
+    } else {
+      afx::StreamArgs sa;
+      sa.c = ca;
+      sa.c.slabs = ws + L.header_bytes + items_bytes;
+      sa.items = reinterpret_cast<const afx::WorkItem*>(ws + L.header_bytes);
+      sa.n_items = (int)n_items; sa.n_slots = n_slots;
+      sa.slot_owner = reinterpret_cast<int*>(ws + L.off_slots); sa.slot_done = sa.slot_owner + kMaxSlots;
+      const int threads = std::max(n, n_slots);
+      afx::item_build_kernel<<<(threads + 255) / 256, 256, 0, stream>>>(sa, reinterpret_cast<const int*>(ws + L.off_item_off),
+                                                                         frames_per_step(h) * h->item_steps);
+      const long long want = ceil_div(n_items, h->stream_warps);
+      const int sgrid = (int)std::max<long long>(1, std::min<long long>(want, h->sm_count));
+      h->stream_fn<<<sgrid, h->stream_warps * 32, stream_smem_bytes(h, h->stream_warps), stream>>>(sa);
+      g_launches += 2;
+    }
   }
   if (feature_mask & AFX_FEAT_F0) {
     // ---- pYIN: waves of clips sized by the handle-owned scratch (observation rows + back-pointers + states)

@@ -1,0 +1,517 @@
+// The fused single-pass hot path, second generation: ONE persistent kernel in which every WARP is autonomous.
+// Replaces, for a whole batch, preprocess_audio + extract_mfcc + extract_energy of
+// audio_feature_extraction_toolkit/core/feature_extractor.py:58-74,116-151,153-179 (reference).
+//
+// Work is cut into ITEMS (a run of consecutive warp steps of one clip, afx_step.cuh) listed in a device-built table;
+// warps claim items from one atomic counter.  There is no CTA-wide barrier after the table set-up:
+//
+//  S  a warp streams its item: raw samples by 1-D TMA bulk copies into its private tile (the next tile -- of this item
+//     or of the item the warp has already claimed -- is in flight while the current one is transformed), MFCC rows,
+//     per-frame log-mel extrema and hop-block sums of squares go to the clip's slab (a slot of an L2-resident ring).
+//     The frame grid is the absolute one (speculation 1 of afx_clip.cuh) unless hop does not divide 512 (pretrimmed).
+//  The warp that completes the LAST item of a clip (per-slot arrival counter, release/acquire through L2) finishes it
+//  alone, while every other warp keeps streaming:
+//  T  trim decision from the hop-block sums;  F  head / tail fix-up steps;  R  top_db clamp: steps whose log-mel
+//  minimum lies below (clip max - 80 dB) are redone with the clamp;  C  delta / delta-delta + moment sums;
+//  Z  RMS per frame from the block sums, statistics, summary + meta rows.  Then the slot is handed to clip + n_slots.
+#pragma once
+#include "afx_clip.cuh"
+#include "afx_step.cuh"
+
+namespace afx {
+
+constexpr int kStreamMaxWarps = 16;
+
+struct __align__(16) WorkItem {       // 32 bytes, built on the device (item_build_kernel)
+  long long audio_off;                // sample offset of the clip in the packed buffer
+  int L0;                             // clip length
+  int clip;
+  int f_begin;                        // first frame of the item (absolute grid; trimmed grid when pretrimmed)
+  int lo, hi;                         // sample range of the signal ([0, L0) or the trim range when pretrimmed)
+  unsigned nitems_cnt;                // items of this clip << 8 | frames in this item
+};
+
+struct __align__(16) WarpScratch {    // per-warp shared-memory state that need not live in registers across a step
+  WorkItem item[2];                   // current / next table entry (TMA destinations)
+  Slab2 sl;                           // slab rows of the current clip
+  int pad[2];
+};
+
+struct StreamArgs {
+  ClipArgs c;
+  const WorkItem* items;
+  int n_items;
+  int n_slots;
+  int* slot_owner;                    // [n_slots] clip that may use the slot (initially the slot index)
+  int* slot_done;                     // [n_slots] items of the owner that have been completed
+};
+
+// one thread per clip: the clip's items (item_off: host-built prefix; frames_per_item: multiple of the step width)
+__global__ void item_build_kernel(StreamArgs sa, const int* __restrict__ item_off, int frames_per_item) {
+  const ClipArgs& a = sa.c;
+  const int clip = blockIdx.x * blockDim.x + threadIdx.x;
+  if (clip < sa.n_slots) { sa.slot_owner[clip] = clip; sa.slot_done[clip] = 0; }
+  if (clip >= a.n_clips) return;
+  const int L0 = a.lengths[clip];
+  int T = L0 > 0 ? 1 + L0 / a.hop : 0, lo = 0, hi = L0;
+  if (a.pretrimmed) {
+    const ClipInfo ci = a.info[clip];
+    T = (ci.status == 0 && (a.mask & 0x6u)) ? ci.n_frames : 0;
+    lo = ci.start; hi = ci.end;
+  }
+  const int i0 = item_off[clip], ni = item_off[clip + 1] - i0;
+  WorkItem it;
+  it.audio_off = a.offsets[clip]; it.L0 = L0; it.clip = clip; it.lo = lo; it.hi = hi;
+  for (int j = 0; j < ni; ++j) {
+    const long long fb = (long long)j * frames_per_item;
+    const int b = (int)(fb < T ? fb : T), e = (int)(fb + frames_per_item < T ? fb + frames_per_item : T);
+    it.f_begin = b;
+    it.nitems_cnt = ((unsigned)ni << 8) | (unsigned)(e - b);
+    const_cast<WorkItem*>(sa.items)[i0 + j] = it;
+  }
+}
+
+__device__ __forceinline__ Slab2 carve_slab2(const ClipArgs& a, int slot) {
+  Slab2 s;
+  char* p = a.slabs + (size_t)slot * a.slab_bytes;
+  s.mfcc = reinterpret_cast<float*>(p);
+  s.ext = s.mfcc + (size_t)a.a_max * a.n16;
+  s.blk = s.ext + 2 * (size_t)a.a_max;
+  return s;
+}
+
+// ---- T: librosa.effects.trim(top_db) from the block sums, one warp (same arithmetic as trim_decide)
+__device__ __forceinline__ ClipInfo trim_decide_warp(const float* usum, int nu, int L0, int hop, float top_db, int lane) {
+  const int n_rms = 1 + L0 / kTrimHop;
+  const int nb = (L0 + kTrimHop - 1) / kTrimHop;
+  const int R = kTrimHop / hop;
+  float mx = 0.f;
+  int bad = 0;
+  for (int i = lane; i < n_rms; i += 32) {
+    const float s = (trim_block(usum, i - 2, nb, R, nu) + trim_block(usum, i - 1, nb, R, nu)) +
+                    (trim_block(usum, i, nb, R, nu) + trim_block(usum, i + 1, nb, R, nu));
+    bad |= !isfinite(s);     // a NaN / Inf sample poisons its block sum (librosa.util.valid_audio)
+    mx = fmaxf(mx, sqrtf(s * (1.0f / kTrimFrame)));
+  }
+  mx = warp_max(mx);
+  bad = __any_sync(0xffffffffu, bad);
+  const float ref_db = 10.0f * log10f(fmaxf(1e-10f, mx * mx));
+  int first = 0x7fffffff, last = -1;
+  for (int i = lane; i < n_rms; i += 32) {
+    const float s = (trim_block(usum, i - 2, nb, R, nu) + trim_block(usum, i - 1, nb, R, nu)) +
+                    (trim_block(usum, i, nb, R, nu) + trim_block(usum, i + 1, nb, R, nu));
+    const float r = sqrtf(s * (1.0f / kTrimFrame));
+    float db = 10.0f * log10f(fmaxf(1e-10f, r * r));
+    db -= ref_db;
+    if (db > -top_db) { first = min(first, i); last = max(last, i); }
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    first = min(first, __shfl_xor_sync(0xffffffffu, first, o));
+    last = max(last, __shfl_xor_sync(0xffffffffu, last, o));
+  }
+  ClipInfo ci;
+  ci.start = 0; ci.end = 0; ci.len = 0; ci.n_frames = 0; ci.max_key = 0u; ci.pad0 = ci.pad1 = 0; ci.status = 0;
+  if (L0 <= 0) ci.status = 1;                 // AFX_CLIP_EMPTY
+  else if (bad) ci.status = 2;                // AFX_CLIP_NONFINITE
+  else if (last < 0) ci.status = 1;           // every frame silent -> empty signal
+  else {
+    ci.start = first * kTrimHop;
+    ci.end = min(L0, (last + 1) * kTrimHop);
+    ci.len = ci.end - ci.start;
+    const int T = 1 + ci.len / hop;
+    if (ci.len <= 0) ci.status = 1;
+    else if (T < kDeltaWidth) ci.status = 3;  // AFX_CLIP_TOO_SHORT
+    else ci.n_frames = T;
+  }
+  return ci;
+}
+
+// ---- C: delta / delta2 (SavGol 9) -> moments of coefficients [kg, kg + 16) for trimmed frames [0, T), one warp.
+// sM [stat_frames + 8][17] floats is the warp's own buffer.  Lane c < 16 returns the six sums of coefficient kg + c.
+__device__ __forceinline__ void mfcc_phase_warp(const ClipArgs& a, const float* mfcc_rows, int a0, int T, long long out_row0,
+                                                int kg, float* sM, int kStatFramesW, double (&acc)[kMoments], uint64_t pol, int lane) {
+  constexpr int mstride = 17;
+#pragma unroll
+  for (int m = 0; m < kMoments; ++m) acc[m] = 0.0;
+  const int nc = min(16, a.n_mfcc - kg);
+  for (int f_lo = 0; f_lo < T; f_lo += kStatFramesW) {
+    const int f_hi = min(f_lo + kStatFramesW, T);             // exclusive
+    const int e_lo = min(max(f_lo, kStatHalo), T - 1 - kStatHalo) - kStatHalo;
+    const int e_hi = min(max(f_hi - 1, kStatHalo), T - 1 - kStatHalo) + kStatHalo;   // inclusive
+    const int ne = e_hi - e_lo + 1;                           // <= kStatFramesW + 8
+    __syncwarp();
+    {
+      const float* src = mfcc_rows + (size_t)(a0 + e_lo) * a.n16 + kg;
+      for (int i = lane; i < ne * 16; i += 32) {
+        const int e = i >> 4, c = i & 15;
+        sM[e * mstride + c] = ld_slab(src + (size_t)e * a.n16 + c, pol);
+      }
+    }
+    __syncwarp();
+    for (int c = 0; c < nc; ++c) {
+      double s1 = 0, s2 = 0, s3 = 0, s4 = 0, sd1 = 0, sd2 = 0;
+      for (int f = f_lo + lane; f < f_hi; f += 32) {
+        const int te = min(max(f, kStatHalo), T - 1 - kStatHalo) - e_lo;   // centre row of the 9-tap window
+        const float* col = sM + c;
+        // savgol(9, polyorder=deriv=1): sum k x[t+k] / 60 ; (9, 2, 2): sum c_k x[t+k] / 462  (double, cast to f32)
+        const double xm4 = col[(te - 4) * mstride], xm3 = col[(te - 3) * mstride], xm2 = col[(te - 2) * mstride],
+                     xm1 = col[(te - 1) * mstride], x0 = col[te * mstride], xp1 = col[(te + 1) * mstride],
+                     xp2 = col[(te + 2) * mstride], xp3 = col[(te + 3) * mstride], xp4 = col[(te + 4) * mstride];
+        const double d1 = (4.0 * (xp4 - xm4) + 3.0 * (xp3 - xm3) + 2.0 * (xp2 - xm2) + (xp1 - xm1)) / 60.0;
+        const double d2 = (28.0 * (xp4 + xm4) + 7.0 * (xp3 + xm3) - 8.0 * (xp2 + xm2) - 17.0 * (xp1 + xm1) - 20.0 * x0) / 462.0;
+        const float d1f = (float)d1, d2f = (float)d2;
+        const float xf = col[(f - e_lo) * mstride];
+        const double x = xf;
+        s1 += x; s2 += x * x; s3 += x * x * x; s4 += (x * x) * (x * x);
+        sd1 += (double)d1f; sd2 += (double)d2f;
+        if (a.frames_out) {
+          float* fr = a.frames_out + (size_t)(out_row0 + f) * a.frame_width;
+          fr[kg + c] = xf; fr[a.n_mfcc + kg + c] = d1f; fr[2 * a.n_mfcc + kg + c] = d2f;
+        }
+      }
+      s1 = warp_sum(s1); s2 = warp_sum(s2); s3 = warp_sum(s3); s4 = warp_sum(s4);
+      sd1 = warp_sum(sd1); sd2 = warp_sum(sd2);
+      if (lane == c) { acc[0] += s1; acc[1] += s2; acc[2] += s3; acc[3] += s4; acc[4] += sd1; acc[5] += sd2; }
+    }
+  }
+  __syncwarp();
+}
+
+// ---- the kernel.  STOCK: the mel tables carry the stock run lengths of this frame length (MelCnt<NFFT, true>)
+template <int NFFT, int HOP, bool STOCK = false>
+__global__ void __launch_bounds__(kStreamMaxWarps * 32, 1) stream_kernel(StreamArgs sa) {
+  const ClipArgs& a = sa.c;
+  using G = Geo<NFFT, HOP>;
+  constexpr int FPW = G::FPW;
+  constexpr int WB = WarpBuf<NFFT, HOP>::kBytes;
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  // layout: [16 tile mbarriers][16 item mbarriers][16 warp scratch blocks][twiddle 8 KB][W_2048 table][window]
+  //         [DCT rows per lane][mel weights][per-warp buffers]
+  Smem sm;
+  sm.mbar = reinterpret_cast<uint64_t*>(smem_raw);
+  constexpr int SCR = kStreamMaxWarps * (int)sizeof(WarpScratch);
+  WarpScratch* s_scr = reinterpret_cast<WarpScratch*>(smem_raw + 256);
+  sm.tw = reinterpret_cast<float2*>(smem_raw + 256 + SCR);
+  constexpr int PTW_BYTES = NFFT == 2048 ? 4112 : 0;
+  sm.ptw = reinterpret_cast<float2*>(smem_raw + 256 + SCR + 8192);
+  sm.win = reinterpret_cast<float*>(smem_raw + 256 + SCR + 8192 + PTW_BYTES);
+  float* sDct = sm.win + NFFT;
+  const int dstride = 2 * a.n16 + 4;
+  float* sMel = sDct + 32 * dstride;
+  sm.dct = sDct; sm.melw = sMel;
+  unsigned char* wbufs = reinterpret_cast<unsigned char*>(sMel + a.mel_floats);
+  sm.raw = nullptr; sm.planes = nullptr;
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  for (int i = tid; i < 1024; i += (int)blockDim.x) sm.tw[i] = a.tab.twiddle[i];
+  for (int i = tid; i < NFFT; i += (int)blockDim.x) sm.win[i] = a.tab.window_half[i];
+  if (NFFT == 2048) for (int i = tid; i <= 512; i += (int)blockDim.x) sm.ptw[i] = a.tab.post_twiddle[i];
+  for (int i = tid; i < 64 * a.n16; i += (int)blockDim.x) {
+    const int l = i / (2 * a.n16), rem = i - l * 2 * a.n16, hsel = rem / a.n16, k = rem - hsel * a.n16;
+    sDct[l * dstride + rem] = a.dct_t[(hsel ? 63 - l : l) * a.n16 + k];
+  }
+  for (int i = tid; i < a.mel_floats; i += (int)blockDim.x) sMel[i] = a.tab.mel_w[i];
+  if (tid < 2 * kStreamMaxWarps) mbar_init(sm.mbar + tid, 1);
+  if (tid == 0) fence_mbar_init();
+  __syncthreads();
+  // ---- from here on every warp is on its own
+
+  WarpCtx2 wc;
+  wc.tile = reinterpret_cast<float*>(wbufs + (size_t)warp * WB);
+  wc.planeB = reinterpret_cast<float*>(wbufs + (size_t)warp * WB + (WB - kPlaneBFloats * 4));
+  wc.mbar = sm.mbar + warp;
+  wc.parity = 0;
+  wc.pol_in = l2_policy_evict_first();
+  wc.pol_slab = l2_policy_evict_last();
+  uint64_t* mb_item = sm.mbar + kStreamMaxWarps + warp;
+  unsigned par_item = 0;
+  WarpScratch& scr = s_scr[warp];
+  WorkItem* my_items = scr.item;
+  const int n = a.n_mfcc;
+
+  auto claim = [&]() -> int {
+    int v = 0;
+    if (lane == 0) v = atomicAdd(a.counter, 1);
+    return __shfl_sync(0xffffffffu, v, 0);
+  };
+  auto fetch_item = [&](int idx, int buf) {   // async copy of one table entry into this warp's slot `buf`
+    if (lane == 0) {
+      fence_proxy_async();
+      mbar_expect_tx(mb_item, (unsigned)sizeof(WorkItem));
+      tma_load_1d(my_items + buf, sa.items + idx, (unsigned)sizeof(WorkItem), mb_item);
+    }
+  };
+
+  int cur = claim();
+  if (cur >= sa.n_items) return;
+  fetch_item(cur, 0);
+  int buf = 0;
+  bool item_in_flight = true;    // the entry of `cur` has been requested but not waited for
+  bool tile_in_flight = false;   // the first tile of `cur` was prefetched by the previous item's last step
+  unsigned tile_bytes = 0;
+
+  for (;;) {   // ---- one item per iteration
+    if (item_in_flight) { mbar_wait(mb_item, par_item); par_item ^= 1u; item_in_flight = false; }
+    __syncwarp();
+    const WorkItem& it = my_items[buf];
+    const int clip = it.clip, L0 = it.L0;
+    const float* clip_audio = a.audio + it.audio_off;
+    const int slot = clip % sa.n_slots;
+    if (lane == 0) scr.sl = carve_slab2(a, slot);
+    __syncwarp();
+    const Slab2& sl = scr.sl;
+    const int nxt = claim();     // the item after this one; its entry is requested after the first step
+    bool nxt_requested = false;
+    {  // the slot belongs to `clip` once the finisher of clip - n_slots has released it
+      if (lane == 0) {
+        const volatile int* ow = sa.slot_owner + slot;
+        while (*ow != clip) __nanosleep(256);
+      }
+      __syncwarp();
+      __threadfence();
+    }
+
+    // job state: pass 0 = the item (S); 1 / 2 = head / tail fix-ups (F); 3 = redo with the clamp (R)
+    int pass = 0;
+    Region rg{it.lo, it.lo, it.hi};
+    rg.raw = a.raw;
+    int f_begin = it.f_begin, f_end = it.f_begin + (int)(it.nitems_cnt & 0xffu);
+    int shift = 0;
+    bool own = true;
+    float floor_db = -3.0e38f;
+    ClipInfo ci;
+    ci.start = 0; ci.end = 0; ci.len = 0; ci.n_frames = 0; ci.max_key = 0u; ci.pad0 = ci.pad1 = 0; ci.status = 1;
+    int a0 = 0, head_end = 0;
+    const bool want_frames = (a.mask & 0x6u) != 0;
+    bool fin = false;            // this warp completed the clip's last item and finishes the clip
+
+    for (;;) {   // ---- one job per iteration: steps [f_begin, f_end) of rg, FPW frames each
+      // step iterator: groups of 32 steps; in the redo pass only steps whose unclamped row minimum lies below the floor
+      int g0 = f_begin;
+      unsigned bits = 0u;
+      auto load_group = [&]() {
+        const int f = g0 + FPW * lane;
+        bool v = f < f_end;
+        if (pass == 3 && v) {
+          float m = 3.0e38f;
+          for (int j = 0; j < FPW; ++j) if (f + j < f_end) m = fminf(m, __ldcg(sl.ext + 2 * (shift + f + j) + 1));
+          v = m < floor_db;
+        }
+        bits = __ballot_sync(0xffffffffu, v);
+      };
+      auto next_frame = [&]() -> int {   // pops the next step of the job; f_end when exhausted
+        while (bits == 0u) {
+          if (g0 + 32 * FPW >= f_end) return f_end;
+          g0 += 32 * FPW;
+          load_group();
+        }
+        const int j = __ffs(bits) - 1;
+        bits &= bits - 1u;
+        return g0 + FPW * j;
+      };
+      if (f_begin < f_end) load_group();
+      int fA = f_begin < f_end ? next_frame() : f_end;
+      unsigned cur_bytes = 0;
+      if (fA < f_end) {
+        const int gA0 = rg.origin + fA * HOP - NFFT / 2;
+        if (pass == 0 && tile_in_flight) {
+          cur_bytes = tile_bytes;
+        } else {
+          int g_lo = 0, s_lo = 0;
+          cur_bytes = pair_copy_range(rg, gA0, G::SPAN, L0, g_lo, s_lo);
+          if (lane == 0 && cur_bytes) {
+            fence_proxy_async();
+            mbar_expect_tx(wc.mbar, cur_bytes);
+            tma_load_1d_hint(wc.tile + s_lo, clip_audio + g_lo, cur_bytes, wc.mbar, wc.pol_in);
+          }
+        }
+      } else if (pass == 0 && tile_in_flight) {
+        // cannot happen: a prefetched item has at least one step
+      }
+      tile_in_flight = false;
+      while (fA < f_end) {
+        const int gA = rg.origin + fA * HOP - NFFT / 2;
+        const int fN = next_frame();
+        unsigned next_bytes = 0;
+        const float* next_src = clip_audio;
+        int s_lo = 0;
+        if (fN < f_end) {
+          int g_lo = 0;
+          next_bytes = pair_copy_range(rg, rg.origin + fN * HOP - NFFT / 2, G::SPAN, L0, g_lo, s_lo);
+          next_src = clip_audio + g_lo;
+        } else if (pass == 0 && nxt_requested) {
+          // last step of the item: the next item's first tile rides this step's prefetch slot
+          if (item_in_flight) { mbar_wait(mb_item, par_item); par_item ^= 1u; item_in_flight = false; }
+          __syncwarp();
+          const WorkItem nx = my_items[buf ^ 1];
+          if ((nx.nitems_cnt & 0xffu) != 0u) {
+            Region rn{nx.lo, nx.lo, nx.hi};
+            int g_lo = 0;
+            next_bytes = pair_copy_range(rn, nx.lo + nx.f_begin * HOP - NFFT / 2, G::SPAN, nx.L0, g_lo, s_lo);
+            next_src = a.audio + nx.audio_off + g_lo;
+            tile_in_flight = next_bytes != 0u;
+            tile_bytes = next_bytes;
+          }
+        }
+        if (cur_bytes) { mbar_wait(wc.mbar, wc.parity); wc.parity ^= 1u; }
+        Step2<NFFT, HOP>::template run<MelCnt<NFFT, STOCK>>(a, sm, sl, wc, rg, gA, L0, min(FPW, f_end - fA), shift + fA, own, fA,
+                                                            floor_db, next_bytes, next_src, wc.tile + s_lo);
+        if (pass == 0 && !nxt_requested && nxt < sa.n_items) { fetch_item(nxt, buf ^ 1); nxt_requested = true; item_in_flight = true; }
+        fA = fN; cur_bytes = next_bytes;
+      }
+
+      // ---- the job is done: what next?
+      if (pass == 0) {
+        __threadfence();
+        int last = 0;
+        if (lane == 0) last = atomicAdd(sa.slot_done + slot, 1) + 1 == (int)(it.nitems_cnt >> 8);
+        last = __shfl_sync(0xffffffffu, last, 0);
+        if (!last) break;
+        fin = true;
+        __threadfence();
+        // this warp finishes the clip.  A tile prefetched for the next item would be overwritten by the fix-up
+        // steps: let it land and drop it (the next item re-issues it)
+        if (tile_in_flight) { mbar_wait(wc.mbar, wc.parity); wc.parity ^= 1u; tile_in_flight = false; }
+        if (a.pretrimmed) {
+          ci = a.info[clip];
+          a0 = 0;
+          pass = 2;   // no T, no F
+        } else {
+          const int fe0 = L0 > 0 ? 1 + L0 / HOP : 0;
+          const int nu = FPW * ((fe0 + FPW - 1) / FPW);   // hop-block sums written by pass 0
+          ci = trim_decide_warp(sl.blk, nu, L0, HOP, a.trim_top_db, lane);
+          a0 = ci.start / HOP;
+        }
+      }
+      if (ci.status != 0 || !want_frames) break;
+      rg = Region{ci.start, ci.start, ci.end};
+      rg.raw = a.raw;
+      shift = a0;
+      own = false;
+      f_begin = 0; f_end = 0;
+      if (pass == 0) {          // -> head fix-up: frames t with t*hop < n_fft/2 reach in front of the trimmed signal
+        pass = 1;
+        if (ci.start > 0) { head_end = min(ci.n_frames, (NFFT / 2 + HOP - 1) / HOP); f_end = head_end; }
+        continue;
+      }
+      if (pass == 1) {          // -> tail fix-up: frames t with t*hop + n_fft/2 > len reach behind it
+        pass = 2;
+        if (ci.end < L0) {
+          const int t_tail = (ci.len >= NFFT / 2) ? (ci.len - NFFT / 2) / HOP + 1 : 0;
+          f_begin = max(t_tail, head_end); f_end = ci.n_frames;
+        }
+        continue;
+      }
+      if (pass == 2) {          // -> R: power_to_db(top_db) clamps at the clip-global maximum - top_db
+        pass = 3;
+        if (!(a.mask & 0x2u)) break;
+        __threadfence();
+        float mx = -3.0e38f, mn = 3.0e38f;
+        for (int t = lane; t < ci.n_frames; t += 32) {
+          const float2 e = __ldcg(reinterpret_cast<const float2*>(sl.ext) + a0 + t);
+          mx = fmaxf(mx, e.x); mn = fminf(mn, e.y);
+        }
+        mx = warp_max(mx); mn = warp_min(mn);
+        floor_db = mx - a.mfcc_top_db;
+        if (mn >= floor_db) break;       // nothing is clamped: the speculative DCT rows are exact
+        f_end = ci.n_frames;
+        continue;
+      }
+      break;   // pass 3 done
+    }
+
+    if (fin) {
+      // ---- this warp owns the finished clip: C, Z, then release the slot
+      __threadfence();
+      if (lane == 0) {
+        a.info[clip] = ci;
+        int* m = a.meta + (size_t)clip * 4;
+        m[0] = ci.status; m[1] = ci.start; m[2] = ci.end; m[3] = ci.n_frames;
+      }
+      float* out = a.summaries + (size_t)clip * a.summary_width;
+      for (int i = lane; i < a.summary_width; i += 32) out[i] = 0.f;
+      __syncwarp();
+      const int T = ci.n_frames;
+      const long long out_row0 = a.frame_off[clip];
+      if (T > 0) {
+        const double invT = 1.0 / (double)T;
+        if (a.mask & 0x2u) {
+          for (int kg = 0; kg < n; kg += 16) {
+            double acc[kMoments];
+            mfcc_phase_warp(a, sl.mfcc, a0, T, out_row0, kg, wc.tile, (WB / 4) / 17 - 2 * kStatHalo, acc, wc.pol_slab, lane);
+            const int c = kg + lane;
+            if (lane < 16 && c < n) {
+              const double s1 = acc[0], s2 = acc[1], s3 = acc[2], s4 = acc[3];
+              const double mean = s1 * invT;
+              const double ex2 = s2 * invT, ex3 = s3 * invT, ex4 = s4 * invT;
+              const double m2 = fmax(ex2 - mean * mean, 0.0);
+              const double m3 = ex3 - 3.0 * mean * ex2 + 2.0 * mean * mean * mean;
+              const double m4 = ex4 - 4.0 * mean * ex3 + 6.0 * mean * mean * ex2 - 3.0 * mean * mean * mean * mean;
+              out[4 + c] = (float)mean;
+              out[4 + n + c] = (float)sqrt(m2);
+              out[4 + 2 * n + c] = (float)(acc[4] * invT);
+              out[4 + 3 * n + c] = (float)(acc[5] * invT);
+              out[4 + 4 * n + 3 + c] = (m2 > 0.0) ? (float)(m3 / (m2 * sqrt(m2))) : 0.f;
+              out[4 + 4 * n + 3 + n + c] = (m2 > 0.0) ? (float)(m4 / (m2 * m2) - 3.0) : 0.f;
+            }
+          }
+        }
+        if (a.mask & 0x4u) {   // RMS energy (core/feature_extractor.py:164-173): frame t covers hop blocks t - G0 .. t + G0 - 1
+          constexpr int GPF = NFFT / HOP;
+          const int ub = a.pretrimmed ? 0 : a0;                   // first block of the trimmed signal
+          const int ue = ub + (ci.len + HOP - 1) / HOP;           // blocks at or past ue hold no trimmed sample
+          double s1 = 0, s2 = 0, s3 = 0, s4 = 0;
+          float mn = 3.0e38f, mx = -3.0e38f;
+          for (int t = lane; t < T; t += 32) {
+            const int u0 = ub + t - G::G0;
+            float bs[GPF];
+#pragma unroll
+            for (int g = 0; g < GPF; ++g) { const int u = u0 + g; bs[g] = (u >= ub && u < ue) ? __ldcg(sl.blk + u) : 0.f; }
+            float s = 0.f;
+            if (GPF >= 4) {
+#pragma unroll
+              for (int g = 0; g < GPF; g += 4) s += (bs[g] + bs[g + 1]) + (bs[g + 2] + bs[g + 3]);
+            } else {
+#pragma unroll
+              for (int g = 0; g < GPF; ++g) s += bs[g];
+            }
+            const float rf = sqrtf(s * (1.0f / NFFT));
+            const double r = rf;
+            s1 += r; s2 += r * r; s3 += r * r * r; s4 += (r * r) * (r * r);
+            mn = fminf(mn, rf); mx = fmaxf(mx, rf);
+            if (a.frames_out) a.frames_out[(size_t)(out_row0 + t) * a.frame_width + 3 * n] = rf;
+          }
+          s1 = warp_sum(s1); s2 = warp_sum(s2); s3 = warp_sum(s3); s4 = warp_sum(s4);
+          mn = warp_min(mn); mx = warp_max(mx);
+          if (lane == 0) {
+            const double mean = s1 * invT;
+            const double ex2 = s2 * invT, ex3 = s3 * invT, ex4 = s4 * invT;
+            const double m2 = fmax(ex2 - mean * mean, 0.0);
+            const double m3 = ex3 - 3.0 * mean * ex2 + 2.0 * mean * mean * mean;
+            const double m4 = ex4 - 4.0 * mean * ex3 + 6.0 * mean * mean * ex2 - 3.0 * mean * mean * mean * mean;
+            float* e = out + 4 + 4 * n;
+            e[0] = (float)mean; e[1] = (float)sqrt(m2); e[2] = mx - mn;
+            e[3 + 2 * n] = (m2 > 0.0) ? (float)(m3 / (m2 * sqrt(m2))) : 0.f;
+            e[3 + 2 * n + 1] = (m2 > 0.0) ? (float)(m4 / (m2 * m2) - 3.0) : 0.f;
+          }
+        }
+      }
+      // release the slot to clip + n_slots
+      __syncwarp();
+      if (lane == 0) {
+        sa.slot_done[slot] = 0;
+        __threadfence();
+        *reinterpret_cast<volatile int*>(sa.slot_owner + slot) = clip + sa.n_slots;
+      }
+      __syncwarp();
+    }
+
+    // ---- next item
+    if (nxt >= sa.n_items) break;
+    if (!nxt_requested) { fetch_item(nxt, buf ^ 1); item_in_flight = true; }
+    cur = nxt; buf ^= 1;
+  }
+}
+
+}  // namespace afx

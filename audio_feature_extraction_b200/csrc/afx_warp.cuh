@@ -424,7 +424,11 @@ struct WarpStep<1024, HOP> {
     float eg[G::NG];
 #pragma unroll
     for (int g = 0; g < G::NG; ++g) eg[g] = 0.f;
+#ifdef AFX_FORCE_FAST   // development builds that count the instructions of the interior step (tools/dev)
+    const bool fast = true;
+#else
     const bool fast = (gA >= 1) && (gA >= rg.lo) && (gA + G::SPAN <= rg.hi);   // warp-uniform
+#endif
     if (fast) load<true>(r, im, eg, wc.raw + 4, gA, rg, L0, a.coef, sm, lane);
     else load<false>(r, im, eg, wc.raw + 4, gA, rg, L0, a.coef, sm, lane);
     prefetch_next(wc, next_bytes, next_src, next_dst, lane);
@@ -491,7 +495,11 @@ struct WarpStep<512, HOP> {
     float eg[G::NG];
 #pragma unroll
     for (int g = 0; g < G::NG; ++g) eg[g] = 0.f;
+#ifdef AFX_FORCE_FAST   // development builds that count the instructions of the interior step (tools/dev)
+    const bool fast = true;
+#else
     const bool fast = (gA >= 1) && (gA >= rg.lo) && (gA + G::SPAN <= rg.hi);   // warp-uniform
+#endif
     if (fast) load<true>(r, im, eg, wc.raw + 4, gA, rg, L0, a.coef, sm, lane);
     else load<false>(r, im, eg, wc.raw + 4, gA, rg, L0, a.coef, sm, lane);
     prefetch_next(wc, next_bytes, next_src, next_dst, lane);
@@ -561,7 +569,11 @@ struct WarpStep<2048, HOP> {
     float eg[G::NG];
 #pragma unroll
     for (int g = 0; g < G::NG; ++g) eg[g] = 0.f;
+#ifdef AFX_FORCE_FAST   // development builds that count the instructions of the interior step (tools/dev)
+    const bool fast = true;
+#else
     const bool fast = (gA >= 1) && (gA >= rg.lo) && (gA + G::SPAN <= rg.hi);   // warp-uniform
+#endif
     if (fast) load<true>(r, im, eg, wc.raw + 4, gA, rg, L0, a.coef, sm, lane);
     else load<false>(r, im, eg, wc.raw + 4, gA, rg, L0, a.coef, sm, lane);
     prefetch_next(wc, next_bytes, next_src, next_dst, lane);
