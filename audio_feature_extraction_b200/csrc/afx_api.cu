@@ -82,7 +82,7 @@ struct afx_handle_s {
   void (*stream_fn)(afx::StreamArgs) = nullptr;   // stream_kernel<frame_length, hop_length>: warp-autonomous streaming kernel
   bool use_stream = true;
   int stream_warps = 16;   // warps per CTA of the streaming kernel (one CTA per SM)
-  int item_steps = 8;      // warp steps per work item
+  int item_steps = 0;      // warp steps per work item; 0 = chosen per batch (item_steps_for)
   void (*vit_fn)(afx::VitArgs) = nullptr;     // viterbi_kernel<half width or 0>
   // device tables
   float* d_window = nullptr;
@@ -90,6 +90,8 @@ struct afx_handle_s {
   float* d_ptw = nullptr;
   float* d_mel_w = nullptr;
   int* d_mel_k0 = nullptr;
+  float* d_mel_lin = nullptr; int* d_mel_kl = nullptr; float* d_mel_w0 = nullptr;
+  int mel_w0_floats = 4;
   float* d_dct_t = nullptr;
   afx::Tables tab;
   // pinned staging for the per-call header arrays
@@ -253,15 +255,25 @@ inline size_t stream_warp_bytes(const afx_handle_s* h) {
 }
 size_t stream_smem_bytes(const afx_handle_s* h, int warps) {
   const int n_fft = h->cfg.frame_length;
-  return 256 + (size_t)afx::kStreamMaxWarps * sizeof(afx::WarpScratch) + 8192 + (n_fft == 2048 ? 4112 : 0) + (size_t)n_fft * 4 +
-         (size_t)32 * (2 * h->n16 + 4) * 4 + (size_t)h->mel_floats * 4 + (size_t)warps * stream_warp_bytes(h);
+  return 512 + (size_t)afx::kStreamWarpSlots * sizeof(afx::WarpScratch) + 8192 + (n_fft == 2048 ? 4112 : 0) +
+         (size_t)32 * (2 * h->n16 + 4) * 4 + (size_t)(128 * 5 + h->mel_w0_floats) * 4 + (size_t)warps * stream_warp_bytes(h);
 }
 
 // work items of the streaming kernel: runs of item_steps warp steps over the frames of the untrimmed clip (an upper
 // bound of the trimmed frames when the trim runs first); every clip has at least one item, whose completion
 // triggers the clip's finishing phases
-inline long long items_of(const afx_handle_s* h, long long len) {
-  const long long fpi = (long long)frames_per_step(h) * h->item_steps;
+// steps per item: large enough that the per-item costs (slot check, arrival atomic + fences) vanish, small enough that
+// every resident warp still gets >= 8 items (a single 5 s clip must spread over the whole GPU: 2-step items)
+inline int item_steps_for(const afx_handle_s* h, int64_t n_clips, const int32_t* h_lengths) {
+  if (h->item_steps > 0) return h->item_steps;
+  const int fpw = frames_per_step(h);
+  long long steps = 0;
+  for (int64_t i = 0; i < n_clips; ++i) steps += ceil_div(h_lengths[i] > 0 ? frames_ub(h, h_lengths[i]) : 0, fpw);
+  const long long want = steps / (8LL * h->sm_count * h->stream_warps);
+  return (int)std::max<long long>(2, std::min<long long>({want, 32LL, 255LL / fpw}));
+}
+inline long long items_of(const afx_handle_s* h, long long len, int item_steps) {
+  const long long fpi = (long long)frames_per_step(h) * item_steps;
   return std::max<long long>(1, ceil_div(len > 0 ? frames_ub(h, len) : 0, fpi));
 }
 inline int slots_for(const afx_handle_s* h, long long n_clips, long long max_len) {
@@ -337,6 +349,17 @@ int afx_create(const afx_config_t* cfg, afx_handle_t* out) {
   CUDA_TRY(upload(mel.w, &h->d_mel_w));
   CUDA_TRY(upload(mel.k0, &h->d_mel_k0));
   CUDA_TRY(upload(dct_t, &h->d_dct_t));
+  if (mel.lin_max_err > 2e-6) { delete h; return fail(AFX_ERR_UNSUPPORTED, "mel filterbank: linear weight form is off by %.3g", mel.lin_max_err); }
+  {
+    std::vector<float> w0 = mel.w0;
+    w0.resize((std::max<size_t>(w0.size(), (size_t)mel.cnt0) + 3) & ~(size_t)3, 0.f);
+    for (int i = 0; i < mel.cnt0; ++i) w0[i] = mel.dense[(size_t)0 * (1 + cfg->frame_length / 2) + mel.k00 + i];
+    h->mel_w0_floats = (int)w0.size();
+    CUDA_TRY(upload(mel.lin, &h->d_mel_lin));
+    CUDA_TRY(upload(mel.kl, &h->d_mel_kl));
+    CUDA_TRY(upload(w0, &h->d_mel_w0));
+  }
+  h->tab.mel_lin = reinterpret_cast<const float4*>(h->d_mel_lin); h->tab.mel_kl = h->d_mel_kl; h->tab.mel_w0 = h->d_mel_w0;
   h->tab.window_half = h->d_window;
   h->tab.twiddle = reinterpret_cast<const float2*>(h->d_twiddle);
   h->tab.post_twiddle = reinterpret_cast<const float2*>(h->d_ptw);
@@ -368,7 +391,13 @@ int afx_create(const afx_config_t* cfg, afx_handle_t* out) {
     if (const char* e = getenv("AFX_CLIP_IMPL")) h->use_stream = strcmp(e, "cta") != 0;
     if (const char* e = getenv("AFX_ITEM_STEPS")) { const int v = atoi(e); if (v >= 1 && v * frames_per_step(h) <= 255) h->item_steps = v; }
     int w = afx::kStreamMaxWarps;
-    if (const char* e = getenv("AFX_STREAM_WARPS")) { const int v = atoi(e); if (v >= 1 && v <= afx::kStreamMaxWarps) w = v; }
+    if (const char* e = getenv("AFX_STREAM_WARPS")) {
+      const int v = atoi(e);
+      if (v >= 1 && v <= afx::kStreamMaxWarps) w = v;
+      else if (v == 20 && h->stream_fn == (stream_fn_t)afx::stream_kernel<1024, 256, true>) {   // experiment: 96 registers per thread
+        h->stream_fn = afx::stream_kernel<1024, 256, true, 20>; w = 20;
+      }
+    }
     while (w > 1 && stream_smem_bytes(h, w) + 1024 > (size_t)prop.sharedMemPerBlockOptin) --w;
     if (stream_smem_bytes(h, w) + 1024 > (size_t)prop.sharedMemPerBlockOptin) { delete h; return fail(AFX_ERR_UNSUPPORTED, "the streaming kernel does not fit this device's shared memory"); }
     h->stream_warps = w;
@@ -424,6 +453,7 @@ int afx_destroy(afx_handle_t h) {
   cudaSetDevice(h->cfg.device);
   cudaDeviceSynchronize();
   cudaFree(h->d_window); cudaFree(h->d_twiddle); cudaFree(h->d_ptw); cudaFree(h->d_pyin); cudaFree(h->d_f0_ws); cudaFree(h->d_mel_w); cudaFree(h->d_mel_k0); cudaFree(h->d_dct_t);
+  cudaFree(h->d_mel_lin); cudaFree(h->d_mel_kl); cudaFree(h->d_mel_w0);
   if (h->h_stage) cudaFreeHost(h->h_stage);
   if (h->stage_ev) cudaEventDestroy(h->stage_ev);
   cudaFree(h->d_ws); cudaFree(h->d_audio[0]); cudaFree(h->d_audio[1]); cudaFree(h->d_sum); cudaFree(h->d_meta);
@@ -448,7 +478,8 @@ int64_t afx_max_frames(afx_handle_t h, int64_t length) { return h ? frames_ub(h,
 static size_t workspace_bytes_impl(afx_handle_t h, int64_t n_clips, const int32_t* h_lengths) {
   if (!h || n_clips < 0 || (n_clips > 0 && !h_lengths)) return 0;
   long long max_len = 0, items = 0;
-  for (int64_t i = 0; i < n_clips; ++i) { max_len = std::max<long long>(max_len, h_lengths[i]); items += items_of(h, h_lengths[i]); }
+  const int isteps = item_steps_for(h, n_clips, h_lengths);
+  for (int64_t i = 0; i < n_clips; ++i) { max_len = std::max<long long>(max_len, h_lengths[i]); items += items_of(h, h_lengths[i], isteps); }
   const size_t cta = (size_t)grid_for(h, n_clips) * slab_bytes_for(h, max_len);
   const size_t stream = align_up((size_t)items * sizeof(afx::WorkItem), 256) + (size_t)slots_for(h, n_clips, max_len) * slab_bytes_for(h, max_len);
   return header_layout(n_clips).header_bytes + std::max(cta, stream) + 1024;
@@ -499,6 +530,7 @@ int afx_extract(afx_handle_t h, const float* d_audio, const int64_t* h_offsets, 
   int* s_item_off = reinterpret_cast<int*>(st + L.off_item_off);
   const int yF = std::max(1, h->yin_frames_per_chunk);
   long long fo = 0, max_len = 0, yc = 0, n_items = 0;
+  const int isteps = item_steps_for(h, n_clips, h_lengths);
   for (int i = 0; i < n; ++i) {
     if (h_lengths[i] < 0) return fail(AFX_ERR_INVALID_ARG, "afx_extract: clip %d has negative length", i);
     if (h_offsets[i] < 0 || (h_offsets[i] & 3) != 0) return fail(AFX_ERR_INVALID_ARG, "afx_extract: clip %d offset %lld is not a multiple of 4 samples", i, (long long)h_offsets[i]);
@@ -507,7 +539,7 @@ int afx_extract(afx_handle_t h, const float* d_audio, const int64_t* h_offsets, 
     s_frame_off[i] = fo;
     s_ychunk[i] = (int)yc;
     s_item_off[i] = (int)n_items;
-    n_items += items_of(h, h_lengths[i]);
+    n_items += items_of(h, h_lengths[i], isteps);
     if (n_items > 0x7fffff00LL) return fail(AFX_ERR_UNSUPPORTED, "afx_extract: batch too large");
     yc += ceil_div(frames_ub(h, h_lengths[i]), yF);
     if (yc > 0x7fffff00LL) return fail(AFX_ERR_UNSUPPORTED, "afx_extract: batch too large");
@@ -573,11 +605,11 @@ int afx_extract(afx_handle_t h, const float* d_audio, const int64_t* h_offsets, 
       sa.c = ca;
       sa.c.slabs = ws + L.header_bytes + items_bytes;
       sa.items = reinterpret_cast<const afx::WorkItem*>(ws + L.header_bytes);
-      sa.n_items = (int)n_items; sa.n_slots = n_slots;
+      sa.n_items = (int)n_items; sa.n_slots = n_slots; sa.mel_w0_floats = h->mel_w0_floats;
       sa.slot_owner = reinterpret_cast<int*>(ws + L.off_slots); sa.slot_done = sa.slot_owner + kMaxSlots;
       const int threads = std::max(n, n_slots);
       afx::item_build_kernel<<<(threads + 255) / 256, 256, 0, stream>>>(sa, reinterpret_cast<const int*>(ws + L.off_item_off),
-                                                                         frames_per_step(h) * h->item_steps);
+                                                                         frames_per_step(h) * isteps);
       const long long want = ceil_div(n_items, h->stream_warps);
       const int sgrid = (int)std::max<long long>(1, std::min<long long>(want, h->sm_count));
       h->stream_fn<<<sgrid, h->stream_warps * 32, stream_smem_bytes(h, h->stream_warps), stream>>>(sa);

@@ -38,6 +38,10 @@ struct Tables {
   int           mel_woff[4];   // float2 offset of each quarter in mel_w
   int           mel_k00, mel_cnt0, mel_woff0;   // segment 0 (below the first mel point): first bin, run, float2 offset
   const float*  dct;           // [n_mfcc][128] ortho DCT-II rows
+  // streaming kernel: linear form of the in-segment mel weights (afx_tables.h, MelSparse::lin / kl / w0)
+  const float4* mel_lin;       // [128] (U0, dU, D0, dD) of (q, lane) at index 32 q + lane
+  const int*    mel_kl;        // [128] first bin | bins << 16
+  const float*  mel_w0;        // [mel_cnt0 rounded up to 4] rising weights of segment 0
 };
 
 __device__ __forceinline__ unsigned float_to_key(float f) {

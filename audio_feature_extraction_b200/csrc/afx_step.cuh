@@ -59,41 +59,53 @@ __device__ __forceinline__ c64 shfl_xor2(c64 v, int m) {
   return pk2(__shfl_xor_sync(0xffffffffu, lo2(v), m), __shfl_xor_sync(0xffffffffu, hi2(v), m));
 }
 
+// Reduce 16 packed (frame A, frame B) values per lane over the warp by shuffles alone: at each of four steps a lane keeps
+// one half of its values and hands the other half to its partner (15 exchanges), the last step splits the pair itself.
+// On return lane j holds the warp total of value j >> 1, frame A on even lanes and frame B on odd lanes.  The kernel is
+// bound by the shared-memory data pipe: 31 SHFL (~0.6 data-pipe cycles each next to LDS traffic, tools/microbench/
+// mio_bench.cu) replace the 64 wavefronts of a transposed reduction through shared memory.
+__device__ __forceinline__ float warp_reduce_scatter_pairs16(c64 (&v)[16], int lane) {
+  int dist = 16;
+#pragma unroll
+  for (int half = 8; half >= 1; half >>= 1, dist >>= 1) {
+    const bool hi = (lane & dist) != 0;
+#pragma unroll
+    for (int i = 0; i < half; ++i) {
+      const c64 send = hi ? v[i] : v[i + half];
+      const c64 keep = hi ? v[i + half] : v[i];
+      v[i] = add2(keep, shfl_xor2(send, dist));
+    }
+  }
+  const bool odd = (lane & 1) != 0;
+  const float send = odd ? lo2(v[0]) : hi2(v[0]);
+  const float keep = odd ? hi2(v[0]) : lo2(v[0]);
+  return keep + __shfl_xor_sync(0xffffffffu, send, 1);
+}
+
 // ---- DCT-II (ortho) of the clamped log-mel rows of two frames, 16 coefficients at a time (mirror pairs as in
-// afx_warp.cuh).  Lane partials are packed (frame A, frame B) pairs: Pc[k][lane]; lane j then sums one half of row
-// j % 16 with 128-bit loads (two pairs each), halves meet by one shuffle, lanes < 16 hold frame A's coefficient.
+// afx_warp.cuh): lane partials as packed (frame A, frame B) pairs, reduced by warp_reduce_scatter_pairs16.
 __device__ __forceinline__ void dct_pair2(const ClipArgs& a, const Smem& sm, float* mfcc_rows, float* planeB,
                                           const float (&da)[4], const float (&db)[4], int row, bool vB, int lane, uint64_t pol) {
-  c64* Pc = reinterpret_cast<c64*>(planeB);   // [16][34]
+  (void)planeB;
   const int stride = 2 * a.n16 + 4;
   const c64 d0 = pk2(da[0], db[0]), d1 = pk2(da[1], db[1]), d2 = pk2(da[2], db[2]), d3 = pk2(da[3], db[3]);
   const c64 e0 = add2(d0, d3), o0 = sub2(d0, d3), e1 = add2(d1, d2), o1 = sub2(d1, d2);
-  const int r = lane & 15, h = lane >> 4;
   for (int kg = 0; kg < a.n16; kg += 16) {
     const float* c0row = sm.dct + lane * stride + kg;   // band lane
     const float* c1row = c0row + a.n16;                 // band 63 - lane
+    c64 p[16];
 #pragma unroll
     for (int k4 = 0; k4 < 4; ++k4) {
       const float4 c0 = *reinterpret_cast<const float4*>(c0row + 4 * k4);
       const float4 c1 = *reinterpret_cast<const float4*>(c1row + 4 * k4);
-      Pc[(4 * k4 + 0) * 34 + lane] = fma2(e0, bc2(c0.x), mul2(e1, bc2(c1.x)));
-      Pc[(4 * k4 + 1) * 34 + lane] = fma2(o0, bc2(c0.y), mul2(o1, bc2(c1.y)));
-      Pc[(4 * k4 + 2) * 34 + lane] = fma2(e0, bc2(c0.z), mul2(e1, bc2(c1.z)));
-      Pc[(4 * k4 + 3) * 34 + lane] = fma2(o0, bc2(c0.w), mul2(o1, bc2(c1.w)));
+      p[4 * k4 + 0] = fma2(e0, bc2(c0.x), mul2(e1, bc2(c1.x)));
+      p[4 * k4 + 1] = fma2(o0, bc2(c0.y), mul2(o1, bc2(c1.y)));
+      p[4 * k4 + 2] = fma2(e0, bc2(c0.z), mul2(e1, bc2(c1.z)));
+      p[4 * k4 + 3] = fma2(o0, bc2(c0.w), mul2(o1, bc2(c1.w)));
     }
-    __syncwarp();
-    const float4* src = reinterpret_cast<const float4*>(Pc + r * 34 + 16 * h);
-    c64 s = 0ull, t = 0ull;
-#pragma unroll
-    for (int i = 0; i < 8; ++i) {
-      const float4 v = src[i];
-      s = add2(s, pk2(v.x, v.y)); t = add2(t, pk2(v.z, v.w));
-    }
-    s = add2(s, t);
-    s = add2(s, shfl_xor2(s, 16));
-    const float cval = h ? hi2(s) : lo2(s);
-    if (h == 0 || vB) st_slab(mfcc_rows + (size_t)(row + h) * a.n16 + kg + r, cval, pol);
-    __syncwarp();
+    const float cval = warp_reduce_scatter_pairs16(p, lane);
+    const int h = lane & 1;
+    if (h == 0 || vB) st_slab(mfcc_rows + (size_t)(row + h) * a.n16 + kg + (lane >> 1), cval, pol);
   }
 }
 
@@ -137,6 +149,28 @@ __device__ __forceinline__ void finish_step2(const ClipArgs& a, const Smem& sm, 
   }
 }
 
+// Inter-stage twiddles z[k1] *= W^(k1 * lane) for k1 < ROWS (registers k1 + ROWS, ... repeat the pattern).  Only the
+// rows k1 = 1..7 and 8, 16, 24 of the table are read (10 instead of 31 shared-memory loads); W^((8 a + b) lane) is the
+// product of two of them: one more rounding (6e-8) per twiddle, 21 complex products per step on a pipe with headroom.
+template <int ROWS>
+__device__ __forceinline__ void twiddle_rows(c64 (&z)[32], const float2* tw, int lane) {
+  float2 B[8], A[4];
+#pragma unroll
+  for (int b = 1; b < 8; ++b) B[b] = tw[b * 32 + lane];
+#pragma unroll
+  for (int a = 1; a < ROWS / 8; ++a) A[a] = tw[8 * a * 32 + lane];
+#pragma unroll
+  for (int j = 0; j < 32; ++j) {
+    const int k1 = j % ROWS, a = k1 >> 3, b = k1 & 7;
+    if (k1 == 0) continue;
+    float2 w;
+    if (a == 0) w = B[b];
+    else if (b == 0) w = A[a];
+    else { w.x = fmaf(A[a].x, B[b].x, -A[a].y * B[b].y); w.y = fmaf(A[a].x, B[b].y, A[a].y * B[b].x); }
+    z[j] = cmul2(z[j], w.x, w.y);
+  }
+}
+
 // issue this warp's next tile: the transposes are done with the tile region (all lanes passed the __syncwarp)
 __device__ __forceinline__ void prefetch_tile(WarpCtx2& wc, unsigned bytes, const float* src, float* dst, int lane) {
   if (lane == 0 && bytes) {
@@ -156,6 +190,151 @@ __device__ __forceinline__ c64 load_rows2(const float* rp0, int p, int gA, const
     return fma2(m, ncoef2, x);   // fl(x - c * x[-1]) per half, as preemph_op
   }
   return pk2(load_y<false>(rp0, 64 * p + lane, gA, rg, L0, coef), load_y<false>(rp0, 64 * p + 32 + lane, gA, rg, L0, coef));
+}
+
+// ---- periodic Hamming window without a table: 0.5 w[n] = 0.27 - 0.23 cos(2 pi n / N) with n = 32 n1 + lane, i.e. the
+// cosine of a sum of a compile-time angle (n1) and a per-lane angle whose (cos, -sin) sits in the twiddle table:
+// two FFMA per value instead of one shared-memory wavefront (the kernel is bound by the shared-memory data pipe)
+__device__ __forceinline__ constexpr float kcos32(int k) {
+  constexpr float t[32] = {1.0f, 0.98078528040323043f, 0.92387953251128674f, 0.83146961230254524f, 0.70710678118654752f,
+    0.55557023301960218f, 0.38268343236508978f, 0.19509032201612825f, 0.0f, -0.19509032201612825f, -0.38268343236508978f,
+    -0.55557023301960218f, -0.70710678118654752f, -0.83146961230254524f, -0.92387953251128674f, -0.98078528040323043f, -1.0f,
+    -0.98078528040323043f, -0.92387953251128674f, -0.83146961230254524f, -0.70710678118654752f, -0.55557023301960218f,
+    -0.38268343236508978f, -0.19509032201612825f, 0.0f, 0.19509032201612825f, 0.38268343236508978f, 0.55557023301960218f,
+    0.70710678118654752f, 0.83146961230254524f, 0.92387953251128674f, 0.98078528040323043f};
+  return t[k & 31];
+}
+__device__ __forceinline__ constexpr float ksin32(int k) { return kcos32(k - 8); }
+// half window at angle (2 pi k32 / 32 + lane angle); (cl, msl) = (cos, -sin) of the lane angle
+__device__ __forceinline__ float half_hamming(int k32, float cl, float msl) {
+  // cos(A + b) = cos A cos b - sin A sin b;  -0.23 cos(A + b) = (-0.23 cos A) cl + (-0.23 sin A) msl
+  return fmaf(-0.23f * kcos32(k32), cl, fmaf(-0.23f * ksin32(k32), msl, 0.27f));
+}
+
+// predicated shared-memory loads: a lane whose predicate is off issues no access (and so takes part in no bank
+// conflict) and gets zero
+__device__ __forceinline__ c64 lds64_if(const c64* p, bool on) {
+  c64 v;
+  asm volatile("{\n\t.reg .pred q;\n\tsetp.ne.s32 q, %2, 0;\n\tmov.b64 %0, 0;\n\t@q ld.shared.b64 %0, [%1];\n\t}" : "=l"(v) : "r"(smem_u32(p)), "r"((int)on));
+  return v;
+}
+__device__ __forceinline__ float lds32_if(const float* p, bool on) {
+  float v;
+  asm volatile("{\n\t.reg .pred q;\n\tsetp.ne.s32 q, %2, 0;\n\tmov.f32 %0, 0f00000000;\n\t@q ld.shared.f32 %0, [%1];\n\t}" : "=f"(v) : "r"(smem_u32(p)), "r"((int)on));
+  return v;
+}
+
+// per-lane mel tables in shared memory (afx_tables.h: MelSparse::lin / kl / w0)
+struct MelLane {
+  const float4* lin;   // [128] (U0, dU, D0, dD)
+  const int* kl;       // [128] first bin | bins << 16
+  const float* w0;     // segment 0
+};
+
+// ---- sparse Slaney mel by segments with weights evaluated on the fly: inside its segment (q, lane) needs
+// U(k0 + i) = U0 + i dU and D(k0 + i) = D0 + i dD (one FFMA each, the scalar broadcasts into the packed FFMA2 for free),
+// and a lane whose segment has ended issues no load (lds64_if), which thins out the bank conflicts of the gather
+// (the padded walk would otherwise fetch other lanes' bins only to weight them with zero).
+// VT = c64: NP packed frame pairs per bin; d[2 p + h][q] as mel_db2.
+template <int NP, typename MC, typename LoadP>
+__device__ __forceinline__ void mel_db3(const ClipArgs& a, const MelLane& ml, LoadP loadp, float (&d)[2 * NP][4], int lane) {
+  c64 U[4][NP], D[4][NP];
+#pragma unroll
+  for (int q = 0; q < 4; ++q) {
+#pragma unroll
+    for (int f = 0; f < NP; ++f) { U[q][f] = 0ull; D[q][f] = 0ull; }
+    const float4 c = ml.lin[32 * q + lane];
+    const int kl = ml.kl[32 * q + lane];
+    const int k0 = kl & 0xffff, len = kl >> 16;
+    auto body = [&](int i) {
+      const float u = fmaf((float)i, c.y, c.x), dd = fmaf((float)i, c.w, c.z);
+      c64 p[NP];
+      loadp(k0 + i, i < len, p);
+#pragma unroll
+      for (int f = 0; f < NP; ++f) { U[q][f] = fma2(p[f], bc2(u), U[q][f]); D[q][f] = fma2(p[f], bc2(dd), D[q][f]); }
+    };
+    if constexpr (MC::kStatic) {
+      constexpr int kCnt[4] = {mel_cnt_static<MC>(0), mel_cnt_static<MC>(1), mel_cnt_static<MC>(2), mel_cnt_static<MC>(3)};
+#pragma unroll
+      for (int i = 0; i < kCnt[q]; ++i) body(i);
+    } else {
+      const int cnt = a.tab.mel_cnt[q];
+#pragma unroll 2
+      for (int i = 0; i < cnt; ++i) body(i);
+    }
+  }
+  c64 u00[NP];   // segment 0: the bins below the first mel point rise into band 0
+#pragma unroll
+  for (int f = 0; f < NP; ++f) u00[f] = 0ull;
+  {
+    auto body0 = [&](int i) {
+      const float w = ml.w0[i];
+      c64 p[NP];
+      loadp(a.tab.mel_k00 + i, true, p);
+#pragma unroll
+      for (int f = 0; f < NP; ++f) u00[f] = fma2(p[f], bc2(w), u00[f]);
+    };
+    if constexpr (MC::kStatic) {
+#pragma unroll
+      for (int i = 0; i < MC::cz; ++i) body0(i);
+    } else {
+      for (int i = 0; i < a.tab.mel_cnt0; ++i) body0(i);
+    }
+  }
+#pragma unroll
+  for (int f = 0; f < NP; ++f) {
+    c64 up0 = __shfl_up_sync(0xffffffffu, U[0][f], 1);     // band lane - 1
+    c64 up1 = __shfl_down_sync(0xffffffffu, U[1][f], 1);   // band 62 - lane = (q1, lane + 1)
+    c64 up2 = __shfl_up_sync(0xffffffffu, U[2][f], 1);     // band 63 + lane = (q2, lane - 1)
+    c64 up3 = __shfl_down_sync(0xffffffffu, U[3][f], 1);   // band 126 - lane = (q3, lane + 1)
+    if (lane == 0) { up0 = u00[f]; up2 = U[1][f]; }        // band 63 is (q1, lane 0)
+    if (lane == 31) { up1 = U[0][f]; up3 = U[2][f]; }      // bands 31 and 95 are (q0, 31) and (q2, 31)
+    const c64 m0 = add2(D[0][f], up0), m1 = add2(D[1][f], up1), m2 = add2(D[2][f], up2), m3 = add2(D[3][f], up3);
+    d[2 * f][0] = to_db(lo2(m0)); d[2 * f + 1][0] = to_db(hi2(m0));
+    d[2 * f][1] = to_db(lo2(m1)); d[2 * f + 1][1] = to_db(hi2(m1));
+    d[2 * f][2] = to_db(lo2(m2)); d[2 * f + 1][2] = to_db(hi2(m2));
+    d[2 * f][3] = to_db(lo2(m3)); d[2 * f + 1][3] = to_db(hi2(m3));
+  }
+}
+// scalar variant (one frame per step, n_fft = 2048): loadp(k) returns the power of bin k
+template <typename MC, typename LoadP>
+__device__ __forceinline__ void mel_db3s(const ClipArgs& a, const MelLane& ml, LoadP loadp, float (&d)[1][4], int lane) {
+  float U[4], D[4];
+#pragma unroll
+  for (int q = 0; q < 4; ++q) {
+    U[q] = 0.f; D[q] = 0.f;
+    const float4 c = ml.lin[32 * q + lane];
+    const int kl = ml.kl[32 * q + lane];
+    const int k0 = kl & 0xffff, len = kl >> 16;
+    auto body = [&](int i) {
+      const float p = loadp(k0 + i, i < len);
+      U[q] = fmaf(fmaf((float)i, c.y, c.x), p, U[q]); D[q] = fmaf(fmaf((float)i, c.w, c.z), p, D[q]);
+    };
+    if constexpr (MC::kStatic) {
+      constexpr int kCnt[4] = {mel_cnt_static<MC>(0), mel_cnt_static<MC>(1), mel_cnt_static<MC>(2), mel_cnt_static<MC>(3)};
+#pragma unroll
+      for (int i = 0; i < kCnt[q]; ++i) body(i);
+    } else {
+      const int cnt = a.tab.mel_cnt[q];
+#pragma unroll 2
+      for (int i = 0; i < cnt; ++i) body(i);
+    }
+  }
+  float u00 = 0.f;
+  if constexpr (MC::kStatic) {
+#pragma unroll
+    for (int i = 0; i < MC::cz; ++i) u00 = fmaf(ml.w0[i], loadp(a.tab.mel_k00 + i, true), u00);
+  } else {
+    for (int i = 0; i < a.tab.mel_cnt0; ++i) u00 = fmaf(ml.w0[i], loadp(a.tab.mel_k00 + i, true), u00);
+  }
+  float up0 = __shfl_up_sync(0xffffffffu, U[0], 1);
+  float up1 = __shfl_down_sync(0xffffffffu, U[1], 1);
+  float up2 = __shfl_up_sync(0xffffffffu, U[2], 1);
+  float up3 = __shfl_down_sync(0xffffffffu, U[3], 1);
+  if (lane == 0) { up0 = u00; up2 = U[1]; }
+  if (lane == 31) { up1 = U[0]; up3 = U[2]; }
+  d[0][0] = to_db(D[0] + up0); d[0][1] = to_db(D[1] + up1);
+  d[0][2] = to_db(D[2] + up2); d[0][3] = to_db(D[3] + up3);
 }
 
 template <int NFFT, int HOP> struct Step2;
@@ -179,14 +358,15 @@ struct Step2<1024, HOP> {
       y[2 * p] = lo2(Y); y[2 * p + 1] = hi2(Y);
       if (2 * p >= R0 && 2 * p < R0 + 2 * SH) E[(2 * p - R0) / SH] = fma2(Y, Y, E[(2 * p - R0) / SH]);
     }
+    const float2 wl = sm.tw[32 + lane];   // W_1024^lane = (cos, -sin) of the lane's share of the window angle
 #pragma unroll
     for (int n1 = 0; n1 < 32; ++n1) {
-      const float w = sm.win[32 * n1 + lane];
+      const float w = half_hamming(n1, wl.x, wl.y);
       z[bitrev32(n1)] = pk2(w * y[n1], w * y[n1 + SH]);
     }
   }
   template <typename MC>
-  static __device__ __forceinline__ void run(const ClipArgs& a, const Smem& sm, const Slab2& sl, WarpCtx2& wc, const Region& rg,
+  static __device__ __forceinline__ void run(const ClipArgs& a, const Smem& sm, const MelLane& ml, const Slab2& sl, WarpCtx2& wc, const Region& rg,
                                              int gA, int L0, int nv, int row, bool own_sums, int usum_idx, float floor_db,
                                              unsigned next_bytes, const float* next_src, float* next_dst) {
     const int lane = threadIdx.x & 31;
@@ -200,11 +380,7 @@ struct Step2<1024, HOP> {
     if (fast) load<true>(z, E, wc.tile + 4, gA, rg, L0, a.coef, sm, lane);
     else load<false>(z, E, wc.tile + 4, gA, rg, L0, a.coef, sm, lane);
     fft32_dit2(z);
-#pragma unroll
-    for (int k1 = 1; k1 < 32; ++k1) {   // twiddle by W_1024^(k1 * lane)
-      const float2 w = sm.tw[k1 * 32 + lane];
-      z[k1] = cmul2(z[k1], w.x, w.y);
-    }
+    twiddle_rows<32>(z, sm.tw, lane);   // z[k1] *= W_1024^(k1 * lane)
     transpose32_bitrev64(z, wc.tile, lane);
     prefetch_tile(wc, next_bytes, next_src, next_dst, lane);
     fft32_dit2(z);   // z[k2] = Z[lane + 32 k2]
@@ -224,7 +400,7 @@ struct Step2<1024, HOP> {
     }
     __syncwarp();
     float d[2][4];
-    mel_db2<1, MC>(a, sm, [P2](int k, c64 (&p)[1]) { p[0] = P2[k]; }, d, lane);
+    mel_db3<1, MC>(a, ml, [P2](int k, bool on, c64 (&p)[1]) { p[0] = lds64_if(P2 + k, on); }, d, lane);
     __syncwarp();   // P2 consumed: region B is free for the DCT reduction
     float eb[2] = {lo2(E[0]) + hi2(E[0]), lo2(E[1]) + hi2(E[1])};
     finish_step2<1024, HOP>(a, sm, sl, wc, d, eb, nv, row, own_sums, usum_idx, floor_db, lane);
@@ -253,15 +429,16 @@ struct Step2<512, HOP> {
         if (2 * p >= R0 && 2 * p < R0 + 4 * SH) E[(2 * p - R0) / SH] = fma2(Y, Y, E[(2 * p - R0) / SH]);
       }
     }
+    const float2 wl = sm.tw[32 + lane];   // W_512^lane
 #pragma unroll
     for (int n1 = 0; n1 < 16; ++n1) {
-      const float w = sm.win[32 * n1 + lane];
+      const float w = half_hamming(2 * n1, wl.x, wl.y);
       z[bitrev16(n1)] = pk2(w * y[n1], w * y[n1 + SH]);
       z[16 + bitrev16(n1)] = pk2(w * y[n1 + 2 * SH], w * y[n1 + 3 * SH]);
     }
   }
   template <typename MC>
-  static __device__ __forceinline__ void run(const ClipArgs& a, const Smem& sm, const Slab2& sl, WarpCtx2& wc, const Region& rg,
+  static __device__ __forceinline__ void run(const ClipArgs& a, const Smem& sm, const MelLane& ml, const Slab2& sl, WarpCtx2& wc, const Region& rg,
                                              int gA, int L0, int nv, int row, bool own_sums, int usum_idx, float floor_db,
                                              unsigned next_bytes, const float* next_src, float* next_dst) {
     static_assert(HOP >= 64, "hop-block sums are accumulated per row pair");
@@ -276,12 +453,7 @@ struct Step2<512, HOP> {
     if (fast) load<true>(z, E, wc.tile + 4, gA, rg, L0, a.coef, sm, lane);
     else load<false>(z, E, wc.tile + 4, gA, rg, L0, a.coef, sm, lane);
     fft16x2_dit2(z);
-#pragma unroll
-    for (int j = 0; j < 32; ++j) {      // twiddle by W_512^(k1 * lane), k1 = j & 15
-      if ((j & 15) == 0) continue;
-      const float2 w = sm.tw[(j & 15) * 32 + lane];
-      z[j] = cmul2(z[j], w.x, w.y);
-    }
+    twiddle_rows<16>(z, sm.tw, lane);   // z[16 s + k1] *= W_512^(k1 * lane)
     transpose32_bitrev64(z, wc.tile, lane);
     prefetch_tile(wc, next_bytes, next_src, next_dst, lane);
     fft32_dit2(z);   // lane 16 s + k1: z[k2] = Z_s[k1 + 16 k2]
@@ -302,7 +474,7 @@ struct Step2<512, HOP> {
     }
     __syncwarp();
     float d[4][4];
-    mel_db2<2, MC>(a, sm, [P2](int k, c64 (&p)[2]) { p[0] = P2[k]; p[1] = P2[PSTRIDE + k]; }, d, lane);
+    mel_db3<2, MC>(a, ml, [P2](int k, bool on, c64 (&p)[2]) { p[0] = lds64_if(P2 + k, on); p[1] = lds64_if(P2 + PSTRIDE + k, on); }, d, lane);
     __syncwarp();
     float eb[4];
 #pragma unroll
@@ -320,7 +492,7 @@ struct Step2<2048, HOP> {
   template <bool FAST>
   static __device__ __forceinline__ void load(c64 (&z)[32], c64& E, const float* rp0, int gA, const Region& rg, int L0,
                                               float coef, const Smem& sm, int lane) {
-    const c64* win2 = reinterpret_cast<const c64*>(sm.win);
+    const float2 wa = sm.ptw[2 * lane], wb = sm.ptw[2 * lane + 1];   // W_2048^(2 lane), W_2048^(2 lane + 1)
     constexpr int R0 = G::G0 * (HOP / 64), R1 = R0 + HOP / 64;   // rows (64 samples each) of the owned hop block
 #pragma unroll
     for (int n1 = 0; n1 < 32; ++n1) {
@@ -333,11 +505,11 @@ struct Step2<2048, HOP> {
         Y = pk2(load_y<false>(rp0, t, gA, rg, L0, coef), load_y<false>(rp0, t + 1, gA, rg, L0, coef));
       }
       if (n1 >= R0 && n1 < R1) E = fma2(Y, Y, E);
-      z[bitrev32(n1)] = mul2(win2[32 * n1 + lane], Y);
+      z[bitrev32(n1)] = mul2(pk2(half_hamming(n1, wa.x, wa.y), half_hamming(n1, wb.x, wb.y)), Y);
     }
   }
   template <typename MC>
-  static __device__ __forceinline__ void run(const ClipArgs& a, const Smem& sm, const Slab2& sl, WarpCtx2& wc, const Region& rg,
+  static __device__ __forceinline__ void run(const ClipArgs& a, const Smem& sm, const MelLane& ml, const Slab2& sl, WarpCtx2& wc, const Region& rg,
                                              int gA, int L0, int nv, int row, bool own_sums, int usum_idx, float floor_db,
                                              unsigned next_bytes, const float* next_src, float* next_dst) {
     static_assert(HOP >= 64, "hop-block sums are accumulated per 64-sample row");
@@ -352,11 +524,7 @@ struct Step2<2048, HOP> {
     if (fast) load<true>(z, E, wc.tile + 4, gA, rg, L0, a.coef, sm, lane);
     else load<false>(z, E, wc.tile + 4, gA, rg, L0, a.coef, sm, lane);
     fft32_dit2(z);
-#pragma unroll
-    for (int k1 = 1; k1 < 32; ++k1) {
-      const float2 w = sm.tw[k1 * 32 + lane];
-      z[k1] = cmul2(z[k1], w.x, w.y);
-    }
+    twiddle_rows<32>(z, sm.tw, lane);
     transpose32_bitrev64(z, wc.tile, lane);
     prefetch_tile(wc, next_bytes, next_src, next_dst, lane);
     fft32_dit2(z);   // z[k2] = Z[lane + 32 k2]
@@ -380,7 +548,7 @@ struct Step2<2048, HOP> {
     }
     __syncwarp();
     float d[1][4];
-    mel_db<1, MC>(a, sm, [P](int k, float (&p)[1]) { p[0] = P[k]; }, d, lane);
+    mel_db3s<MC>(a, ml, [P](int k, bool on) { return lds32_if(P + k, on); }, d, lane);
     __syncwarp();
     float eb[1] = {lo2(E) + hi2(E)};
     finish_step2<2048, HOP>(a, sm, sl, wc, d, eb, nv, row, own_sums, usum_idx, floor_db, lane);

@@ -21,6 +21,7 @@
 namespace afx {
 
 constexpr int kStreamMaxWarps = 16;
+constexpr int kStreamWarpSlots = 24;   // per-CTA mbarrier / scratch slots (an experimental 20-warp variant exists)
 
 struct __align__(16) WorkItem {       // 32 bytes, built on the device (item_build_kernel)
   long long audio_off;                // sample offset of the clip in the packed buffer
@@ -44,6 +45,7 @@ struct StreamArgs {
   int n_slots;
   int* slot_owner;                    // [n_slots] clip that may use the slot (initially the slot index)
   int* slot_done;                     // [n_slots] items of the owner that have been completed
+  int mel_w0_floats;                  // floats of Tables::mel_w0 (multiple of 4)
 };
 
 // one thread per clip: the clip's items (item_off: host-built prefix; frames_per_item: multiple of the step width)
@@ -128,91 +130,96 @@ __device__ __forceinline__ ClipInfo trim_decide_warp(const float* usum, int nu, 
 }
 
 // ---- C: delta / delta2 (SavGol 9) -> moments of coefficients [kg, kg + 16) for trimmed frames [0, T), one warp.
-// sM [stat_frames + 8][17] floats is the warp's own buffer.  Lane c < 16 returns the six sums of coefficient kg + c.
+// Lane = (coefficient c = lane & 15, half h = lane >> 4): half h takes the frames f = h (mod 2), so a lane carries its
+// six sums across the whole clip and the halves meet in one shuffle at the end (no reduction per sub-chunk).  sM
+// [stat_rows][16] floats is the warp's own buffer (row pitch 16: the two halves read adjacent rows = disjoint banks).
+// The 9-tap filters run in float32: scipy accumulates them in float64 and rounds to float32; evaluating in float32
+// moves a delta by <= a few ulp of the largest tap product (~1e-5 for |mfcc| ~ 500), far inside the 1e-3 tolerance.
+// Lanes c < 16 of half 0 return the six sums of coefficient kg + c (valid where kg + c < n_mfcc).
 __device__ __forceinline__ void mfcc_phase_warp(const ClipArgs& a, const float* mfcc_rows, int a0, int T, long long out_row0,
-                                                int kg, float* sM, int kStatFramesW, double (&acc)[kMoments], uint64_t pol, int lane) {
-  constexpr int mstride = 17;
-#pragma unroll
-  for (int m = 0; m < kMoments; ++m) acc[m] = 0.0;
-  const int nc = min(16, a.n_mfcc - kg);
-  for (int f_lo = 0; f_lo < T; f_lo += kStatFramesW) {
-    const int f_hi = min(f_lo + kStatFramesW, T);             // exclusive
+                                                int kg, float* sM, int stat_frames, double (&acc)[kMoments], uint64_t pol, int lane) {
+  const int c = lane & 15, h = lane >> 4;
+  const bool on = kg + c < a.n_mfcc;
+  double s1 = 0, s2 = 0, s3 = 0, s4 = 0;
+  float sd1 = 0.f, sd2 = 0.f;   // running sums of the float32 deltas (a few hundred terms of magnitude <~ 10)
+  double sd1d = 0, sd2d = 0;
+  for (int f_lo = 0; f_lo < T; f_lo += stat_frames) {
+    const int f_hi = min(f_lo + stat_frames, T);             // exclusive
     const int e_lo = min(max(f_lo, kStatHalo), T - 1 - kStatHalo) - kStatHalo;
     const int e_hi = min(max(f_hi - 1, kStatHalo), T - 1 - kStatHalo) + kStatHalo;   // inclusive
-    const int ne = e_hi - e_lo + 1;                           // <= kStatFramesW + 8
+    const int ne = e_hi - e_lo + 1;                           // <= stat_frames + 8
     __syncwarp();
     {
       const float* src = mfcc_rows + (size_t)(a0 + e_lo) * a.n16 + kg;
-      for (int i = lane; i < ne * 16; i += 32) {
-        const int e = i >> 4, c = i & 15;
-        sM[e * mstride + c] = ld_slab(src + (size_t)e * a.n16 + c, pol);
-      }
+      for (int i = lane; i < ne * 16; i += 32) sM[i] = ld_slab(src + (size_t)(i >> 4) * a.n16 + (i & 15), pol);
     }
     __syncwarp();
-    for (int c = 0; c < nc; ++c) {
-      double s1 = 0, s2 = 0, s3 = 0, s4 = 0, sd1 = 0, sd2 = 0;
-      for (int f = f_lo + lane; f < f_hi; f += 32) {
-        const int te = min(max(f, kStatHalo), T - 1 - kStatHalo) - e_lo;   // centre row of the 9-tap window
-        const float* col = sM + c;
-        // savgol(9, polyorder=deriv=1): sum k x[t+k] / 60 ; (9, 2, 2): sum c_k x[t+k] / 462  (double, cast to f32)
-        const double xm4 = col[(te - 4) * mstride], xm3 = col[(te - 3) * mstride], xm2 = col[(te - 2) * mstride],
-                     xm1 = col[(te - 1) * mstride], x0 = col[te * mstride], xp1 = col[(te + 1) * mstride],
-                     xp2 = col[(te + 2) * mstride], xp3 = col[(te + 3) * mstride], xp4 = col[(te + 4) * mstride];
-        const double d1 = (4.0 * (xp4 - xm4) + 3.0 * (xp3 - xm3) + 2.0 * (xp2 - xm2) + (xp1 - xm1)) / 60.0;
-        const double d2 = (28.0 * (xp4 + xm4) + 7.0 * (xp3 + xm3) - 8.0 * (xp2 + xm2) - 17.0 * (xp1 + xm1) - 20.0 * x0) / 462.0;
-        const float d1f = (float)d1, d2f = (float)d2;
-        const float xf = col[(f - e_lo) * mstride];
-        const double x = xf;
-        s1 += x; s2 += x * x; s3 += x * x * x; s4 += (x * x) * (x * x);
-        sd1 += (double)d1f; sd2 += (double)d2f;
-        if (a.frames_out) {
-          float* fr = a.frames_out + (size_t)(out_row0 + f) * a.frame_width;
-          fr[kg + c] = xf; fr[a.n_mfcc + kg + c] = d1f; fr[2 * a.n_mfcc + kg + c] = d2f;
-        }
+    const float* col = sM + c;
+    for (int f = f_lo + ((f_lo ^ h) & 1); f < f_hi; f += 2) {
+      const int te = min(max(f, kStatHalo), T - 1 - kStatHalo) - e_lo;   // centre row of the 9-tap window
+      const float xm4 = col[(te - 4) * 16], xm3 = col[(te - 3) * 16], xm2 = col[(te - 2) * 16], xm1 = col[(te - 1) * 16],
+                  x0 = col[te * 16], xp1 = col[(te + 1) * 16], xp2 = col[(te + 2) * 16], xp3 = col[(te + 3) * 16],
+                  xp4 = col[(te + 4) * 16];
+      // savgol(9, polyorder = deriv = 1): sum k x[t+k] / 60 ; (9, 2, 2): sum c_k x[t+k] / 462
+      const float d1f = fmaf(4.0f / 60.0f, xp4 - xm4, fmaf(3.0f / 60.0f, xp3 - xm3, fmaf(2.0f / 60.0f, xp2 - xm2, (1.0f / 60.0f) * (xp1 - xm1))));
+      const float d2f = fmaf(28.0f / 462.0f, xp4 + xm4, fmaf(7.0f / 462.0f, xp3 + xm3, fmaf(-8.0f / 462.0f, xp2 + xm2,
+                        fmaf(-17.0f / 462.0f, xp1 + xm1, (-20.0f / 462.0f) * x0))));
+      const float xf = col[(f - e_lo) * 16];
+      const double x = xf, x2 = x * x;
+      s1 += x; s2 += x2; s3 += x2 * x; s4 += x2 * x2;
+      sd1 += d1f; sd2 += d2f;
+      if (a.frames_out && on) {
+        float* fr = a.frames_out + (size_t)(out_row0 + f) * a.frame_width;
+        fr[kg + c] = xf; fr[a.n_mfcc + kg + c] = d1f; fr[2 * a.n_mfcc + kg + c] = d2f;
       }
-      s1 = warp_sum(s1); s2 = warp_sum(s2); s3 = warp_sum(s3); s4 = warp_sum(s4);
-      sd1 = warp_sum(sd1); sd2 = warp_sum(sd2);
-      if (lane == c) { acc[0] += s1; acc[1] += s2; acc[2] += s3; acc[3] += s4; acc[4] += sd1; acc[5] += sd2; }
     }
+    sd1d += (double)sd1; sd2d += (double)sd2; sd1 = 0.f; sd2 = 0.f;   // fold per sub-chunk: keeps the float sums short
   }
+  acc[0] = s1 + __shfl_xor_sync(0xffffffffu, s1, 16); acc[1] = s2 + __shfl_xor_sync(0xffffffffu, s2, 16);
+  acc[2] = s3 + __shfl_xor_sync(0xffffffffu, s3, 16); acc[3] = s4 + __shfl_xor_sync(0xffffffffu, s4, 16);
+  acc[4] = sd1d + __shfl_xor_sync(0xffffffffu, sd1d, 16); acc[5] = sd2d + __shfl_xor_sync(0xffffffffu, sd2d, 16);
   __syncwarp();
 }
 
 // ---- the kernel.  STOCK: the mel tables carry the stock run lengths of this frame length (MelCnt<NFFT, true>)
-template <int NFFT, int HOP, bool STOCK = false>
-__global__ void __launch_bounds__(kStreamMaxWarps * 32, 1) stream_kernel(StreamArgs sa) {
+template <int NFFT, int HOP, bool STOCK = false, int MAXW = kStreamMaxWarps>
+__global__ void __launch_bounds__(MAXW * 32, 1) stream_kernel(StreamArgs sa) {
   const ClipArgs& a = sa.c;
   using G = Geo<NFFT, HOP>;
   constexpr int FPW = G::FPW;
   constexpr int WB = WarpBuf<NFFT, HOP>::kBytes;
   extern __shared__ __align__(16) unsigned char smem_raw[];
-  // layout: [16 tile mbarriers][16 item mbarriers][16 warp scratch blocks][twiddle 8 KB][W_2048 table][window]
-  //         [DCT rows per lane][mel weights][per-warp buffers]
+  // layout: [16 tile mbarriers][16 item mbarriers][16 warp scratch blocks][twiddle 8 KB][W_2048 table]
+  //         [DCT rows per lane][mel lane tables][per-warp buffers]
   Smem sm;
   sm.mbar = reinterpret_cast<uint64_t*>(smem_raw);
-  constexpr int SCR = kStreamMaxWarps * (int)sizeof(WarpScratch);
-  WarpScratch* s_scr = reinterpret_cast<WarpScratch*>(smem_raw + 256);
-  sm.tw = reinterpret_cast<float2*>(smem_raw + 256 + SCR);
+  constexpr int SCR = kStreamWarpSlots * (int)sizeof(WarpScratch);
+  WarpScratch* s_scr = reinterpret_cast<WarpScratch*>(smem_raw + 512);
+  sm.tw = reinterpret_cast<float2*>(smem_raw + 512 + SCR);
   constexpr int PTW_BYTES = NFFT == 2048 ? 4112 : 0;
-  sm.ptw = reinterpret_cast<float2*>(smem_raw + 256 + SCR + 8192);
-  sm.win = reinterpret_cast<float*>(smem_raw + 256 + SCR + 8192 + PTW_BYTES);
-  float* sDct = sm.win + NFFT;
+  sm.ptw = reinterpret_cast<float2*>(smem_raw + 512 + SCR + 8192);
+  sm.win = nullptr;   // the window is evaluated on the fly (half_hamming)
+  float* sDct = reinterpret_cast<float*>(smem_raw + 512 + SCR + 8192 + PTW_BYTES);
   const int dstride = 2 * a.n16 + 4;
-  float* sMel = sDct + 32 * dstride;
-  sm.dct = sDct; sm.melw = sMel;
-  unsigned char* wbufs = reinterpret_cast<unsigned char*>(sMel + a.mel_floats);
+  float4* sLin = reinterpret_cast<float4*>(sDct + 32 * dstride);
+  int* sKl = reinterpret_cast<int*>(sLin + 128);
+  float* sW0 = reinterpret_cast<float*>(sKl + 128);
+  sm.dct = sDct; sm.melw = nullptr;
+  MelLane ml;
+  ml.lin = sLin; ml.kl = sKl; ml.w0 = sW0;
+  unsigned char* wbufs = reinterpret_cast<unsigned char*>(sW0 + sa.mel_w0_floats);
   sm.raw = nullptr; sm.planes = nullptr;
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   for (int i = tid; i < 1024; i += (int)blockDim.x) sm.tw[i] = a.tab.twiddle[i];
-  for (int i = tid; i < NFFT; i += (int)blockDim.x) sm.win[i] = a.tab.window_half[i];
   if (NFFT == 2048) for (int i = tid; i <= 512; i += (int)blockDim.x) sm.ptw[i] = a.tab.post_twiddle[i];
   for (int i = tid; i < 64 * a.n16; i += (int)blockDim.x) {
     const int l = i / (2 * a.n16), rem = i - l * 2 * a.n16, hsel = rem / a.n16, k = rem - hsel * a.n16;
     sDct[l * dstride + rem] = a.dct_t[(hsel ? 63 - l : l) * a.n16 + k];
   }
-  for (int i = tid; i < a.mel_floats; i += (int)blockDim.x) sMel[i] = a.tab.mel_w[i];
-  if (tid < 2 * kStreamMaxWarps) mbar_init(sm.mbar + tid, 1);
+  for (int i = tid; i < 128; i += (int)blockDim.x) { sLin[i] = a.tab.mel_lin[i]; sKl[i] = a.tab.mel_kl[i]; }
+  for (int i = tid; i < sa.mel_w0_floats; i += (int)blockDim.x) sW0[i] = a.tab.mel_w0[i];
+  if (tid < 2 * kStreamWarpSlots) mbar_init(sm.mbar + tid, 1);
   if (tid == 0) fence_mbar_init();
   __syncthreads();
   // ---- from here on every warp is on its own
@@ -224,7 +231,7 @@ __global__ void __launch_bounds__(kStreamMaxWarps * 32, 1) stream_kernel(StreamA
   wc.parity = 0;
   wc.pol_in = l2_policy_evict_first();
   wc.pol_slab = l2_policy_evict_last();
-  uint64_t* mb_item = sm.mbar + kStreamMaxWarps + warp;
+  uint64_t* mb_item = sm.mbar + kStreamWarpSlots + warp;
   unsigned par_item = 0;
   WarpScratch& scr = s_scr[warp];
   WorkItem* my_items = scr.item;
@@ -355,7 +362,7 @@ __global__ void __launch_bounds__(kStreamMaxWarps * 32, 1) stream_kernel(StreamA
           }
         }
         if (cur_bytes) { mbar_wait(wc.mbar, wc.parity); wc.parity ^= 1u; }
-        Step2<NFFT, HOP>::template run<MelCnt<NFFT, STOCK>>(a, sm, sl, wc, rg, gA, L0, min(FPW, f_end - fA), shift + fA, own, fA,
+        Step2<NFFT, HOP>::template run<MelCnt<NFFT, STOCK>>(a, sm, ml, sl, wc, rg, gA, L0, min(FPW, f_end - fA), shift + fA, own, fA,
                                                             floor_db, next_bytes, next_src, wc.tile + s_lo);
         if (pass == 0 && !nxt_requested && nxt < sa.n_items) { fetch_item(nxt, buf ^ 1); nxt_requested = true; item_in_flight = true; }
         fA = fN; cur_bytes = next_bytes;
@@ -439,7 +446,7 @@ __global__ void __launch_bounds__(kStreamMaxWarps * 32, 1) stream_kernel(StreamA
         if (a.mask & 0x2u) {
           for (int kg = 0; kg < n; kg += 16) {
             double acc[kMoments];
-            mfcc_phase_warp(a, sl.mfcc, a0, T, out_row0, kg, wc.tile, (WB / 4) / 17 - 2 * kStatHalo, acc, wc.pol_slab, lane);
+            mfcc_phase_warp(a, sl.mfcc, a0, T, out_row0, kg, wc.tile, ((WB / 4) / 16 - 2 * kStatHalo) & ~1, acc, wc.pol_slab, lane);
             const int c = kg + lane;
             if (lane < 16 && c < n) {
               const double s1 = acc[0], s2 = acc[1], s3 = acc[2], s4 = acc[3];

@@ -66,6 +66,13 @@ struct MelSparse {
   int woff[4];                // float2 offset of each quarter in w
   int k00, cnt0, woff0;       // segment 0: first bin, run length, float2 offset
   int nnz;
+  // streaming kernel (afx_step.cuh): inside a segment both weights are linear in the bin index, so (q, lane) carries
+  // lin[4 (32 q + lane) ..] = (U0, dU, D0, dD) with U(k0 + i) = U0 + i dU, D(k0 + i) = D0 + i dD (double arithmetic,
+  // rounded once), and kl[32 q + lane] = first bin | (bins in the segment << 16); w0[i] = segment 0's rising weights
+  std::vector<float> lin;
+  std::vector<int> kl;
+  std::vector<float> w0;
+  double lin_max_err = 0;     // largest |linear weight - librosa float32 weight| over all in-segment entries
 };
 
 inline MelSparse mel_sparse(int sr, int n_fft, int n_mels = 128) {
@@ -133,6 +140,31 @@ inline MelSparse mel_sparse(int sr, int n_fft, int n_mels = 128) {
   ms.woff0 = off;
   ms.w.resize(2 * (size_t)(off + ((ms.cnt0 + 1) & ~1)), 0.f);   // keeps the float count a multiple of 4
   for (int i = 0; i < ms.cnt0; ++i) ms.w[2 * (size_t)(off + i)] = wU(0, ms.k00 + i);
+  // linear form of the in-segment weights for the streaming kernel
+  ms.lin.assign(4 * 128, 0.f);
+  ms.kl.assign(128, 0);
+  for (int q = 0; q < 4; ++q)
+    for (int l = 0; l < 32; ++l) {
+      const int s = mel_band_of(q, l) + 1;                 // segment between mel_f[s] and mel_f[s + 1]
+      const bool has = slast[s] >= sfirst[s];
+      const int k0 = has ? sfirst[s] : 0, len = has ? slast[s] - sfirst[s] + 1 : 0;
+      const double width = mel_f[s + 1] - mel_f[s];
+      // rising side of band s (absent for s = n_mels), falling side of band s - 1
+      const double en_u = s < n_mels ? 2.0 / (mel_f[s + 2] - mel_f[s]) : 0.0;
+      const double en_d = 2.0 / (mel_f[s + 1] - mel_f[s - 1]);
+      const double U0 = (fftfreqs[k0] - mel_f[s]) / width * en_u, dU = val / width * en_u;
+      const double D0 = (mel_f[s + 1] - fftfreqs[k0]) / width * en_d, dD = -val / width * en_d;
+      float* o = &ms.lin[4 * (size_t)(32 * q + l)];
+      o[0] = (float)U0; o[1] = (float)dU; o[2] = (float)D0; o[3] = (float)dD;
+      ms.kl[32 * q + l] = k0 | (len << 16);
+      for (int i = 0; i < len; ++i) {
+        const float u = fmaf((float)i, o[1], o[0]), d = fmaf((float)i, o[3], o[2]);
+        ms.lin_max_err = std::fmax(ms.lin_max_err, std::fabs((double)u - (double)wU(s, k0 + i)));
+        ms.lin_max_err = std::fmax(ms.lin_max_err, std::fabs((double)d - (double)wD(s, k0 + i)));
+      }
+    }
+  ms.w0.assign(4, 0.f);
+  for (int i = 0; i < ms.cnt0 && i < 4; ++i) ms.w0[i] = wU(0, ms.k00 + i);
   // every non-zero weight must be covered exactly once
   {
     long covered = 0;
