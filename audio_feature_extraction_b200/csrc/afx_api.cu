@@ -18,7 +18,6 @@
 #include <vector>
 
 #include "afx_common.cuh"
-#include "afx_clip.cuh"
 #include "afx_stream.cuh"
 #include "afx_extras.cuh"
 #include "afx_pyin.cuh"
@@ -74,13 +73,9 @@ struct afx_handle_s {
   int yin_c = 0, yin_cap = 0, yin_rec_bytes = 0, yin_lag_pad = 0, yin_tile = 0, yin_frames_per_chunk = 0;
   size_t yin_smem = 0, vit_smem = 0;
   void* d_f0_ws = nullptr; size_t d_f0_ws_bytes = 0;   // handle-owned scratch of the F0 path (observation rows, back-pointers)
-  int clip_warps = 16;     // warps per CTA of the fused kernel
-  int ctas_per_sm = 1;
   int mel_floats = 0;      // floats in the padded sparse mel weight table
   int sm_count;
-  void (*clip_fn)(afx::ClipArgs) = nullptr;   // clip_kernel<frame_length, hop_length> (AFX_CLIP_IMPL=cta: the round-1 CTA-per-clip kernel)
   void (*stream_fn)(afx::StreamArgs) = nullptr;   // stream_kernel<frame_length, hop_length>: warp-autonomous streaming kernel
-  bool use_stream = true;
   int stream_warps = 16;   // warps per CTA of the streaming kernel (one CTA per SM)
   int item_steps = 0;      // warp steps per work item; 0 = chosen per batch (item_steps_for)
   void (*vit_fn)(afx::VitArgs) = nullptr;     // viterbi_kernel<half width or 0>
@@ -181,13 +176,13 @@ size_t slab_bytes_for(const afx_handle_s* h, long long max_len) {
   const size_t rows = (size_t)slab_rows(h, max_len);
   return align_up((rows * ((size_t)h->n16 + 4) + 8) * sizeof(float), 256);   // MFCC rows, rms, row max / min, hop-block sums
 }
-inline int grid_for(const afx_handle_s* h, long long n_clips) { return (int)std::max<long long>(1, std::min<long long>(n_clips, (long long)h->sm_count * h->ctas_per_sm)); }
 
 // the speculative single pass needs every trimmed frame centre (start = k*512) on the absolute hop grid
-inline bool single_pass(const afx_handle_s* h) { return afx::kTrimHop % h->cfg.hop_length == 0 && h->cfg.hop_length >= 16; }
+inline bool runtime_hop(int n_fft, int hop) { return !(hop * 2 == n_fft || hop * 4 == n_fft || hop * 8 == n_fft); }
+inline bool single_pass(const afx_handle_s* h) { return afx::kTrimHop % h->cfg.hop_length == 0 && !runtime_hop(h->cfg.frame_length, h->cfg.hop_length); }
 
-// the fused kernel is instantiated per (frame_length, hop_length): hop = frame_length / 2, / 4, / 8
-typedef void (*clip_fn_t)(afx::ClipArgs);
+// the streaming kernel is instantiated per (frame_length, hop_length) for hop = frame_length / 2, / 4, / 8, plus one
+// run-time-hop variant per frame length.
 // stock: the mel tables have MelCnt<n_fft, true>'s run lengths -> the variant with the unrolled segment walk
 // (instantiated for the stock hop of each frame length: 1024/256, 512/128, 2048/512)
 template <int NFFT>
@@ -195,36 +190,6 @@ bool mel_counts_are_stock(const afx::host::MelSparse& m) {
   using MC = afx::MelCnt<NFFT, true>;
   return m.cnt[0] == MC::c0 && m.cnt[1] == MC::c1 && m.cnt[2] == MC::c2 && m.cnt[3] == MC::c3 && m.cnt0 == MC::cz;
 }
-clip_fn_t clip_kernel_for(int n_fft, int hop, const afx::host::MelSparse& mel) {
-  if (n_fft == 1024 && hop == 256 && mel_counts_are_stock<1024>(mel)) return afx::clip_kernel<1024, 256, true>;
-  if (n_fft == 512 && hop == 128 && mel_counts_are_stock<512>(mel)) return afx::clip_kernel<512, 128, true>;
-  if (n_fft == 2048 && hop == 512 && mel_counts_are_stock<2048>(mel)) return afx::clip_kernel<2048, 512, true>;
-  if (n_fft == 1024) {
-    if (hop == 512) return afx::clip_kernel<1024, 512>;
-    if (hop == 256) return afx::clip_kernel<1024, 256>;
-    if (hop == 128) return afx::clip_kernel<1024, 128>;
-  } else if (n_fft == 512) {
-    if (hop == 256) return afx::clip_kernel<512, 256>;
-    if (hop == 128) return afx::clip_kernel<512, 128>;
-    if (hop == 64) return afx::clip_kernel<512, 64>;
-  } else if (n_fft == 2048) {
-    if (hop == 1024) return afx::clip_kernel<2048, 1024>;
-    if (hop == 512) return afx::clip_kernel<2048, 512>;
-    if (hop == 256) return afx::clip_kernel<2048, 256>;
-  }
-  return nullptr;
-}
-
-size_t clip_smem_bytes(const afx_handle_s* h, int* tile_floats_out) {
-  const int n_fft = h->cfg.frame_length;
-  const int fpw = n_fft == 2048 ? 1 : (n_fft == 1024 ? 2 : 4);           // afx::Geo<>::FPW
-  const int tile_floats = (fpw - 1) * h->cfg.hop_length + n_fft + 8;     // per-warp raw tile, afx::Geo<>::RAWW
-  if (tile_floats_out) *tile_floats_out = tile_floats;
-  return 128 + 8192 + (n_fft == 2048 ? 4112 : 0) + (size_t)n_fft * 4 + (size_t)(afx::kMoments * afx::kMaxMfcc + 64) * 8 +
-         (size_t)32 * (2 * h->n16 + 4) * 4 + (size_t)h->mel_floats * 4 +
-         (size_t)h->clip_warps * (tile_floats + afx::kPlaneFloats) * 4;
-}
-
 typedef void (*stream_fn_t)(afx::StreamArgs);
 stream_fn_t stream_kernel_for(int n_fft, int hop, const afx::host::MelSparse& mel) {
   if (n_fft == 1024 && hop == 256 && mel_counts_are_stock<1024>(mel)) return afx::stream_kernel<1024, 256, true>;
@@ -243,14 +208,22 @@ stream_fn_t stream_kernel_for(int n_fft, int hop, const afx::host::MelSparse& me
     if (hop == 512) return afx::stream_kernel<2048, 512>;
     if (hop == 256) return afx::stream_kernel<2048, 256>;
   }
+  // any other hop <= n_fft / 2: the run-time-hop variant (frames of a step are read separately, the trim runs first)
+  if (hop >= 1 && hop <= n_fft / 2) {
+    if (n_fft == 1024) return afx::stream_kernel<1024, 0>;
+    if (n_fft == 512) return afx::stream_kernel<512, 0>;
+    if (n_fft == 2048) return afx::stream_kernel<2048, 0>;
+  }
   return nullptr;
 }
+
 
 inline int frames_per_step(const afx_handle_s* h) { return h->cfg.frame_length == 2048 ? 1 : (h->cfg.frame_length == 1024 ? 2 : 4); }
 
 // bytes of one warp's buffer of the streaming kernel (afx::WarpBuf<>::kBytes)
 inline size_t stream_warp_bytes(const afx_handle_s* h) {
-  const size_t tile = (size_t)((frames_per_step(h) - 1) * h->cfg.hop_length + h->cfg.frame_length + 8) * 4;
+  const bool rt = runtime_hop(h->cfg.frame_length, h->cfg.hop_length);   // afx::Geo<n_fft, 0>: sized for hop = n_fft / 2
+  const size_t tile = (size_t)((frames_per_step(h) - 1) * (rt ? h->cfg.frame_length / 2 : h->cfg.hop_length) + h->cfg.frame_length + (rt ? 12 : 8)) * 4;
   return align_up(std::max<size_t>(tile + afx::kPlaneBFloats * 4, afx::kPlaneTBytes), 16);
 }
 size_t stream_smem_bytes(const afx_handle_s* h, int warps) {
@@ -312,9 +285,6 @@ int afx_create(const afx_config_t* cfg, afx_handle_t* out) {
     return fail(AFX_ERR_UNSUPPORTED, "frame_length %d not supported (512, 1024 or 2048)", cfg->frame_length);
   if (cfg->hop_length < 1 || cfg->hop_length > cfg->frame_length / 2)
     return fail(AFX_ERR_INVALID_ARG, "hop_length %d out of range [1, frame_length/2]", cfg->hop_length);
-  if (!clip_kernel_for(cfg->frame_length, cfg->hop_length, afx::host::MelSparse{}))
-    return fail(AFX_ERR_UNSUPPORTED, "frame_length %d / hop_length %d: this build has kernels for hop = frame_length/2, /4, /8",
-                cfg->frame_length, cfg->hop_length);
   if (cfg->n_mfcc < 1 || cfg->n_mfcc > afx::kMaxMfcc) return fail(AFX_ERR_INVALID_ARG, "n_mfcc %d out of range [1,64]", cfg->n_mfcc);
   if (cfg->n_mels != afx::kNMels) return fail(AFX_ERR_UNSUPPORTED, "n_mels must be 128");
   if (cfg->sr < 1000) return fail(AFX_ERR_INVALID_ARG, "sr %d too small", cfg->sr);
@@ -370,25 +340,8 @@ int afx_create(const afx_config_t* cfg, afx_handle_t* out) {
   h->tab.dct = nullptr;
 
   CUDA_TRY(cudaFuncSetAttribute(afx::trim_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-  h->clip_fn = clip_kernel_for(cfg->frame_length, cfg->hop_length, mel);
-  // two 8-warp CTAs per SM (one clip each: the serial trim / fix-up / statistics phases of one hide behind the
-  // streaming phase of the other) when their shared memory fits twice; else one 16-warp CTA
-  {
-    const int cand[4][2] = {{8, 2}, {16, 1}, {12, 1}, {8, 1}};
-    bool found = false;
-    const char* e = getenv("AFX_CLIP_WARPS");
-    for (int c = 0; c < 4 && !found; ++c) {
-      h->clip_warps = cand[c][0]; h->ctas_per_sm = cand[c][1];
-      if (e && atoi(e) != h->clip_warps) continue;
-      const size_t need = clip_smem_bytes(h, nullptr) + 1024;   // + the per-CTA reserve
-      found = need * h->ctas_per_sm <= (size_t)prop.sharedMemPerMultiprocessor && need - 1024 <= (size_t)prop.sharedMemPerBlockOptin;
-    }
-    if (!found) { delete h; return fail(AFX_ERR_UNSUPPORTED, "no CTA shape of the fused kernel fits this device's shared memory"); }
-  }
-  CUDA_TRY(cudaFuncSetAttribute(h->clip_fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)clip_smem_bytes(h, nullptr)));
   {  // the warp-autonomous streaming kernel: one CTA per SM with as many warps as shared memory (and 128 registers) allow
     h->stream_fn = stream_kernel_for(cfg->frame_length, cfg->hop_length, mel);
-    if (const char* e = getenv("AFX_CLIP_IMPL")) h->use_stream = strcmp(e, "cta") != 0;
     if (const char* e = getenv("AFX_ITEM_STEPS")) { const int v = atoi(e); if (v >= 1 && v * frames_per_step(h) <= 255) h->item_steps = v; }
     int w = afx::kStreamMaxWarps;
     if (const char* e = getenv("AFX_STREAM_WARPS")) {
@@ -480,9 +433,8 @@ static size_t workspace_bytes_impl(afx_handle_t h, int64_t n_clips, const int32_
   long long max_len = 0, items = 0;
   const int isteps = item_steps_for(h, n_clips, h_lengths);
   for (int64_t i = 0; i < n_clips; ++i) { max_len = std::max<long long>(max_len, h_lengths[i]); items += items_of(h, h_lengths[i], isteps); }
-  const size_t cta = (size_t)grid_for(h, n_clips) * slab_bytes_for(h, max_len);
   const size_t stream = align_up((size_t)items * sizeof(afx::WorkItem), 256) + (size_t)slots_for(h, n_clips, max_len) * slab_bytes_for(h, max_len);
-  return header_layout(n_clips).header_bytes + std::max(cta, stream) + 1024;
+  return header_layout(n_clips).header_bytes + stream + 1024;
 }
 // header + work-item table + the ring of per-clip slabs; there is no smaller configuration, so both agree
 size_t afx_workspace_bytes(afx_handle_t h, int64_t n_clips, const int32_t* h_lengths) { return workspace_bytes_impl(h, n_clips, h_lengths); }
@@ -554,11 +506,10 @@ int afx_extract(afx_handle_t h, const float* d_audio, const int64_t* h_offsets, 
   if (!one_pass && ceil_div(max_len, afx::kTrimHop) > max_trim_blocks)
     return fail(AFX_ERR_UNSUPPORTED, "afx_extract: clips longer than %lld samples need hop_length dividing 512", max_trim_blocks * afx::kTrimHop);
 
-  const int grid = grid_for(h, n);
   const size_t slab_bytes = slab_bytes_for(h, max_len);
   const int n_slots = slots_for(h, n, max_len);
   const size_t items_bytes = align_up((size_t)n_items * sizeof(afx::WorkItem), 256);
-  if (workspace_bytes < L.header_bytes + (h->use_stream ? items_bytes + (size_t)n_slots * slab_bytes : (size_t)grid * slab_bytes))
+  if (workspace_bytes < L.header_bytes + items_bytes + (size_t)n_slots * slab_bytes)
     return fail(AFX_ERR_WORKSPACE, "afx_extract: workspace of %zu bytes is below afx_workspace_bytes", workspace_bytes);
   char* ws = static_cast<char*>(d_workspace);
   if ((reinterpret_cast<uintptr_t>(ws) & 255u) != 0) return fail(AFX_ERR_INVALID_ARG, "afx_extract: workspace must be 256-byte aligned");
@@ -586,21 +537,16 @@ int afx_extract(afx_handle_t h, const float* d_audio, const int64_t* h_offsets, 
   }
   {
     afx::ClipArgs ca;
-    int tile_floats = 0;
-    const size_t smem = clip_smem_bytes(h, &tile_floats);
     ca.audio = d_audio; ca.offsets = d_offsets; ca.lengths = d_lengths; ca.frame_off = d_frame_off; ca.info = d_info;
     ca.counter = reinterpret_cast<int*>(ws + L.off_counter); ca.n_clips = n;
-    ca.slabs = ws + L.header_bytes; ca.slab_bytes = slab_bytes; ca.a_max = slab_rows(h, max_len);
-    ca.tab = h->tab; ca.dct_t = h->d_dct_t; ca.hop = hop; ca.mel_floats = h->mel_floats;
+    ca.slabs = nullptr; ca.slab_bytes = slab_bytes; ca.a_max = slab_rows(h, max_len);
+    ca.tab = h->tab; ca.dct_t = h->d_dct_t; ca.hop = hop;
     ca.coef = coef; ca.trim_top_db = trim_top_db; ca.mfcc_top_db = h->cfg.mfcc_top_db; ca.raw = raw ? 1 : 0;
     ca.n_mfcc = h->cfg.n_mfcc; ca.n16 = h->n16; ca.summary_width = afx_summary_width(h); ca.frame_width = afx_frame_width(h);
     ca.mask = feature_mask; ca.summaries = d_summaries; ca.meta = d_meta; ca.frames_out = d_frames;
     ca.pretrimmed = one_pass ? 0 : 1;
     PhaseTimer pt(h, stream, AFX_PHASE_FRAMES);
-    if (!h->use_stream) {
-      h->clip_fn<<<grid, h->clip_warps * 32, smem, stream>>>(ca);
-      ++g_launches;
-    } else {
+    {
       afx::StreamArgs sa;
       sa.c = ca;
       sa.c.slabs = ws + L.header_bytes + items_bytes;
@@ -826,9 +772,10 @@ int afx_clip_kernel_variant(int32_t sr, int32_t frame_length, int32_t hop_length
   if (sr < 1 || (frame_length != 512 && frame_length != 1024 && frame_length != 2048)) return -1;
   const auto mel = afx::host::mel_sparse(sr, frame_length, afx::kNMels);
   if (mel_runs) { for (int q = 0; q < 4; ++q) mel_runs[q] = mel.cnt[q]; mel_runs[4] = mel.cnt0; }
-  const clip_fn_t fn = clip_kernel_for(frame_length, hop_length, mel);
+  const stream_fn_t fn = stream_kernel_for(frame_length, hop_length, mel);
   if (!fn) return -1;
-  return fn == clip_kernel_for(frame_length, hop_length, afx::host::MelSparse{}) ? 0 : 1;
+  if (runtime_hop(frame_length, hop_length)) return 2;
+  return fn == stream_kernel_for(frame_length, hop_length, afx::host::MelSparse{}) ? 0 : 1;
 }
 
 int64_t afx_resample_filter(int32_t sr, int32_t native_sr, float* taps, int64_t taps_capacity, int32_t* up, int32_t* down,

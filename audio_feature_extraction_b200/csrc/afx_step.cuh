@@ -346,23 +346,36 @@ struct Step2<1024, HOP> {
   using G = Geo<1024, HOP>;
   template <bool FAST>
   static __device__ __forceinline__ void load(c64 (&z)[32], c64 (&E)[2], const float* rp0, int gA, const Region& rg, int L0,
-                                              float coef, const Smem& sm, int lane) {
-    constexpr int SH = HOP / 32;            // rows by which frame B trails frame A
-    constexpr int NR = 32 + SH;             // rows of the step
-    constexpr int R0 = G::G0 * SH;          // first row of the owned hop blocks
+                                              float coef, int hop, const Smem& sm, int lane) {
     const c64 nc2 = bc2(-coef);
-    float y[NR];
-#pragma unroll
-    for (int p = 0; p < NR / 2; ++p) {
-      const c64 Y = load_rows2<FAST>(rp0, p, gA, rg, L0, coef, nc2, lane);
-      y[2 * p] = lo2(Y); y[2 * p + 1] = hi2(Y);
-      if (2 * p >= R0 && 2 * p < R0 + 2 * SH) E[(2 * p - R0) / SH] = fma2(Y, Y, E[(2 * p - R0) / SH]);
-    }
     const float2 wl = sm.tw[32 + lane];   // W_1024^lane = (cos, -sin) of the lane's share of the window angle
+    if constexpr (HOP == 0) {
+      // run-time hop: the two frames are read separately; E[f] = sum of squares of frame f (its RMS, not a hop block)
 #pragma unroll
-    for (int n1 = 0; n1 < 32; ++n1) {
-      const float w = half_hamming(n1, wl.x, wl.y);
-      z[bitrev32(n1)] = pk2(w * y[n1], w * y[n1 + SH]);
+      for (int p = 0; p < 16; ++p) {
+        const c64 YA = load_rows2<FAST>(rp0, p, gA, rg, L0, coef, nc2, lane);
+        const c64 YB = load_rows2<FAST>(rp0 + hop, p, gA + hop, rg, L0, coef, nc2, lane);
+        E[0] = fma2(YA, YA, E[0]); E[1] = fma2(YB, YB, E[1]);
+        const float w0 = half_hamming(2 * p, wl.x, wl.y), w1 = half_hamming(2 * p + 1, wl.x, wl.y);
+        z[bitrev32(2 * p)] = pk2(w0 * lo2(YA), w0 * lo2(YB));
+        z[bitrev32(2 * p + 1)] = pk2(w1 * hi2(YA), w1 * hi2(YB));
+      }
+    } else {
+      constexpr int SH = HOP / 32;            // rows by which frame B trails frame A
+      constexpr int NR = 32 + SH;             // rows of the step
+      constexpr int R0 = G::G0 * SH;          // first row of the owned hop blocks
+      float y[NR];
+#pragma unroll
+      for (int p = 0; p < NR / 2; ++p) {
+        const c64 Y = load_rows2<FAST>(rp0, p, gA, rg, L0, coef, nc2, lane);
+        y[2 * p] = lo2(Y); y[2 * p + 1] = hi2(Y);
+        if (2 * p >= R0 && 2 * p < R0 + 2 * SH) E[(2 * p - R0) / SH] = fma2(Y, Y, E[(2 * p - R0) / SH]);
+      }
+#pragma unroll
+      for (int n1 = 0; n1 < 32; ++n1) {
+        const float w = half_hamming(n1, wl.x, wl.y);
+        z[bitrev32(n1)] = pk2(w * y[n1], w * y[n1 + SH]);
+      }
     }
   }
   template <typename MC>
@@ -372,19 +385,22 @@ struct Step2<1024, HOP> {
     const int lane = threadIdx.x & 31;
     c64 z[32];
     c64 E[2] = {0ull, 0ull};
+    const int hop = HOP ? HOP : a.hop;
+    const int span = (G::FPW - 1) * hop + G::SPAN - (G::FPW - 1) * G::HOPMAX;
+    const float* rp0 = wc.tile + 4 + (HOP ? 0 : (gA & 3));   // sample gA + t sits at rp0[t]
 #ifdef AFX_FORCE_FAST   // development builds that count the instructions of the interior step (tools/dev)
     const bool fast = true;
 #else
-    const bool fast = (gA >= 1) && (gA >= rg.lo) && (gA + G::SPAN <= rg.hi);   // warp-uniform
+    const bool fast = (gA >= 1) && (gA >= rg.lo) && (gA + span <= rg.hi);   // warp-uniform
 #endif
-    if (fast) load<true>(z, E, wc.tile + 4, gA, rg, L0, a.coef, sm, lane);
-    else load<false>(z, E, wc.tile + 4, gA, rg, L0, a.coef, sm, lane);
+    if (fast) load<true>(z, E, rp0, gA, rg, L0, a.coef, hop, sm, lane);
+    else load<false>(z, E, rp0, gA, rg, L0, a.coef, hop, sm, lane);
     fft32_dit2(z);
     twiddle_rows<32>(z, sm.tw, lane);   // z[k1] *= W_1024^(k1 * lane)
     transpose32_bitrev64(z, wc.tile, lane);
     prefetch_tile(wc, next_bytes, next_src, next_dst, lane);
     fft32_dit2(z);   // z[k2] = Z[lane + 32 k2]
-    // split the two real spectra, power -> P2[k] = (|A_k|^2, |B_k|^2), k = 0..512 (afx_warp.cuh)
+    // split the two real spectra, power -> P2[k] = (|A_k|^2, |B_k|^2), k = 0..512 
     c64* P2 = reinterpret_cast<c64*>(wc.planeB);
     const int src = (32 - lane) & 31;
 #pragma unroll
@@ -415,43 +431,60 @@ struct Step2<512, HOP> {
   static constexpr int PSTRIDE = 260;   // pairs between the two signals' power spectra (257 used)
   template <bool FAST>
   static __device__ __forceinline__ void load(c64 (&z)[32], c64 (&E)[4], const float* rp0, int gA, const Region& rg, int L0,
-                                              float coef, const Smem& sm, int lane) {
-    constexpr int SH = HOP / 32;            // rows between consecutive frames
-    constexpr int NR = G::SPAN / 32;        // rows of the step (even)
-    constexpr int R0 = G::G0 * SH;
+                                              float coef, int hop, const Smem& sm, int lane) {
     const c64 nc2 = bc2(-coef);
-    float y[NR];
-#pragma unroll
-    for (int p = 0; p < NR / 2; ++p) {
-      const c64 Y = load_rows2<FAST>(rp0, p, gA, rg, L0, coef, nc2, lane);
-      y[2 * p] = lo2(Y); y[2 * p + 1] = hi2(Y);
-      if (SH >= 2) {
-        if (2 * p >= R0 && 2 * p < R0 + 4 * SH) E[(2 * p - R0) / SH] = fma2(Y, Y, E[(2 * p - R0) / SH]);
-      }
-    }
     const float2 wl = sm.tw[32 + lane];   // W_512^lane
+    if constexpr (HOP == 0) {
 #pragma unroll
-    for (int n1 = 0; n1 < 16; ++n1) {
-      const float w = half_hamming(2 * n1, wl.x, wl.y);
-      z[bitrev16(n1)] = pk2(w * y[n1], w * y[n1 + SH]);
-      z[16 + bitrev16(n1)] = pk2(w * y[n1 + 2 * SH], w * y[n1 + 3 * SH]);
+      for (int p = 0; p < 8; ++p) {
+        c64 Y[4];
+#pragma unroll
+        for (int f = 0; f < 4; ++f) { Y[f] = load_rows2<FAST>(rp0 + f * hop, p, gA + f * hop, rg, L0, coef, nc2, lane); E[f] = fma2(Y[f], Y[f], E[f]); }
+        const float w0 = half_hamming(4 * p, wl.x, wl.y), w1 = half_hamming(4 * p + 2, wl.x, wl.y);
+        z[bitrev16(2 * p)] = pk2(w0 * lo2(Y[0]), w0 * lo2(Y[1]));
+        z[bitrev16(2 * p + 1)] = pk2(w1 * hi2(Y[0]), w1 * hi2(Y[1]));
+        z[16 + bitrev16(2 * p)] = pk2(w0 * lo2(Y[2]), w0 * lo2(Y[3]));
+        z[16 + bitrev16(2 * p + 1)] = pk2(w1 * hi2(Y[2]), w1 * hi2(Y[3]));
+      }
+    } else {
+      constexpr int SH = HOP / 32;            // rows between consecutive frames
+      constexpr int NR = G::SPAN / 32;        // rows of the step (even)
+      constexpr int R0 = G::G0 * SH;
+      float y[NR];
+#pragma unroll
+      for (int p = 0; p < NR / 2; ++p) {
+        const c64 Y = load_rows2<FAST>(rp0, p, gA, rg, L0, coef, nc2, lane);
+        y[2 * p] = lo2(Y); y[2 * p + 1] = hi2(Y);
+        if (SH >= 2) {
+          if (2 * p >= R0 && 2 * p < R0 + 4 * SH) E[(2 * p - R0) / SH] = fma2(Y, Y, E[(2 * p - R0) / SH]);
+        }
+      }
+#pragma unroll
+      for (int n1 = 0; n1 < 16; ++n1) {
+        const float w = half_hamming(2 * n1, wl.x, wl.y);
+        z[bitrev16(n1)] = pk2(w * y[n1], w * y[n1 + SH]);
+        z[16 + bitrev16(n1)] = pk2(w * y[n1 + 2 * SH], w * y[n1 + 3 * SH]);
+      }
     }
   }
   template <typename MC>
   static __device__ __forceinline__ void run(const ClipArgs& a, const Smem& sm, const MelLane& ml, const Slab2& sl, WarpCtx2& wc, const Region& rg,
                                              int gA, int L0, int nv, int row, bool own_sums, int usum_idx, float floor_db,
                                              unsigned next_bytes, const float* next_src, float* next_dst) {
-    static_assert(HOP >= 64, "hop-block sums are accumulated per row pair");
+    static_assert(HOP == 0 || HOP >= 64, "hop-block sums are accumulated per row pair");
     const int lane = threadIdx.x & 31;
     c64 z[32];
     c64 E[4] = {0ull, 0ull, 0ull, 0ull};
+    const int hop = HOP ? HOP : a.hop;
+    const int span = (G::FPW - 1) * hop + G::SPAN - (G::FPW - 1) * G::HOPMAX;
+    const float* rp0 = wc.tile + 4 + (HOP ? 0 : (gA & 3));   // sample gA + t sits at rp0[t]
 #ifdef AFX_FORCE_FAST   // development builds that count the instructions of the interior step (tools/dev)
     const bool fast = true;
 #else
-    const bool fast = (gA >= 1) && (gA >= rg.lo) && (gA + G::SPAN <= rg.hi);   // warp-uniform
+    const bool fast = (gA >= 1) && (gA >= rg.lo) && (gA + span <= rg.hi);   // warp-uniform
 #endif
-    if (fast) load<true>(z, E, wc.tile + 4, gA, rg, L0, a.coef, sm, lane);
-    else load<false>(z, E, wc.tile + 4, gA, rg, L0, a.coef, sm, lane);
+    if (fast) load<true>(z, E, rp0, gA, rg, L0, a.coef, hop, sm, lane);
+    else load<false>(z, E, rp0, gA, rg, L0, a.coef, hop, sm, lane);
     fft16x2_dit2(z);
     twiddle_rows<16>(z, sm.tw, lane);   // z[16 s + k1] *= W_512^(k1 * lane)
     transpose32_bitrev64(z, wc.tile, lane);
@@ -491,16 +524,20 @@ struct Step2<2048, HOP> {
   using G = Geo<2048, HOP>;
   template <bool FAST>
   static __device__ __forceinline__ void load(c64 (&z)[32], c64& E, const float* rp0, int gA, const Region& rg, int L0,
-                                              float coef, const Smem& sm, int lane) {
+                                              float coef, int hop, const Smem& sm, int lane) {
+    (void)hop;
     const float2 wa = sm.ptw[2 * lane], wb = sm.ptw[2 * lane + 1];   // W_2048^(2 lane), W_2048^(2 lane + 1)
-    constexpr int R0 = G::G0 * (HOP / 64), R1 = R0 + HOP / 64;   // rows (64 samples each) of the owned hop block
+    constexpr int R0 = HOP ? G::G0 * (HOP / 64) : 0, R1 = HOP ? R0 + HOP / 64 : 32;   // rows (64 samples each) of the owned hop block (run-time hop: the whole frame)
 #pragma unroll
     for (int n1 = 0; n1 < 32; ++n1) {
       const int t = 64 * n1 + 2 * lane;
       c64 Y;
-      if (FAST) {
+      if (FAST && HOP != 0) {
         const float2 x01 = *reinterpret_cast<const float2*>(rp0 + t);
         Y = pk2(preemph_op(x01.x, rp0[t - 1], coef), preemph_op(x01.y, x01.x, coef));
+      } else if (FAST) {   // run-time hop: the tile offset may be odd, no 64-bit loads
+        const float xa = rp0[t], xb = rp0[t + 1];
+        Y = pk2(preemph_op(xa, rp0[t - 1], coef), preemph_op(xb, xa, coef));
       } else {
         Y = pk2(load_y<false>(rp0, t, gA, rg, L0, coef), load_y<false>(rp0, t + 1, gA, rg, L0, coef));
       }
@@ -512,17 +549,20 @@ struct Step2<2048, HOP> {
   static __device__ __forceinline__ void run(const ClipArgs& a, const Smem& sm, const MelLane& ml, const Slab2& sl, WarpCtx2& wc, const Region& rg,
                                              int gA, int L0, int nv, int row, bool own_sums, int usum_idx, float floor_db,
                                              unsigned next_bytes, const float* next_src, float* next_dst) {
-    static_assert(HOP >= 64, "hop-block sums are accumulated per 64-sample row");
+    static_assert(HOP == 0 || HOP >= 64, "hop-block sums are accumulated per 64-sample row");
     const int lane = threadIdx.x & 31;
     c64 z[32];
     c64 E = 0ull;
+    const int hop = HOP ? HOP : a.hop;
+    const int span = (G::FPW - 1) * hop + G::SPAN - (G::FPW - 1) * G::HOPMAX;
+    const float* rp0 = wc.tile + 4 + (HOP ? 0 : (gA & 3));   // sample gA + t sits at rp0[t]
 #ifdef AFX_FORCE_FAST   // development builds that count the instructions of the interior step (tools/dev)
     const bool fast = true;
 #else
-    const bool fast = (gA >= 1) && (gA >= rg.lo) && (gA + G::SPAN <= rg.hi);   // warp-uniform
+    const bool fast = (gA >= 1) && (gA >= rg.lo) && (gA + span <= rg.hi);   // warp-uniform
 #endif
-    if (fast) load<true>(z, E, wc.tile + 4, gA, rg, L0, a.coef, sm, lane);
-    else load<false>(z, E, wc.tile + 4, gA, rg, L0, a.coef, sm, lane);
+    if (fast) load<true>(z, E, rp0, gA, rg, L0, a.coef, hop, sm, lane);
+    else load<false>(z, E, rp0, gA, rg, L0, a.coef, hop, sm, lane);
     fft32_dit2(z);
     twiddle_rows<32>(z, sm.tw, lane);
     transpose32_bitrev64(z, wc.tile, lane);

@@ -8,18 +8,45 @@
 //  S  a warp streams its item: raw samples by 1-D TMA bulk copies into its private tile (the next tile -- of this item
 //     or of the item the warp has already claimed -- is in flight while the current one is transformed), MFCC rows,
 //     per-frame log-mel extrema and hop-block sums of squares go to the clip's slab (a slot of an L2-resident ring).
-//     The frame grid is the absolute one (speculation 1 of afx_clip.cuh) unless hop does not divide 512 (pretrimmed).
+//     The frame grid of the trimmed signal starts at trim_start, a multiple of 512; when hop divides 512 every trimmed
+//     frame centre is also a hop multiple of the UNtrimmed signal, so the pass runs speculatively on the absolute grid
+//     before the trim decision exists (else trim_kernel runs first and the items cover the trimmed frames: `pretrimmed`).
 //  The warp that completes the LAST item of a clip (per-slot arrival counter, release/acquire through L2) finishes it
 //  alone, while every other warp keeps streaming:
 //  T  trim decision from the hop-block sums;  F  head / tail fix-up steps;  R  top_db clamp: steps whose log-mel
 //  minimum lies below (clip max - 80 dB) are redone with the clamp;  C  delta / delta-delta + moment sums;
 //  Z  RMS per frame from the block sums, statistics, summary + meta rows.  Then the slot is handed to clip + n_slots.
 #pragma once
-#include "afx_clip.cuh"
+#include "afx_common.cuh"
+#include "afx_trim.cuh"
 #include "afx_step.cuh"
 
 namespace afx {
 
+constexpr int kMoments = 6;                               // sum x, x^2, x^3, x^4, sum delta, sum delta2
+
+// raw sample range a warp step starting at absolute sample gA needs; tile position p holds sample gA - 4 + p.
+// Returns the bytes to copy (0: nothing of the step lies inside [lo, hi)).
+__device__ __forceinline__ unsigned pair_copy_range(const Region& rg, int gA, int span, int L0, int& g_lo, int& s_lo) {
+  const int lo = max(rg.lo, gA), hi = min(rg.hi, gA + span);
+  if (hi <= lo) return 0u;
+  g_lo = max(0, lo - 1) & ~3;
+  const int g_hi4 = (min(hi, L0) + 3) & ~3;
+  s_lo = g_lo - (gA & ~3) + 4;                                      // multiple of 4, >= 0 (gA itself is one unless the hop is a run-time value)
+  return (unsigned)(g_hi4 - g_lo) * 4u;
+}
+
+// ---- T: librosa.effects.trim(top_db) from the block sums (core/feature_extractor.py:72)
+//   r_i = sqrt(mean(y_pre[512 i - 1024 .. 512 i + 1024)^2)), zero padded, i = 0 .. L0/512
+//   keep frames with 10 log10(max(1e-10, r_i^2)) - 10 log10(max(1e-10, max_i r_i^2)) > -top_db
+//   start = 512 * first, end = min(L0, 512 * (last + 1))
+__device__ __forceinline__ float trim_block(const float* usum, int b, int nb, int R, int nu) {
+  // sum of squares of 512-sample block b from the hop-sized unit sums (fixed order); zero outside the clip
+  if (b < 0 || b >= nb) return 0.f;
+  float s = 0.f;
+  for (int i = 0; i < R; ++i) { const int u = b * R + i; if (u < nu) s += __ldcg(usum + u); }
+  return s;
+}
 constexpr int kStreamMaxWarps = 16;
 constexpr int kStreamWarpSlots = 24;   // per-CTA mbarrier / scratch slots (an experimental 20-warp variant exists)
 
@@ -82,7 +109,7 @@ __device__ __forceinline__ Slab2 carve_slab2(const ClipArgs& a, int slot) {
   return s;
 }
 
-// ---- T: librosa.effects.trim(top_db) from the block sums, one warp (same arithmetic as trim_decide)
+// ---- T: librosa.effects.trim(top_db) from the block sums, one warp (same arithmetic as trim_kernel)
 __device__ __forceinline__ ClipInfo trim_decide_warp(const float* usum, int nu, int L0, int hop, float top_db, int lane) {
   const int n_rms = 1 + L0 / kTrimHop;
   const int nb = (L0 + kTrimHop - 1) / kTrimHop;
@@ -188,6 +215,8 @@ __global__ void __launch_bounds__(MAXW * 32, 1) stream_kernel(StreamArgs sa) {
   using G = Geo<NFFT, HOP>;
   constexpr int FPW = G::FPW;
   constexpr int WB = WarpBuf<NFFT, HOP>::kBytes;
+  const int hop = HOP ? HOP : a.hop;                    // HOP == 0: any hop <= n_fft / 2, trim done beforehand (pretrimmed)
+  const int span = (FPW - 1) * hop + NFFT;
   extern __shared__ __align__(16) unsigned char smem_raw[];
   // layout: [16 tile mbarriers][16 item mbarriers][16 warp scratch blocks][twiddle 8 KB][W_2048 table]
   //         [DCT rows per lane][mel lane tables][per-warp buffers]
@@ -198,17 +227,15 @@ __global__ void __launch_bounds__(MAXW * 32, 1) stream_kernel(StreamArgs sa) {
   sm.tw = reinterpret_cast<float2*>(smem_raw + 512 + SCR);
   constexpr int PTW_BYTES = NFFT == 2048 ? 4112 : 0;
   sm.ptw = reinterpret_cast<float2*>(smem_raw + 512 + SCR + 8192);
-  sm.win = nullptr;   // the window is evaluated on the fly (half_hamming)
   float* sDct = reinterpret_cast<float*>(smem_raw + 512 + SCR + 8192 + PTW_BYTES);
   const int dstride = 2 * a.n16 + 4;
   float4* sLin = reinterpret_cast<float4*>(sDct + 32 * dstride);
   int* sKl = reinterpret_cast<int*>(sLin + 128);
   float* sW0 = reinterpret_cast<float*>(sKl + 128);
-  sm.dct = sDct; sm.melw = nullptr;
+  sm.dct = sDct;
   MelLane ml;
   ml.lin = sLin; ml.kl = sKl; ml.w0 = sW0;
   unsigned char* wbufs = reinterpret_cast<unsigned char*>(sW0 + sa.mel_w0_floats);
-  sm.raw = nullptr; sm.planes = nullptr;
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   for (int i = tid; i < 1024; i += (int)blockDim.x) sm.tw[i] = a.tab.twiddle[i];
@@ -321,12 +348,12 @@ __global__ void __launch_bounds__(MAXW * 32, 1) stream_kernel(StreamArgs sa) {
       int fA = f_begin < f_end ? next_frame() : f_end;
       unsigned cur_bytes = 0;
       if (fA < f_end) {
-        const int gA0 = rg.origin + fA * HOP - NFFT / 2;
+        const int gA0 = rg.origin + fA * hop - NFFT / 2;
         if (pass == 0 && tile_in_flight) {
           cur_bytes = tile_bytes;
         } else {
           int g_lo = 0, s_lo = 0;
-          cur_bytes = pair_copy_range(rg, gA0, G::SPAN, L0, g_lo, s_lo);
+          cur_bytes = pair_copy_range(rg, gA0, span, L0, g_lo, s_lo);
           if (lane == 0 && cur_bytes) {
             fence_proxy_async();
             mbar_expect_tx(wc.mbar, cur_bytes);
@@ -338,14 +365,14 @@ __global__ void __launch_bounds__(MAXW * 32, 1) stream_kernel(StreamArgs sa) {
       }
       tile_in_flight = false;
       while (fA < f_end) {
-        const int gA = rg.origin + fA * HOP - NFFT / 2;
+        const int gA = rg.origin + fA * hop - NFFT / 2;
         const int fN = next_frame();
         unsigned next_bytes = 0;
         const float* next_src = clip_audio;
         int s_lo = 0;
         if (fN < f_end) {
           int g_lo = 0;
-          next_bytes = pair_copy_range(rg, rg.origin + fN * HOP - NFFT / 2, G::SPAN, L0, g_lo, s_lo);
+          next_bytes = pair_copy_range(rg, rg.origin + fN * hop - NFFT / 2, span, L0, g_lo, s_lo);
           next_src = clip_audio + g_lo;
         } else if (pass == 0 && nxt_requested) {
           // last step of the item: the next item's first tile rides this step's prefetch slot
@@ -355,7 +382,7 @@ __global__ void __launch_bounds__(MAXW * 32, 1) stream_kernel(StreamArgs sa) {
           if ((nx.nitems_cnt & 0xffu) != 0u) {
             Region rn{nx.lo, nx.lo, nx.hi};
             int g_lo = 0;
-            next_bytes = pair_copy_range(rn, nx.lo + nx.f_begin * HOP - NFFT / 2, G::SPAN, nx.L0, g_lo, s_lo);
+            next_bytes = pair_copy_range(rn, nx.lo + nx.f_begin * hop - NFFT / 2, span, nx.L0, g_lo, s_lo);
             next_src = a.audio + nx.audio_off + g_lo;
             tile_in_flight = next_bytes != 0u;
             tile_bytes = next_bytes;
@@ -385,10 +412,10 @@ __global__ void __launch_bounds__(MAXW * 32, 1) stream_kernel(StreamArgs sa) {
           a0 = 0;
           pass = 2;   // no T, no F
         } else {
-          const int fe0 = L0 > 0 ? 1 + L0 / HOP : 0;
+          const int fe0 = L0 > 0 ? 1 + L0 / hop : 0;
           const int nu = FPW * ((fe0 + FPW - 1) / FPW);   // hop-block sums written by pass 0
-          ci = trim_decide_warp(sl.blk, nu, L0, HOP, a.trim_top_db, lane);
-          a0 = ci.start / HOP;
+          ci = trim_decide_warp(sl.blk, nu, L0, hop, a.trim_top_db, lane);
+          a0 = ci.start / hop;
         }
       }
       if (ci.status != 0 || !want_frames) break;
@@ -399,13 +426,13 @@ __global__ void __launch_bounds__(MAXW * 32, 1) stream_kernel(StreamArgs sa) {
       f_begin = 0; f_end = 0;
       if (pass == 0) {          // -> head fix-up: frames t with t*hop < n_fft/2 reach in front of the trimmed signal
         pass = 1;
-        if (ci.start > 0) { head_end = min(ci.n_frames, (NFFT / 2 + HOP - 1) / HOP); f_end = head_end; }
+        if (ci.start > 0) { head_end = min(ci.n_frames, (NFFT / 2 + hop - 1) / hop); f_end = head_end; }
         continue;
       }
       if (pass == 1) {          // -> tail fix-up: frames t with t*hop + n_fft/2 > len reach behind it
         pass = 2;
         if (ci.end < L0) {
-          const int t_tail = (ci.len >= NFFT / 2) ? (ci.len - NFFT / 2) / HOP + 1 : 0;
+          const int t_tail = (ci.len >= NFFT / 2) ? (ci.len - NFFT / 2) / hop + 1 : 0;
           f_begin = max(t_tail, head_end); f_end = ci.n_frames;
         }
         continue;
@@ -465,20 +492,20 @@ __global__ void __launch_bounds__(MAXW * 32, 1) stream_kernel(StreamArgs sa) {
           }
         }
         if (a.mask & 0x4u) {   // RMS energy (core/feature_extractor.py:164-173): frame t covers hop blocks t - G0 .. t + G0 - 1
-          constexpr int GPF = NFFT / HOP;
+          constexpr int GPF = HOP ? NFFT / HOP : 1;               // run-time hop: blk[t] is the sum of squares of frame t itself
           const int ub = a.pretrimmed ? 0 : a0;                   // first block of the trimmed signal
-          const int ue = ub + (ci.len + HOP - 1) / HOP;           // blocks at or past ue hold no trimmed sample
+          const int ue = HOP ? ub + (ci.len + hop - 1) / hop : T; // blocks at or past ue hold no trimmed sample
           double s1 = 0, s2 = 0, s3 = 0, s4 = 0;
           float mn = 3.0e38f, mx = -3.0e38f;
           for (int t = lane; t < T; t += 32) {
-            const int u0 = ub + t - G::G0;
+            const int u0 = ub + t - (HOP ? G::G0 : 0);
             float bs[GPF];
 #pragma unroll
             for (int g = 0; g < GPF; ++g) { const int u = u0 + g; bs[g] = (u >= ub && u < ue) ? __ldcg(sl.blk + u) : 0.f; }
             float s = 0.f;
             if (GPF >= 4) {
 #pragma unroll
-              for (int g = 0; g < GPF; g += 4) s += (bs[g] + bs[g + 1]) + (bs[g + 2] + bs[g + 3]);
+              for (int g = 0; g + 3 < GPF; g += 4) s += (bs[g] + bs[g + 1]) + (bs[g + 2] + bs[g + 3]);
             } else {
 #pragma unroll
               for (int g = 0; g < GPF; ++g) s += bs[g];

@@ -83,5 +83,7 @@ def test_stock_configurations_select_the_unrolled_kernel_variant(built_lib):
     assert built_lib.afx_clip_kernel_variant(22050, 1024, 512, None) == 0     # stock tables, other hop
     assert built_lib.afx_clip_kernel_variant(16000, 1024, 256, None) == 0     # other sample rate: table-driven walk
     assert built_lib.afx_clip_kernel_variant(8000, 512, 128, None) == 0
-    assert built_lib.afx_clip_kernel_variant(22050, 1024, 100, None) == -1
+    assert built_lib.afx_clip_kernel_variant(22050, 1024, 100, None) == 2      # any other hop <= n_fft / 2: run-time-hop variant
+    assert built_lib.afx_clip_kernel_variant(16000, 512, 160, None) == 2
+    assert built_lib.afx_clip_kernel_variant(22050, 1024, 600, None) == -1
     assert built_lib.afx_clip_kernel_variant(22050, 1000, 250, None) == -1

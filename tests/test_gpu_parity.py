@@ -69,6 +69,13 @@ def test_c2_config_framewise_and_summary_parity(torch_cuda):
     dict(sr=16000, frame_length=512, hop_length=64, n_mfcc=13),
     dict(sr=44100, frame_length=2048, hop_length=256, n_mfcc=13),
     dict(sr=44100, frame_length=2048, hop_length=1024, n_mfcc=13),   # hop does not divide 512: separate trim pass
+    # any hop the reference accepts (core/feature_extractor.py:10-17): the run-time-hop variant of the streaming kernel
+    dict(sr=16000, frame_length=512, hop_length=160, n_mfcc=13),     # 04_feature_extraction_experiment's 10 ms hop
+    dict(sr=22050, frame_length=1024, hop_length=200, n_mfcc=13),
+    dict(sr=44100, frame_length=2048, hop_length=441, n_mfcc=13),
+    dict(sr=22050, frame_length=1024, hop_length=33, n_mfcc=13),     # odd hop: tiles at every alignment
+    dict(sr=16000, frame_length=512, hop_length=128, n_mfcc=64),     # widest coefficient set (four groups of 16)
+    dict(sr=16000, frame_length=512, hop_length=64, n_mfcc=49),
 ], ids=lambda c: f"{c['sr']}-{c['frame_length']}-{c['hop_length']}-{c['n_mfcc']}")
 def test_other_configs_framewise_and_summary_parity(torch_cuda, cfg):
     from audio_feature_extraction_b200 import AudioFeatureExtractor

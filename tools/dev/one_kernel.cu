@@ -6,9 +6,6 @@
 #define ONE_STOCK true
 #endif
 template __global__ void afx::stream_kernel<ONE_NFFT, ONE_HOP, ONE_STOCK>(afx::StreamArgs);
-#ifdef ONE_OLD
-template __global__ void afx::clip_kernel<ONE_NFFT, ONE_HOP, ONE_STOCK>(afx::ClipArgs);
-#endif
 
 // the warp step alone (static instruction count of one step = everything attributed to this kernel minus its short frame)
 namespace afx {
@@ -21,19 +18,5 @@ __global__ void __launch_bounds__(512, 1) step_only_kernel(ClipArgs a, Slab2 sl,
   for (int s = 0; s < steps; ++s)
     Step2<NFFT, HOP>::template run<MelCnt<NFFT, STOCK>>(a, sm, ml, sl, wc, rg, s * 512, L0, 2, s * 2, true, s * 2, -3.0e38f, 5152u, a.audio + s, wc.tile);
 }
-#ifdef ONE_OLD
-template <int NFFT, int HOP, bool STOCK>
-__global__ void __launch_bounds__(512, 1) step_only_old_kernel(ClipArgs a, Slab sl, Smem sm, float* tile_base, int steps, int L0) {
-  WarpCtx wc;
-  wc.raw = tile_base + threadIdx.x / 32 * 4096; wc.plane = wc.raw + 2048; wc.mbar = sm.mbar; wc.parity = 0;
-  wc.pol_in = 0; wc.pol_slab = 0;
-  Region rg{0, 0, L0};
-  int bad = 0;
-  for (int s = 0; s < steps; ++s)
-    WarpStep<NFFT, HOP>::template run<MelCnt<NFFT, STOCK>>(a, sm, sl, wc, rg, s * 512, L0, 2, s * 2, true, s * 2, -3.0e38f, 5152u, a.audio + s, wc.raw, bad);
-  if (bad) sl.rms[0] = 1.f;
-}
-template __global__ void step_only_old_kernel<ONE_NFFT, ONE_HOP, ONE_STOCK>(ClipArgs, Slab, Smem, float*, int, int);
-#endif
 template __global__ void step_only_kernel<ONE_NFFT, ONE_HOP, ONE_STOCK>(ClipArgs, Slab2, Smem, MelLane, float*, int, int);
 }
