@@ -78,6 +78,7 @@ struct afx_handle_s {
   void (*stream_fn)(afx::StreamArgs) = nullptr;   // stream_kernel<frame_length, hop_length>: warp-autonomous streaming kernel
   int stream_warps = 16;   // warps per CTA of the streaming kernel (one CTA per SM)
   int item_steps = 0;      // warp steps per work item; 0 = chosen per batch (item_steps_for)
+  int slab_ring_mb = 48;   // budget of the slab ring (AFX_SLAB_RING_MB)
   void (*vit_fn)(afx::VitArgs) = nullptr;     // viterbi_kernel<half width or 0>
   // device tables
   float* d_window = nullptr;
@@ -251,7 +252,8 @@ inline long long items_of(const afx_handle_s* h, long long len, int item_steps) 
 }
 inline int slots_for(const afx_handle_s* h, long long n_clips, long long max_len) {
   const size_t sb = slab_bytes_for(h, max_len);
-  const long long by_l2 = std::max<long long>(64, (long long)((size_t)(48u << 20) / sb));
+  // the ring must stay L2-resident next to the input stream (evict_last lines crowd the stream's lines out of the cache)
+  const long long by_l2 = std::max<long long>(64, (long long)(((size_t)h->slab_ring_mb << 20) / sb));
   return (int)std::max<long long>(1, std::min<long long>({n_clips, by_l2, (long long)kMaxSlots}));
 }
 
@@ -342,6 +344,7 @@ int afx_create(const afx_config_t* cfg, afx_handle_t* out) {
   CUDA_TRY(cudaFuncSetAttribute(afx::trim_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
   {  // the warp-autonomous streaming kernel: one CTA per SM with as many warps as shared memory (and 128 registers) allow
     h->stream_fn = stream_kernel_for(cfg->frame_length, cfg->hop_length, mel);
+    if (const char* e = getenv("AFX_SLAB_RING_MB")) { const int v = atoi(e); if (v >= 1 && v <= 4096) h->slab_ring_mb = v; }
     if (const char* e = getenv("AFX_ITEM_STEPS")) { const int v = atoi(e); if (v >= 1 && v * frames_per_step(h) <= 255) h->item_steps = v; }
     int w = afx::kStreamMaxWarps;
     if (const char* e = getenv("AFX_STREAM_WARPS")) {
@@ -358,7 +361,9 @@ int afx_create(const afx_config_t* cfg, afx_handle_t* out) {
   }
   {  // pYIN constants and tables (F0 group); an unsupported f0 range only disables that group
     afx::host::PyinConsts& pc = h->pc;
-    h->f0_ok = afx::host::pyin_consts(cfg->sr, cfg->frame_length, cfg->hop_length, cfg->f0_min, cfg->f0_max, pc) &&
+    // the block autocorrelation of yin_obs_kernel needs the analysis window (frame_length / 2) to be a whole number of hops
+    h->f0_ok = (cfg->frame_length / 2) % cfg->hop_length == 0 && !runtime_hop(cfg->frame_length, cfg->hop_length) &&
+               afx::host::pyin_consts(cfg->sr, cfg->frame_length, cfg->hop_length, cfg->f0_min, cfg->f0_max, pc) &&
                pc.n_lags <= 32 * afx::kYinMaxGroups * 2 - 4 && pc.max_period <= 32 * 22;
     if (h->f0_ok) {
       std::vector<double> all;

@@ -51,6 +51,9 @@ def parse_args():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-f0", action="store_true")
     ap.add_argument("--f0-clips", type=int, default=2960, help="clips of the full-path (with pYIN) sample; 2960 = 4 resident waves of the Viterbi kernel (5 CTAs x 148 SMs)")
+    ap.add_argument("--f0-cpu-clips", type=int, default=0, help="clips of the CPU baseline of the full path (pYIN oracle: seconds per clip); 0 = 2 per host core")
+    ap.add_argument("--no-legs", action="store_true", help="skip the bounded extra legs (C1 latency, C3, C4, ragged and clamp-heavy C2)")
+    ap.add_argument("--leg-clips", type=int, default=2000)
     return ap.parse_args()
 
 
@@ -205,6 +208,14 @@ def _workload_name(args, cfg, n_clips):
             f"hop {cfg['hop_length']} n_mfcc {cfg['n_mfcc']}, features {'+'.join(args.features.split(','))}")
 
 
+def _config(args, cfg):
+    """the workload description both arms print (identical dicts: the driver compares them)"""
+    gb = args.clips * cfg["seconds"] * cfg["sr"] * 4 / 1e9
+    return {"workload": _workload_name(args, cfg, args.clips),
+            "l2": "inputs (%.1f GB/GPU) larger than L2, no flush" % gb if gb > 0.13 else "inputs (%.2f GB/GPU) NOT larger than L2: diagnostic run, not a bench value" % gb,
+            "sharding": f"clips by rank x{args.gpus}, NCCL gather of summary rows to rank 0 each step" if args.gpus > 1 else "single GPU"}
+
+
 def _hours(n_clips, cfg):
     return n_clips * cfg["seconds"] / 3600.0
 
@@ -243,7 +254,7 @@ def run_reference(args):
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": 1e3 * sec / args.steps, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": _workload_name(args, cfg, args.clips), "sample": sample},
+        "config": _config(args, cfg), "sample": sample,
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": cpu.cores, "kind": "port", "sample": sample},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
@@ -262,14 +273,113 @@ def _peak_hbm():
         return 6650.0, "fallback (B200_PROFILING.md)"
 
 
-def _ncu_traffic(kernel: str, n_clips: int):
-    """dram bytes per launch of `kernel`: bytes per clip from the committed ncu --set full capture (the launch covers
-    the whole batch, so the capture on a smaller batch is scaled by the clip count)."""
+def _ncu_traffic(kernel: str, audio_seconds: float):
+    """dram bytes per launch of `kernel`, NOT measured by this run: bytes per audio-second from the committed
+    ncu --set full capture (profiles/ncu_traffic.json), scaled by the audio this launch covers.  Returns (bytes, source)."""
     p = ROOT / "profiles" / "ncu_traffic.json"
     try:
-        return json.loads(p.read_text())[kernel]["dram_bytes_per_clip"] * n_clips
+        e = json.loads(p.read_text())[kernel]
+        return e["dram_bytes_per_audio_second"] * audio_seconds, f"profiles/ncu_traffic.json ({e['capture']}), scaled by audio seconds; not measured by this run"
+    except Exception:
+        return None, "no committed capture for this kernel"
+
+
+def _f0_compute_roofline():
+    """issue / FP64-pipe utilisation of the pYIN kernels from the committed ncu capture (profiles/ncu_f0.json); the F0
+    path is compute-bound by construction, so these -- not HBM bytes -- are its roofline"""
+    try:
+        return json.loads((ROOT / "profiles" / "ncu_f0.json").read_text())
     except Exception:
         return None
+
+
+def _timed_extract(ex, audio, offsets, lengths, groups, reps=3):
+    import torch
+    ex.extract_batch_device(audio, offsets, lengths, groups)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(reps):
+        summ, meta, _ = ex.extract_batch_device(audio, offsets, lengths, groups)
+    e1.record(); torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / reps, summ, meta
+
+
+def _extra_legs(args, ex, audio, offsets, lengths, cfg, dev):
+    """Bounded measurements beside the headline (a few hundred ms of GPU each): the other BASELINE.json configs and the
+    cases the headline workload never exercises (ragged lengths, the top_db redo pass)."""
+    import torch
+    from audio_feature_extraction_b200 import AudioFeatureExtractor
+    from audio_feature_extraction_b200.synth import CONFIGS, make_batch_torch
+    from audio_feature_extraction_b200.wav import write_wav
+    peak = _peak_hbm()[0]
+    out = {}
+    nl = min(args.leg_clips, len(lengths))
+    stride = int(offsets[1] - offsets[0]) if len(offsets) > 1 else int(audio.numel())
+    sec = lambda lens: float(np.asarray(lens, dtype=np.int64).sum()) / cfg["sr"]
+
+    def entry(ms, lens, ok, sr, extra=None):
+        audio_s = float(np.asarray(lens, dtype=np.int64).sum()) / sr
+        e = {"value": audio_s / 3600.0 / (ms * 1e-3), "unit": UNIT, "ms": ms, "clips": int(len(lens)), "clips_ok": int(ok),
+             "hbm_frac": 4.0 * audio_s * sr / (ms * 1e-3) / 1e9 / peak}
+        if extra:
+            e.update(extra)
+        return e
+
+    # (a) C2 reference point on the same clip count
+    ms0, _, m0 = _timed_extract(ex, audio, offsets[:nl], lengths[:nl], GROUPS)
+    out["c2_same_count"] = entry(ms0, lengths[:nl], (m0[:, 0] == 0).sum().item(), cfg["sr"])
+    # (b) ragged: every clip spans 1-3 slots of the batch and is cut at a random point: 0.5 s .. 30 s
+    rng = np.random.default_rng(7)
+    ro, rl, i = [], [], 0
+    while i + 3 <= nl:
+        k = int(rng.integers(1, 4))
+        ro.append(int(offsets[i])); rl.append(int(rng.integers(int(0.5 * cfg["sr"]), k * stride - 8)))
+        i += k
+    ro, rl = np.asarray(ro, np.int64), np.asarray(rl, np.int32)
+    ms, _, m = _timed_extract(ex, audio, ro, rl, GROUPS)
+    out["c2_ragged_0.5_30s"] = entry(ms, rl, (m[:, 0] == 0).sum().item(), cfg["sr"], {"note": "clips of 0.5-30 s (1-3 batch slots, the -70 dBFS heads/tails inside count as pauses)"})
+    # (c) clamp-heavy: a 0.4 s gap in every clip -- digital silence (even clips) or -100 dBFS noise (odd clips) -- puts
+    # > 80 dB of log-mel range inside the trimmed region, so power_to_db's top_db clamp bites and the redo pass runs
+    hostile = audio[:nl * stride].clone().view(nl, stride)
+    g0 = int(4.0 * cfg["sr"]); g1 = g0 + int(0.4 * cfg["sr"])
+    hostile[0::2, g0:g1] = 0.0
+    hostile[1::2, g0:g1] *= 1e-5 / 0.03
+    ms, _, m = _timed_extract(ex, hostile.view(-1), offsets[:nl], lengths[:nl], GROUPS)
+    out["c2_clamp_redo"] = entry(ms, lengths[:nl], (m[:, 0] == 0).sum().item(), cfg["sr"],
+                                 {"slowdown_vs_clean": ms / ms0, "note": "0.4 s of digital silence / -100 dBFS noise inside every clip: the top_db redo pass is in the timed region"})
+    del hostile
+    # (d) C3 / C4: the other frame lengths, MFCC+energy and the full feature set
+    for name in ("c3", "c4"):
+        c = CONFIGS[name]
+        a2, o2, l2 = make_batch_torch(nl, sr=c["sr"], seconds=c["seconds"], f_lo=c["f_lo"], f_hi=c["f_hi"], kind=c["kind"], seed=77, device=dev, align=8)
+        o2, l2 = o2.numpy(), l2.numpy()
+        ex2 = AudioFeatureExtractor(device=dev.index or 0, **_ex_kwargs(c))
+        ms, _, m = _timed_extract(ex2, a2, o2, l2, GROUPS)
+        e = entry(ms, l2, (m[:, 0] == 0).sum().item(), c["sr"], {"geometry": f"{c['sr']} Hz, frame {c['frame_length']} hop {c['hop_length']} n_mfcc {c['n_mfcc']}"})
+        nf = min(nl, 592)
+        msf, _, mf = _timed_extract(ex2, a2, o2[:nf], l2[:nf], ("f0", "mfcc", "energy"), reps=1)
+        e["with_f0"] = entry(msf, l2[:nf], (mf[:, 0] == 0).sum().item(), c["sr"])
+        out[name] = e
+        del a2, ex2
+    # (e) C1: one 5 s clip through the reference-facing call extract_features(path) (README: "< 0.1 s / file")
+    import tempfile
+    c1 = CONFIGS["c1"]
+    one = audio[:int(c1["seconds"] * c1["sr"])].cpu().numpy()
+    with tempfile.TemporaryDirectory() as td:
+        path = os.path.join(td, "c1.wav")
+        write_wav(path, one, c1["sr"])
+        t0 = time.perf_counter()
+        ex1 = AudioFeatureExtractor(device=dev.index or 0, **_ex_kwargs(c1))
+        f = ex1.extract_features(path)
+        cold = time.perf_counter() - t0
+        warm = []
+        for _ in range(5):
+            t0 = time.perf_counter(); ex1.extract_features(path); warm.append(time.perf_counter() - t0)
+        t0 = time.perf_counter(); ex1.extract_features(path, features_to_extract=["mfcc", "energy"]); warm_nof0 = time.perf_counter() - t0
+    out["c1_single_file_latency"] = {"cold_s": cold, "warm_s_median": float(np.median(warm)), "warm_s_mfcc_energy_only": warm_nof0,
+                                     "keys": len(f), "note": "wall time of extract_features(path) incl. WAV read, H2D, all kernels, D2H; cold includes handle creation"}
+    return out
 
 
 def run_native(args):
@@ -354,10 +464,11 @@ def run_native(args):
     peak, peak_src = _peak_hbm()
     dom_ms = phases[dom]["ms_per_step"]
     achieved = bytes_per_step / (dom_ms * 1e-3) / 1e9
-    kernel_name = {"frames": "clip_kernel", "trim": "trim_kernel", "yin": "yin_kernel", "viterbi": "viterbi_kernel",
+    kernel_name = {"frames": "stream_kernel", "trim": "trim_kernel", "yin": "yin_obs_kernel", "viterbi": "viterbi_kernel",
                    "pcm": "pcm16_to_f32_kernel"}.get(dom, dom)
+    traffic, traffic_src = _ncu_traffic(kernel_name, n * cfg["seconds"])
     roofline = {"bound": "hbm", "kernel": kernel_name, "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                "traffic": _ncu_traffic(kernel_name, n), "peak_source": peak_src,
+                "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src,
                 "algorithmic_bytes_per_launch": bytes_per_step / max(phases[dom]["launches_per_step"], 1),
                 "avg_launch_ms": dom_ms / max(phases[dom]["launches_per_step"], 1),
                 "whole_path_frac": bytes_per_step / (ms_per_step * 1e-3) / 1e9 / peak, "phases": phases}
@@ -408,7 +519,8 @@ def run_native(args):
                "host_numa_binding": numa}
         del host16
 
-    # ---- the full path with pYIN F0 on a bounded sample (compute-bound by construction; reported beside the headline)
+    # ---- the reference's DEFAULT feature set (extract_features always runs pYIN, core/feature_extractor.py:197) on a
+    # bounded sample: device time per phase, and the CPU oracle with pYIN beside it
     f0_path = None
     if "f0" not in groups and not args.no_f0 and rank == 0:
         nf = min(n, args.f0_clips)
@@ -416,12 +528,32 @@ def run_native(args):
         allg = ("f0", "mfcc", "energy")
         ex.extract_batch_device(audio, offsets[:nf], lengths[:nf], allg)
         torch.cuda.synchronize()
+        L.afx_profile_read(h, None, None, 1); L.afx_profile_enable(h, 1)
         ev0.record()
         s_f0, m_f0, _ = ex.extract_batch_device(audio, offsets[:nf], lengths[:nf], allg)
         ev1.record(); torch.cuda.synchronize()
         ms_f0 = ev0.elapsed_time(ev1)
+        L.afx_profile_enable(h, 0)
+        fm = (C.c_double * N.N_PHASES)(); fn = (C.c_int64 * N.N_PHASES)()
+        N.check(L.afx_profile_read(h, fm, fn, 1))
         f0_path = {"value": _hours(nf, cfg) / (ms_f0 * 1e-3), "unit": UNIT, "clips": nf, "ms": ms_f0,
-                   "features": "f0+mfcc+energy", "voiced_quality_mean": float(s_f0[:, 3].mean().item())}
+                   "features": "f0+mfcc+energy", "voiced_quality_mean": float(s_f0[:, 3].mean().item()),
+                   "phases_ms": {N.PHASES[p]: fm[p] for p in range(N.N_PHASES) if fn[p]},
+                   "hbm_frac": (4.0 * float(lengths[:nf].astype(np.int64).sum()) / (ms_f0 * 1e-3) / 1e9) / _peak_hbm()[0],
+                   "compute_roofline": _f0_compute_roofline()}
+        if world == 1 and not args.no_cpu_baseline:
+            cores = len(os.sched_getaffinity(0))
+            ncf = args.f0_cpu_clips or 2 * cores
+            stride = int(offsets[1] - offsets[0]) if n > 1 else int(audio.numel())
+            cpu = CpuPath(audio[:ncf * stride].cpu().numpy().reshape(ncf, stride), int(lengths[0]), _ex_kwargs(cfg), allg)
+            sec = cpu.run(list(range(ncf)))
+            cpu.close()
+            f0_path["cpu_baseline"] = {"value": _hours(ncf, cfg) / sec, "unit": UNIT, "cores": cpu.cores, "kind": "port",
+                                       "sample": f"first {ncf} clips of the GPU batch through the oracle WITH pYIN, multiprocessing.Pool({cpu.cores}), {sec:.1f} s wall"}
+
+    legs = None
+    if rank == 0 and world == 1 and not args.no_legs:
+        legs = _extra_legs(args, ex, audio, offsets, lengths, cfg, dev)
 
     # ---- CPU baseline beside it (rank 0, N = 1 only): the oracle on a bounded sample of the same clips
     cpu_baseline = None
@@ -442,9 +574,8 @@ def run_native(args):
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f32", "data": "synthetic",
-            "config": {"workload": _workload_name(args, cfg, n), "clips_ok": ok, "l2": "inputs (%.1f GB/GPU) larger than L2, no flush" % (audio.numel() * 4 / 1e9),
-                       "sharding": f"clips by rank x{world}, NCCL gather of summary rows to rank 0 each step" if world > 1 else "single GPU"},
-            "roofline": roofline, "cpu_baseline": cpu_baseline, "e2e": e2e, "f0_path": f0_path, "gpu_launches": int(launches), "clocks": clocks,
+            "config": _config(args, cfg), "clips_ok": ok,
+            "roofline": roofline, "cpu_baseline": cpu_baseline, "e2e": e2e, "f0_path": f0_path, "legs": legs, "gpu_launches": int(launches), "clocks": clocks,
         }
         _emit(line)
     if world > 1:
