@@ -171,37 +171,83 @@ class AudioFeatureExtractor:
         m = meta.cpu().numpy()
         return self.rows_to_dicts(s, m, names, features_to_extract, skip_errors=skip_errors)
 
+    def rows_for_files(self, files: Sequence[str], features_to_extract: Optional[Sequence[str]] = None):
+        """Summary and meta rows (host numpy, one row per file, in order) of WAV files: probed and decoded by the native
+        threaded reader into ONE pinned buffer (raw 16-bit samples when every file is 16-bit mono PCM) that
+        afx_extract_host_packed streams to the GPU in waves; files at another sample rate go through load_audio (device
+        resampler).  An unreadable file keeps an AFX_CLIP_EMPTY row, so rows stay aligned with `files`."""
+        import torch
+        from ..wav import probe_batch, load_batch, WAV_STATUS
+
+        n = len(files)
+        L = N.lib()
+        h = self._h()   # (creates the handle: summary_width is known from here on)
+        hs = np.zeros((n, self.summary_width), np.float32)
+        hm = np.zeros((n, 4), np.int32)
+        hm[:, 0] = N.CLIP_EMPTY
+        if n == 0:
+            return hs, hm
+        info = probe_batch(list(files))
+        keep = [i for i in range(n) if info["status"][i] == 0 and int(info["sr"][i]) == self.sr]
+        other = [i for i in range(n) if info["status"][i] == 0 and int(info["sr"][i]) != self.sr]
+        for i in range(n):
+            if info["status"][i] != 0:
+                self.logger.error(f"載入音頻文件失敗: {files[i]}: {WAV_STATUS.get(int(info['status'][i]), 'unreadable')}")
+        if keep:
+            names = [files[i] for i in keep]
+            frames = info["frames"][keep].astype(np.int64)
+            pcm16 = bool(np.all((info["tag"][keep] == 1) & (info["bits"][keep] == 16) & (info["channels"][keep] == 1)))
+            strides = (frames + 7) // 8 * 8
+            offsets = np.zeros(len(keep), dtype=np.int64)
+            offsets[1:] = np.cumsum(strides)[:-1]
+            total = int(strides.sum()) + 8
+            host = torch.zeros(total, dtype=torch.int16 if pcm16 else torch.float32, pin_memory=True)
+            st = load_batch(names, frames, host, offsets, as_pcm16=pcm16)
+            lengths = np.where(st == 0, frames, 0).astype(np.int32)   # a file that failed to decode becomes an empty clip
+            ks = np.zeros((len(keep), self.summary_width), np.float32)
+            km = np.zeros((len(keep), 4), np.int32)
+            N.check(L.afx_extract_host_packed(h, host.data_ptr(), N.SAMPLE_S16 if pcm16 else N.SAMPLE_F32, total,
+                                              offsets.ctypes.data, lengths.ctypes.data, len(keep), _mask_of(features_to_extract),
+                                              ks.ctypes.data, km.ctypes.data))
+            hs[keep] = ks; hm[keep] = km
+        if other:
+            dev = torch.device("cuda", self.device)
+            clips, idx = [], []
+            for i in other:
+                try:
+                    clips.append(self.load_audio(files[i])[0]); idx.append(i)
+                except Exception:   # load_audio has logged it (reference :54-56)
+                    pass
+            if clips:
+                buf, offsets, lengths = self.pack_clips(clips)
+                summ, meta, _ = self.extract_batch_device(buf.to(dev, non_blocking=True), offsets, lengths, features_to_extract)
+                hs[idx] = summ.cpu().numpy(); hm[idx] = meta.cpu().numpy()
+        return hs, hm
+
     def batch_process_sharded(self, audio_dir: str, features_to_extract: Optional[Sequence[str]] = None):
         """batch_process over the ranks of an initialised torch.distributed job (one process per GPU): the sorted
-        *.wav list is block-partitioned by rank, every rank extracts its shard on its own GPU, the summary rows are
-        gathered to rank 0 (NCCL), which returns the list of dicts; the other ranks return None."""
+        *.wav list is block-partitioned by rank, every rank runs its shard through rows_for_files (native ingest +
+        afx_extract_host_packed) on its own GPU, and the per-file rows are gathered to rank 0 -- over NCCL when that
+        is the job's backend, else as host tensors -- which returns the list of dicts; the other ranks return None."""
         import torch
         import torch.distributed as dist
         from ..distributed import extract_sharded
 
         files = sorted(str(p) for p in Path(audio_dir).glob("*.wav"))
-        dev = torch.device("cuda", self.device)
-        self._h()
+        on_gpu = dist.is_available() and dist.is_initialized() and dist.get_backend() == "nccl"
+        dev = torch.device("cuda", self.device) if on_gpu else torch.device("cpu")
 
         def rows(shard):
-            clips, ok = [], []
-            for f in shard:
-                try:
-                    clips.append(self.load_audio(f)[0]); ok.append(True)
-                except Exception as e:   # unreadable file: reported as a failed row, skipped on rank 0 (reference :233-235)
-                    self.logger.error(f"處理文件 {Path(f).name} 失敗: {str(e)}")
-                    clips.append(np.zeros(0, np.float32)); ok.append(False)
-            if not clips:
-                return (torch.zeros((0, self.summary_width), dtype=torch.float32, device=dev),
-                        torch.zeros((0, 4), dtype=torch.int32, device=dev))
-            buf, offsets, lengths = self.pack_clips(clips)
-            summ, meta, _ = self.extract_batch_device(buf.to(dev, non_blocking=True), offsets, lengths, features_to_extract)
-            return summ, meta
+            hs, hm = self.rows_for_files(shard, features_to_extract)
+            return torch.from_numpy(hs).to(dev), torch.from_numpy(hm).to(dev)
 
         summ, meta = extract_sharded(rows, files)
         if summ is None:
             return None
-        return self.rows_to_dicts(summ.cpu().numpy(), meta.cpu().numpy(), files, features_to_extract, skip_errors=True)
+        results = self.rows_to_dicts(summ.cpu().numpy(), meta.cpu().numpy(), files, features_to_extract, skip_errors=True)
+        for r in results:
+            self.logger.info(f"成功處理文件: {Path(r['file_path']).name}")
+        return results
 
     def rows_to_dicts(self, s: np.ndarray, m: np.ndarray, names: Sequence[str], features_to_extract=None,
                       skip_errors: bool = False) -> List[Dict[str, Any]]:

@@ -23,9 +23,10 @@ def shard_range(n: int, rank: int, world: int) -> Tuple[int, int]:
     return (rank * n) // world, ((rank + 1) * n) // world
 
 
-def gather_rows(local: "torch.Tensor", dst: int = 0, group=None) -> Optional["torch.Tensor"]:
+def gather_rows(local: "torch.Tensor", dst: int = 0, group=None, counts: Optional[Sequence[int]] = None) -> Optional["torch.Tensor"]:
     """Gather 2-D row blocks of different heights to `dst` (NCCL for CUDA tensors, gloo for CPU tensors).
-    Returns the row-wise concatenation in rank order on `dst`, None elsewhere."""
+    Returns the row-wise concatenation in rank order on `dst`, None elsewhere.  `counts` (rows per rank) skips the
+    exchange of the heights -- and with it the host synchronisation -- when every rank already knows them."""
     import torch
     import torch.distributed as dist
 
@@ -33,9 +34,11 @@ def gather_rows(local: "torch.Tensor", dst: int = 0, group=None) -> Optional["to
     rank = dist.get_rank(group)
     if world == 1:
         return local
-    counts = [torch.zeros(1, dtype=torch.int64, device=local.device) for _ in range(world)]
-    dist.all_gather(counts, torch.tensor([local.shape[0]], dtype=torch.int64, device=local.device), group=group)
-    counts = [int(c.item()) for c in counts]
+    if counts is None:
+        cs = [torch.zeros(1, dtype=torch.int64, device=local.device) for _ in range(world)]
+        dist.all_gather(cs, torch.tensor([local.shape[0]], dtype=torch.int64, device=local.device), group=group)
+        counts = [int(c.item()) for c in cs]
+    counts = [int(c) for c in counts]
     width = local.shape[1]
     cap = max(max(counts), 1)
     padded = torch.zeros((cap, width), dtype=local.dtype, device=local.device)
@@ -61,7 +64,9 @@ def extract_sharded(extract_rows: Callable[[Sequence], Tuple["torch.Tensor", "to
     summ, meta = extract_rows(items[lo:hi])
     if world == 1:
         return summ, meta
-    return gather_rows(summ, dst, group), gather_rows(meta, dst, group)
+    # block partition: every rank can compute every shard's height, no exchange of counts (and no host sync) needed
+    counts = [shard_range(len(items), r, world)[1] - shard_range(len(items), r, world)[0] for r in range(world)]
+    return gather_rows(summ, dst, group, counts), gather_rows(meta, dst, group, counts)
 
 
 def parse_cpulist(text: str) -> List[int]:

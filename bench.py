@@ -45,7 +45,7 @@ def parse_args():
     ap.add_argument("--config", default="c2", help="synth.CONFIGS key (c2 = the headline workload)")
     ap.add_argument("--clips", type=int, default=10000, help="clips per GPU")
     ap.add_argument("--features", default="mfcc,energy")
-    ap.add_argument("--e2e-clips", type=int, default=0, help="clips of the host-buffer (e2e) leg; 0 = all clips on one GPU, clips/4 per rank otherwise")
+    ap.add_argument("--e2e-clips", type=int, default=5000, help="clips per GPU of the host-buffer (e2e) leg, the same at every N (pinned host memory: 2.2 GB of 16-bit PCM per rank)")
     ap.add_argument("--cpu-clips", type=int, default=0, help="clips of the CPU baseline sample; 0 = auto")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
@@ -284,6 +284,17 @@ def _ncu_traffic(kernel: str, audio_seconds: float):
         return None, "no committed capture for this kernel"
 
 
+def _h2d_ceiling(world):
+    """host->device copy rate of this pool's boxes with `world` ranks copying at once (tools/h2d_probe.py, committed under
+    profiles/h2d_probe.json): the ceiling of the e2e leg, which ships 2 bytes per sample"""
+    try:
+        d = json.loads((ROOT / "profiles" / "h2d_probe.json").read_text())
+        e = d[str(world)]
+        return {"aggregate_gbs": e["aggregate_gbs"], "audio_hours_per_sec_at_16bit": e["aggregate_gbs"] * 1e9 / 2 / 22050 / 3600, "source": e["source"]}
+    except Exception:
+        return None
+
+
 def _f0_compute_roofline():
     """issue / FP64-pipe utilisation of the pYIN kernels from the committed ncu capture (profiles/ncu_f0.json); the F0
     path is compute-bound by construction, so these -- not HBM bytes -- are its roofline"""
@@ -411,13 +422,21 @@ def run_native(args):
     ex = AudioFeatureExtractor(device=local, **_ex_kwargs(cfg))
     h = ex._h()
     SS = ex.summary_width
-    gathered = [torch.empty((n, SS), dtype=torch.float32, device=dev) for _ in range(world)] if (world > 1 and rank == 0) else None
+    from audio_feature_extraction_b200.distributed import extract_sharded
+    items = range(world * n)   # weak scaling: rank r's resident batch is shard r of the job's clip list
+    last = {}
+
+    def rows(_shard):
+        summ, meta, _ = ex.extract_batch_device(audio, offsets, lengths, groups)
+        last["summ"], last["meta"] = summ, meta
+        return summ, meta
 
     def step():
-        summ, meta, _ = ex.extract_batch_device(audio, offsets, lengths, groups)
-        if world > 1:   # the path's only inter-GPU step: per-file summary rows -> rank 0 (NCCL over NVLink)
-            dist.gather(summ, gathered, dst=0)
-        return summ, meta
+        # the product's multi-GPU entry (distributed.extract_sharded, the engine of batch_process_sharded): this rank's
+        # shard through the fused kernel, then the path's only inter-GPU step -- one NCCL gather of the per-file
+        # summary (+ meta) rows to rank 0
+        extract_sharded(rows, items)
+        return last["summ"], last["meta"]
 
     def barrier():
         if world > 1:
@@ -478,8 +497,7 @@ def run_native(args):
     # device; the float32-buffer variant is reported next to it.
     e2e = None
     if not args.no_e2e:
-        ne = args.e2e_clips or (n if world == 1 else max(1, n // 4))   # the whole workload on one GPU; a quarter per rank when 8 ranks pin host memory at once
-        ne = min(ne, n)
+        ne = min(args.e2e_clips or n, n)   # the same clips per GPU at every N, so the N-GPU curve is like for like
         stride = int(offsets[1] - offsets[0]) if n > 1 else int(audio.numel())
         span = ne * stride
         mask = sum({"f0": 1, "mfcc": 2, "energy": 4}[g] for g in groups)
@@ -503,19 +521,22 @@ def run_native(args):
                 dist.all_reduce(tt, op=dist.ReduceOp.MAX)
             return float(tt.item())
 
-        host32 = torch.empty(span, dtype=torch.float32, pin_memory=True)
-        host32.copy_(audio[:span]); torch.cuda.synchronize()
-        dt32 = timed(host32, N.SAMPLE_F32)
-        assert np.array_equal(hm[:, 0], meta[:ne, 0].cpu().numpy())
+        dt32 = None
+        if world == 1:   # the float32-buffer variant beside the headline (one GPU only: it pins twice the host memory)
+            host32 = torch.empty(span, dtype=torch.float32, pin_memory=True)
+            host32.copy_(audio[:span]); torch.cuda.synchronize()
+            dt32 = timed(host32, N.SAMPLE_F32)
+            assert np.array_equal(hm[:, 0], meta[:ne, 0].cpu().numpy())
+            del host32
         host16 = torch.empty(span, dtype=torch.int16, pin_memory=True)
         host16.copy_((audio[:span] * 32768.0).round().clamp_(-32768, 32767).to(torch.int16)); torch.cuda.synchronize()
-        del host32
         dt16 = timed(host16, N.SAMPLE_S16)
         ok16 = int((hm[:, 0] == 0).sum())
         e2e = {"value": world * _hours(ne, cfg) * args.steps / dt16, "unit": UNIT,
                "h2d_bytes_per_step": int(2 * span), "d2h_bytes_per_step": int(ne * (4 * SS + 16)),
                "clips_per_gpu": ne, "clips_ok": ok16, "api": "afx_extract_host_packed (pinned 16-bit PCM host buffer, converted on the device)",
-               "float32_buffer": {"value": world * _hours(ne, cfg) * args.steps / dt32, "h2d_bytes_per_step": int(4 * span)},
+               "float32_buffer": {"value": world * _hours(ne, cfg) * args.steps / dt32, "h2d_bytes_per_step": int(4 * span)} if dt32 else None,
+               "h2d_ceiling": _h2d_ceiling(world),
                "host_numa_binding": numa}
         del host16
 

@@ -681,3 +681,55 @@ def test_pyin_parity_sweep_over_seeded_clips(torch_cuda):
         assert res["voicing_agreement"] >= F0_VOICING, res
         assert res["worst_cents"] <= F0_CENTS, res
         assert res["frames"] > 1500
+
+
+def _sharded_worker(rank, world, port, backend, wav_dir, out_path):
+    import os
+    import torch
+    import torch.distributed as dist
+    os.environ["MASTER_ADDR"] = "127.0.0.1"; os.environ["MASTER_PORT"] = str(port)
+    ndev = torch.cuda.device_count()
+    dev = rank % ndev
+    torch.cuda.set_device(dev)
+    kw = dict(device_id=torch.device("cuda", dev)) if backend == "nccl" else {}
+    dist.init_process_group(backend, rank=rank, world_size=world, **kw)
+    try:
+        from audio_feature_extraction_b200 import AudioFeatureExtractor
+        ex = AudioFeatureExtractor(device=dev)
+        res = ex.batch_process_sharded(wav_dir)
+        if rank == 0:
+            torch.save(res, out_path)
+        else:
+            assert res is None
+    finally:
+        dist.destroy_process_group()
+
+
+def test_batch_process_sharded_two_ranks_matches_single_rank(torch_cuda, tmp_path):
+    """BASELINE.json configs[4]: batch_process sharded by clip over the ranks of a torch.distributed job, per-file rows
+    gathered to rank 0 (NCCL when the box has two GPUs; on a one-GPU box both ranks share the GPU and gather over gloo)."""
+    import socket
+    import torch
+    import torch.multiprocessing as mp
+    from audio_feature_extraction_b200 import AudioFeatureExtractor
+    from audio_feature_extraction_b200.synth import make_clip
+    from audio_feature_extraction_b200.wav import write_wav
+
+    d = tmp_path / "wavs"; d.mkdir()
+    for i in range(9):
+        write_wav(str(d / f"clip_{i:02d}.wav"), make_clip(900 + i, seconds=0.8 + 0.3 * i), 22050)
+    (d / "broken.wav").write_bytes(b"RIFFxxxxWAVEjunk")          # logged and skipped (reference :233-235)
+    write_wav(str(d / "other_rate.wav"), make_clip(950, sr=16000, seconds=1.5), 16000)   # resampled on the device
+    single = {r["file_path"]: r for r in AudioFeatureExtractor().batch_process(str(d))}
+    backend = "nccl" if torch.cuda.device_count() >= 2 else "gloo"
+    s = socket.socket(); s.bind(("127.0.0.1", 0)); port = s.getsockname()[1]; s.close()
+    out = tmp_path / "rank0.pt"
+    mp.spawn(_sharded_worker, args=(2, port, backend, str(d), str(out)), nprocs=2, join=True)
+    sharded = torch.load(out, weights_only=False)
+    assert [r["file_path"] for r in sharded] == sorted(single)          # enumeration order of the sorted list, broken file skipped
+    for r in sharded:
+        ref = single[r["file_path"]]
+        assert r.keys() == ref.keys()
+        for k, v in r.items():
+            if k != "file_path":
+                np.testing.assert_allclose(np.asarray(v, dtype=np.float64), np.asarray(ref[k], dtype=np.float64), rtol=0, atol=0)
