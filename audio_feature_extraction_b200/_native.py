@@ -23,9 +23,9 @@ EXPORTS = [
     "afx_summary_width", "afx_frame_width", "afx_max_frames", "afx_workspace_bytes",
     "afx_workspace_min_bytes", "afx_extract", "afx_extract_host", "afx_extract_host_packed",
     "afx_launch_count", "afx_profile_enable", "afx_profile_read", "afx_preprocess", "afx_frame_extras", "afx_wav_probe_batch", "afx_wav_load_batch", "afx_f0_postprocess", "afx_resample_length", "afx_resample_filter", "afx_resample", "afx_dtw_frame_distance", "afx_dtw_accumulated_cost",
-    "afx_clip_kernel_variant",
+    "afx_clip_kernel_variant", "afx_debug_header_bytes",
 ]
-PHASES = ("trim", "frames", "mfcc", "finalize", "pcm", "yin", "viterbi", "reserved")
+PHASES = ("trim", "frames", "reserved2", "reserved3", "pcm", "yin", "viterbi", "reserved7")
 N_PHASES = 8
 SAMPLE_F32, SAMPLE_S16 = 0, 1
 EXTRAS_WIDTH = 5

@@ -535,6 +535,7 @@ int afx_extract(afx_handle_t h, const float* d_audio, const int64_t* h_offsets, 
     afx::TrimArgs ta;
     ta.audio = d_audio; ta.offsets = d_offsets; ta.lengths = d_lengths; ta.info = d_info;
     ta.clip_begin = 0; ta.hop = hop; ta.coef = coef; ta.top_db = trim_top_db; ta.raw = raw ? 1 : 0;
+    ta.min_frames = (feature_mask & AFX_FEAT_MFCC) ? afx::kDeltaWidth : 1;
     const size_t smem = (size_t)(ceil_div(max_len, afx::kTrimHop) + 4) * sizeof(float);
     PhaseTimer pt(h, stream, AFX_PHASE_TRIM);
     afx::trim_kernel<<<n, afx::kTrimThreads, smem, stream>>>(ta);
@@ -709,7 +710,8 @@ int afx_wav_probe_batch(const char* const* paths, int64_t n, int threads, int32_
     return fail(AFX_ERR_INVALID_ARG, "afx_wav_probe_batch: null argument");
   afx::wav::parallel_for(n, threads, [&](int64_t i) {
     afx::wav::Info info;
-    status[i] = paths[i] ? afx::wav::probe(paths[i], info) : afx::wav::OPEN_FAILED;
+    try { status[i] = paths[i] ? afx::wav::probe(paths[i], info) : afx::wav::OPEN_FAILED; }
+    catch (...) { status[i] = afx::wav::UNSUPPORTED; }   // e.g. std::bad_alloc: reported per file, never across the C boundary
     sr[i] = info.sr; channels[i] = info.channels; frames[i] = info.frames; format[i] = (info.tag << 8) | info.bits;
   });
   return AFX_OK;
@@ -723,8 +725,10 @@ int afx_wav_load_batch(const char* const* paths, int64_t n, int threads, int sam
     return fail(AFX_ERR_INVALID_ARG, "afx_wav_load_batch: unknown sample format %d", sample_format);
   afx::wav::parallel_for(n, threads, [&](int64_t i) {
     if (!paths[i] || h_offsets[i] < 0 || h_frames[i] < 0) { status[i] = afx::wav::OPEN_FAILED; return; }
-    if (sample_format == AFX_SAMPLE_S16) status[i] = afx::wav::load(paths[i], h_frames[i], nullptr, static_cast<int16_t*>(h_out) + h_offsets[i]);
-    else status[i] = afx::wav::load(paths[i], h_frames[i], static_cast<float*>(h_out) + h_offsets[i], nullptr);
+    try {
+      if (sample_format == AFX_SAMPLE_S16) status[i] = afx::wav::load(paths[i], h_frames[i], nullptr, static_cast<int16_t*>(h_out) + h_offsets[i]);
+      else status[i] = afx::wav::load(paths[i], h_frames[i], static_cast<float*>(h_out) + h_offsets[i], nullptr);
+    } catch (...) { status[i] = afx::wav::UNSUPPORTED; }   // the reference's batch_process logs and skips a bad file (:233-235)
   });
   return AFX_OK;
 }

@@ -110,7 +110,7 @@ __device__ __forceinline__ Slab2 carve_slab2(const ClipArgs& a, int slot) {
 }
 
 // ---- T: librosa.effects.trim(top_db) from the block sums, one warp (same arithmetic as trim_kernel)
-__device__ __forceinline__ ClipInfo trim_decide_warp(const float* usum, int nu, int L0, int hop, float top_db, int lane) {
+__device__ __forceinline__ ClipInfo trim_decide_warp(const float* usum, int nu, int L0, int hop, float top_db, int min_frames, int lane) {
   const int n_rms = 1 + L0 / kTrimHop;
   const int nb = (L0 + kTrimHop - 1) / kTrimHop;
   const int R = kTrimHop / hop;
@@ -150,7 +150,7 @@ __device__ __forceinline__ ClipInfo trim_decide_warp(const float* usum, int nu, 
     ci.len = ci.end - ci.start;
     const int T = 1 + ci.len / hop;
     if (ci.len <= 0) ci.status = 1;
-    else if (T < kDeltaWidth) ci.status = 3;  // AFX_CLIP_TOO_SHORT
+    else if (T < min_frames) ci.status = 3;   // AFX_CLIP_TOO_SHORT: only librosa.feature.delta (MFCC group) needs 9 frames
     else ci.n_frames = T;
   }
   return ci;
@@ -414,7 +414,7 @@ __global__ void __launch_bounds__(MAXW * 32, 1) stream_kernel(StreamArgs sa) {
         } else {
           const int fe0 = L0 > 0 ? 1 + L0 / hop : 0;
           const int nu = FPW * ((fe0 + FPW - 1) / FPW);   // hop-block sums written by pass 0
-          ci = trim_decide_warp(sl.blk, nu, L0, hop, a.trim_top_db, lane);
+          ci = trim_decide_warp(sl.blk, nu, L0, hop, a.trim_top_db, (a.mask & 0x2u) ? kDeltaWidth : 1, lane);
           a0 = ci.start / hop;
         }
       }

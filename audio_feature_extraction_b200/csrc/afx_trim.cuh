@@ -25,6 +25,7 @@ struct TrimArgs {
   float coef;                 // pre-emphasis
   float top_db;
   int raw;                    // input already pre-emphasised: no first-sample rule
+  int min_frames;             // kDeltaWidth when the MFCC group is asked for (librosa.feature.delta needs 9 frames), else 1
 };
 
 __device__ __forceinline__ float preemph_sample(float x, float xm1, float coef) {
@@ -131,7 +132,7 @@ __global__ void __launch_bounds__(kTrimThreads) trim_kernel(TrimArgs a) {
       ci.len = ci.end - ci.start;
       const int T = 1 + ci.len / a.hop;
       if (ci.len <= 0) ci.status = 1;
-      else if (T < kDeltaWidth) ci.status = 3;  // AFX_CLIP_TOO_SHORT
+      else if (T < a.min_frames) ci.status = 3;  // AFX_CLIP_TOO_SHORT
       else ci.n_frames = T;
     }
     a.info[clip] = ci;

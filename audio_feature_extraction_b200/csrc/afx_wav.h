@@ -6,6 +6,7 @@
 // libsndfile's scaling).  PCM16 mono files can also be delivered as raw 16-bit samples (converted on the device), which
 // halves the host->device bytes.  No resampling.  Pure host code, no CUDA.
 #pragma once
+#include <algorithm>
 #include <atomic>
 #include <cstdint>
 #include <cstdio>
@@ -15,6 +16,8 @@
 
 namespace afx {
 namespace wav {
+
+constexpr int kMaxChannels = 64;   // channel counts a mono mix-down is sized for
 
 enum Status { OK = 0, OPEN_FAILED = 1, NOT_WAVE = 2, MISSING_CHUNK = 3, UNSUPPORTED = 4, LENGTH_MISMATCH = 5, NOT_PCM16_MONO = 6 };
 
@@ -53,7 +56,7 @@ inline int parse(FILE* f, Info& info) {
     pos += 8 + (int64_t)size + (size & 1);
   }
   if (!have_fmt || !have_data) return MISSING_CHUNK;
-  if (info.channels < 1) return UNSUPPORTED;
+  if (info.channels < 1 || info.channels > kMaxChannels) return UNSUPPORTED;   // a crafted fmt chunk must not size a multi-GB decode buffer
   const bool pcm_ok = info.tag == 1 && (info.bits == 8 || info.bits == 16 || info.bits == 24 || info.bits == 32);
   const bool flt_ok = info.tag == 3 && (info.bits == 32 || info.bits == 64);
   if (!pcm_ok && !flt_ok) return UNSUPPORTED;
@@ -104,7 +107,7 @@ inline int load(const char* path, int64_t frames, float* out_f32, int16_t* out_s
     return got == (size_t)frames ? OK : LENGTH_MISMATCH;
   }
   const int bps = info.bits / 8, ch = info.channels;
-  const int64_t chunk_frames = 1 << 15;
+  const int64_t chunk_frames = std::max<int64_t>(1, (int64_t)(1 << 18) / ((int64_t)ch * bps));   // 256 KB of file per read, whatever the channel count
   std::vector<unsigned char> buf((size_t)chunk_frames * ch * bps);
   for (int64_t done = 0; done < frames;) {
     const int64_t n = frames - done < chunk_frames ? frames - done : chunk_frames;
@@ -132,7 +135,7 @@ inline void parallel_for(int64_t n, int threads, Fn fn) {
   if (threads < 1) threads = 1;
   if ((int64_t)threads > n) threads = (int)(n > 0 ? n : 1);
   std::atomic<int64_t> next{0};
-  auto work = [&]() { for (;;) { const int64_t i = next.fetch_add(1); if (i >= n) break; fn(i); } };
+  auto work = [&]() { for (;;) { const int64_t i = next.fetch_add(1); if (i >= n) break; fn(i); } };   // fn must not throw (callers catch per item)
   if (threads == 1) { work(); return; }
   std::vector<std::thread> pool;
   for (int t = 0; t < threads; ++t) pool.emplace_back(work);

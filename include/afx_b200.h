@@ -97,8 +97,8 @@ int afx_frame_width(afx_handle_t h);
 /* Number of frame rows clip i can produce at most: 1 + length/hop_length (librosa centre padding). */
 int64_t afx_max_frames(afx_handle_t h, int64_t length);
 
-/* Bytes of device scratch afx_extract needs for this batch: a small header plus one private slab per
- * resident CTA of the fused kernel (sized by the longest clip).  afx_workspace_min_bytes returns the same. */
+/* Bytes of device scratch afx_extract needs for this batch: a header, the work-item table of the streaming kernel and a
+ * ring of per-clip slabs (sized by the longest clip, kept L2-resident).  afx_workspace_min_bytes returns the same. */
 size_t afx_workspace_bytes(afx_handle_t h, int64_t n_clips, const int32_t* h_lengths);
 size_t afx_workspace_min_bytes(afx_handle_t h, int64_t n_clips, const int32_t* h_lengths);
 
@@ -118,7 +118,10 @@ size_t afx_workspace_min_bytes(afx_handle_t h, int64_t n_clips, const int32_t* h
  *   d_frames     device float32 [sum_i afx_max_frames(len_i), FW] or NULL; clip i's rows start at
  *                row sum_{j<i} afx_max_frames(len_j); only the first meta[i][3] rows are written
  *   d_workspace  device scratch of workspace_bytes (>= afx_workspace_bytes), 256-byte aligned
- *   stream       cudaStream_t as void* (NULL = legacy default stream); the call only enqueues work
+ *   stream       cudaStream_t as void* (NULL = legacy default stream).  The call only enqueues work, except that the
+ *                pYIN group may synchronise `stream` once to grow the handle-owned F0 scratch.
+ * A handle is NOT thread-safe and serves ONE stream at a time: its pinned header staging and F0 scratch are shared by
+ * all calls on it; use one handle per stream / host thread.
  */
 int afx_extract(afx_handle_t h, const float* d_audio, const int64_t* h_offsets, const int32_t* h_lengths,
                 int64_t n_clips, uint32_t feature_mask, float* d_summaries, int32_t* d_meta,
@@ -168,19 +171,30 @@ int afx_f0_postprocess(afx_handle_t h, int64_t n_clips, const int32_t* h_lengths
  *   d_in / d_out          device float32; clip i at d_in[h_in_offsets[i] .. + h_in_lengths[i]) -> d_out[h_out_offsets[i] ..)
  * Only enqueues work on `stream` (after waiting for a previous afx_resample on the same handle).
  */
-/* host only (no device needed): which instantiation of the fused kernel afx_create picks for (sr, frame_length, hop_length):
- * 1 = the stock variant (compile-time run lengths of the mel segment walk: 22.05 kHz / 1024 / 256, 16 kHz / 512 / 128,
- * 44.1 kHz / 2048 / 512), 0 = the table-driven variant, -1 = no kernel for this frame / hop pairing.  mel_runs (nullable)
- * receives the five run lengths of the mel tables built for (sr, frame_length): quarters 0..3 and segment 0. */
-int afx_clip_kernel_variant(int32_t sr, int32_t frame_length, int32_t hop_length, int32_t* mel_runs);
 int64_t afx_resample_length(afx_handle_t h, int32_t native_sr, int64_t n_in);
+int afx_resample(afx_handle_t h, const float* d_in, const int64_t* h_in_offsets, const int32_t* h_in_lengths, int64_t n_clips,
+                 int32_t native_sr, float* d_out, const int64_t* h_out_offsets, void* stream);
 /* host only (no device needed): the phase-ordered filter afx_resample uses for native_sr -> sr, taps[up][taps_per_phase] =
  * h_padded[p + up * j] of scipy.signal.resample_poly's padded Kaiser design; returns up * taps_per_phase (-1 on bad
  * arguments) and copies the taps when taps_capacity is large enough */
 int64_t afx_resample_filter(int32_t sr, int32_t native_sr, float* taps, int64_t taps_capacity, int32_t* up, int32_t* down,
                             int32_t* taps_per_phase, int32_t* n_pre_remove);
-int afx_resample(afx_handle_t h, const float* d_in, const int64_t* h_in_offsets, const int32_t* h_in_lengths, int64_t n_clips,
-                 int32_t native_sr, float* d_out, const int64_t* h_out_offsets, void* stream);
+
+/* host only (no device needed): which instantiation of the fused (streaming) kernel afx_create picks for
+ * (sr, frame_length, hop_length), the reference's constructor arguments (core/feature_extractor.py:10-17):
+ *    1 = the stock variant (compile-time run lengths of the mel segment walk: 22.05 kHz / 1024 / 256, 16 kHz / 512 / 128,
+ *        44.1 kHz / 2048 / 512),
+ *    0 = the table-driven variant (hop = frame_length / 2, / 4, / 8 at any sample rate),
+ *    2 = the run-time-hop variant (any other hop_length <= frame_length / 2; MFCC and energy groups only -- the pYIN group
+ *        needs frame_length / 2 to be a whole number of hops),
+ *   -1 = no kernel (frame_length other than 512 / 1024 / 2048, or hop_length > frame_length / 2).
+ * mel_runs (nullable) receives the five run lengths of the mel tables built for (sr, frame_length): quarters 0..3 and
+ * segment 0. */
+int afx_clip_kernel_variant(int32_t sr, int32_t frame_length, int32_t hop_length, int32_t* mel_runs);
+
+/* diagnostic aid: bytes of the batch header at the front of a workspace for n_clips clips (offsets, lengths, prefixes,
+ * per-clip records, work counters); the work-item table and the slab ring follow it */
+size_t afx_debug_header_bytes(int64_t n_clips);
 
 /*
  * DTW stage downstream of the extractor, batched over pairs of feature sequences, float64:
@@ -246,9 +260,8 @@ int afx_wav_load_batch(const char* const* paths, int64_t n, int threads, int sam
  * number of launches since the last reset. */
 #define AFX_PHASE_TRIM     0   /* separate trim pass, only when hop_length does not divide 512 (trim_kernel) */
 #define AFX_PHASE_FRAMES   1   /* the fused single-pass kernel: pre-emphasis, trim, frames -> FFT -> mel -> dB -> DCT,
-                                  RMS, delta / delta2, statistics -> summary rows       (clip_kernel) */
-#define AFX_PHASE_MFCC     2   /* unused since the fusion (kept for ABI stability) */
-#define AFX_PHASE_FINALIZE 3   /* unused since the fusion */
+                                  energies, delta / delta2, statistics -> summary rows  (item_build_kernel + stream_kernel) */
+/* slots 2 and 3 are reserved (always zero) */
 #define AFX_PHASE_PCM      4   /* PCM16 -> float32                         (pcm16_to_f32_kernel) */
 #define AFX_PHASE_YIN      5   /* YIN difference / CMND / pYIN observations */
 #define AFX_PHASE_VITERBI  6   /* pYIN HMM decode */

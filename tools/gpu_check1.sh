@@ -1,7 +1,6 @@
 #!/bin/bash
 set -u
 mkdir -p gpurun_out
-timeout 900 python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu.log 2>&1; echo "pytest exit $?"; tail -15 gpurun_out/pytest_gpu.log
-python tools/h2d_probe_ranks.py > gpurun_out/h2d_1.json 2>/dev/null; cat gpurun_out/h2d_1.json
-timeout 600 python bench.py --no-legs --no-f0 > gpurun_out/bench_1.json 2> gpurun_out/bench_1.err; echo "bench exit $?"; python -c "
-import json;d=json.load(open('gpurun_out/bench_1.json'));print({k:d[k] for k in ('value','ms_per_step','e2e')})"
+timeout 1200 python -m pytest tests -m gpu -x -q -s > gpurun_out/pytest_gpu.log 2>&1; echo "pytest exit $?"; grep -E "knife edge|flip rate|passed|failed|Error|error" gpurun_out/pytest_gpu.log | tail -15
+timeout 600 python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/smoke.log 2>&1; echo "smoke exit $?"; tail -3 gpurun_out/smoke.log
+AFX_KNIFE_N=100000 timeout 900 python -m pytest tests/test_gpu_knife_edge.py -m gpu -x -q -s -k flip_rate > gpurun_out/knife_100k.log 2>&1; echo "knife100k exit $?"; grep -E "flip rate|passed|failed" gpurun_out/knife_100k.log
