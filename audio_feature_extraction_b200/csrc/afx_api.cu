@@ -79,6 +79,7 @@ struct afx_handle_s {
   int stream_warps = 16;   // warps per CTA of the streaming kernel (one CTA per SM)
   int item_steps = 0;      // warp steps per work item; 0 = chosen per batch (item_steps_for)
   int slab_ring_mb = 48;   // budget of the slab ring (AFX_SLAB_RING_MB)
+  int l2_mode = 1;         // L2 eviction hints of the streaming kernel (AFX_L2_MODE, StreamArgs::l2_mode)
   void (*vit_fn)(afx::VitArgs) = nullptr;     // viterbi_kernel<half width or 0>
   // device tables
   float* d_window = nullptr;
@@ -236,25 +237,33 @@ size_t stream_smem_bytes(const afx_handle_s* h, int warps) {
 // work items of the streaming kernel: runs of item_steps warp steps over the frames of the untrimmed clip (an upper
 // bound of the trimmed frames when the trim runs first); every clip has at least one item, whose completion
 // triggers the clip's finishing phases
+// ring of per-clip slabs: L2-resident when it fits the budget, but never fewer than ~1024 slots (capped at 1 GB):
+// every resident warp streams a different clip when clips are short, and a finishing clip keeps its slot for the
+// duration of its single-warp finisher, so a starved ring stalls the streaming warps (measured on C3: 184 slots 30 ms,
+// 1970 slots 11.6 ms per 8000 clips)
+inline int slots_for(const afx_handle_s* h, long long n_clips, long long max_len) {
+  const size_t sb = slab_bytes_for(h, max_len);
+  const long long by_l2 = (long long)(((size_t)h->slab_ring_mb << 20) / sb);
+  const long long floor_slots = std::min<long long>(1024, (long long)(((size_t)1024 << 20) / sb));
+  return (int)std::max<long long>(2, std::min<long long>({n_clips, std::max<long long>({by_l2, floor_slots, 64LL}), (long long)kMaxSlots}));
+}
+
 // steps per item: large enough that the per-item costs (slot check, arrival atomic + fences) vanish, small enough that
-// every resident warp still gets >= 8 items (a single 5 s clip must spread over the whole GPU: 2-step items)
+// every resident warp still gets >= 8 items (a single 5 s clip must spread over the whole GPU: 2-step items) and that the
+// clips being streamed at any moment (resident warps x item steps / steps per clip) fill at most a third of the slab ring
 inline int item_steps_for(const afx_handle_s* h, int64_t n_clips, const int32_t* h_lengths) {
   if (h->item_steps > 0) return h->item_steps;
   const int fpw = frames_per_step(h);
-  long long steps = 0;
-  for (int64_t i = 0; i < n_clips; ++i) steps += ceil_div(h_lengths[i] > 0 ? frames_ub(h, h_lengths[i]) : 0, fpw);
-  const long long want = steps / (8LL * h->sm_count * h->stream_warps);
-  return (int)std::max<long long>(2, std::min<long long>({want, 32LL, 255LL / fpw}));
+  long long steps = 0, max_len = 0;
+  for (int64_t i = 0; i < n_clips; ++i) { steps += ceil_div(h_lengths[i] > 0 ? frames_ub(h, h_lengths[i]) : 0, fpw); max_len = std::max<long long>(max_len, h_lengths[i]); }
+  const long long warps = (long long)h->sm_count * h->stream_warps;
+  const long long by_balance = steps / (8LL * warps);
+  const long long by_ring = n_clips > 0 ? (long long)slots_for(h, n_clips, max_len) * (steps / std::max<int64_t>(n_clips, 1)) / (3LL * warps) : 2;
+  return (int)std::max<long long>(2, std::min<long long>({by_balance, by_ring, 32LL, 255LL / fpw}));
 }
 inline long long items_of(const afx_handle_s* h, long long len, int item_steps) {
   const long long fpi = (long long)frames_per_step(h) * item_steps;
   return std::max<long long>(1, ceil_div(len > 0 ? frames_ub(h, len) : 0, fpi));
-}
-inline int slots_for(const afx_handle_s* h, long long n_clips, long long max_len) {
-  const size_t sb = slab_bytes_for(h, max_len);
-  // the ring must stay L2-resident next to the input stream (evict_last lines crowd the stream's lines out of the cache)
-  const long long by_l2 = std::max<long long>(64, (long long)(((size_t)h->slab_ring_mb << 20) / sb));
-  return (int)std::max<long long>(1, std::min<long long>({n_clips, by_l2, (long long)kMaxSlots}));
 }
 
 }  // namespace
@@ -344,6 +353,7 @@ int afx_create(const afx_config_t* cfg, afx_handle_t* out) {
   CUDA_TRY(cudaFuncSetAttribute(afx::trim_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
   {  // the warp-autonomous streaming kernel: one CTA per SM with as many warps as shared memory (and 128 registers) allow
     h->stream_fn = stream_kernel_for(cfg->frame_length, cfg->hop_length, mel);
+    if (const char* e = getenv("AFX_L2_MODE")) h->l2_mode = atoi(e) & 3;
     if (const char* e = getenv("AFX_SLAB_RING_MB")) { const int v = atoi(e); if (v >= 1 && v <= 4096) h->slab_ring_mb = v; }
     if (const char* e = getenv("AFX_ITEM_STEPS")) { const int v = atoi(e); if (v >= 1 && v * frames_per_step(h) <= 255) h->item_steps = v; }
     int w = afx::kStreamMaxWarps;
@@ -557,7 +567,7 @@ int afx_extract(afx_handle_t h, const float* d_audio, const int64_t* h_offsets, 
       sa.c = ca;
       sa.c.slabs = ws + L.header_bytes + items_bytes;
       sa.items = reinterpret_cast<const afx::WorkItem*>(ws + L.header_bytes);
-      sa.n_items = (int)n_items; sa.n_slots = n_slots; sa.mel_w0_floats = h->mel_w0_floats;
+      sa.n_items = (int)n_items; sa.n_slots = n_slots; sa.mel_w0_floats = h->mel_w0_floats; sa.l2_mode = h->l2_mode;
       sa.slot_owner = reinterpret_cast<int*>(ws + L.off_slots); sa.slot_done = sa.slot_owner + kMaxSlots;
       const int threads = std::max(n, n_slots);
       afx::item_build_kernel<<<(threads + 255) / 256, 256, 0, stream>>>(sa, reinterpret_cast<const int*>(ws + L.off_item_off),

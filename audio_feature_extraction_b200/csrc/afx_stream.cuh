@@ -73,6 +73,7 @@ struct StreamArgs {
   int* slot_owner;                    // [n_slots] clip that may use the slot (initially the slot index)
   int* slot_done;                     // [n_slots] items of the owner that have been completed
   int mel_w0_floats;                  // floats of Tables::mel_w0 (multiple of 4)
+  int l2_mode;                        // bit 0: input tiles evict_normal instead of evict_first; bit 1: slab rows evict_normal instead of evict_last
 };
 
 // one thread per clip: the clip's items (item_off: host-built prefix; frames_per_item: multiple of the step width)
@@ -177,8 +178,11 @@ __device__ __forceinline__ void mfcc_phase_warp(const ClipArgs& a, const float* 
     const int ne = e_hi - e_lo + 1;                           // <= stat_frames + 8
     __syncwarp();
     {
+      // rows of 16 coefficients (64 B): four lanes per row, 128-bit L2 loads, eight rows per warp instruction
       const float* src = mfcc_rows + (size_t)(a0 + e_lo) * a.n16 + kg;
-      for (int i = lane; i < ne * 16; i += 32) sM[i] = ld_slab(src + (size_t)(i >> 4) * a.n16 + (i & 15), pol);
+#pragma unroll 4
+      for (int i = lane; i < ne * 4; i += 32)
+        *reinterpret_cast<float4*>(sM + 4 * i) = __ldcg(reinterpret_cast<const float4*>(src + (size_t)(i >> 2) * a.n16) + (i & 3));
     }
     __syncwarp();
     const float* col = sM + c;
@@ -256,8 +260,8 @@ __global__ void __launch_bounds__(MAXW * 32, 1) stream_kernel(StreamArgs sa) {
   wc.planeB = reinterpret_cast<float*>(wbufs + (size_t)warp * WB + (WB - kPlaneBFloats * 4));
   wc.mbar = sm.mbar + warp;
   wc.parity = 0;
-  wc.pol_in = l2_policy_evict_first();
-  wc.pol_slab = l2_policy_evict_last();
+  wc.pol_in = (sa.l2_mode & 1) ? l2_policy_evict_normal() : l2_policy_evict_first();
+  wc.pol_slab = (sa.l2_mode & 2) ? l2_policy_evict_normal() : l2_policy_evict_last();
   uint64_t* mb_item = sm.mbar + kStreamWarpSlots + warp;
   unsigned par_item = 0;
   WarpScratch& scr = s_scr[warp];
