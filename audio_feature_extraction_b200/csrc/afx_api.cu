@@ -582,7 +582,7 @@ int afx_extract(afx_handle_t h, const float* d_audio, const int64_t* h_offsets, 
     // ---- pYIN: waves of clips sized by the handle-owned scratch (observation rows + back-pointers + states)
     const afx::host::PyinConsts& pc = h->pc;
     const size_t per_frame = (size_t)h->yin_rec_bytes + (size_t)4 * pc.n_bins + 2;
-    size_t budget = (size_t)4096 << 20;
+    size_t budget = (size_t)12288 << 20;   // observation rows + back-pointers: ~3.6 MB per 10 s clip; 12 GB = four full rounds of the Viterbi kernel
     if (const char* e = getenv("AFX_F0_SCRATCH_MB")) { const long long v = atoll(e); if (v >= 16) budget = (size_t)v << 20; }
     long long max_f = 1;
     for (int i = 0; i < n; ++i) max_f = std::max(max_f, s_frame_off[i + 1] - s_frame_off[i]);
@@ -607,6 +607,12 @@ int afx_extract(afx_handle_t h, const float* d_audio, const int64_t* h_offsets, 
         const long long f = s_frame_off[c1 + 1] - s_frame_off[c1];
         if (c1 > c0 && F + f > cap_frames) break;
         F += f; ++c1;
+      }
+      // a wave that is not the last one is cut to whole rounds of the Viterbi kernel (one CTA per clip, kVitMinCtas CTAs
+      // per SM): a partial round at the end of every wave would leave SMs idle for a whole clip's decode
+      {
+        const int unit = h->sm_count * afx::kVitMinCtas;
+        if (c1 < n && c1 - c0 > unit) c1 = c0 + (c1 - c0) / unit * unit;
       }
       {
         afx::YinArgs ya;

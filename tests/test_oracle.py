@@ -154,6 +154,44 @@ def test_pyin_220hz_tone_is_exact_bin():
     assert not voiced[:8].any() and np.isnan(f0[:8]).all()
 
 
+@pytest.mark.parametrize("sr,fl,hop,freq", [(22050, 1024, 256, 110.0), (22050, 1024, 256, 440.0), (16000, 512, 128, 155.563492),
+                                            (44100, 2048, 512, 329.627557)])
+def test_pyin_analytic_tones_decode_to_the_nearest_pitch_bin(sr, fl, hop, freq):
+    """Independent check of the pYIN restatement: a steady harmonic tone must be voiced on every interior
+    frame and decode to the 0.1-semitone bin nearest its fundamental -- known without any reference implementation."""
+    t = np.arange(int(0.8 * sr)) / sr
+    y = sum(np.sin(2 * np.pi * freq * k * t) / k for k in range(1, 5))
+    y = (0.3 * y / np.max(np.abs(y))).astype(np.float32)
+    f0, voiced, vp = O.pyin(y, O.note_c2_hz, O.note_c7_hz, sr=sr, frame_length=fl, hop_length=hop)
+    body = slice(6, len(f0) - 6)
+    assert voiced[body].all()
+    b = int(round(120 * np.log2(freq / O.note_c2_hz)))
+    np.testing.assert_allclose(f0[body], O.note_c2_hz * 2 ** (b / 120), rtol=1e-12)
+    assert np.all(vp[body] > 0.5)
+
+
+def test_pyin_analytic_glide_silence_and_noise():
+    sr = 22050
+    # a slow glide 200 -> 260 Hz (4.5 semitones per second, far inside the 35.92 octaves/s transition limit): the track
+    # must follow within one bin (10 cents) of the instantaneous frequency
+    n = int(1.0 * sr)
+    t = np.arange(n) / sr
+    finst = 200.0 * (260.0 / 200.0) ** t
+    phase = 2 * np.pi * np.cumsum(finst) / sr
+    y = (0.3 * sum(np.sin(k * phase) / k for k in range(1, 4)) / 1.6).astype(np.float32)
+    f0, voiced, _ = O.pyin(y, O.note_c2_hz, O.note_c7_hz, sr=sr, frame_length=1024, hop_length=256)
+    idx = np.arange(8, len(f0) - 8)
+    assert voiced[idx].all()
+    cents = 1200 * np.abs(np.log2(f0[idx] / finst[np.minimum(idx * 256, n - 1)]))
+    assert cents.max() <= 15.0, cents.max()
+    # digital silence and white noise: no pitch
+    f0s, vs, vps = O.pyin(np.zeros(sr // 2, np.float32), O.note_c2_hz, O.note_c7_hz, sr=sr, frame_length=1024, hop_length=256)
+    assert not vs.any() and np.isnan(f0s).all() and np.all(vps < 0.5)
+    rng = np.random.default_rng(1)
+    f0n, vn, _ = O.pyin((0.1 * rng.standard_normal(sr)).astype(np.float32), O.note_c2_hz, O.note_c7_hz, sr=sr, frame_length=1024, hop_length=256)
+    assert vn.mean() < 0.2
+
+
 def test_transition_matrix_structure():
     A = O.pyin_transition(601, 51)
     assert A.shape == (1202, 1202)

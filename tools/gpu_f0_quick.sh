@@ -1,8 +1,8 @@
 #!/bin/bash
-# parity tests + F0-path bench (2000 clips): prints throughput and per-phase device times
 set -u
 mkdir -p gpurun_out
-timeout 600 python -m pytest tests -m gpu -x -q 2>&1 | tail -5
-timeout 300 python bench.py --features f0,mfcc,energy --clips ${F0_CLIPS:-2000} --steps 3 --warmup 1 --no-e2e --no-cpu-baseline > gpurun_out/bench_f0.json 2> gpurun_out/bench_f0.err
-python -c "
-import json; d=json.load(open('gpurun_out/bench_f0.json')); print(d['value'], d['ms_per_step'], d['roofline']['phases'])"; tail -3 gpurun_out/bench_f0.err
+for mb in 4096 12288; do
+AFX_F0_SCRATCH_MB=$mb timeout 600 python bench.py --no-e2e --no-cpu-baseline --no-legs 2>/dev/null | python -c "
+import json,sys;d=json.loads(sys.stdin.read());f=d['f0_path'];print('scratch $mb MB: f0_path',round(f['value'],1),'audio-hours/s',round(f['ms'],2),'ms',{k:round(v,2) for k,v in f['phases_ms'].items()})"
+done
+timeout 600 python -m pytest tests -m gpu -x -q -k "pyin or f0" 2>&1 | tail -2
