@@ -553,56 +553,76 @@ __global__ void __launch_bounds__(kVitThreads, kVitMinCtas) viterbi_kernel(VitAr
     const int nc = *reinterpret_cast<const int*>(rec);
     const double lu = *reinterpret_cast<const double*>(rec + 8);
     if constexpr (HW > 0) {
-      // ---- filter path: thread <-> 4 consecutive targets of one voicing block
+      // ---- filter path.  Stage 1 (int32 pre-filter): thread <-> 4 consecutive targets of one voicing block, so that
+      // each 128-bit key load feeds 16 (target, predecessor) pairs.  Stage 2 (float64 scan of the surviving chunks):
+      // lane <-> ONE target, consecutive lanes on consecutive targets -- with the stage-1 assignment (lanes 4 targets =
+      // 32 bytes apart) every 64-bit load of F ran into 4-way bank conflicts, which made this kernel shared-memory
+      // bound (ncu r02h: 1 217 conflict wavefronts of ~3 400 per time step).  The chunk masks of a thread's 4 targets
+      // travel packed in one register: one shuffle per round of 32 targets.
       constexpr int W = 2 * HW + 1, NCH = (W + kVitChunk - 1) / kVitChunk, NI4 = (W + 3 + 3) / 4;
+      static_assert(NCH <= 8, "chunk masks are packed 8 bits per target");
       const int NT = (nb + 3) >> 2;
-      for (int task = tid; task < 2 * NT; task += kVitThreads) {
-        const int s = task >= NT ? 1 : 0;
-        const int j0 = 4 * (task - s * NT);
-        const int4* kp = reinterpret_cast<const int4*>(Kq + s * KS + j0);   // keys of predecessors j0 - HW + i, i = 0, 1, ...
-        int acc[4][NCH];
+      for (int t0 = 32 * warp; t0 < 2 * NT; t0 += kVitThreads) {   // warp-uniform: 32 tasks = 128 targets per round
+        const int task = t0 + lane;
+        unsigned packed = 0u;
+        if (task < 2 * NT) {
+          const int s = task >= NT ? 1 : 0;
+          const int j0 = 4 * (task - s * NT);
+          const int4* kp = reinterpret_cast<const int4*>(Kq + s * KS + j0);   // keys of predecessors j0 - HW + i, i = 0, 1, ...
+          int acc[4][NCH];
 #pragma unroll
-        for (int r = 0; r < 4; ++r)
+          for (int r = 0; r < 4; ++r)
 #pragma unroll
-          for (int c = 0; c < NCH; ++c) acc[r][c] = -2147483647;
+            for (int c = 0; c < NCH; ++c) acc[r][c] = -2147483647;
 #pragma unroll
-        for (int i4 = 0; i4 < NI4; ++i4) {
-          const int4 kv = kp[i4];
-          const int keys[4] = {kv.x, kv.y, kv.z, kv.w};
+          for (int i4 = 0; i4 < NI4; ++i4) {
+            const int4 kv = kp[i4];
+            const int keys[4] = {kv.x, kv.y, kv.z, kv.w};
 #pragma unroll
-          for (int u = 0; u < 4; ++u)
+            for (int u = 0; u < 4; ++u)
 #pragma unroll
-            for (int r = 0; r < 4; ++r) {
-              const int d = 4 * i4 + u - r;
-              if (d >= 0 && d < W) acc[r][d / kVitChunk] = __viaddmax_s32(keys[u], a.wk[d], acc[r][d / kVitChunk]);
-            }
-        }
-        const double* Fs = Fp + s * FS + PAD - HW;   // Fs[j + d] = F[j - HW + d]
-#pragma unroll
-        for (int r = 0; r < 4; ++r) {
-          const int j = j0 + r;
-          if (j >= nb) break;
-          int m = acc[r][0];
-#pragma unroll
-          for (int c = 1; c < NCH; ++c) m = max(m, acc[r][c]);
-          const int thr = ((m >> 6) - 3) * 64;      // every chunk that could hold the true float64 maximum
-          unsigned cmask = 0u;
-#pragma unroll
-          for (int c = 0; c < NCH; ++c) cmask |= (acc[r][c] >= thr) ? (1u << c) : 0u;
-          double best = -1.0e308; int arg = 0;
-          while (cmask) {                           // ascending chunks, strict >: first index on float64 ties
-            const int c = __ffs(cmask) - 1;
-            cmask &= cmask - 1;
-            const double* fc = Fs + j + c * kVitChunk;
-            const double* wc = ltr + c * kVitChunk;   // ltr is -1e308 beyond d = 2 HW: those entries never win
-#pragma unroll
-            for (int dd = 0; dd < kVitChunk; ++dd) {
-              const double cand = fc[dd] + wc[dd];
-              if (cand > best) { best = cand; arg = c * kVitChunk + dd; }
-            }
+              for (int r = 0; r < 4; ++r) {
+                const int d = 4 * i4 + u - r;
+                if (d >= 0 && d < W) acc[r][d / kVitChunk] = __viaddmax_s32(keys[u], a.wk[d], acc[r][d / kVitChunk]);
+              }
           }
-          hs[s * NBE + j] = best;
-          harg[s * NBE + j] = (unsigned short)(j - HW + arg);
+#pragma unroll
+          for (int r = 0; r < 4; ++r) {
+            if (j0 + r >= nb) break;
+            int m = acc[r][0];
+#pragma unroll
+            for (int c = 1; c < NCH; ++c) m = max(m, acc[r][c]);
+            const int thr = ((m >> 6) - 3) * 64;      // every chunk that could hold the true float64 maximum
+            unsigned cmask = 0u;
+#pragma unroll
+            for (int c = 0; c < NCH; ++c) cmask |= (acc[r][c] >= thr) ? (1u << c) : 0u;
+            packed |= cmask << (8 * r);
+          }
+        }
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          const int src = 8 * q + (lane >> 2), r = lane & 3;
+          unsigned cmask = (__shfl_sync(0xffffffffu, packed, src) >> (8 * r)) & 0xffu;   // 0: no such target
+          const int task2 = t0 + src;
+          const int s = task2 >= NT ? 1 : 0;
+          const int j = 4 * (task2 - s * NT) + r;
+          if (cmask) {
+            const double* Fs = Fp + s * FS + PAD - HW;   // Fs[j + d] = F[j - HW + d]
+            double best = -1.0e308; int arg = 0;
+            while (cmask) {                           // ascending chunks, strict >: first index on float64 ties
+              const int c = __ffs(cmask) - 1;
+              cmask &= cmask - 1;
+              const double* fc = Fs + j + c * kVitChunk;
+              const double* wc = ltr + c * kVitChunk;   // ltr is -1e308 beyond d = 2 HW: those entries never win
+#pragma unroll
+              for (int dd = 0; dd < kVitChunk; ++dd) {
+                const double cand = fc[dd] + wc[dd];
+                if (cand > best) { best = cand; arg = c * kVitChunk + dd; }
+              }
+            }
+            hs[s * NBE + j] = best;
+            harg[s * NBE + j] = (unsigned short)(j - HW + arg);
+          }
         }
       }
     } else {
