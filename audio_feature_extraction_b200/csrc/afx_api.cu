@@ -231,7 +231,7 @@ inline size_t stream_warp_bytes(const afx_handle_s* h) {
 size_t stream_smem_bytes(const afx_handle_s* h, int warps) {
   const int n_fft = h->cfg.frame_length;
   return 512 + (size_t)afx::kStreamWarpSlots * sizeof(afx::WarpScratch) + 8192 + (n_fft == 2048 ? 4112 : 0) +
-         (size_t)32 * (2 * h->n16 + 4) * 4 + (size_t)(128 * 5 + h->mel_w0_floats) * 4 + (size_t)warps * stream_warp_bytes(h);
+         (size_t)32 * (2 * h->n16 + 4) * 4 + (size_t)(128 * 5 + afx::kMelW0Max) * 4 + (size_t)warps * stream_warp_bytes(h);
 }
 
 // work items of the streaming kernel: runs of item_steps warp steps over the frames of the untrimmed clip (an upper
@@ -336,6 +336,7 @@ int afx_create(const afx_config_t* cfg, afx_handle_t* out) {
     w0.resize((std::max<size_t>(w0.size(), (size_t)mel.cnt0) + 3) & ~(size_t)3, 0.f);
     for (int i = 0; i < mel.cnt0; ++i) w0[i] = mel.dense[(size_t)0 * (1 + cfg->frame_length / 2) + mel.k00 + i];
     h->mel_w0_floats = (int)w0.size();
+    if (h->mel_w0_floats > afx::kMelW0Max) { delete h; return fail(AFX_ERR_UNSUPPORTED, "mel filterbank: %d bins below the first mel point (at most %d)", mel.cnt0, afx::kMelW0Max); }
     CUDA_TRY(upload(mel.lin, &h->d_mel_lin));
     CUDA_TRY(upload(mel.kl, &h->d_mel_kl));
     CUDA_TRY(upload(w0, &h->d_mel_w0));

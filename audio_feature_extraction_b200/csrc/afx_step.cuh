@@ -213,14 +213,15 @@ __device__ __forceinline__ float half_hamming(int k32, float cl, float msl) {
 
 // predicated shared-memory loads: a lane whose predicate is off issues no access (and so takes part in no bank
 // conflict) and gets zero
-__device__ __forceinline__ c64 lds64_if(const c64* p, bool on) {
+// (the predicate i < n is formed inside the asm block: one SETP, no bool -> int -> predicate round trip)
+__device__ __forceinline__ c64 lds64_if(const c64* p, int i, int n) {
   c64 v;
-  asm volatile("{\n\t.reg .pred q;\n\tsetp.ne.s32 q, %2, 0;\n\tmov.b64 %0, 0;\n\t@q ld.shared.b64 %0, [%1];\n\t}" : "=l"(v) : "r"(smem_u32(p)), "r"((int)on));
+  asm volatile("{\n\t.reg .pred q;\n\tsetp.lt.s32 q, %2, %3;\n\tmov.b64 %0, 0;\n\t@q ld.shared.b64 %0, [%1];\n\t}" : "=l"(v) : "r"(smem_u32(p)), "r"(i), "r"(n));
   return v;
 }
-__device__ __forceinline__ float lds32_if(const float* p, bool on) {
+__device__ __forceinline__ float lds32_if(const float* p, int i, int n) {
   float v;
-  asm volatile("{\n\t.reg .pred q;\n\tsetp.ne.s32 q, %2, 0;\n\tmov.f32 %0, 0f00000000;\n\t@q ld.shared.f32 %0, [%1];\n\t}" : "=f"(v) : "r"(smem_u32(p)), "r"((int)on));
+  asm volatile("{\n\t.reg .pred q;\n\tsetp.lt.s32 q, %2, %3;\n\tmov.f32 %0, 0f00000000;\n\t@q ld.shared.f32 %0, [%1];\n\t}" : "=f"(v) : "r"(smem_u32(p)), "r"(i), "r"(n));
   return v;
 }
 
@@ -249,7 +250,7 @@ __device__ __forceinline__ void mel_db3(const ClipArgs& a, const MelLane& ml, Lo
     auto body = [&](int i) {
       const float u = fmaf((float)i, c.y, c.x), dd = fmaf((float)i, c.w, c.z);
       c64 p[NP];
-      loadp(k0 + i, i < len, p);
+      loadp(k0 + i, i, len, p);
 #pragma unroll
       for (int f = 0; f < NP; ++f) { U[q][f] = fma2(p[f], bc2(u), U[q][f]); D[q][f] = fma2(p[f], bc2(dd), D[q][f]); }
     };
@@ -270,7 +271,7 @@ __device__ __forceinline__ void mel_db3(const ClipArgs& a, const MelLane& ml, Lo
     auto body0 = [&](int i) {
       const float w = ml.w0[i];
       c64 p[NP];
-      loadp(a.tab.mel_k00 + i, true, p);
+      loadp(a.tab.mel_k00 + i, 0, 1, p);
 #pragma unroll
       for (int f = 0; f < NP; ++f) u00[f] = fma2(p[f], bc2(w), u00[f]);
     };
@@ -307,7 +308,7 @@ __device__ __forceinline__ void mel_db3s(const ClipArgs& a, const MelLane& ml, L
     const int kl = ml.kl[32 * q + lane];
     const int k0 = kl & 0xffff, len = kl >> 16;
     auto body = [&](int i) {
-      const float p = loadp(k0 + i, i < len);
+      const float p = loadp(k0 + i, i, len);
       U[q] = fmaf(fmaf((float)i, c.y, c.x), p, U[q]); D[q] = fmaf(fmaf((float)i, c.w, c.z), p, D[q]);
     };
     if constexpr (MC::kStatic) {
@@ -323,9 +324,9 @@ __device__ __forceinline__ void mel_db3s(const ClipArgs& a, const MelLane& ml, L
   float u00 = 0.f;
   if constexpr (MC::kStatic) {
 #pragma unroll
-    for (int i = 0; i < MC::cz; ++i) u00 = fmaf(ml.w0[i], loadp(a.tab.mel_k00 + i, true), u00);
+    for (int i = 0; i < MC::cz; ++i) u00 = fmaf(ml.w0[i], loadp(a.tab.mel_k00 + i, 0, 1), u00);
   } else {
-    for (int i = 0; i < a.tab.mel_cnt0; ++i) u00 = fmaf(ml.w0[i], loadp(a.tab.mel_k00 + i, true), u00);
+    for (int i = 0; i < a.tab.mel_cnt0; ++i) u00 = fmaf(ml.w0[i], loadp(a.tab.mel_k00 + i, 0, 1), u00);
   }
   float up0 = __shfl_up_sync(0xffffffffu, U[0], 1);
   float up1 = __shfl_down_sync(0xffffffffu, U[1], 1);
@@ -416,7 +417,7 @@ struct Step2<1024, HOP> {
     }
     __syncwarp();
     float d[2][4];
-    mel_db3<1, MC>(a, ml, [P2](int k, bool on, c64 (&p)[1]) { p[0] = lds64_if(P2 + k, on); }, d, lane);
+    mel_db3<1, MC>(a, ml, [P2](int k, int i, int n, c64 (&p)[1]) { p[0] = lds64_if(P2 + k, i, n); }, d, lane);
     __syncwarp();   // P2 consumed: region B is free for the DCT reduction
     float eb[2] = {lo2(E[0]) + hi2(E[0]), lo2(E[1]) + hi2(E[1])};
     finish_step2<1024, HOP>(a, sm, sl, wc, d, eb, nv, row, own_sums, usum_idx, floor_db, lane);
@@ -507,7 +508,7 @@ struct Step2<512, HOP> {
     }
     __syncwarp();
     float d[4][4];
-    mel_db3<2, MC>(a, ml, [P2](int k, bool on, c64 (&p)[2]) { p[0] = lds64_if(P2 + k, on); p[1] = lds64_if(P2 + PSTRIDE + k, on); }, d, lane);
+    mel_db3<2, MC>(a, ml, [P2](int k, int i, int n, c64 (&p)[2]) { p[0] = lds64_if(P2 + k, i, n); p[1] = lds64_if(P2 + PSTRIDE + k, i, n); }, d, lane);
     __syncwarp();
     float eb[4];
 #pragma unroll
@@ -588,7 +589,7 @@ struct Step2<2048, HOP> {
     }
     __syncwarp();
     float d[1][4];
-    mel_db3s<MC>(a, ml, [P](int k, bool on) { return lds32_if(P + k, on); }, d, lane);
+    mel_db3s<MC>(a, ml, [P](int k, int i, int n) { return lds32_if(P + k, i, n); }, d, lane);
     __syncwarp();
     float eb[1] = {lo2(E) + hi2(E)};
     finish_step2<2048, HOP>(a, sm, sl, wc, d, eb, nv, row, own_sums, usum_idx, floor_db, lane);

@@ -48,6 +48,7 @@ __device__ __forceinline__ float trim_block(const float* usum, int b, int nb, in
   return s;
 }
 constexpr int kStreamMaxWarps = 16;
+constexpr int kMelW0Max = 64;          // floats reserved for the rising weights of mel segment 0 (bins below the first mel point)
 constexpr int kStreamWarpSlots = 24;   // per-CTA mbarrier / scratch slots (an experimental 20-warp variant exists)
 
 struct __align__(16) WorkItem {       // 32 bytes, built on the device (item_build_kernel)
@@ -231,15 +232,18 @@ __global__ void __launch_bounds__(MAXW * 32, 1) stream_kernel(StreamArgs sa) {
   sm.tw = reinterpret_cast<float2*>(smem_raw + 512 + SCR);
   constexpr int PTW_BYTES = NFFT == 2048 ? 4112 : 0;
   sm.ptw = reinterpret_cast<float2*>(smem_raw + 512 + SCR + 8192);
-  float* sDct = reinterpret_cast<float*>(smem_raw + 512 + SCR + 8192 + PTW_BYTES);
+  // every table of fixed size first, the per-warp buffers next, the n16-dependent DCT rows last: all the addresses
+  // the step uses are then compile-time offsets (+ warp * WB), none has to live in a register or be recomputed
+  constexpr int FIXED = 512 + SCR + 8192 + PTW_BYTES;
+  float4* sLin = reinterpret_cast<float4*>(smem_raw + FIXED);
+  int* sKl = reinterpret_cast<int*>(smem_raw + FIXED + 2048);
+  float* sW0 = reinterpret_cast<float*>(smem_raw + FIXED + 2048 + 512);
+  unsigned char* wbufs = smem_raw + FIXED + 2048 + 512 + kMelW0Max * 4;
+  float* sDct = reinterpret_cast<float*>(wbufs + (size_t)(blockDim.x >> 5) * WB);
   const int dstride = 2 * a.n16 + 4;
-  float4* sLin = reinterpret_cast<float4*>(sDct + 32 * dstride);
-  int* sKl = reinterpret_cast<int*>(sLin + 128);
-  float* sW0 = reinterpret_cast<float*>(sKl + 128);
   sm.dct = sDct;
   MelLane ml;
   ml.lin = sLin; ml.kl = sKl; ml.w0 = sW0;
-  unsigned char* wbufs = reinterpret_cast<unsigned char*>(sW0 + sa.mel_w0_floats);
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   for (int i = tid; i < 1024; i += (int)blockDim.x) sm.tw[i] = a.tab.twiddle[i];

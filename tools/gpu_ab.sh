@@ -7,7 +7,7 @@ echo "pytest exit $?" >> gpurun_out/pytest_gpu.log
 tail -25 gpurun_out/pytest_gpu.log
 B="python bench.py --steps 5 --warmup 3 --no-e2e --no-cpu-baseline --no-f0"
 timeout 300 $B > gpurun_out/bench_stream.json 2> gpurun_out/bench_stream.err; echo "stream exit $?"; python -c "
-import json;d=json.load(open('gpurun_out/bench_stream.json'));print('ms_per_step',d['ms_per_step'],'frac',d['roofline']['frac'],'clips_ok',d['config']['clips_ok'])"; tail -3 gpurun_out/bench_stream.err
+import json;d=json.load(open('gpurun_out/bench_stream.json'));print('ms_per_step',d['ms_per_step'],'frac',d['roofline']['frac'],'clips_ok',d['clips_ok'])"; tail -3 gpurun_out/bench_stream.err
 if [ "${NCU:-0}" = "1" ]; then
 SMALL="python bench.py --clips ${NCU_CLIPS:-2368} --steps 2 --warmup 1 --no-e2e --no-cpu-baseline --no-f0"
 $SMALL > gpurun_out/plain2.log 2>&1 &&
