@@ -358,13 +358,9 @@ int afx_create(const afx_config_t* cfg, afx_handle_t* out) {
     if (const char* e = getenv("AFX_SLAB_RING_MB")) { const int v = atoi(e); if (v >= 1 && v <= 4096) h->slab_ring_mb = v; }
     if (const char* e = getenv("AFX_ITEM_STEPS")) { const int v = atoi(e); if (v >= 1 && v * frames_per_step(h) <= 255) h->item_steps = v; }
     int w = afx::kStreamMaxWarps;
-    if (const char* e = getenv("AFX_STREAM_WARPS")) {
-      const int v = atoi(e);
-      if (v >= 1 && v <= afx::kStreamMaxWarps) w = v;
-      else if (v == 20 && h->stream_fn == (stream_fn_t)afx::stream_kernel<1024, 256, true>) {   // experiment: 96 registers per thread
-        h->stream_fn = afx::stream_kernel<1024, 256, true, 20>; w = 20;
-      }
-    }
+    if (const char* e = getenv("AFX_STREAM_WARPS")) { const int v = atoi(e); if (v >= 1 && v <= afx::kStreamMaxWarps) w = v; }
+    // (measured on C2: 12 warps 13.3 ms, 14 warps 11.7 ms, 16 warps 11.3 ms; variants compiled for 18 / 20 warps at 96
+    // registers spill in the step and lose: 12.7 / 13.7 ms; 12 warps at 157 registers without spills: 12.0 ms)
     while (w > 1 && stream_smem_bytes(h, w) + 1024 > (size_t)prop.sharedMemPerBlockOptin) --w;
     if (stream_smem_bytes(h, w) + 1024 > (size_t)prop.sharedMemPerBlockOptin) { delete h; return fail(AFX_ERR_UNSUPPORTED, "the streaming kernel does not fit this device's shared memory"); }
     h->stream_warps = w;

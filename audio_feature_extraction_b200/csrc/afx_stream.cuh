@@ -49,7 +49,7 @@ __device__ __forceinline__ float trim_block(const float* usum, int b, int nb, in
 }
 constexpr int kStreamMaxWarps = 16;
 constexpr int kMelW0Max = 64;          // floats reserved for the rising weights of mel segment 0 (bins below the first mel point)
-constexpr int kStreamWarpSlots = 24;   // per-CTA mbarrier / scratch slots (an experimental 20-warp variant exists)
+constexpr int kStreamWarpSlots = 16;   // per-CTA mbarrier / scratch slots
 
 struct __align__(16) WorkItem {       // 32 bytes, built on the device (item_build_kernel)
   long long audio_off;                // sample offset of the clip in the packed buffer
