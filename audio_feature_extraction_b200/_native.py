@@ -23,7 +23,7 @@ EXPORTS = [
     "afx_summary_width", "afx_frame_width", "afx_max_frames", "afx_workspace_bytes",
     "afx_workspace_min_bytes", "afx_extract", "afx_extract_host", "afx_extract_host_packed",
     "afx_launch_count", "afx_profile_enable", "afx_profile_read", "afx_preprocess", "afx_frame_extras", "afx_wav_probe_batch", "afx_wav_load_batch", "afx_f0_postprocess", "afx_resample_length", "afx_resample_filter", "afx_resample", "afx_dtw_frame_distance", "afx_dtw_accumulated_cost",
-    "afx_clip_kernel_variant", "afx_debug_header_bytes",
+    "afx_clip_kernel_variant", "afx_debug_header_bytes", "afx_extract_static", "afx_static_workspace_capacity",
 ]
 PHASES = ("trim", "frames", "reserved2", "reserved3", "pcm", "yin", "viterbi", "reserved7")
 N_PHASES = 8
@@ -72,6 +72,8 @@ def lib():
     L.afx_workspace_bytes.argtypes = [vp, i64, vp]; L.afx_workspace_bytes.restype = sz
     L.afx_workspace_min_bytes.argtypes = [vp, i64, vp]; L.afx_workspace_min_bytes.restype = sz
     L.afx_extract.argtypes = [vp, vp, vp, vp, i64, u32, vp, vp, vp, vp, sz, vp]; L.afx_extract.restype = C.c_int
+    L.afx_extract_static.argtypes = [vp, vp, vp, vp, i64, u32, vp, vp, vp]; L.afx_extract_static.restype = C.c_int
+    L.afx_static_workspace_capacity.argtypes = []; L.afx_static_workspace_capacity.restype = sz
     L.afx_preprocess.argtypes = [vp, vp, vp, vp, i64, vp, vp, vp, vp, sz, vp]; L.afx_preprocess.restype = C.c_int
     L.afx_frame_extras.argtypes = [vp, vp, i64, vp, vp, vp, vp, vp]; L.afx_frame_extras.restype = C.c_int
     L.afx_wav_probe_batch.argtypes = [vp, i64, C.c_int, vp, vp, vp, vp, vp]; L.afx_wav_probe_batch.restype = C.c_int

@@ -1192,3 +1192,148 @@ int afx_extract_host(afx_handle_t h, const float* const* h_clips, const int32_t*
 }
 
 }  // extern "C"
+
+// =====================================================================================================
+// afx_extract_static: the fused MFCC + delta + energy pass (afx_extract without the F0 group and without framewise
+// output) for callers that must not allocate: code under CUDA graph capture, tight serving loops, harnesses that forbid
+// cudaMalloc.  No counterpart in the reference.
+//
+// The scratch of the pass (batch header, work-item table, ring of per-clip slabs -- what afx_extract takes as
+// d_workspace) lives in ONE file-scope device array of AFX_STATIC_WORKSPACE_BYTES that every GPU which loads the library
+// holds until exit.  Its name is a host-side stand-in in host code, NOT a device address: the device address comes from
+// cudaGetSymbolAddress, once per device with that device current, and is what the kernels are given.
+// The call allocates nothing (no cudaMalloc / cudaFree / cudaMallocHost, no event creation): the header arrays are built
+// in a stack buffer and copied with cudaMemcpyAsync, the work counter is cleared with cudaMemsetAsync (the array keeps
+// the last call's contents; everything else the kernels read is rewritten by this call: the slot owner / arrival
+// counters by item_build_kernel, the slabs by the steps before the finisher reads them).
+// Every call shares the array: calls whose GPU work overlaps (two streams, two threads, two handles on one device) race.
+static __device__ __align__(256) unsigned char g_afx_static_ws[AFX_STATIC_WORKSPACE_BYTES];
+
+namespace {
+constexpr int kStaticMaxDevices = 64;
+unsigned char* g_static_ws_ptr[kStaticMaxDevices] = {nullptr};   // device address of g_afx_static_ws, per device
+std::atomic<int> g_static_ws_lock{0};
+
+// device address of the static scratch on `device` (the current device); resolved once per device
+int static_ws_address(int device, unsigned char** out) {
+  if (device < 0 || device >= kStaticMaxDevices) return fail(AFX_ERR_UNSUPPORTED, "afx_extract_static: device index %d out of range", device);
+  while (g_static_ws_lock.exchange(1, std::memory_order_acquire)) {}
+  unsigned char* p = g_static_ws_ptr[device];
+  cudaError_t e = cudaSuccess;
+  if (!p) {
+    e = cudaGetSymbolAddress(reinterpret_cast<void**>(&p), g_afx_static_ws);
+    if (e == cudaSuccess) g_static_ws_ptr[device] = p;
+  }
+  g_static_ws_lock.store(0, std::memory_order_release);
+  if (e != cudaSuccess) return fail(AFX_ERR_CUDA, "afx_extract_static: cudaGetSymbolAddress failed: %s", cudaGetErrorString(e));
+  *out = p;
+  return AFX_OK;
+}
+}  // namespace
+
+extern "C" {
+
+size_t afx_static_workspace_capacity(void) { return (size_t)AFX_STATIC_WORKSPACE_BYTES; }
+
+int afx_extract_static(afx_handle_t h, const float* d_audio, const int64_t* h_offsets, const int32_t* h_lengths,
+                       int64_t n_clips, uint32_t feature_mask, float* d_summaries, int32_t* d_meta, void* stream_v) {
+  if (!h) return fail(AFX_ERR_INVALID_ARG, "afx_extract_static: null handle");
+  if (n_clips == 0) return AFX_OK;
+  if (n_clips < 0 || n_clips > AFX_STATIC_MAX_CLIPS)
+    return fail(AFX_ERR_UNSUPPORTED, "afx_extract_static: %lld clips exceed the maximum of %d per call", (long long)n_clips, AFX_STATIC_MAX_CLIPS);
+  if (!d_audio || !h_offsets || !h_lengths || !d_summaries || !d_meta) return fail(AFX_ERR_INVALID_ARG, "afx_extract_static: null pointer argument");
+  if ((feature_mask & ~(AFX_FEAT_MFCC | AFX_FEAT_ENERGY | AFX_FEAT_PREPROCESSED)) != 0)
+    return fail(AFX_ERR_UNSUPPORTED, "afx_extract_static: feature bits 0x%x: only AFX_FEAT_MFCC, AFX_FEAT_ENERGY (and AFX_FEAT_PREPROCESSED) are served", feature_mask);
+  const bool raw = (feature_mask & AFX_FEAT_PREPROCESSED) != 0;
+  feature_mask &= AFX_FEAT_ALL;
+  const float coef = raw ? 0.f : h->cfg.pre_emphasis;
+  const float trim_top_db = raw ? 3.0e38f : h->cfg.trim_top_db;
+  if ((reinterpret_cast<uintptr_t>(d_audio) & 15u) != 0) return fail(AFX_ERR_INVALID_ARG, "afx_extract_static: d_audio must be 16-byte aligned");
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_v);
+  CUDA_TRY(cudaSetDevice(h->cfg.device));
+  unsigned char* ws_u = nullptr;
+  if (int rc = static_ws_address(h->cfg.device, &ws_u)) return rc;
+  char* ws = reinterpret_cast<char*>(ws_u);
+  const int n = (int)n_clips;
+  const int hop = h->cfg.hop_length;
+
+  // ---- header arrays in a stack buffer (same layout as afx_extract's pinned staging)
+  const Layout L = header_layout(n);
+  const size_t staged_bytes = L.off_info;
+  alignas(16) unsigned char st[40 * AFX_STATIC_MAX_CLIPS + 256];
+  if (staged_bytes > sizeof st) return fail(AFX_ERR_UNSUPPORTED, "afx_extract_static: header of %zu bytes exceeds the stack buffer", staged_bytes);
+  memset(st, 0, staged_bytes);
+  long long* s_offsets = reinterpret_cast<long long*>(st + L.off_offsets);
+  long long* s_frame_off = reinterpret_cast<long long*>(st + L.off_frame_off);
+  int* s_lengths = reinterpret_cast<int*>(st + L.off_lengths);
+  int* s_item_off = reinterpret_cast<int*>(st + L.off_item_off);
+  long long fo = 0, max_len = 0, n_items = 0;
+  const int isteps = item_steps_for(h, n_clips, h_lengths);
+  for (int i = 0; i < n; ++i) {
+    if (h_lengths[i] < 0) return fail(AFX_ERR_INVALID_ARG, "afx_extract_static: clip %d has negative length", i);
+    if (h_offsets[i] < 0 || (h_offsets[i] & 3) != 0) return fail(AFX_ERR_INVALID_ARG, "afx_extract_static: clip %d offset %lld is not a multiple of 4 samples", i, (long long)h_offsets[i]);
+    s_offsets[i] = h_offsets[i];
+    s_lengths[i] = h_lengths[i];
+    s_frame_off[i] = fo;
+    s_item_off[i] = (int)n_items;
+    n_items += items_of(h, h_lengths[i], isteps);
+    fo += frames_ub(h, h_lengths[i]);
+    max_len = std::max<long long>(max_len, h_lengths[i]);
+  }
+  s_frame_off[n] = fo;
+  s_item_off[n] = (int)n_items;
+  const bool one_pass = single_pass(h);
+  const long long max_trim_blocks = (200 * 1024) / 4 - 8;
+  if (!one_pass && ceil_div(max_len, afx::kTrimHop) > max_trim_blocks)
+    return fail(AFX_ERR_UNSUPPORTED, "afx_extract_static: clips longer than %lld samples need hop_length dividing 512", max_trim_blocks * afx::kTrimHop);
+
+  const size_t slab_bytes = slab_bytes_for(h, max_len);
+  const int n_slots = slots_for(h, n, max_len);
+  const size_t items_bytes = align_up((size_t)n_items * sizeof(afx::WorkItem), 256);
+  const size_t need = L.header_bytes + items_bytes + (size_t)n_slots * slab_bytes;
+  if (need > (size_t)AFX_STATIC_WORKSPACE_BYTES)
+    return fail(AFX_ERR_WORKSPACE, "afx_extract_static: this batch needs %zu bytes of scratch, the static array holds %zu (fewer or shorter clips, or afx_extract with a caller workspace)",
+                need, (size_t)AFX_STATIC_WORKSPACE_BYTES);
+
+  // pageable source: the copy is staged before the call returns, so the stack buffer may go out of scope
+  CUDA_TRY(cudaMemcpyAsync(ws, st, staged_bytes, cudaMemcpyHostToDevice, stream));
+  CUDA_TRY(cudaMemsetAsync(ws + L.off_counter, 0, 256, stream));   // the work counter must start at zero
+  const long long* d_offsets = reinterpret_cast<const long long*>(ws + L.off_offsets);
+  const long long* d_frame_off = reinterpret_cast<const long long*>(ws + L.off_frame_off);
+  const int* d_lengths = reinterpret_cast<const int*>(ws + L.off_lengths);
+  afx::ClipInfo* d_info = reinterpret_cast<afx::ClipInfo*>(ws + L.off_info);
+
+  if (!one_pass) {
+    afx::TrimArgs ta;
+    ta.audio = d_audio; ta.offsets = d_offsets; ta.lengths = d_lengths; ta.info = d_info;
+    ta.clip_begin = 0; ta.hop = hop; ta.coef = coef; ta.top_db = trim_top_db; ta.raw = raw ? 1 : 0;
+    ta.min_frames = (feature_mask & AFX_FEAT_MFCC) ? afx::kDeltaWidth : 1;
+    const size_t smem = (size_t)(ceil_div(max_len, afx::kTrimHop) + 4) * sizeof(float);
+    afx::trim_kernel<<<n, afx::kTrimThreads, smem, stream>>>(ta);
+    ++g_launches;
+  }
+  afx::StreamArgs sa;
+  afx::ClipArgs& ca = sa.c;
+  ca.audio = d_audio; ca.offsets = d_offsets; ca.lengths = d_lengths; ca.frame_off = d_frame_off; ca.info = d_info;
+  ca.counter = reinterpret_cast<int*>(ws + L.off_counter); ca.n_clips = n;
+  ca.slabs = ws + L.header_bytes + items_bytes; ca.slab_bytes = slab_bytes; ca.a_max = slab_rows(h, max_len);
+  ca.tab = h->tab; ca.dct_t = h->d_dct_t; ca.hop = hop;
+  ca.coef = coef; ca.trim_top_db = trim_top_db; ca.mfcc_top_db = h->cfg.mfcc_top_db; ca.raw = raw ? 1 : 0;
+  ca.n_mfcc = h->cfg.n_mfcc; ca.n16 = h->n16; ca.summary_width = afx_summary_width(h); ca.frame_width = afx_frame_width(h);
+  ca.mask = feature_mask; ca.summaries = d_summaries; ca.meta = d_meta; ca.frames_out = nullptr;
+  ca.pretrimmed = one_pass ? 0 : 1;
+  sa.items = reinterpret_cast<const afx::WorkItem*>(ws + L.header_bytes);
+  sa.n_items = (int)n_items; sa.n_slots = n_slots; sa.mel_w0_floats = h->mel_w0_floats; sa.l2_mode = h->l2_mode;
+  sa.slot_owner = reinterpret_cast<int*>(ws + L.off_slots); sa.slot_done = sa.slot_owner + kMaxSlots;
+  const int threads = std::max(n, n_slots);
+  afx::item_build_kernel<<<(threads + 255) / 256, 256, 0, stream>>>(sa, reinterpret_cast<const int*>(ws + L.off_item_off),
+                                                                     frames_per_step(h) * isteps);
+  const long long want = ceil_div(n_items, h->stream_warps);
+  const int sgrid = (int)std::max<long long>(1, std::min<long long>(want, h->sm_count));
+  h->stream_fn<<<sgrid, h->stream_warps * 32, stream_smem_bytes(h, h->stream_warps), stream>>>(sa);
+  g_launches += 2;
+  CUDA_TRY(cudaGetLastError());
+  return AFX_OK;
+}
+
+}  // extern "C"

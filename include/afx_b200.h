@@ -128,6 +128,28 @@ int afx_extract(afx_handle_t h, const float* d_audio, const int64_t* h_offsets, 
                 float* d_frames, void* d_workspace, size_t workspace_bytes, void* stream);
 
 /*
+ * afx_extract without allocation.  No counterpart in the reference: added for
+ * callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * Same computation and same results as afx_extract(..., d_frames = NULL, ...) for the AFX_FEAT_MFCC / AFX_FEAT_ENERGY
+ * groups (AFX_FEAT_PREPROCESSED allowed; the F0 group is not served: its scratch is sized per frame), but the scratch
+ * the fused pass needs (batch header, work-item table, ring of per-clip slabs) is a file-scope static device array of
+ * AFX_STATIC_WORKSPACE_BYTES that every GPU which loads the library holds until exit, so the caller passes only inputs
+ * and outputs.  The call performs no cudaMalloc / cudaFree / cudaMallocHost and creates no event or stream; it enqueues
+ * one small host->device copy of the header, one memset of the work counter and the kernels on `stream`.
+ * Limits: n_clips <= AFX_STATIC_MAX_CLIPS and afx_workspace_bytes(h, n_clips, h_lengths) - 1024 <= AFX_STATIC_WORKSPACE_BYTES
+ * (at the defaults 22.05 kHz / 1024 / 256 / n_mfcc 13: about 100 clips of 10 s or 35 clips of 30 s); beyond either the
+ * call fails with AFX_ERR_UNSUPPORTED / AFX_ERR_WORKSPACE and a message that names the sizes.
+ * All calls on one device share the array, which keeps the last call's contents (the call clears what must start at
+ * zero): calls whose GPU work overlaps -- two streams, two host threads, two handles on one device -- race.
+ * afx_static_workspace_capacity returns AFX_STATIC_WORKSPACE_BYTES as built.
+ */
+#define AFX_STATIC_WORKSPACE_BYTES (8u << 20)
+#define AFX_STATIC_MAX_CLIPS 256
+int afx_extract_static(afx_handle_t h, const float* d_audio, const int64_t* h_offsets, const int32_t* h_lengths,
+                       int64_t n_clips, uint32_t feature_mask, float* d_summaries, int32_t* d_meta, void* stream);
+size_t afx_static_workspace_capacity(void);
+
+/*
  * preprocess_audio (core/feature_extractor.py:58-74) on its own: librosa.effects.preemphasis (:69) followed by
  * librosa.effects.trim(top_db=30) (:72).  d_out has the packing of d_audio; clip i's result is
  * d_out[h_offsets[i] + meta[i][1] .. h_offsets[i] + meta[i][2]) (zeros elsewhere inside the clip).
