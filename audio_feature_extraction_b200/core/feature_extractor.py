@@ -12,6 +12,8 @@ import logging
 from pathlib import Path
 from typing import Any, Dict, List, Optional, Sequence, Tuple
 
+import os
+
 import numpy as np
 
 from .. import _native as N
@@ -72,6 +74,7 @@ class AudioFeatureExtractor:
         self.logger = logging.getLogger(__name__)
         self._handle = None
         self._ws = None
+        self._pin_bufs = {}   # reused pinned ingest buffers of batch_process, per sample dtype
 
     # ------------------------------------------------------------------ native handle
     def _h(self):
@@ -171,13 +174,75 @@ class AudioFeatureExtractor:
         m = meta.cpu().numpy()
         return self.rows_to_dicts(s, m, names, features_to_extract, skip_errors=skip_errors)
 
+    def _extract_wav_group(self, names: Sequence[str], frames: np.ndarray, pcm16: bool, features_to_extract=None):
+        """Summary / meta rows (host numpy) and decode status of WAV files already at self.sr.  The files are cut into
+        chunks of ~128 M samples; a helper thread decodes chunk i + 1 into one of two reused pinned buffers (native
+        threaded reader) while afx_extract_host_packed streams chunk i to the GPU, so file decoding overlaps the H2D
+        copies and the kernels (both calls release the GIL).  Raw 16-bit samples when pcm16 (converted on the device)."""
+        import threading
+        import torch
+        from ..wav import load_batch
+
+        L = N.lib()
+        h = self._h()
+        n = len(names)
+        frames = np.asarray(frames, dtype=np.int64)
+        hs = np.zeros((n, self.summary_width), np.float32)
+        hm = np.zeros((n, 4), np.int32)
+        st = np.zeros(n, np.int32)
+        if n == 0:
+            return hs, hm, st
+        strides = (frames + 7) // 8 * 8
+        cap = max(int(os.environ.get("AFX_INGEST_CHUNK_SAMPLES", 128 << 20)), int(strides.max()) + 8)
+        cuts, acc = [0], 0
+        for i in range(n):                                   # greedy cut into chunks of at most `cap` samples
+            if acc + int(strides[i]) > cap and i > cuts[-1]:
+                cuts.append(i); acc = 0
+            acc += int(strides[i])
+        cuts.append(n)
+        chunks = [(cuts[k], cuts[k + 1]) for k in range(len(cuts) - 1)]
+        need = max(int(strides[a:b].sum()) for a, b in chunks) + 8
+        dtype = torch.int16 if pcm16 else torch.float32
+        bufs = self._pin_bufs.get(dtype)
+        if bufs is None or bufs[0].numel() < need:
+            # int16 garbage between clips is harmless (never read as signal); float32 gaps must not hold NaN patterns
+            mk = torch.empty if pcm16 else torch.zeros
+            bufs = [mk(need, dtype=dtype, pin_memory=True) for _ in range(min(2, len(chunks)))]
+            self._pin_bufs[dtype] = bufs
+        mask = _mask_of(features_to_extract)
+
+        def decode(k):
+            a, b = chunks[k]
+            off = np.zeros(b - a, np.int64)
+            off[1:] = np.cumsum(strides[a:b])[:-1]
+            st[a:b] = load_batch(names[a:b], frames[a:b], bufs[k % len(bufs)], off, as_pcm16=pcm16)
+            return off
+
+        off = decode(0)
+        for k, (a, b) in enumerate(chunks):
+            nxt, box = None, {}
+            if k + 1 < len(chunks):
+                nxt = threading.Thread(target=lambda: box.setdefault("off", decode(k + 1)))
+                nxt.start()
+            lengths = np.where(st[a:b] == 0, frames[a:b], 0).astype(np.int32)   # a file that failed to decode: empty clip
+            ks = np.zeros((b - a, self.summary_width), np.float32)
+            km = np.zeros((b - a, 4), np.int32)
+            total = int(strides[a:b].sum()) + 8
+            N.check(L.afx_extract_host_packed(h, bufs[k % len(bufs)].data_ptr(), N.SAMPLE_S16 if pcm16 else N.SAMPLE_F32, total,
+                                              off.ctypes.data, lengths.ctypes.data, b - a, mask, ks.ctypes.data, km.ctypes.data))
+            hs[a:b] = ks; hm[a:b] = km
+            if nxt is not None:
+                nxt.join()
+                off = box["off"]
+        return hs, hm, st
+
     def rows_for_files(self, files: Sequence[str], features_to_extract: Optional[Sequence[str]] = None):
         """Summary and meta rows (host numpy, one row per file, in order) of WAV files: probed and decoded by the native
         threaded reader into ONE pinned buffer (raw 16-bit samples when every file is 16-bit mono PCM) that
         afx_extract_host_packed streams to the GPU in waves; files at another sample rate go through load_audio (device
         resampler).  An unreadable file keeps an AFX_CLIP_EMPTY row, so rows stay aligned with `files`."""
         import torch
-        from ..wav import probe_batch, load_batch, WAV_STATUS
+        from ..wav import probe_batch, WAV_STATUS
 
         n = len(files)
         L = N.lib()
@@ -195,20 +260,10 @@ class AudioFeatureExtractor:
                 self.logger.error(f"載入音頻文件失敗: {files[i]}: {WAV_STATUS.get(int(info['status'][i]), 'unreadable')}")
         if keep:
             names = [files[i] for i in keep]
-            frames = info["frames"][keep].astype(np.int64)
             pcm16 = bool(np.all((info["tag"][keep] == 1) & (info["bits"][keep] == 16) & (info["channels"][keep] == 1)))
-            strides = (frames + 7) // 8 * 8
-            offsets = np.zeros(len(keep), dtype=np.int64)
-            offsets[1:] = np.cumsum(strides)[:-1]
-            total = int(strides.sum()) + 8
-            host = torch.zeros(total, dtype=torch.int16 if pcm16 else torch.float32, pin_memory=True)
-            st = load_batch(names, frames, host, offsets, as_pcm16=pcm16)
-            lengths = np.where(st == 0, frames, 0).astype(np.int32)   # a file that failed to decode becomes an empty clip
-            ks = np.zeros((len(keep), self.summary_width), np.float32)
-            km = np.zeros((len(keep), 4), np.int32)
-            N.check(L.afx_extract_host_packed(h, host.data_ptr(), N.SAMPLE_S16 if pcm16 else N.SAMPLE_F32, total,
-                                              offsets.ctypes.data, lengths.ctypes.data, len(keep), _mask_of(features_to_extract),
-                                              ks.ctypes.data, km.ctypes.data))
+            ks, km, st = self._extract_wav_group(names, info["frames"][keep], pcm16, features_to_extract)
+            for j in np.nonzero(st)[0]:
+                self.logger.error(f"載入音頻文件失敗: {names[j]}: {WAV_STATUS.get(int(st[j]), 'unreadable')}")
             hs[keep] = ks; hm[keep] = km
         if other:
             dev = torch.device("cuda", self.device)
@@ -254,8 +309,11 @@ class AudioFeatureExtractor:
         mask = _mask_of(features_to_extract)
         n = self.n_mfcc
         out = []
+        rows = np.asarray(s).tolist()          # one bulk float32 -> Python float conversion for the whole batch
+        status = np.asarray(m)[:, 0].tolist()
+        e0 = 4 + 4 * n
         for i, name in enumerate(names):
-            st = int(m[i, 0])
+            st = status[i]
             if st != N.CLIP_OK:
                 err = FeatureExtractionError(f"{name}: {_STATUS_MSG.get(st, 'status %d' % st)}")
                 if skip_errors:
@@ -263,21 +321,20 @@ class AudioFeatureExtractor:
                     continue
                 self.logger.error(f"特徵提取失敗: {err}")  # reference :212
                 raise err
-            row = s[i]
+            row = rows[i]
             d: Dict[str, Any] = {"file_path": name}  # reference :203
             if mask & N.AFX_FEAT_F0:  # reference :110-113
-                d.update(f0_mean=float(row[0]), f0_std=float(row[1]), f0_missing_rate=float(row[2]), f0_quality=float(row[3]))
+                d.update(f0_mean=row[0], f0_std=row[1], f0_missing_rate=row[2], f0_quality=row[3])
             if mask & N.AFX_FEAT_MFCC:  # reference :147-150
-                d.update(mfcc_mean=row[4:4 + n].tolist(), mfcc_std=row[4 + n:4 + 2 * n].tolist(),
-                         mfcc_delta_mean=row[4 + 2 * n:4 + 3 * n].tolist(), mfcc_delta2_mean=row[4 + 3 * n:4 + 4 * n].tolist())
-            e0 = 4 + 4 * n
+                d.update(mfcc_mean=row[4:4 + n], mfcc_std=row[4 + n:4 + 2 * n],
+                         mfcc_delta_mean=row[4 + 2 * n:4 + 3 * n], mfcc_delta2_mean=row[4 + 3 * n:e0])
             if mask & N.AFX_FEAT_ENERGY:  # reference :176-178
-                d.update(energy_mean=float(row[e0]), energy_std=float(row[e0 + 1]), energy_range=float(row[e0 + 2]))
+                d.update(energy_mean=row[e0], energy_std=row[e0 + 1], energy_range=row[e0 + 2])
             if self.extended_stats:  # README.md:25-28 of the reference (skew / kurtosis)
                 if mask & N.AFX_FEAT_MFCC:
-                    d.update(mfcc_skew=row[e0 + 3:e0 + 3 + n].tolist(), mfcc_kurtosis=row[e0 + 3 + n:e0 + 3 + 2 * n].tolist())
+                    d.update(mfcc_skew=row[e0 + 3:e0 + 3 + n], mfcc_kurtosis=row[e0 + 3 + n:e0 + 3 + 2 * n])
                 if mask & N.AFX_FEAT_ENERGY:
-                    d.update(energy_skew=float(row[e0 + 3 + 2 * n]), energy_kurtosis=float(row[e0 + 4 + 2 * n]))
+                    d.update(energy_skew=row[e0 + 3 + 2 * n], energy_kurtosis=row[e0 + 4 + 2 * n])
             out.append(d)
         return out
 
@@ -539,12 +596,12 @@ class AudioFeatureExtractor:
 
     def batch_process(self, audio_dir: str, features_to_extract: Optional[Sequence[str]] = None) -> List[Dict[str, Any]]:
         """批量處理音頻文件 (reference :215-237): every *.wav of the directory in one batched pass.
-        Files are probed and decoded by the native threaded reader (afx_wav_*) straight into ONE pinned host buffer
-        (raw 16-bit samples when every file is 16-bit mono PCM: half the PCIe bytes, converted on the device), which
-        afx_extract_host_packed streams to the GPU in waves overlapped with the kernels.  Files that fail to load or to
-        extract are logged and skipped, in the reference's enumeration order."""
-        import torch
-        from ..wav import probe_batch, load_batch, WAV_STATUS
+        Files are probed and decoded by the native threaded reader (afx_wav_*) straight into reused pinned host buffers
+        (raw 16-bit samples when every file is 16-bit mono PCM: half the PCIe bytes, converted on the device), chunk by
+        chunk, while afx_extract_host_packed streams the previous chunk to the GPU in waves overlapped with the kernels
+        (_extract_wav_group).  Files that fail to load or to extract are logged and skipped, in the reference's
+        enumeration order."""
+        from ..wav import probe_batch, WAV_STATUS
 
         files = [str(p) for p in Path(audio_dir).glob("*.wav")]
         if not files:
@@ -567,21 +624,8 @@ class AudioFeatureExtractor:
         if not keep:
             return []
         names = [files[i] for i in keep]
-        frames = info["frames"][keep].astype(np.int64)
         pcm16 = bool(np.all((info["tag"][keep] == 1) & (info["bits"][keep] == 16) & (info["channels"][keep] == 1)))
-        strides = (frames + 7) // 8 * 8
-        offsets = np.zeros(len(keep), dtype=np.int64)
-        offsets[1:] = np.cumsum(strides)[:-1]
-        total = int(strides.sum()) + 8
-        host = torch.zeros(total, dtype=torch.int16 if pcm16 else torch.float32, pin_memory=True)
-        st = load_batch(names, frames, host, offsets, as_pcm16=pcm16)
-        lengths = np.where(st == 0, frames, 0).astype(np.int32)   # a file that failed to decode becomes an empty clip
-        n = len(names)
-        hs = np.zeros((n, self.summary_width), np.float32)
-        hm = np.zeros((n, 4), np.int32)
-        N.check(L.afx_extract_host_packed(h, host.data_ptr(), N.SAMPLE_S16 if pcm16 else N.SAMPLE_F32, total,
-                                          offsets.ctypes.data, lengths.ctypes.data, n, _mask_of(features_to_extract),
-                                          hs.ctypes.data, hm.ctypes.data))
+        hs, hm, st = self._extract_wav_group(names, info["frames"][keep], pcm16, features_to_extract)
         for i in np.nonzero(st)[0]:
             self.logger.error(f"載入音頻文件失敗: {names[i]}: {WAV_STATUS.get(int(st[i]), 'unreadable')}")
         results = self.rows_to_dicts(hs, hm, names, features_to_extract, skip_errors=True)
