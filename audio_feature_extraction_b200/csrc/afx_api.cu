@@ -70,7 +70,7 @@ struct afx_handle_s {
   double* d_pyin = nullptr;            // all double tables, one allocation
   afx::PyinTables ptab;
   const double *d_lt_same = nullptr, *d_edge_corr = nullptr, *d_freqs = nullptr;
-  int yin_c = 0, yin_cap = 0, yin_rec_bytes = 0, yin_lag_pad = 0, yin_tile = 0, yin_frames_per_chunk = 0;
+  int yin_c = 0, yin_cap = 0, yin_rec_bytes = 0, yin_lag_pad = 0, yin_tile = 0, yin_frames_per_chunk = 0, yin_blk_len = 0, yin_rb = 1;
   size_t yin_smem = 0, vit_smem = 0;
   void* d_f0_ws = nullptr; size_t d_f0_ws_bytes = 0;   // handle-owned scratch of the F0 path (observation rows, back-pointers)
   int mel_floats = 0;      // floats in the padded sparse mel weight table
@@ -80,6 +80,7 @@ struct afx_handle_s {
   int item_steps = 0;      // warp steps per work item; 0 = chosen per batch (item_steps_for)
   int slab_ring_mb = 48;   // budget of the slab ring (AFX_SLAB_RING_MB)
   int l2_mode = 1;         // L2 eviction hints of the streaming kernel (AFX_L2_MODE, StreamArgs::l2_mode)
+  void (*yin_fn)(afx::YinArgs) = nullptr;     // yin_obs_kernel<lags per lane, frame mode>
   void (*vit_fn)(afx::VitArgs) = nullptr;     // viterbi_kernel<half width or 0>
   // device tables
   float* d_window = nullptr;
@@ -368,9 +369,9 @@ int afx_create(const afx_config_t* cfg, afx_handle_t* out) {
   }
   {  // pYIN constants and tables (F0 group); an unsupported f0 range only disables that group
     afx::host::PyinConsts& pc = h->pc;
-    // the block autocorrelation of yin_obs_kernel needs the analysis window (frame_length / 2) to be a whole number of hops
-    h->f0_ok = (cfg->frame_length / 2) % cfg->hop_length == 0 && !runtime_hop(cfg->frame_length, cfg->hop_length) &&
-               afx::host::pyin_consts(cfg->sr, cfg->frame_length, cfg->hop_length, cfg->f0_min, cfg->f0_max, pc) &&
+    // yin_obs_kernel shares the autocorrelation products between overlapping frames when the analysis window
+    // (frame_length / 2) is a whole number of hops (block mode); any other hop gets one block per frame (frame mode)
+    h->f0_ok = afx::host::pyin_consts(cfg->sr, cfg->frame_length, cfg->hop_length, cfg->f0_min, cfg->f0_max, pc) &&
                pc.n_lags <= 32 * afx::kYinMaxGroups * 2 - 4 && pc.max_period <= 32 * 22;
     if (h->f0_ok) {
       std::vector<double> all;
@@ -386,18 +387,17 @@ int afx_create(const afx_config_t* cfg, afx_handle_t* out) {
       h->yin_cap = ((pc.n_lags / 2 + 2) + 3) & ~3;
       h->yin_rec_bytes = (int)align_up(24 + 10 * (size_t)h->yin_cap, 16);
       h->yin_lag_pad = (pc.max_period + 1 + 127) & ~127;
-      h->yin_tile = afx::kYinBlocks * cfg->hop_length + h->yin_lag_pad + 8;
-      h->yin_frames_per_chunk = afx::kYinBlocks - (cfg->frame_length / (2 * cfg->hop_length) - 1);
+      {
+        const int W = cfg->frame_length / 2, hop = cfg->hop_length;
+        const bool block_mode = W % hop == 0 && hop % 4 == 0 && W / hop <= 8;
+        h->yin_blk_len = block_mode ? hop : W;
+        h->yin_rb = block_mode ? W / hop : 1;
+      }
+      h->yin_tile = ((afx::kYinBlocks - 1) * cfg->hop_length + h->yin_blk_len + h->yin_lag_pad + 12 + 3) & ~3;   // A and S follow the tile: 16-byte rows
+      h->yin_frames_per_chunk = afx::kYinBlocks - (h->yin_rb - 1);
       const size_t ph1 = (size_t)h->yin_tile * 4 + (size_t)afx::kYinBlocks * h->yin_lag_pad * 4 + ((size_t)h->yin_tile + 2) * 8;
       const size_t ph2 = (size_t)afx::kYinWarps * h->yin_cap * (2 * 8 + 4);   // trough heights + periods (double) + packed compact list
       h->yin_smem = align_up(std::max(ph1, ph2), 16);
-      h->vit_smem = align_up(afx::VitGeo(pc.n_bins, pc.half_width).bytes(pc.n_bins), 16);
-      if (h->yin_smem > (size_t)prop.sharedMemPerBlockOptin || h->vit_smem > (size_t)prop.sharedMemPerBlockOptin) h->f0_ok = false;
-    }
-    if (h->f0_ok) {
-      const void* yk = h->yin_c == 8 ? (const void*)afx::yin_obs_kernel<8> : h->yin_c == 11 ? (const void*)afx::yin_obs_kernel<11>
-                     : h->yin_c == 16 ? (const void*)afx::yin_obs_kernel<16> : (const void*)afx::yin_obs_kernel<22>;
-      CUDA_TRY(cudaFuncSetAttribute(yk, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->yin_smem));
       // Viterbi band search: the int32-filtered variant for the half widths of the stock geometries, else the generic one
       h->vit_fn = afx::viterbi_kernel<0>;
       const char* vsel = getenv("AFX_VITERBI");
@@ -405,6 +405,16 @@ int afx_create(const afx_config_t* cfg, afx_handle_t* out) {
         if (pc.half_width == 25) h->vit_fn = afx::viterbi_kernel<25>;
         else if (pc.half_width == 15) h->vit_fn = afx::viterbi_kernel<15>;
       }
+      h->vit_smem = align_up(afx::VitGeo(pc.n_bins, pc.half_width, h->vit_fn != afx::viterbi_kernel<0>).bytes(pc.n_bins), 16);
+      if (h->yin_smem > (size_t)prop.sharedMemPerBlockOptin || h->vit_smem > (size_t)prop.sharedMemPerBlockOptin) h->f0_ok = false;
+    }
+    if (h->f0_ok) {
+      const bool fm = h->yin_rb == 1 && h->yin_blk_len != cfg->hop_length;   // frame mode: blocks at any alignment
+      h->yin_fn = h->yin_c == 8 ? (fm ? afx::yin_obs_kernel<8, true> : afx::yin_obs_kernel<8, false>)
+                : h->yin_c == 11 ? (fm ? afx::yin_obs_kernel<11, true> : afx::yin_obs_kernel<11, false>)
+                : h->yin_c == 16 ? (fm ? afx::yin_obs_kernel<16, true> : afx::yin_obs_kernel<16, false>)
+                                 : (fm ? afx::yin_obs_kernel<22, true> : afx::yin_obs_kernel<22, false>);
+      CUDA_TRY(cudaFuncSetAttribute(h->yin_fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->yin_smem));
       CUDA_TRY(cudaFuncSetAttribute(h->vit_fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->vit_smem));
     }
   }
@@ -616,16 +626,14 @@ int afx_extract(afx_handle_t h, const float* d_audio, const int64_t* h_offsets, 
         ya.audio = d_audio; ya.offsets = d_offsets; ya.lengths = d_lengths; ya.info = d_info;
         ya.chunk_off = d_ychunk; ya.frame_off = d_frame_off; ya.clip_begin = c0; ya.clip_end = c1; ya.frame_base = s_frame_off[c0];
         ya.n_fft = h->cfg.frame_length; ya.hop = hop; ya.win = pc.win_length; ya.min_period = pc.min_period; ya.max_period = pc.max_period;
+        ya.blk_len = h->yin_blk_len; ya.blk_stride = hop; ya.rb = h->yin_rb;
         ya.n_bins = pc.n_bins; ya.frames_per_chunk = h->yin_frames_per_chunk; ya.lag_pad = h->yin_lag_pad; ya.tile = h->yin_tile;
         ya.cap = h->yin_cap; ya.rec_bytes = h->yin_rec_bytes; ya.coef = coef; ya.raw = raw ? 1 : 0; ya.sr = (double)h->cfg.sr; ya.fmin = h->cfg.f0_min;
         ya.tab = h->ptab; ya.obs = d_obs;
         const int grid_y = s_ychunk[c1] - s_ychunk[c0];
         PhaseTimer pt(h, stream, AFX_PHASE_YIN);
         if (grid_y > 0) {
-          if (h->yin_c == 8) afx::yin_obs_kernel<8><<<grid_y, afx::kYinThreads, h->yin_smem, stream>>>(ya);
-          else if (h->yin_c == 11) afx::yin_obs_kernel<11><<<grid_y, afx::kYinThreads, h->yin_smem, stream>>>(ya);
-          else if (h->yin_c == 16) afx::yin_obs_kernel<16><<<grid_y, afx::kYinThreads, h->yin_smem, stream>>>(ya);
-          else afx::yin_obs_kernel<22><<<grid_y, afx::kYinThreads, h->yin_smem, stream>>>(ya);
+          h->yin_fn<<<grid_y, afx::kYinThreads, h->yin_smem, stream>>>(ya);
           ++g_launches;
         }
       }

@@ -43,9 +43,13 @@ struct YinArgs {
   int clip_begin, clip_end;
   long long frame_base;        // frame_off[clip_begin]
   int n_fft, hop, win, min_period, max_period, n_bins;
-  int frames_per_chunk;        // F = 16 - (n_fft / (2 hop) - 1)
+  int blk_len, blk_stride, rb; // autocorrelation blocks: block k = tile [k stride, k stride + len), a frame's window is rb
+                               // consecutive blocks.  Block mode (hop | n_fft/2, hop % 4 == 0): len = stride = hop,
+                               // rb = n_fft / (2 hop) -- every product formed once.  Frame mode (any other hop):
+                               // len = n_fft / 2, stride = hop, rb = 1 -- one block per frame
+  int frames_per_chunk;        // F = 16 - (rb - 1)
   int lag_pad;                 // lags 0 .. max_period padded to a multiple of 128
-  int tile;                    // floats in the y tile: 16 hop + lag_pad + 8
+  int tile;                    // floats in the y tile: 15 stride + len + lag_pad + 12
   int cap;                     // candidate slots per frame record
   int rec_bytes;               // bytes per frame record
   float coef;
@@ -63,7 +67,7 @@ __device__ __forceinline__ double shfl_d(double v, int src) { return __shfl_sync
 __device__ __forceinline__ double shfl_up_d(double v, int d) { return __shfl_up_sync(0xffffffffu, v, d); }
 
 
-template <int C>   // lags per lane in phase 2: 32 * C >= max_period
+template <int C, bool MASKED>   // C: lags per lane in phase 2, 32 * C >= max_period; MASKED: blocks at any alignment / length (frame mode)
 __global__ void __launch_bounds__(kYinThreads, 2) yin_obs_kernel(YinArgs a) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   // phase 0/1 layout: [ys float tile][A float 16 x lag_pad][S double tile + 1]; phase 2b aliases it with trough lists
@@ -88,11 +92,11 @@ __global__ void __launch_bounds__(kYinThreads, 2) yin_obs_kernel(YinArgs a) {
   const int F = a.frames_per_chunk;
   const int t0 = chunk * F;
   if (T <= 0 || t0 >= T) return;
-  const int H = a.hop, W = a.win, RB = a.n_fft / (2 * H);   // RB blocks per frame window
+  const int BS = a.blk_stride, W = a.win, RB = a.rb;   // RB blocks per frame window
   const float* __restrict__ x = a.audio + a.offsets[clip];
   const int L0 = a.lengths[clip];
-  // tile index i holds y[n0 + 1 + i] (trimmed coordinates), n0 = (t0 - RB) * H: block k = tile [k H, (k+1) H)
-  const int n0 = (t0 - RB) * H;
+  // tile index i holds y[n0 + 1 + i] (trimmed coordinates), n0 = t0 hop - W: frame t0 + f owns tile [f BS, f BS + W)
+  const int n0 = t0 * a.hop - W;
 
   // ---- phase 0: pre-emphasised tile, zero outside the trimmed signal
   for (int i = tid; i < a.tile; i += kYinThreads) {
@@ -131,23 +135,41 @@ __global__ void __launch_bounds__(kYinThreads, 2) yin_obs_kernel(YinArgs a) {
   {
     const int P = a.lag_pad >> 7;   // groups of 128 lags
     float* Ak = A + warp * a.lag_pad;
-    const float4* yb = reinterpret_cast<const float4*>(ys + warp * H);        // block samples, 16-byte aligned
+    // the block starts at tile index b; the walk starts at the 16-byte boundary below it and the samples before the
+    // block / past its end enter with weight zero (fmaf(0, y, acc) = acc: the sums are those of the unshifted walk;
+    // block mode: b is a multiple of 4 and so is the length, nothing is masked)
+    const int b = warp * BS, b4 = MASKED ? b & ~3 : b, sh = MASKED ? b & 3 : 0, e = sh + a.blk_len;
+    const int steps = MASKED ? (e + 3) >> 2 : a.blk_len >> 2;
+    const float4* yb = reinterpret_cast<const float4*>(ys + b4);
     for (int p = 0; p < P; ++p) {
       const int tau0 = 128 * p + 4 * lane;
-      const float4* yl = reinterpret_cast<const float4*>(ys + warp * H + tau0);
+      const float4* yl = reinterpret_cast<const float4*>(ys + b4 + tau0);
       float acc0 = 0.f, acc1 = 0.f, acc2 = 0.f, acc3 = 0.f;
       float4 v0 = yl[0];
-      const int steps = H >> 2;
-#pragma unroll 4
-      for (int m = 0; m < steps; ++m) {
-        const float4 s4 = yb[m];
-        const float4 v1 = yl[m + 1];   // <= tile index 16 H + lag_pad - 1 (tile = 16 H + lag_pad + 8)
+      auto step = [&](float4 s4, int m) {
+        const float4 v1 = yl[m + 1];   // <= tile index b4 + 4 steps + lag_pad + 3 < tile
         // acc[c] += sum_r s[r] * y[i + r + tau0 + c]
         acc0 = fmaf(s4.x, v0.x, acc0); acc1 = fmaf(s4.x, v0.y, acc1); acc2 = fmaf(s4.x, v0.z, acc2); acc3 = fmaf(s4.x, v0.w, acc3);
         acc0 = fmaf(s4.y, v0.y, acc0); acc1 = fmaf(s4.y, v0.z, acc1); acc2 = fmaf(s4.y, v0.w, acc2); acc3 = fmaf(s4.y, v1.x, acc3);
         acc0 = fmaf(s4.z, v0.z, acc0); acc1 = fmaf(s4.z, v0.w, acc1); acc2 = fmaf(s4.z, v1.x, acc2); acc3 = fmaf(s4.z, v1.y, acc3);
         acc0 = fmaf(s4.w, v0.w, acc0); acc1 = fmaf(s4.w, v1.x, acc1); acc2 = fmaf(s4.w, v1.y, acc2); acc3 = fmaf(s4.w, v1.z, acc3);
         v0 = v1;
+      };
+      if constexpr (!MASKED) {
+#pragma unroll 4
+        for (int m = 0; m < steps; ++m) step(yb[m], m);
+      } else {
+        for (int m = 0; m < steps; ++m) {
+          float4 s4 = yb[m];
+          const int i = 4 * m;
+          if (i < sh || i + 3 >= e) {   // first / last step
+            if (i < sh || i >= e) s4.x = 0.f;
+            if (i + 1 < sh || i + 1 >= e) s4.y = 0.f;
+            if (i + 2 < sh || i + 2 >= e) s4.z = 0.f;
+            if (i + 3 < sh || i + 3 >= e) s4.w = 0.f;
+          }
+          step(s4, m);
+        }
       }
       *reinterpret_cast<float4*>(Ak + tau0) = make_float4(acc0, acc1, acc2, acc3);
     }
@@ -163,7 +185,7 @@ __global__ void __launch_bounds__(kYinThreads, 2) yin_obs_kernel(YinArgs a) {
   bool vld[C];         // lag inside [min_period, max_period]
   double y_prev = 0.0, y_next = 0.0;   // neighbours across the lane boundary
   if (frame_ok) {
-    const int i0 = f * H;                        // tile index of x[1]
+    const int i0 = f * BS;                       // tile index of x[1]
     const double E0r = S[i0 + W] - S[i0];
     const double E0 = fabs(E0r) < 1e-6 ? 0.0 : E0r;
     double dl[C];
@@ -442,11 +464,11 @@ struct VitArgs {
 // on the right (pads hold -1e308) and skewed by one slot per 8 (anchors sit 8 apart: conflict-free 64-bit loads)
 struct VitGeo {
   int pad, lq, fs, nb_even, ks;
-  __host__ __device__ VitGeo(int nb, int hw) {
+  __host__ __device__ VitGeo(int nb, int hw, bool filter_path) {
     pad = (hw + 7) & ~7;
     lq = (2 * hw + 1 + 3) / 4;
     const int n = pad + nb + 4 * lq + 8;
-    fs = (n + (n >> 3) + 8) & ~1;
+    fs = filter_path ? (n + 1) & ~1 : (n + (n >> 3) + 8) & ~1;   // only the generic path skews its rows
     nb_even = (nb + 1) & ~1;
     ks = (2 * hw + nb + 16 + 3) & ~3;   // int32 key row of the filter path: index hw + k, k = -hw .. nb + hw + 12
   }
@@ -466,7 +488,7 @@ template <int HW>
 __global__ void __launch_bounds__(kVitThreads, kVitMinCtas) viterbi_kernel(VitArgs a) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int nb = a.n_bins, hw = a.half_width, ns = 2 * nb;
-  const VitGeo geo(nb, hw);
+  const VitGeo geo(nb, hw, HW > 0);
   const int FS = geo.fs, NBE = geo.nb_even, PAD = geo.pad, LQ = geo.lq;
   double* Fp = reinterpret_cast<double*>(smem_raw);   // [2][FS] V_{t-1} + edge_corr, padded + skewed
   double* hs = Fp + 2 * FS;                            // [2][NBE] band maxima
@@ -479,6 +501,7 @@ __global__ void __launch_bounds__(kVitThreads, kVitMinCtas) viterbi_kernel(VitAr
   __shared__ double s_pv[kVitWarps];
   __shared__ int s_pi[kVitWarps];
   __shared__ double s_red[3][kVitWarps];
+  __shared__ unsigned short s_queue[HW > 0 ? kVitWarps : 1][HW > 0 ? 128 : 1];   // pass-2 work items of a warp's round
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int clip = a.clip_begin + blockIdx.x;
@@ -517,7 +540,7 @@ __global__ void __launch_bounds__(kVitThreads, kVitMinCtas) viterbi_kernel(VitAr
   };
 
   // ---- t = 0: V_0 = logobs_0 + log(p_init + tiny)
-  double G; int kstar;
+  double G, Gkey = 0.0; int kstar;   // Gkey: reference of the filter keys
   {
     const int n0c = *reinterpret_cast<const int*>(rec0);
     const double lu0 = *reinterpret_cast<const double*>(rec0 + 8);
@@ -541,6 +564,7 @@ __global__ void __launch_bounds__(kVitThreads, kVitMinCtas) viterbi_kernel(VitAr
         Kq[HW + j] = max(__double2int_rd((Fp[fidx(j)] - G) * 16384.0), -33554431) * 64;
         Kq[KS + HW + j] = max(__double2int_rd((Fp[FS + fidx(j)] - G) * 16384.0), -33554431) * 64;
       }
+      Gkey = G;
     }
   }
 
@@ -562,6 +586,11 @@ __global__ void __launch_bounds__(kVitThreads, kVitMinCtas) viterbi_kernel(VitAr
       constexpr int W = 2 * HW + 1, NCH = (W + kVitChunk - 1) / kVitChunk, NI4 = (W + 3 + 3) / 4;
       static_assert(NCH <= 8, "chunk masks are packed 8 bits per target");
       const int NT = (nb + 3) >> 2;
+      // A target whose filtered band maximum lies a safe margin below fb = G + log(tiny) (the global fallback) cannot
+      // win in phase C: its chunks are not scanned (true h < (m >> 6) + 2 steps; one more step covers the float64
+      // roundings of fb).  Keys are relative to Gkey, the maximum of the step before the previous one.
+      int fbq = -2147483647;
+      { const double fbx = (G + a.log_tiny - Gkey) * 16384.0; if (fbx > -2.0e9) fbq = __double2int_rd(fbx); }
       for (int t0 = 32 * warp; t0 < 2 * NT; t0 += kVitThreads) {   // warp-uniform: 32 tasks = 128 targets per round
         const int task = t0 + lane;
         unsigned packed = 0u;
@@ -596,29 +625,69 @@ __global__ void __launch_bounds__(kVitThreads, kVitMinCtas) viterbi_kernel(VitAr
             unsigned cmask = 0u;
 #pragma unroll
             for (int c = 0; c < NCH; ++c) cmask |= (acc[r][c] >= thr) ? (1u << c) : 0u;
+            if ((m >> 6) + 3 <= fbq) cmask = 0u;
             packed |= cmask << (8 * r);
           }
         }
+        // chunk scan of one target, ascending entries, strict >: the first index wins float64 ties
+        auto scan_chunk = [&](const double* Fj, int c, double& best, int& arg) {
+          const double* fc = Fj + c * kVitChunk;
+          const double* wc = ltr + c * kVitChunk;   // ltr is -1e308 beyond d = 2 HW: those entries never win
+#pragma unroll
+          for (int dd = 0; dd < kVitChunk; ++dd) {
+            const double cand = fc[dd] + wc[dd];
+            if (cand > best) { best = cand; arg = c * kVitChunk + dd; }
+          }
+        };
+        // pass 1: every target scans its first surviving chunk (one chunk for ~90 % of the targets: adjacent predecessors
+        // tie exactly on the log-triangle ramps F is made of, and one tie in eight straddles a chunk boundary)
+        unsigned rest_all = 0u;   // remaining chunk masks of this lane's four pass-1 targets, 8 bits each
 #pragma unroll
         for (int q = 0; q < 4; ++q) {
           const int src = 8 * q + (lane >> 2), r = lane & 3;
-          unsigned cmask = (__shfl_sync(0xffffffffu, packed, src) >> (8 * r)) & 0xffu;   // 0: no such target
+          unsigned cmask = (__shfl_sync(0xffffffffu, packed, src) >> (8 * r)) & 0xffu;   // 0: skipped or no such target
           const int task2 = t0 + src;
           const int s = task2 >= NT ? 1 : 0;
           const int j = 4 * (task2 - s * NT) + r;
-          if (cmask) {
-            const double* Fs = Fp + s * FS + PAD - HW;   // Fs[j + d] = F[j - HW + d]
-            double best = -1.0e308; int arg = 0;
-            while (cmask) {                           // ascending chunks, strict >: first index on float64 ties
+          if (task2 < 2 * NT && j < nb) {
+            double best = -1.0e308; int arg = HW;
+            if (cmask) {
               const int c = __ffs(cmask) - 1;
               cmask &= cmask - 1;
-              const double* fc = Fs + j + c * kVitChunk;
-              const double* wc = ltr + c * kVitChunk;   // ltr is -1e308 beyond d = 2 HW: those entries never win
+              scan_chunk(Fp + s * FS + PAD - HW + j, c, best, arg);
+            }
+            hs[s * NBE + j] = best;
+            harg[s * NBE + j] = (unsigned short)(j - HW + arg);
+            rest_all |= cmask << (8 * q);
+          }
+        }
+        // pass 2: the few targets with more chunks, compacted over the warp (in a lane-per-target loop all 32 lanes
+        // wait for them: 1.4 lock-step scans per target instead of 1.1)
+        if (__any_sync(0xffffffffu, rest_all != 0u)) {
+          unsigned short* qu = s_queue[warp];
+          const unsigned lt_mask = (1u << lane) - 1u;
+          int L = 0;
 #pragma unroll
-              for (int dd = 0; dd < kVitChunk; ++dd) {
-                const double cand = fc[dd] + wc[dd];
-                if (cand > best) { best = cand; arg = c * kVitChunk + dd; }
-              }
+          for (int q = 0; q < 4; ++q) {
+            const unsigned rq = (rest_all >> (8 * q)) & 0xffu;
+            const unsigned bal = __ballot_sync(0xffffffffu, rq != 0u);
+            if (rq) qu[L + __popc(bal & lt_mask)] = (unsigned short)((q << 13) | (lane << 8) | rq);
+            L += __popc(bal);
+          }
+          __syncwarp();   // queue and the pass-1 results of this warp are visible
+          for (int i = lane; i < L; i += 32) {
+            const unsigned it = qu[i];
+            unsigned rq = it & 0xffu;
+            const int ln = (it >> 8) & 31, q = it >> 13;
+            const int task2 = t0 + 8 * q + (ln >> 2);
+            const int s = task2 >= NT ? 1 : 0;
+            const int j = 4 * (task2 - s * NT) + (ln & 3);
+            double best = hs[s * NBE + j];
+            int arg = (int)harg[s * NBE + j] - (j - HW);
+            while (rq) {
+              const int c = __ffs(rq) - 1;
+              rq &= rq - 1;
+              scan_chunk(Fp + s * FS + PAD - HW + j, c, best, arg);
             }
             hs[s * NBE + j] = best;
             harg[s * NBE + j] = (unsigned short)(j - HW + arg);
@@ -711,6 +780,7 @@ __global__ void __launch_bounds__(kVitThreads, kVitMinCtas) viterbi_kernel(VitAr
       }
     }
     if (bu > bv) { bv = bu; bi = biu; }   // every unvoiced index is larger than every voiced one: strict >
+    Gkey = G;                         // the keys just written are relative to this step's G
     block_argmax(bv, bi, G, kstar);   // contains a barrier: Fp complete before the next phase A
   }
 

@@ -207,8 +207,8 @@ int64_t afx_resample_filter(int32_t sr, int32_t native_sr, float* taps, int64_t 
  *    1 = the stock variant (compile-time run lengths of the mel segment walk: 22.05 kHz / 1024 / 256, 16 kHz / 512 / 128,
  *        44.1 kHz / 2048 / 512),
  *    0 = the table-driven variant (hop = frame_length / 2, / 4, / 8 at any sample rate),
- *    2 = the run-time-hop variant (any other hop_length <= frame_length / 2; MFCC and energy groups only -- the pYIN group
- *        needs frame_length / 2 to be a whole number of hops),
+ *    2 = the run-time-hop variant (any other hop_length <= frame_length / 2; every feature group: the pYIN front end
+ *        then forms one autocorrelation block per frame instead of sharing hop-sized blocks between frames),
  *   -1 = no kernel (frame_length other than 512 / 1024 / 2048, or hop_length > frame_length / 2).
  * mel_runs (nullable) receives the five run lengths of the mel tables built for (sr, frame_length): quarters 0..3 and
  * segment 0. */

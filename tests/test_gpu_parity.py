@@ -262,7 +262,13 @@ F0_VOICING = 0.999      # "voicing decisions matching on at least 99.9% of frame
     (dict(sr=22050, frame_length=1024, hop_length=256, n_mfcc=13), [3.0, 2.0, 1.2, 4.0]),      # C1 / C2 geometry
     (dict(sr=16000, frame_length=512, hop_length=128, n_mfcc=40), [2.5, 1.5]),                  # C3
     (dict(sr=44100, frame_length=2048, hop_length=512, n_mfcc=13), [2.0, 1.5]),                 # C4
-], ids=["22050-1024-256", "16000-512-128", "44100-2048-512"])
+    # hops that do not divide frame_length / 2 (the reference hands any hop to librosa.pyin, core/feature_extractor.py:
+    # 87-94): yin_obs_kernel in frame mode (one autocorrelation block per frame), generic Viterbi half width
+    (dict(sr=16000, frame_length=512, hop_length=160, n_mfcc=13), [2.0, 1.3]),
+    (dict(sr=22050, frame_length=1024, hop_length=200, n_mfcc=13), [2.0, 1.1]),
+    (dict(sr=44100, frame_length=2048, hop_length=441, n_mfcc=13), [1.5]),
+    (dict(sr=22050, frame_length=1024, hop_length=64, n_mfcc=13), [1.0]),                       # 16 hops per frame
+], ids=["22050-1024-256", "16000-512-128", "44100-2048-512", "16000-512-160", "22050-1024-200", "44100-2048-441", "22050-1024-64"])
 def test_pyin_f0_track_and_statistics(torch_cuda, cfg, secs):
     """extract_f0 (core/feature_extractor.py:76-114): the decoded pYIN track frame by frame and the four summary keys."""
     from audio_feature_extraction_b200 import AudioFeatureExtractor
