@@ -258,6 +258,9 @@ class AudioFeatureExtractor:
         for i in range(n):
             if info["status"][i] != 0:
                 self.logger.error(f"載入音頻文件失敗: {files[i]}: {WAV_STATUS.get(int(info['status'][i]), 'unreadable')}")
+        # longest clips first: the clip a warp finishes last should be a short one (tools/ragged_probe.py: a ragged
+        # 0.5 - 30 s batch runs 13 % faster longest-first than in random order); the rows go back by index
+        keep.sort(key=lambda i: -int(info["frames"][i]))
         if keep:
             names = [files[i] for i in keep]
             pcm16 = bool(np.all((info["tag"][keep] == 1) & (info["bits"][keep] == 16) & (info["channels"][keep] == 1)))
@@ -625,7 +628,11 @@ class AudioFeatureExtractor:
             return []
         names = [files[i] for i in keep]
         pcm16 = bool(np.all((info["tag"][keep] == 1) & (info["bits"][keep] == 16) & (info["channels"][keep] == 1)))
-        hs, hm, st = self._extract_wav_group(names, info["frames"][keep], pcm16, features_to_extract)
+        # the device pass takes the longest clips first (see rows_for_files); rows return to the enumeration order
+        order = np.argsort(-info["frames"][keep].astype(np.int64), kind="stable")
+        hs_o, hm_o, st_o = self._extract_wav_group([names[k] for k in order], info["frames"][keep][order], pcm16, features_to_extract)
+        hs, hm, st = np.empty_like(hs_o), np.empty_like(hm_o), np.empty_like(st_o)
+        hs[order] = hs_o; hm[order] = hm_o; st[order] = st_o
         for i in np.nonzero(st)[0]:
             self.logger.error(f"載入音頻文件失敗: {names[i]}: {WAV_STATUS.get(int(st[i]), 'unreadable')}")
         results = self.rows_to_dicts(hs, hm, names, features_to_extract, skip_errors=True)

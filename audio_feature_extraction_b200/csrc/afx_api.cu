@@ -402,8 +402,16 @@ int afx_create(const afx_config_t* cfg, afx_handle_t* out) {
       h->vit_fn = afx::viterbi_kernel<0>;
       const char* vsel = getenv("AFX_VITERBI");
       if (!(vsel && !strcmp(vsel, "generic"))) {
-        if (pc.half_width == 25) h->vit_fn = afx::viterbi_kernel<25>;
-        else if (pc.half_width == 15) h->vit_fn = afx::viterbi_kernel<15>;
+        // half width = 5 * round(35.92 * 12 * hop / sr): 25 at 22.05 kHz / 256 and 44.1 kHz / 512, 15 at 16 kHz / 128,
+        // 20 at the 10 ms hops (16 kHz / 160, 22.05 kHz / 200, 44.1 kHz / 441), 10 / 30 at half / 1.5 x those
+        switch (pc.half_width) {
+          case 10: h->vit_fn = afx::viterbi_kernel<10>; break;
+          case 15: h->vit_fn = afx::viterbi_kernel<15>; break;
+          case 20: h->vit_fn = afx::viterbi_kernel<20>; break;
+          case 25: h->vit_fn = afx::viterbi_kernel<25>; break;
+          case 30: h->vit_fn = afx::viterbi_kernel<30>; break;
+          default: break;
+        }
       }
       h->vit_smem = align_up(afx::VitGeo(pc.n_bins, pc.half_width, h->vit_fn != afx::viterbi_kernel<0>).bytes(pc.n_bins), 16);
       if (h->yin_smem > (size_t)prop.sharedMemPerBlockOptin || h->vit_smem > (size_t)prop.sharedMemPerBlockOptin) h->f0_ok = false;

@@ -565,6 +565,7 @@ __global__ void __launch_bounds__(kVitThreads, kVitMinCtas) viterbi_kernel(VitAr
         Kq[KS + HW + j] = max(__double2int_rd((Fp[FS + fidx(j)] - G) * 16384.0), -33554431) * 64;
       }
       Gkey = G;
+      __syncthreads();   // the keys are complete before the first stage 1 reads its neighbours' entries
     }
   }
 
