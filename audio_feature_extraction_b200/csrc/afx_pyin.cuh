@@ -67,6 +67,47 @@ __device__ __forceinline__ double shfl_d(double v, int src) { return __shfl_sync
 __device__ __forceinline__ double shfl_up_d(double v, int d) { return __shfl_up_sync(0xffffffffu, v, d); }
 
 
+// One pass of the block autocorrelation: lane owns the LPL consecutive lags tau_base + LPL lane + c and slides over the
+// block four samples at a time; acc[c] += s[r] * y[i + r + tau + c] in sample order (the same sum whatever LPL is).
+// yb = tile at the (16-byte aligned) start of the walk; sh / e: first / one-past-last walk index that belongs to the block.
+template <int LPL, bool MASKED>
+__device__ __forceinline__ void acf_pass(const float* yb_f, float* Ak, int tau_base, int lane, int steps, int sh, int e) {
+  const int tau0 = tau_base + LPL * lane;
+  const float4* yb = reinterpret_cast<const float4*>(yb_f);
+  const float4* yl = reinterpret_cast<const float4*>(yb_f + tau0);
+  float acc[LPL], v[LPL + 4];
+#pragma unroll
+  for (int c = 0; c < LPL; ++c) acc[c] = 0.f;
+#pragma unroll
+  for (int q = 0; q < LPL / 4; ++q) { const float4 t = yl[q]; v[4 * q] = t.x; v[4 * q + 1] = t.y; v[4 * q + 2] = t.z; v[4 * q + 3] = t.w; }
+#pragma unroll(LPL / 4 + 1)
+  for (int m = 0; m < steps; ++m) {
+    float4 s4 = yb[m];
+    if (MASKED) {
+      const int i = 4 * m;
+      if (i < sh || i + 3 >= e) {   // first / last step
+        if (i < sh || i >= e) s4.x = 0.f;
+        if (i + 1 < sh || i + 1 >= e) s4.y = 0.f;
+        if (i + 2 < sh || i + 2 >= e) s4.z = 0.f;
+        if (i + 3 < sh || i + 3 >= e) s4.w = 0.f;
+      }
+    }
+    const float4 nv = yl[m + LPL / 4];   // <= tile index of the walk start + 4 steps + lag_pad + 3 < tile
+    v[LPL] = nv.x; v[LPL + 1] = nv.y; v[LPL + 2] = nv.z; v[LPL + 3] = nv.w;
+    const float sr[4] = {s4.x, s4.y, s4.z, s4.w};
+#pragma unroll
+    for (int r = 0; r < 4; ++r)
+#pragma unroll
+      for (int c = 0; c < LPL; ++c) acc[c] = fmaf(sr[r], v[r + c], acc[c]);
+#pragma unroll
+    for (int c = 0; c < LPL; ++c) v[c] = v[c + 4];
+  }
+#pragma unroll
+  for (int q = 0; q < LPL / 4; ++q)
+    *reinterpret_cast<float4*>(Ak + tau0 + 4 * q) = make_float4(acc[4 * q], acc[4 * q + 1], acc[4 * q + 2], acc[4 * q + 3]);
+}
+
+
 template <int C, bool MASKED>   // C: lags per lane in phase 2, 32 * C >= max_period; MASKED: blocks at any alignment / length (frame mode)
 __global__ void __launch_bounds__(kYinThreads, 2) yin_obs_kernel(YinArgs a) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -81,6 +122,12 @@ __global__ void __launch_bounds__(kYinThreads, 2) yin_obs_kernel(YinArgs a) {
   const int base = a.chunk_off[a.clip_begin];
   const int task = blockIdx.x;
   int lo = a.clip_begin, hi = a.clip_end;
+  {  // clips of similar length: the clip is near task / (chunks per clip); bracket it there before bisecting
+    const int g = a.clip_begin + (int)(((long long)task * (a.clip_end - a.clip_begin)) / max(1, a.chunk_off[a.clip_end] - base));
+    const int g0 = max(a.clip_begin, g - 1), g1 = min(a.clip_end, g + 2);
+    if (a.chunk_off[g0] - base <= task) lo = g0;
+    if (g1 < a.clip_end && a.chunk_off[g1] - base > task && g1 > lo) hi = g1;
+  }
   while (hi - lo > 1) {
     const int mid = (lo + hi) >> 1;
     if (a.chunk_off[mid] - base <= task) lo = mid; else hi = mid;
@@ -133,46 +180,17 @@ __global__ void __launch_bounds__(kYinThreads, 2) yin_obs_kernel(YinArgs a) {
   }
   // ---- phase 1: block autocorrelations A[k][tau], tau = 0 .. lag_pad - 1, warp k <-> block k
   {
-    const int P = a.lag_pad >> 7;   // groups of 128 lags
     float* Ak = A + warp * a.lag_pad;
     // the block starts at tile index b; the walk starts at the 16-byte boundary below it and the samples before the
     // block / past its end enter with weight zero (fmaf(0, y, acc) = acc: the sums are those of the unshifted walk;
     // block mode: b is a multiple of 4 and so is the length, nothing is masked)
     const int b = warp * BS, b4 = MASKED ? b & ~3 : b, sh = MASKED ? b & 3 : 0, e = sh + a.blk_len;
     const int steps = MASKED ? (e + 3) >> 2 : a.blk_len >> 2;
-    const float4* yb = reinterpret_cast<const float4*>(ys + b4);
-    for (int p = 0; p < P; ++p) {
-      const int tau0 = 128 * p + 4 * lane;
-      const float4* yl = reinterpret_cast<const float4*>(ys + b4 + tau0);
-      float acc0 = 0.f, acc1 = 0.f, acc2 = 0.f, acc3 = 0.f;
-      float4 v0 = yl[0];
-      auto step = [&](float4 s4, int m) {
-        const float4 v1 = yl[m + 1];   // <= tile index b4 + 4 steps + lag_pad + 3 < tile
-        // acc[c] += sum_r s[r] * y[i + r + tau0 + c]
-        acc0 = fmaf(s4.x, v0.x, acc0); acc1 = fmaf(s4.x, v0.y, acc1); acc2 = fmaf(s4.x, v0.z, acc2); acc3 = fmaf(s4.x, v0.w, acc3);
-        acc0 = fmaf(s4.y, v0.y, acc0); acc1 = fmaf(s4.y, v0.z, acc1); acc2 = fmaf(s4.y, v0.w, acc2); acc3 = fmaf(s4.y, v1.x, acc3);
-        acc0 = fmaf(s4.z, v0.z, acc0); acc1 = fmaf(s4.z, v0.w, acc1); acc2 = fmaf(s4.z, v1.x, acc2); acc3 = fmaf(s4.z, v1.y, acc3);
-        acc0 = fmaf(s4.w, v0.w, acc0); acc1 = fmaf(s4.w, v1.x, acc1); acc2 = fmaf(s4.w, v1.y, acc2); acc3 = fmaf(s4.w, v1.z, acc3);
-        v0 = v1;
-      };
-      if constexpr (!MASKED) {
-#pragma unroll 4
-        for (int m = 0; m < steps; ++m) step(yb[m], m);
-      } else {
-        for (int m = 0; m < steps; ++m) {
-          float4 s4 = yb[m];
-          const int i = 4 * m;
-          if (i < sh || i + 3 >= e) {   // first / last step
-            if (i < sh || i >= e) s4.x = 0.f;
-            if (i + 1 < sh || i + 1 >= e) s4.y = 0.f;
-            if (i + 2 < sh || i + 2 >= e) s4.z = 0.f;
-            if (i + 3 < sh || i + 3 >= e) s4.w = 0.f;
-          }
-          step(s4, m);
-        }
-      }
-      *reinterpret_cast<float4*>(Ak + tau0) = make_float4(acc0, acc1, acc2, acc3);
-    }
+    // lags per lane and pass: 12 (48-byte lane pitch: conflict-free 128-bit loads, 48 FMAs per 2 loads) when the padded
+    // lag count is a multiple of 384 (22.05 kHz / 1024: one pass; 44.1 kHz / 2048: two), else 8 or 4
+    if (a.lag_pad % 384 == 0) { for (int t0l = 0; t0l < a.lag_pad; t0l += 384) acf_pass<12, MASKED>(ys + b4, Ak, t0l, lane, steps, sh, e); }
+    else if (a.lag_pad % 256 == 0) { for (int t0l = 0; t0l < a.lag_pad; t0l += 256) acf_pass<8, MASKED>(ys + b4, Ak, t0l, lane, steps, sh, e); }
+    else { for (int t0l = 0; t0l < a.lag_pad; t0l += 128) acf_pass<4, MASKED>(ys + b4, Ak, t0l, lane, steps, sh, e); }
   }
   __syncthreads();
 
@@ -320,17 +338,14 @@ __global__ void __launch_bounds__(kYinThreads, 2) yin_obs_kernel(YinArgs a) {
   am0 = __reduce_or_sync(0xffffffffu, am0); am1 = __reduce_or_sync(0xffffffffu, am1);
   am2 = __reduce_or_sync(0xffffffffu, am2); am3 = __reduce_or_sync(0xffffffffu, am3);
   __syncwarp();
-  // first activation point >= from (101 if none); warp-uniform
-  auto next_act = [&](int from) -> int {
-    const unsigned words[4] = {am0, am1, am2, am3};
-#pragma unroll
-    for (int w = 0; w < 4; ++w) {
-      unsigned m = words[w];
-      const int sh = from - 32 * w;
-      if (sh >= 32) m = 0u; else if (sh > 0) m &= 0xffffffffu << sh;
-      if (m) return 32 * w + __ffs(m) - 1;
-    }
-    return 101;
+  // the activation points in ascending order, popped from the 128-bit set (warp-uniform); 101 when exhausted
+  unsigned cw = am0; int cwi = 0;
+  auto pop_act = [&]() -> int {
+    while (cw == 0u && cwi < 3) { ++cwi; cw = cwi == 1 ? am1 : cwi == 2 ? am2 : am3; }
+    if (cw == 0u) return 101;
+    const int j = 32 * cwi + __ffs(cw) - 1;
+    cw &= cw - 1u;
+    return j;
   };
   // ---- threshold sweep over the compact list, lane-per-candidate in groups of 32.  Between two activation points the
   // active set (hence every rank and the Boltzmann normalisation) is constant, so the thresholds of a segment [j, jn)
@@ -343,8 +358,8 @@ __global__ void __launch_bounds__(kYinThreads, 2) yin_obs_kernel(YinArgs a) {
     const int c = 32 * g + lane;
     if (c < n_c) { const unsigned pk = cpk[c]; cjm[g] = (int)(pk >> 16); cai[g] = (int)(pk & 0xffffu); }
   }
-  for (int j = next_act(1); j <= 100;) {
-    const int jn = next_act(j + 1);
+  for (int j = pop_act(); j <= 100;) {
+    const int jn = pop_act();
     unsigned bal[kYinMaxGroups];
     int n_act = 0;
 #pragma unroll
