@@ -264,9 +264,9 @@ F0_VOICING = 0.999      # "voicing decisions matching on at least 99.9% of frame
     (dict(sr=44100, frame_length=2048, hop_length=512, n_mfcc=13), [2.0, 1.5]),                 # C4
     # hops that do not divide frame_length / 2 (the reference hands any hop to librosa.pyin, core/feature_extractor.py:
     # 87-94): yin_obs_kernel in frame mode (one autocorrelation block per frame), generic Viterbi half width
-    (dict(sr=16000, frame_length=512, hop_length=160, n_mfcc=13), [2.0, 1.3]),
+    (dict(sr=16000, frame_length=512, hop_length=160, n_mfcc=13), [2.0, 1.3, 0.62]),
     (dict(sr=22050, frame_length=1024, hop_length=200, n_mfcc=13), [2.0, 1.1]),
-    (dict(sr=44100, frame_length=2048, hop_length=441, n_mfcc=13), [1.5]),
+    (dict(sr=44100, frame_length=2048, hop_length=441, n_mfcc=13), [1.5, 0.7]),
     (dict(sr=22050, frame_length=1024, hop_length=64, n_mfcc=13), [1.0]),                       # 16 hops per frame
 ], ids=["22050-1024-256", "16000-512-128", "44100-2048-512", "16000-512-160", "22050-1024-200", "44100-2048-441", "22050-1024-64"])
 def test_pyin_f0_track_and_statistics(torch_cuda, cfg, secs):
