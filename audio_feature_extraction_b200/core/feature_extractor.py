@@ -72,6 +72,14 @@ class AudioFeatureExtractor:
         self.extended_stats = extended_stats
         logging.basicConfig(level=logging.INFO)  # reference :38
         self.logger = logging.getLogger(__name__)
+        # The reference stores whatever it is given (:30-36) and librosa frames at any size.  The kernels exist for
+        # frame_length 512 / 1024 / 2048 with any hop_length <= frame_length / 2: say so HERE, not at the first call
+        # (host-only query, no device needed).
+        if N.lib().afx_clip_kernel_variant(int(sr), int(frame_length), int(hop_length), None) < 0:
+            raise ValueError(f"AudioFeatureExtractor: frame_length={frame_length}, hop_length={hop_length} is not supported by the "
+                             "B200 kernels (frame_length must be 512, 1024 or 2048 and 1 <= hop_length <= frame_length / 2)")
+        if not (1 <= int(n_mfcc) <= 64):
+            raise ValueError(f"AudioFeatureExtractor: n_mfcc={n_mfcc} is not supported (1 .. 64)")
         self._handle = None
         self._ws = None
         self._pin_bufs = {}   # reused pinned ingest buffers of batch_process, per sample dtype

@@ -109,7 +109,9 @@ __device__ __forceinline__ void acf_pass(const float* yb_f, float* Ak, int tau_b
 
 
 template <int C, bool MASKED>   // C: lags per lane in phase 2, 32 * C >= max_period; MASKED: blocks at any alignment / length (frame mode)
-__global__ void __launch_bounds__(kYinThreads, 2) yin_obs_kernel(YinArgs a) {
+// (C >= 22, i.e. max_period > 512 -- 44.1 kHz / 2048: the tile, the block sums and the prefix sums take 157 KB, one CTA per
+// SM fits anyway, so the kernel may use up to 128 registers instead of spilling the C float64 values a lane carries)
+__global__ void __launch_bounds__(kYinThreads, C >= 22 ? 1 : 2) yin_obs_kernel(YinArgs a) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   // phase 0/1 layout: [ys float tile][A float 16 x lag_pad][S double tile + 1]; phase 2b aliases it with trough lists
   float* ys = reinterpret_cast<float*>(smem_raw);

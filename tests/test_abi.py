@@ -65,6 +65,19 @@ def test_no_cpu_fallback_without_a_device(built_lib):
     assert ei.value.code == N.ERR_CUDA
 
 
+def test_constructor_rejects_unsupported_geometry_up_front(built_lib):
+    """the reference's constructor accepts any frame_length / hop_length; where no kernel exists the drop-in
+    says so in __init__ (host-only check), not at the first extraction call."""
+    from audio_feature_extraction_b200 import AudioFeatureExtractor
+    for kw in (dict(frame_length=400, hop_length=160), dict(frame_length=1024, hop_length=600), dict(frame_length=1024, hop_length=0),
+               dict(n_mfcc=65), dict(n_mfcc=0)):
+        with pytest.raises(ValueError):
+            AudioFeatureExtractor(**kw)
+    for kw in (dict(sr=16000, frame_length=512, hop_length=160), dict(frame_length=2048, hop_length=441), dict(frame_length=1024, hop_length=33),
+               dict(n_mfcc=64)):
+        AudioFeatureExtractor(**kw)   # no device touched yet
+
+
 def test_product_never_imports_the_oracle():
     pkg = ROOT / "audio_feature_extraction_b200"
     for p in list(pkg.rglob("*.py")) + list(pkg.rglob("*.cu")) + list(pkg.rglob("*.cuh")) + list((ROOT / "audio_feature_extraction_toolkit").rglob("*.py")):
