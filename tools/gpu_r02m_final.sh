@@ -1,5 +1,5 @@
 #!/bin/bash
-# r02m final set: what the driver runs at round end (GPU tests, smoke, both bench arms) + launch list of the bench command
+# final set (r02m, re-run as r02n after the last kernel changes): what the driver runs at round end (GPU tests, smoke, both bench arms) + launch list of the bench command
 # + ncu --set full of the final pYIN kernels and of the streaming kernel
 set -u
 mkdir -p gpurun_out
