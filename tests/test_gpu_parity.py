@@ -309,6 +309,41 @@ def test_pyin_f0_track_and_statistics(torch_cuda, cfg, secs):
     assert agree / total >= F0_VOICING, (agree, total)
 
 
+@pytest.mark.parametrize("sr,frame_length,hop_length,half_width", [
+    (22050, 1024, 100, 10), (16000, 512, 128, 15), (16000, 512, 160, 20), (22050, 1024, 256, 25), (22050, 1024, 300, 30),
+], ids=["hw10", "hw15", "hw20", "hw25", "hw30"])
+def test_filtered_viterbi_equals_generic_band_search(torch_cuda, monkeypatch, sr, frame_length, hop_length, half_width):
+    """Both band searches of viterbi_kernel are exact restatements of the dense maximum (first index on ties): the filtered
+    variant (int32 pre-filter + float64 scan of the surviving chunks, fallback bound, two-pass scan) instantiated for this
+    half width must decode the SAME state sequence as the generic one, frame by frame, on tonal, noisy and gliding clips."""
+    from audio_feature_extraction_b200 import AudioFeatureExtractor
+    from audio_feature_extraction_b200.synth import make_clip
+    assert 5 * round(35.92 * 12 * hop_length / sr) == half_width
+    rng = np.random.default_rng(11)
+    clips = [make_clip(900 + s, sr=sr, seconds=sec, f_lo=80.0, f_hi=600.0, kind=k) for s, (sec, k) in
+             enumerate([(2.5, "speech"), (1.7, "music"), (3.1, "speech"), (1.2, "music")])]
+    clips.append((0.05 * rng.standard_normal(int(1.5 * sr))).astype(np.float32))                       # noise: mostly unvoiced
+    glide = np.sin(2 * np.pi * np.cumsum(np.linspace(100.0, 700.0, 2 * sr)) / sr).astype(np.float32) * 0.4  # fast glide: band edges
+    clips.append(glide + (0.01 * rng.standard_normal(glide.size)).astype(np.float32))
+    kw = dict(sr=sr, frame_length=frame_length, hop_length=hop_length, n_mfcc=13)
+    monkeypatch.delenv("AFX_VITERBI", raising=False)
+    ex_f = AudioFeatureExtractor(**kw)
+    _, meta_f, fr_f, rows = _framewise(ex_f, clips, groups=("f0",))
+    monkeypatch.setenv("AFX_VITERBI", "generic")          # read by afx_create
+    ex_g = AudioFeatureExtractor(**kw)
+    _, meta_g, fr_g, _ = _framewise(ex_g, clips, groups=("f0",))
+    n = ex_f.n_mfcc
+    assert np.array_equal(meta_f, meta_g) and np.all(meta_f[:, 0] == 0)
+    voiced = 0
+    for i in range(len(clips)):
+        T = int(meta_f[i, 3])
+        a, b = fr_f[rows[i]:rows[i] + T, 3 * n + 1], fr_g[rows[i]:rows[i] + T, 3 * n + 1]
+        assert np.array_equal(np.isnan(a), np.isnan(b)), i
+        assert np.array_equal(a[~np.isnan(a)], b[~np.isnan(b)]), i          # same pitch bin in every voiced frame: same states
+        voiced += int(np.sum(~np.isnan(a)))
+    assert voiced > 100
+
+
 def test_reference_method_api_on_preprocessed_waveforms(torch_cuda):
     """The reference's public per-stage methods (core/feature_extractor.py:58-179): preprocess_audio(y) returns the
     pre-emphasised + trimmed waveform; extract_f0 / extract_mfcc / extract_energy take THAT waveform (no second
