@@ -82,6 +82,7 @@ struct afx_handle_s {
   int l2_mode = 1;         // L2 eviction hints of the streaming kernel (AFX_L2_MODE, StreamArgs::l2_mode)
   void (*yin_fn)(afx::YinArgs) = nullptr;     // yin_obs_kernel<lags per lane, frame mode>
   void (*vit_fn)(afx::VitArgs) = nullptr;     // viterbi_kernel<half width or 0>
+  int vit_threads = afx::kVitThreads;
   // device tables
   float* d_window = nullptr;
   float* d_twiddle = nullptr;
@@ -410,14 +411,20 @@ int afx_create(const afx_config_t* cfg, afx_handle_t* out) {
       if (!(vsel && !strcmp(vsel, "generic"))) {
         // half width = 5 * round(35.92 * 12 * hop / sr): 25 at 22.05 kHz / 256 and 44.1 kHz / 512, 15 at 16 kHz / 128,
         // 20 at the 10 ms hops (16 kHz / 160, 22.05 kHz / 200, 44.1 kHz / 441), 10 / 30 at half / 1.5 x those
+        // four warps per clip (thread <-> 2 targets in the filter): every scheduler of the SM hosts one warp of every
+        // resident CTA, so no warp of a CTA reaches the barriers late for sharing its scheduler with a sibling: 36.1 -> 34.4 ms
+        // per 2 960 clips against the five-warp shape (AFX_VIT_WARPS=5 selects it, half width 25 only: development A/B)
+        const char* vw = getenv("AFX_VIT_WARPS");
+        h->vit_threads = 128;
         switch (pc.half_width) {
-          case 10: h->vit_fn = afx::viterbi_kernel<10>; break;
-          case 15: h->vit_fn = afx::viterbi_kernel<15>; break;
-          case 20: h->vit_fn = afx::viterbi_kernel<20>; break;
-          case 25: h->vit_fn = afx::viterbi_kernel<25>; break;
-          case 30: h->vit_fn = afx::viterbi_kernel<30>; break;
-          default: break;
+          case 10: h->vit_fn = afx::viterbi_kernel<10, 4>; break;
+          case 15: h->vit_fn = afx::viterbi_kernel<15, 4>; break;
+          case 20: h->vit_fn = afx::viterbi_kernel<20, 4>; break;
+          case 25: h->vit_fn = afx::viterbi_kernel<25, 4>; break;
+          case 30: h->vit_fn = afx::viterbi_kernel<30, 4>; break;
+          default: h->vit_threads = afx::kVitThreads; break;   // generic band search, five warps
         }
+        if (vw && atoi(vw) == 5 && pc.half_width == 25) { h->vit_fn = afx::viterbi_kernel<25, 5>; h->vit_threads = afx::kVitThreads; }
       }
       h->vit_smem = align_up(afx::VitGeo(pc.n_bins, pc.half_width, h->vit_fn != afx::viterbi_kernel<0>).bytes(pc.n_bins), 16);
       if (h->yin_smem > (size_t)prop.sharedMemPerBlockOptin || h->vit_smem > (size_t)prop.sharedMemPerBlockOptin) h->f0_ok = false;
@@ -665,7 +672,7 @@ int afx_extract(afx_handle_t h, const float* d_audio, const int64_t* h_offsets, 
           const int w = 2 * pc.half_width + 1;
           va.wk[d] = d < w ? (int)std::floor(pc.ltrans_same[w - 1 - d] * 16384.0) * 64 + (63 - d) : -(1 << 30);
         }
-        h->vit_fn<<<c1 - c0, afx::kVitThreads, h->vit_smem, stream>>>(va);
+        h->vit_fn<<<c1 - c0, h->vit_threads, h->vit_smem, stream>>>(va);
         ++g_launches;
       }
       c0 = c1;

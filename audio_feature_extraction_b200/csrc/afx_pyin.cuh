@@ -515,8 +515,12 @@ struct VitGeo {
 // predecessors), then the float64 scan of only those chunks whose filtered maximum lies within 3 quantisation steps of
 // the best one (any chunk that could hold the true float64 maximum: the filter's error is < 2 steps per entry).
 constexpr int kVitChunk = 8;
-template <int HW>
-__global__ void __launch_bounds__(kVitThreads, kVitMinCtas) viterbi_kernel(VitArgs a) {
+// NW: warps per clip.  5 (thread <-> 4 consecutive targets in the filter) or 4 (thread <-> 2 targets: 19 rounds of 32 tasks
+// split 5 / 5 / 5 / 4 over the warps, and every scheduler of the SM hosts exactly one warp of every resident CTA)
+template <int HW, int NW = kVitWarps>
+__global__ void __launch_bounds__(NW * 32, kVitMinCtas) viterbi_kernel(VitArgs a) {
+  constexpr int kThreads = NW * 32, kWarps = NW;
+  constexpr int TPT = NW == 4 ? 2 : 4;   // targets per thread in the filter stage
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int nb = a.n_bins, hw = a.half_width, ns = 2 * nb;
   const VitGeo geo(nb, hw, HW > 0);
@@ -529,10 +533,10 @@ __global__ void __launch_bounds__(kVitThreads, kVitMinCtas) viterbi_kernel(VitAr
   int* Kq = reinterpret_cast<int*>(ltr + 4 * LQ + 8);  // [2][KS] filter keys, index hw + k
   const int KS = geo.ks;
   unsigned short* harg = reinterpret_cast<unsigned short*>(Kq + 2 * KS);   // [2][NBE]
-  __shared__ double s_pv[kVitWarps];
-  __shared__ int s_pi[kVitWarps];
-  __shared__ double s_red[3][kVitWarps];
-  __shared__ unsigned short s_queue[HW > 0 ? kVitWarps : 1][HW > 0 ? 128 : 1];   // pass-2 work items of a warp's round
+  __shared__ double s_pv[kWarps];
+  __shared__ int s_pi[kWarps];
+  __shared__ double s_red[3][kWarps];
+  __shared__ unsigned short s_queue[HW > 0 ? kWarps : 1][HW > 0 ? 128 : 1];   // pass-2 work items of a warp's round
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int clip = a.clip_begin + blockIdx.x;
@@ -545,11 +549,11 @@ __global__ void __launch_bounds__(kVitThreads, kVitMinCtas) viterbi_kernel(VitAr
   unsigned short* ptr0 = a.ptr + (size_t)slot0 * ns;
   auto fidx = [PAD](int k) { const int kp = k + PAD; return HW > 0 ? kp : kp + (kp >> 3); };   // the filter path needs no skew
 
-  for (int i = tid; i < 2 * FS; i += kVitThreads) Fp[i] = -1.0e308;
-  for (int i = tid; i < nb; i += kVitThreads) corr[i] = a.edge_corr[i];
-  for (int i = tid; i < 4 * LQ + 8; i += kVitThreads) ltr[i] = (i <= 2 * hw) ? a.lt_same[2 * hw - i] : -1.0e308;
-  if (HW > 0) for (int i = tid; i < 2 * KS; i += kVitThreads) Kq[i] = -(1 << 30);   // pads never win
-  for (int i = tid; i < 2 * NBE; i += kVitThreads) lobs[i] = a.log_tiny;
+  for (int i = tid; i < 2 * FS; i += kThreads) Fp[i] = -1.0e308;
+  for (int i = tid; i < nb; i += kThreads) corr[i] = a.edge_corr[i];
+  for (int i = tid; i < 4 * LQ + 8; i += kThreads) ltr[i] = (i <= 2 * hw) ? a.lt_same[2 * hw - i] : -1.0e308;
+  if (HW > 0) for (int i = tid; i < 2 * KS; i += kThreads) Kq[i] = -(1 << 30);   // pads never win
+  for (int i = tid; i < 2 * NBE; i += kThreads) lobs[i] = a.log_tiny;
   __syncthreads();
 
   // block argmax (first index) of per-thread (v, i) pairs -> every thread gets (G, k*)
@@ -564,7 +568,7 @@ __global__ void __launch_bounds__(kVitThreads, kVitMinCtas) viterbi_kernel(VitAr
     __syncthreads();
     G = s_pv[0]; ks = s_pi[0];
 #pragma unroll
-    for (int w2 = 1; w2 < kVitWarps; ++w2) {
+    for (int w2 = 1; w2 < kWarps; ++w2) {
       const double ov = s_pv[w2]; const int oi = s_pi[w2];
       if (ov > G || (ov == G && oi < ks)) { G = ov; ks = oi; }
     }
@@ -575,11 +579,11 @@ __global__ void __launch_bounds__(kVitThreads, kVitMinCtas) viterbi_kernel(VitAr
   {
     const int n0c = *reinterpret_cast<const int*>(rec0);
     const double lu0 = *reinterpret_cast<const double*>(rec0 + 8);
-    for (int i = tid; i < n0c; i += kVitThreads)
+    for (int i = tid; i < n0c; i += kThreads)
       lobs[rec_bins(const_cast<unsigned char*>(rec0), a.cap)[i]] = rec_logp(const_cast<unsigned char*>(rec0))[i];
     __syncthreads();
     double bv = -1.0e308; int bi = 0x7fffffff;
-    for (int j = tid; j < nb; j += kVitThreads) {
+    for (int j = tid; j < nb; j += kThreads) {
       const double vv = lobs[j] + a.log_tiny;
       const double vu = lu0 + a.log_init_unvoiced;
       Fp[fidx(j)] = vv + corr[j];
@@ -587,11 +591,11 @@ __global__ void __launch_bounds__(kVitThreads, kVitMinCtas) viterbi_kernel(VitAr
       if (vv > bv) { bv = vv; bi = j; }          // j ascending within a thread: strict > keeps the first index
     }
     double bu = -1.0e308; int biu = 0x7fffffff;   // unvoiced states come after every voiced state
-    for (int j = tid; j < nb; j += kVitThreads) { const double vu = lu0 + a.log_init_unvoiced; if (vu > bu) { bu = vu; biu = nb + j; } }
+    for (int j = tid; j < nb; j += kThreads) { const double vu = lu0 + a.log_init_unvoiced; if (vu > bu) { bu = vu; biu = nb + j; } }
     if (bu > bv) { bv = bu; bi = biu; }
     block_argmax(bv, bi, G, kstar);
     if (HW > 0) {   // filter keys of F_0 relative to G_0 (later steps: relative to the G of the step before, in phase C)
-      for (int j = tid; j < nb; j += kVitThreads) {
+      for (int j = tid; j < nb; j += kThreads) {
         Kq[HW + j] = max(__double2int_rd((Fp[fidx(j)] - G) * 16384.0), -33554431) * 64;
         Kq[KS + HW + j] = max(__double2int_rd((Fp[FS + fidx(j)] - G) * 16384.0), -33554431) * 64;
       }
@@ -617,38 +621,40 @@ __global__ void __launch_bounds__(kVitThreads, kVitMinCtas) viterbi_kernel(VitAr
       // travel packed in one register: one shuffle per round of 32 targets.
       constexpr int W = 2 * HW + 1, NCH = (W + kVitChunk - 1) / kVitChunk, NI4 = (W + 3 + 3) / 4;
       static_assert(NCH <= 8, "chunk masks are packed 8 bits per target");
-      const int NT = (nb + 3) >> 2;
+      constexpr int NLD = (W + TPT - 1 + TPT - 1) / TPT;   // key loads of TPT keys each: predecessors j0 - HW + i, i < W + TPT - 1
+      const int NT = (nb + TPT - 1) / TPT;                 // tasks per voicing block
       // A target whose filtered band maximum lies a safe margin below fb = G + log(tiny) (the global fallback) cannot
       // win in phase C: its chunks are not scanned (true h < (m >> 6) + 2 steps; one more step covers the float64
       // roundings of fb).  Keys are relative to Gkey, the maximum of the step before the previous one.
       int fbq = -2147483647;
       { const double fbx = (G + a.log_tiny - Gkey) * 16384.0; if (fbx > -2.0e9) fbq = __double2int_rd(fbx); }
-      for (int t0 = 32 * warp; t0 < 2 * NT; t0 += kVitThreads) {   // warp-uniform: 32 tasks = 128 targets per round
+      for (int t0 = 32 * warp; t0 < 2 * NT; t0 += kThreads) {   // warp-uniform: 32 tasks = 32 TPT targets per round
         const int task = t0 + lane;
         unsigned packed = 0u;
         if (task < 2 * NT) {
           const int s = task >= NT ? 1 : 0;
-          const int j0 = 4 * (task - s * NT);
-          const int4* kp = reinterpret_cast<const int4*>(Kq + s * KS + j0);   // keys of predecessors j0 - HW + i, i = 0, 1, ...
-          int acc[4][NCH];
+          const int j0 = TPT * (task - s * NT);
+          const int* kp = Kq + s * KS + j0;   // keys of predecessors j0 - HW + i, i = 0, 1, ... (16 / 8-byte aligned)
+          int acc[TPT][NCH];
 #pragma unroll
-          for (int r = 0; r < 4; ++r)
+          for (int r = 0; r < TPT; ++r)
 #pragma unroll
             for (int c = 0; c < NCH; ++c) acc[r][c] = -2147483647;
 #pragma unroll
-          for (int i4 = 0; i4 < NI4; ++i4) {
-            const int4 kv = kp[i4];
-            const int keys[4] = {kv.x, kv.y, kv.z, kv.w};
+          for (int il = 0; il < NLD; ++il) {
+            int keys[TPT];
+            if constexpr (TPT == 4) { const int4 kv = reinterpret_cast<const int4*>(kp)[il]; keys[0] = kv.x; keys[1] = kv.y; keys[2] = kv.z; keys[3] = kv.w; }
+            else { const int2 kv = reinterpret_cast<const int2*>(kp)[il]; keys[0] = kv.x; keys[1] = kv.y; }
 #pragma unroll
-            for (int u = 0; u < 4; ++u)
+            for (int u = 0; u < TPT; ++u)
 #pragma unroll
-              for (int r = 0; r < 4; ++r) {
-                const int d = 4 * i4 + u - r;
+              for (int r = 0; r < TPT; ++r) {
+                const int d = TPT * il + u - r;
                 if (d >= 0 && d < W) acc[r][d / kVitChunk] = __viaddmax_s32(keys[u], a.wk[d], acc[r][d / kVitChunk]);
               }
           }
 #pragma unroll
-          for (int r = 0; r < 4; ++r) {
+          for (int r = 0; r < TPT; ++r) {
             if (j0 + r >= nb) break;
             int m = acc[r][0];
 #pragma unroll
@@ -675,12 +681,12 @@ __global__ void __launch_bounds__(kVitThreads, kVitMinCtas) viterbi_kernel(VitAr
         // tie exactly on the log-triangle ramps F is made of, and one tie in eight straddles a chunk boundary)
         unsigned rest_all = 0u;   // remaining chunk masks of this lane's four pass-1 targets, 8 bits each
 #pragma unroll
-        for (int q = 0; q < 4; ++q) {
-          const int src = 8 * q + (lane >> 2), r = lane & 3;
+        for (int q = 0; q < TPT; ++q) {
+          const int src = (32 / TPT) * q + lane / TPT, r = lane % TPT;
           unsigned cmask = (__shfl_sync(0xffffffffu, packed, src) >> (8 * r)) & 0xffu;   // 0: skipped or no such target
           const int task2 = t0 + src;
           const int s = task2 >= NT ? 1 : 0;
-          const int j = 4 * (task2 - s * NT) + r;
+          const int j = TPT * (task2 - s * NT) + r;
           if (task2 < 2 * NT && j < nb) {
             double best = -1.0e308; int arg = HW;
             if (cmask) {
@@ -700,7 +706,7 @@ __global__ void __launch_bounds__(kVitThreads, kVitMinCtas) viterbi_kernel(VitAr
           const unsigned lt_mask = (1u << lane) - 1u;
           int L = 0;
 #pragma unroll
-          for (int q = 0; q < 4; ++q) {
+          for (int q = 0; q < TPT; ++q) {
             const unsigned rq = (rest_all >> (8 * q)) & 0xffu;
             const unsigned bal = __ballot_sync(0xffffffffu, rq != 0u);
             if (rq) qu[L + __popc(bal & lt_mask)] = (unsigned short)((q << 13) | (lane << 8) | rq);
@@ -711,9 +717,9 @@ __global__ void __launch_bounds__(kVitThreads, kVitMinCtas) viterbi_kernel(VitAr
             const unsigned it = qu[i];
             unsigned rq = it & 0xffu;
             const int ln = (it >> 8) & 31, q = it >> 13;
-            const int task2 = t0 + 8 * q + (ln >> 2);
+            const int task2 = t0 + (32 / TPT) * q + ln / TPT;
             const int s = task2 >= NT ? 1 : 0;
-            const int j = 4 * (task2 - s * NT) + (ln & 3);
+            const int j = TPT * (task2 - s * NT) + ln % TPT;
             double best = hs[s * NBE + j];
             int arg = (int)harg[s * NBE + j] - (j - HW);
             while (rq) {
@@ -728,7 +734,7 @@ __global__ void __launch_bounds__(kVitThreads, kVitMinCtas) viterbi_kernel(VitAr
       }
     } else {
     // ---- phase A: anchors, full band
-    for (int ax = tid; ax < 2 * nA; ax += kVitThreads) {
+    for (int ax = tid; ax < 2 * nA; ax += kThreads) {
       const int s = ax >= nA ? 1 : 0;
       const int j = min((ax - s * nA) * kVitStride, nb - 1);
       const double* Fs = Fp + s * FS;
@@ -756,13 +762,13 @@ __global__ void __launch_bounds__(kVitThreads, kVitMinCtas) viterbi_kernel(VitAr
     // this frame's sparse observations into the dense row; the previous frame's entries back to log(tiny)
     {
       const int ncp = *reinterpret_cast<const int*>(recp);
-      for (int i = tid; i < ncp; i += kVitThreads) lob_old[rec_bins(const_cast<unsigned char*>(recp), a.cap)[i]] = a.log_tiny;
-      for (int i = tid; i < nc; i += kVitThreads) lob_cur[rec_bins(const_cast<unsigned char*>(rec), a.cap)[i]] = rec_logp(const_cast<unsigned char*>(rec))[i];
+      for (int i = tid; i < ncp; i += kThreads) lob_old[rec_bins(const_cast<unsigned char*>(recp), a.cap)[i]] = a.log_tiny;
+      for (int i = tid; i < nc; i += kThreads) lob_cur[rec_bins(const_cast<unsigned char*>(rec), a.cap)[i]] = rec_logp(const_cast<unsigned char*>(rec))[i];
     }
     __syncthreads();
     if constexpr (HW == 0) {
     // ---- phase B: the other targets, restricted to [argmax of the anchor below, argmax of the anchor above]
-    for (int idx = tid; idx < ns; idx += kVitThreads) {
+    for (int idx = tid; idx < ns; idx += kThreads) {
       const int s = idx >= nb ? 1 : 0;
       const int j = idx - s * nb;
       if ((j & (kVitStride - 1)) == 0 || j == nb - 1) continue;
@@ -785,7 +791,7 @@ __global__ void __launch_bounds__(kVitThreads, kVitMinCtas) viterbi_kernel(VitAr
     double bv = -1.0e308, bu = -1.0e308; int bi = 0x7fffffff, biu = 0x7fffffff;
     const double fb = G + a.log_tiny;   // best out-of-band predecessor: k* through a log(tiny) transition
     unsigned short* pt = ptr0 + (size_t)t * ns;
-    for (int j = tid; j < nb; j += kVitThreads) {
+    for (int j = tid; j < nb; j += kThreads) {
       const double h0 = hs[j], h1 = hs[NBE + j];
       const int k0 = harg[j], k1 = nb + harg[NBE + j];
       // voiced target j: predecessors in index order are block 0 (same voicing), then block 1 (switch)
@@ -835,7 +841,7 @@ __global__ void __launch_bounds__(kVitThreads, kVitMinCtas) viterbi_kernel(VitAr
   }
   __syncthreads();
   double s1 = 0, s2 = 0, cntv = 0;
-  for (int t = tid; t < T; t += kVitThreads) {
+  for (int t = tid; t < T; t += kThreads) {
     const int s = st[t];
     const bool voiced = s < nb;
     const double f = voiced ? a.freqs[s] : 0.0;
@@ -851,7 +857,7 @@ __global__ void __launch_bounds__(kVitThreads, kVitMinCtas) viterbi_kernel(VitAr
   __syncthreads();
   if (tid == 0) {
     s1 = s2 = cntv = 0;
-    for (int w2 = 0; w2 < kVitWarps; ++w2) { s1 += s_red[0][w2]; s2 += s_red[1][w2]; cntv += s_red[2][w2]; }
+    for (int w2 = 0; w2 < kWarps; ++w2) { s1 += s_red[0][w2]; s2 += s_red[1][w2]; cntv += s_red[2][w2]; }
     if (cntv > 0.0) {
       const double mean = s1 / cntv;
       const double var = fmax(s2 / cntv - mean * mean, 0.0);
