@@ -67,6 +67,160 @@ __device__ __forceinline__ double shfl_d(double v, int src) { return __shfl_sync
 __device__ __forceinline__ double shfl_up_d(double v, int d) { return __shfl_up_sync(0xffffffffu, v, d); }
 
 
+
+// ---- phase 2b of yin_obs_kernel for one frame (one warp): global minimum, compaction, threshold sweep, pitch bins, record.
+// MAXG = compile-time bound of the trough / candidate groups of 32: the kernel instantiates it for 4 groups (<= 128 troughs:
+// nearly every frame) and for kYinMaxGroups; the group loops are fully unrolled (their arrays live in registers), so the
+// common instantiation is a third of the general one's code -- the kernel stalled on instruction fetch (no_instruction 0.9
+// per issue with 16 warps on data-dependent paths through 146 KB of SASS).
+template <int MAXG>
+__device__ __forceinline__ void yin_phase2b(const YinArgs& a, unsigned char* smem_raw, double* lh, double* lp, int n_tr,
+                                            unsigned char* rec, int warp, int lane) {
+  const double tiny = 2.2250738585072014e-308;
+  // ---- global minimum trough (first index): it gets no_trough_prob * sum(beta[:jmin - 1]) on top of its sweep sum
+  double bh = 1.0e300; int bi = 0x7fffffff;
+#pragma unroll
+  for (int g = 0; g < MAXG; ++g) {
+    if (32 * g >= n_tr) break;
+    const int ai = 32 * g + lane;
+    if (ai < n_tr) { const double h = lh[ai]; if (h < bh) { bh = h; bi = ai; } }
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    const double oh = __shfl_xor_sync(0xffffffffu, bh, o);
+    const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+    if (oh < bh || (oh == bh && oi < bi)) { bh = oh; bi = oi; }
+  }
+  // ---- compaction (order kept): only troughs below some threshold (jmin <= 100; jmin = first j in 1..100 with
+  // h < thresholds[j]) and the global minimum can get a non-zero probability.  packed entry = jmin << 16 | trough index;
+  // am = 128-bit set of the activation points {jmin}
+  unsigned* cpk = reinterpret_cast<unsigned*>(smem_raw + (size_t)kYinWarps * 2 * a.cap * 8) + (size_t)warp * a.cap;
+  const unsigned lt_mask = (1u << lane) - 1u;
+  unsigned am0 = 0u, am1 = 0u, am2 = 0u, am3 = 0u;
+  int n_c = 0;
+#pragma unroll
+  for (int g = 0; g < MAXG; ++g) {
+    if (32 * g >= n_tr) break;
+    const int ai = 32 * g + lane;
+    int j = 102;
+    bool act = false;
+    if (ai < n_tr) {
+      const double h = lh[ai];
+      j = min(100, max(1, (int)(h * 100.0)));
+      while (j > 1 && h < __ldg(a.tab.thresholds + j - 1)) --j;
+      while (j <= 100 && !(h < __ldg(a.tab.thresholds + j))) ++j;
+      act = j <= 100 || ai == bi;
+    }
+    const unsigned bal = __ballot_sync(0xffffffffu, act);
+    if (act) {
+      cpk[n_c + __popc(bal & lt_mask)] = ((unsigned)j << 16) | (unsigned)ai;
+      if (j <= 100) {
+        const unsigned bit = 1u << (j & 31);
+        const int w = j >> 5;
+        am0 |= w == 0 ? bit : 0u; am1 |= w == 1 ? bit : 0u; am2 |= w == 2 ? bit : 0u; am3 |= w == 3 ? bit : 0u;
+      }
+    }
+    n_c += __popc(bal);
+  }
+  am0 = __reduce_or_sync(0xffffffffu, am0); am1 = __reduce_or_sync(0xffffffffu, am1);
+  am2 = __reduce_or_sync(0xffffffffu, am2); am3 = __reduce_or_sync(0xffffffffu, am3);
+  __syncwarp();
+  // the activation points in ascending order, popped from the 128-bit set (warp-uniform); 101 when exhausted
+  unsigned cw = am0; int cwi = 0;
+  auto pop_act = [&]() -> int {
+    while (cw == 0u && cwi < 3) { ++cwi; cw = cwi == 1 ? am1 : cwi == 2 ? am2 : am3; }
+    if (cw == 0u) return 101;
+    const int j = 32 * cwi + __ffs(cw) - 1;
+    cw &= cw - 1u;
+    return j;
+  };
+  // ---- threshold sweep over the compact list, lane-per-candidate in groups of 32.  Between two activation points the
+  // active set (hence every rank and the Boltzmann normalisation) is constant, so the thresholds of a segment [j, jn)
+  // contribute (sum of their beta weights) * boltzmann.pmf(rank; 2, n_active) in one step.
+  int cjm[MAXG], cai[MAXG];
+  double prob[MAXG];
+#pragma unroll
+  for (int g = 0; g < MAXG; ++g) {
+    cjm[g] = 102; cai[g] = -1; prob[g] = 0.0;
+    const int c = 32 * g + lane;
+    if (c < n_c) { const unsigned pk = cpk[c]; cjm[g] = (int)(pk >> 16); cai[g] = (int)(pk & 0xffffu); }
+  }
+  for (int j = pop_act(); j <= 100;) {
+    const int jn = pop_act();
+    unsigned bal[MAXG];
+    int n_act = 0;
+#pragma unroll
+    for (int g = 0; g < MAXG; ++g) {
+      if (32 * g >= n_c) break;
+      bal[g] = __ballot_sync(0xffffffffu, cjm[g] <= j);
+      n_act += __popc(bal[g]);
+    }
+    const double cj = (__ldg(a.tab.beta_suf + j) - __ldg(a.tab.beta_suf + jn)) * __ldg(a.tab.boltz_fact + n_act);
+    int carry = 0;
+#pragma unroll
+    for (int g = 0; g < MAXG; ++g) {
+      if (32 * g >= n_c) break;
+      if (cjm[g] <= j) prob[g] = fma(cj, __ldg(a.tab.boltz_exp + carry + __popc(bal[g] & lt_mask)), prob[g]);
+      carry += __popc(bal[g]);
+    }
+    j = jn;
+  }
+#pragma unroll
+  for (int g = 0; g < MAXG; ++g)
+    if (cai[g] == bi) prob[g] += 0.01 * __ldg(a.tab.beta_cum + min(cjm[g], 101) - 1);
+  // ---- pitch bins; a later candidate (longer period) overwrites an earlier one in the same bin
+  int* lbin = reinterpret_cast<int*>(lh);   // heights are dead: reuse as bin list (-1 = not a candidate)
+  int bin_r[MAXG];
+  __syncwarp();
+#pragma unroll
+  for (int g = 0; g < MAXG; ++g) {
+    bin_r[g] = -1;
+    if (32 * g >= n_c) continue;
+    const int c = 32 * g + lane;
+    if (c < n_c && prob[g] > 0.0) {
+      const double f0 = a.sr / lp[cai[g]];
+      double bf = rint(120.0 * log2(f0 / a.fmin));
+      bf = fmin(fmax(bf, 0.0), (double)a.n_bins);
+      const int b = (int)bf;
+      if (b < a.n_bins) bin_r[g] = b;
+    }
+    if (c < n_c) lbin[c] = bin_r[g];
+  }
+  __syncwarp();
+  double vp = 0.0;
+  int keep_cnt = 0;
+  bool keep[MAXG];
+#pragma unroll
+  for (int g = 0; g < MAXG; ++g) {
+    const int c = 32 * g + lane;
+    keep[g] = false;
+    if (c < n_c && bin_r[g] >= 0) {
+      keep[g] = true;
+      for (int q = c + 1; q < n_c; ++q) { const int bq = lbin[q]; if (bq >= 0) { keep[g] = bq != bin_r[g]; break; } }
+      if (keep[g]) { vp += prob[g]; ++keep_cnt; }
+    }
+  }
+  vp = warp_sum(vp);
+  vp = fmin(fmax(vp, 0.0), 1.0);
+  int kinc = keep_cnt;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) { const int up = __shfl_up_sync(0xffffffffu, kinc, o); if (lane >= o) kinc += up; }
+  const int n_keep = __shfl_sync(0xffffffffu, kinc, 31);
+  {
+    int pos = kinc - keep_cnt;
+    double* out_lp = rec_logp(rec);
+    unsigned short* out_b = rec_bins(rec, a.cap);
+#pragma unroll
+    for (int g = 0; g < MAXG; ++g)
+      if (keep[g]) { out_lp[pos] = log(prob[g] + tiny); out_b[pos] = (unsigned short)bin_r[g]; ++pos; }
+  }
+  if (lane == 0) {
+    *reinterpret_cast<int*>(rec) = n_keep;
+    *reinterpret_cast<double*>(rec + 8) = log((1.0 - vp) / (double)a.n_bins + tiny);
+    *reinterpret_cast<double*>(rec + 16) = vp;
+  }
+}
+
 // One pass of the block autocorrelation: lane owns the LPL consecutive lags tau_base + LPL lane + c and slides over the
 // block four samples at a time; acc[c] += s[r] * y[i + r + tau + c] in sample order (the same sum whatever LPL is).
 // yb = tile at the (16-byte aligned) start of the walk; sh / e: first / one-past-last walk index that belongs to the block.
@@ -306,148 +460,8 @@ __global__ void __launch_bounds__(kYinThreads, C >= 22 ? 1 : 2) yin_obs_kernel(Y
     }
     return;
   }
-  // ---- global minimum trough (first index): it gets no_trough_prob * sum(beta[:jmin - 1]) on top of its sweep sum
-  double bh = 1.0e300; int bi = 0x7fffffff;
-#pragma unroll
-  for (int g = 0; g < kYinMaxGroups; ++g) {
-    if (32 * g >= n_tr) break;
-    const int ai = 32 * g + lane;
-    if (ai < n_tr) { const double h = lh[ai]; if (h < bh) { bh = h; bi = ai; } }
-  }
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) {
-    const double oh = __shfl_xor_sync(0xffffffffu, bh, o);
-    const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
-    if (oh < bh || (oh == bh && oi < bi)) { bh = oh; bi = oi; }
-  }
-  // ---- compaction (order kept): only troughs below some threshold (jmin <= 100; jmin = first j in 1..100 with
-  // h < thresholds[j]) and the global minimum can get a non-zero probability.  packed entry = jmin << 16 | trough index;
-  // am = 128-bit set of the activation points {jmin}
-  unsigned* cpk = reinterpret_cast<unsigned*>(smem_raw + (size_t)kYinWarps * 2 * a.cap * 8) + (size_t)warp * a.cap;
-  const unsigned lt_mask = (1u << lane) - 1u;
-  unsigned am0 = 0u, am1 = 0u, am2 = 0u, am3 = 0u;
-  int n_c = 0;
-#pragma unroll
-  for (int g = 0; g < kYinMaxGroups; ++g) {
-    if (32 * g >= n_tr) break;
-    const int ai = 32 * g + lane;
-    int j = 102;
-    bool act = false;
-    if (ai < n_tr) {
-      const double h = lh[ai];
-      j = min(100, max(1, (int)(h * 100.0)));
-      while (j > 1 && h < __ldg(a.tab.thresholds + j - 1)) --j;
-      while (j <= 100 && !(h < __ldg(a.tab.thresholds + j))) ++j;
-      act = j <= 100 || ai == bi;
-    }
-    const unsigned bal = __ballot_sync(0xffffffffu, act);
-    if (act) {
-      cpk[n_c + __popc(bal & lt_mask)] = ((unsigned)j << 16) | (unsigned)ai;
-      if (j <= 100) {
-        const unsigned bit = 1u << (j & 31);
-        const int w = j >> 5;
-        am0 |= w == 0 ? bit : 0u; am1 |= w == 1 ? bit : 0u; am2 |= w == 2 ? bit : 0u; am3 |= w == 3 ? bit : 0u;
-      }
-    }
-    n_c += __popc(bal);
-  }
-  am0 = __reduce_or_sync(0xffffffffu, am0); am1 = __reduce_or_sync(0xffffffffu, am1);
-  am2 = __reduce_or_sync(0xffffffffu, am2); am3 = __reduce_or_sync(0xffffffffu, am3);
-  __syncwarp();
-  // the activation points in ascending order, popped from the 128-bit set (warp-uniform); 101 when exhausted
-  unsigned cw = am0; int cwi = 0;
-  auto pop_act = [&]() -> int {
-    while (cw == 0u && cwi < 3) { ++cwi; cw = cwi == 1 ? am1 : cwi == 2 ? am2 : am3; }
-    if (cw == 0u) return 101;
-    const int j = 32 * cwi + __ffs(cw) - 1;
-    cw &= cw - 1u;
-    return j;
-  };
-  // ---- threshold sweep over the compact list, lane-per-candidate in groups of 32.  Between two activation points the
-  // active set (hence every rank and the Boltzmann normalisation) is constant, so the thresholds of a segment [j, jn)
-  // contribute (sum of their beta weights) * boltzmann.pmf(rank; 2, n_active) in one step.
-  int cjm[kYinMaxGroups], cai[kYinMaxGroups];
-  double prob[kYinMaxGroups];
-#pragma unroll
-  for (int g = 0; g < kYinMaxGroups; ++g) {
-    cjm[g] = 102; cai[g] = -1; prob[g] = 0.0;
-    const int c = 32 * g + lane;
-    if (c < n_c) { const unsigned pk = cpk[c]; cjm[g] = (int)(pk >> 16); cai[g] = (int)(pk & 0xffffu); }
-  }
-  for (int j = pop_act(); j <= 100;) {
-    const int jn = pop_act();
-    unsigned bal[kYinMaxGroups];
-    int n_act = 0;
-#pragma unroll
-    for (int g = 0; g < kYinMaxGroups; ++g) {
-      if (32 * g >= n_c) break;
-      bal[g] = __ballot_sync(0xffffffffu, cjm[g] <= j);
-      n_act += __popc(bal[g]);
-    }
-    const double cj = (__ldg(a.tab.beta_suf + j) - __ldg(a.tab.beta_suf + jn)) * __ldg(a.tab.boltz_fact + n_act);
-    int carry = 0;
-#pragma unroll
-    for (int g = 0; g < kYinMaxGroups; ++g) {
-      if (32 * g >= n_c) break;
-      if (cjm[g] <= j) prob[g] = fma(cj, __ldg(a.tab.boltz_exp + carry + __popc(bal[g] & lt_mask)), prob[g]);
-      carry += __popc(bal[g]);
-    }
-    j = jn;
-  }
-#pragma unroll
-  for (int g = 0; g < kYinMaxGroups; ++g)
-    if (cai[g] == bi) prob[g] += 0.01 * __ldg(a.tab.beta_cum + min(cjm[g], 101) - 1);
-  // ---- pitch bins; a later candidate (longer period) overwrites an earlier one in the same bin
-  int* lbin = reinterpret_cast<int*>(lh);   // heights are dead: reuse as bin list (-1 = not a candidate)
-  int bin_r[kYinMaxGroups];
-  __syncwarp();
-#pragma unroll
-  for (int g = 0; g < kYinMaxGroups; ++g) {
-    bin_r[g] = -1;
-    if (32 * g >= n_c) continue;
-    const int c = 32 * g + lane;
-    if (c < n_c && prob[g] > 0.0) {
-      const double f0 = a.sr / lp[cai[g]];
-      double bf = rint(120.0 * log2(f0 / a.fmin));
-      bf = fmin(fmax(bf, 0.0), (double)a.n_bins);
-      const int b = (int)bf;
-      if (b < a.n_bins) bin_r[g] = b;
-    }
-    if (c < n_c) lbin[c] = bin_r[g];
-  }
-  __syncwarp();
-  double vp = 0.0;
-  int keep_cnt = 0;
-  bool keep[kYinMaxGroups];
-#pragma unroll
-  for (int g = 0; g < kYinMaxGroups; ++g) {
-    const int c = 32 * g + lane;
-    keep[g] = false;
-    if (c < n_c && bin_r[g] >= 0) {
-      keep[g] = true;
-      for (int q = c + 1; q < n_c; ++q) { const int bq = lbin[q]; if (bq >= 0) { keep[g] = bq != bin_r[g]; break; } }
-      if (keep[g]) { vp += prob[g]; ++keep_cnt; }
-    }
-  }
-  vp = warp_sum(vp);
-  vp = fmin(fmax(vp, 0.0), 1.0);
-  int kinc = keep_cnt;
-#pragma unroll
-  for (int o = 1; o < 32; o <<= 1) { const int up = __shfl_up_sync(0xffffffffu, kinc, o); if (lane >= o) kinc += up; }
-  const int n_keep = __shfl_sync(0xffffffffu, kinc, 31);
-  {
-    int pos = kinc - keep_cnt;
-    double* out_lp = rec_logp(rec);
-    unsigned short* out_b = rec_bins(rec, a.cap);
-#pragma unroll
-    for (int g = 0; g < kYinMaxGroups; ++g)
-      if (keep[g]) { out_lp[pos] = log(prob[g] + tiny); out_b[pos] = (unsigned short)bin_r[g]; ++pos; }
-  }
-  if (lane == 0) {
-    *reinterpret_cast<int*>(rec) = n_keep;
-    *reinterpret_cast<double*>(rec + 8) = log((1.0 - vp) / (double)a.n_bins + tiny);
-    *reinterpret_cast<double*>(rec + 16) = vp;
-  }
+  if (n_tr <= 128) yin_phase2b<4>(a, smem_raw, lh, lp, n_tr, rec, warp, lane);
+  else yin_phase2b<kYinMaxGroups>(a, smem_raw, lh, lp, n_tr, rec, warp, lane);
 }
 
 
