@@ -466,7 +466,7 @@ __global__ void __launch_bounds__(kYinThreads, C >= 22 ? 1 : 2) yin_obs_kernel(Y
 
 
 // =====================================================================================================
-// pYIN HMM decode (librosa.sequence.viterbi on 2 * n_bins states) + F0 statistics, one 5-warp CTA per clip, several
+// pYIN HMM decode (librosa.sequence.viterbi on 2 * n_bins states) + F0 statistics, one 4- or 5-warp CTA per clip, several
 // clips resident per SM (the time recursion is sequential; parallelism comes from co-resident clips).
 //   V_t[j] = logobs_t[j] + max_k (V_{t-1}[k] + logA[k][j]), first index on ties, float64 log domain.
 // Every out-of-band entry of logA is exactly log(tiny) and every in-band entry is larger, so the dense maximum equals
