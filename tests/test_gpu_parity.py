@@ -344,16 +344,19 @@ def test_filtered_viterbi_equals_generic_band_search(torch_cuda, monkeypatch, sr
     assert voiced > 100
 
 
-def test_reference_method_api_on_preprocessed_waveforms(torch_cuda):
+@pytest.mark.parametrize("cfg", [dict(), dict(sr=16000, frame_length=512, hop_length=160, n_mfcc=13)], ids=["defaults", "16000-512-160"])
+def test_reference_method_api_on_preprocessed_waveforms(torch_cuda, cfg):
     """The reference's public per-stage methods (core/feature_extractor.py:58-179): preprocess_audio(y) returns the
     pre-emphasised + trimmed waveform; extract_f0 / extract_mfcc / extract_energy take THAT waveform (no second
-    filter, no second trim) and return the reference's keys."""
+    filter, no second trim) and return the reference's keys.  Also at a hop that takes the run-time-hop kernel and the
+    frame mode of the pYIN front end."""
     from audio_feature_extraction_b200 import AudioFeatureExtractor
     from audio_feature_extraction_b200.synth import make_clip
     from oracle import OracleFeatureExtractor
-    ex, ora = AudioFeatureExtractor(), OracleFeatureExtractor()
+    ex, ora = AudioFeatureExtractor(**cfg), OracleFeatureExtractor(**cfg)
+    sr = cfg.get("sr", 22050)
     for seed in (3, 11):
-        y = make_clip(seed, seconds=2.5)
+        y = make_clip(seed, sr=sr, seconds=2.5)
         yt = ex.preprocess_audio(y)
         ref = ora.preprocess_audio(y)
         assert yt.dtype == np.float32 and yt.shape == ref.shape          # trim indices: bit-exact
@@ -367,7 +370,7 @@ def test_reference_method_api_on_preprocessed_waveforms(torch_cuda):
         for k in got_e:
             assert got_e[k] == pytest.approx(ref_e[k], rel=ENERGY_RTOL), k
     # F0 on one clip (the pYIN oracle takes seconds)
-    y = make_clip(5, seconds=2.0)
+    y = make_clip(5, sr=sr, seconds=2.0)
     yt = ex.preprocess_audio(y)
     got_f, ref_f = ex.extract_f0(yt), ora.extract_f0(ora.preprocess_audio(y))
     assert list(got_f) == ["f0_mean", "f0_std", "f0_missing_rate", "f0_quality"]
